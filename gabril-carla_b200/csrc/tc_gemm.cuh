@@ -1,0 +1,81 @@
+// tcgen05 / TMEM / TMA implicit-GEMM engine shared by every dense contraction of the
+// GABRIL training step (reference: vlm_gaze/models/linear_models.py:124-207 Encoder convs,
+// vlm_gaze/train/train_bc.py:79-82 pre_actor Linear) — forward, dgrad and wgrad.
+//
+// One kernel, two operand regimes:
+//   KIND_FWD   D[pixels, Cout] = A[pixels, K] * B[Cout, K]^T      A K-major (TMA im2col or tiled),
+//              (forward conv, dgrad as a conv over dY, linear)     B K-major or MN-major weight tile
+//   KIND_WGRAD D[Cout, Cin]    = dY[pixels, Cout]^T * X[pixels, Cin]   both MN-major, contraction
+//              (one accumulator per filter tap, several per CTA)       over pixels, split over CTAs
+// Warp roles (192 threads): warp0 = TMA producer, warp1 = TMEM owner + single-thread MMA issuer,
+// warps2..5 = epilogue (tcgen05.ld -> fused bias/residual/ReLU/gate/mask -> global).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+
+namespace tc {
+
+constexpr int kMaxStages = 8;
+constexpr int kMaxMma = 32;
+constexpr int kThreads = 192;
+
+enum Kind { KIND_FWD = 0, KIND_WGRAD = 1 };
+enum OutMode { OUT_BF16 = 0, OUT_F32_STORE = 1, OUT_F32_ATOMIC = 2 };
+
+struct Params {
+  CUtensorMap mapA[4];  // FWD: activation (one per strided-dgrad parity class); WGRAD: dY (tiled)
+  CUtensorMap mapB;     // FWD: weights [Cout][tap][Cin];  WGRAD: activation (im2col or tiled)
+  int kind, n_classes;
+  int a_im2col;  // FWD: A through im2col (else tiled 2D). WGRAD: B through im2col (else tiled 2D)
+  int b_mn;      // FWD: weight tile is MN-major (dgrad: contraction over Cout)
+  int M_total[4];
+  int N_total;
+  int block_n;
+  int n_acc;       // accumulators per CTA (WGRAD: taps per CTA; FWD: 1)
+  int tap_groups;  // WGRAD: ceil(taps / n_acc)
+  int taps;        // filter taps walked by the traversal
+  int kc;          // contraction elements per k-block
+  int kb_total, kb_per_split;
+  int stages;
+  uint32_t a_stage_bytes, b_stage_bytes;
+  uint32_t a_box_bytes, b_box_bytes;
+  int a_boxes, b_boxes;  // TMA boxes per stage (B: per tap for WGRAD)
+  int a_box_w, b_box_w;  // elements one box covers along the MN dimension
+  // im2col traversal geometry (per parity class)
+  int OW[4], OHW[4], lower_w[4], lower_h[4];
+  int trav_stride;
+  int S;  // traversal filter width: tap -> (r', s') = (tap / S, tap % S)
+  int chunks_per_tap;
+  // weight tap mapping r = r_base + r_step*r', s = s_base + s_step*s', wtap = r*S_w + s
+  int r_base[4], s_base[4], r_step, s_step, S_w;
+  // MMA schedule of one k-block
+  int n_mma;
+  uint16_t mma_a_off[kMaxMma];  // byte offset >> 4 from the stage's A base
+  uint16_t mma_b_off[kMaxMma];  // byte offset >> 4 from the stage's B base
+  uint16_t mma_dcol[kMaxMma];   // TMEM column of the accumulator
+  uint8_t mma_acc[kMaxMma];     // accumulator index
+  uint8_t mma_first[kMaxMma];   // first MMA of its accumulator inside the k-block
+  uint64_t desc_a_hi, desc_b_hi;  // smem descriptors with the start-address field zero
+  uint32_t idesc;
+  uint32_t tmem_cols;
+  // epilogue
+  int out_mode;
+  void* out;
+  long long ldo;
+  const float* bias;            // per output column, or null
+  const __nv_bfloat16* resid;   // added before ReLU / gate (same indexing as out), or null
+  const __nv_bfloat16* gate;    // out = gate > 0 ? out : 0 (ReLU backward), or null
+  const float* rowmask;         // per output row multiplier (GMD mask), or null
+  int relu;
+  int remap;  // strided-dgrad: tile row -> (n, 2*jh+ah, 2*jw+aw) of the full-resolution grid
+  int Hs[4], Ws[4], ah[4], aw[4], OHf, OWf;
+  long long tap_stride;  // WGRAD: element (m, tap, n) at out + m*ldo + tap*tap_stride + n
+  int* err_flag;
+};
+
+// Fills the launch geometry and launches; returns a negative gabril status on failure.
+int launch(const Params& p, dim3 grid, size_t smem_bytes, cudaStream_t stream);
+
+}  // namespace tc

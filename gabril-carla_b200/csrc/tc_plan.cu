@@ -1,0 +1,467 @@
+// Host-side planners for the tcgen05 implicit-GEMM kernel: they translate a convolution /
+// linear layer (forward, dgrad, wgrad) into TMA tensor maps, UMMA descriptors and a launch grid.
+// C-ABI entry points: gabril_conv_fwd / gabril_conv_dgrad / gabril_conv_wgrad (declared in
+// include/gabril_b200.h).  Activations are NHWC bf16, weights are [Cout][R*S][Cin] bf16,
+// weight gradients are fp32 in the same [Cout][R*S][Cin] order.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+
+#include "common.cuh"
+#include "tc_gemm.cuh"
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const int*, const int*,
+                                   cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn g_encode_tiled = nullptr;
+EncodeIm2colFn g_encode_im2col = nullptr;
+int g_driver_version = 0;
+int g_num_sms = 148;
+int* g_err_flag = nullptr;  // device int, polled by gabril_poll_error
+
+int resolve_driver() {
+  if (g_encode_tiled && g_encode_im2col) return GABRIL_OK;
+  cudaDriverEntryPointQueryResult qres;
+  void* fn = nullptr;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return GABRIL_ERR_DRIVER;
+  g_encode_tiled = reinterpret_cast<EncodeTiledFn>(fn);
+  fn = nullptr;
+  e = cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return GABRIL_ERR_DRIVER;
+  g_encode_im2col = reinterpret_cast<EncodeIm2colFn>(fn);
+  cudaDriverGetVersion(&g_driver_version);
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+  if (!g_err_flag) {
+    if (cudaMalloc(&g_err_flag, sizeof(int)) != cudaSuccess) return GABRIL_ERR_CUDA;
+    cudaMemset(g_err_flag, 0, sizeof(int));
+  }
+  return GABRIL_OK;
+}
+
+CUtensorMapSwizzle swizzle_for_bytes(int inner_bytes) {
+  if (inner_bytes >= 128) return CU_TENSOR_MAP_SWIZZLE_128B;
+  if (inner_bytes >= 64) return CU_TENSOR_MAP_SWIZZLE_64B;
+  if (inner_bytes >= 32) return CU_TENSOR_MAP_SWIZZLE_32B;
+  return CU_TENSOR_MAP_SWIZZLE_NONE;
+}
+// UMMA smem-descriptor layout_type for a swizzle span in bytes.
+int layout_type_for_bytes(int inner_bytes) {
+  if (inner_bytes >= 128) return 2;
+  if (inner_bytes >= 64) return 4;
+  if (inner_bytes >= 32) return 6;
+  return 0;
+}
+
+int tiled_map(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims,
+              const uint64_t* strides_bytes /* rank-1 */, const uint32_t* box, int inner_bytes) {
+  cuuint64_t gd[5];
+  cuuint64_t gs[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) { gd[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) gs[i] = strides_bytes[i];
+  CUresult r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
+                              const_cast<void*>(ptr), gd, gs, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              swizzle_for_bytes(inner_bytes), CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr, "[gabril] cuTensorMapEncodeTiled failed: %d (rank %d, box0 %u)\n", (int)r, rank,
+            box[0]);
+    return GABRIL_ERR_DRIVER;
+  }
+  return GABRIL_OK;
+}
+
+// NHWC activation seen as (C, W, H, N); the traversal walks `box_pix` base pixels with `stride`.
+int im2col_map(CUtensorMap* m, const void* ptr, int N, int H, int W, int C, int lower_w,
+               int lower_h, int upper_w, int upper_h, int box_c, int box_pix, int stride) {
+  cuuint64_t gd[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t gs[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  int lo[2] = {lower_w, lower_h};
+  int up[2] = {upper_w, upper_h};
+  cuuint32_t es[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUresult r = g_encode_im2col(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), gd,
+                               gs, lo, up, (cuuint32_t)box_c, (cuuint32_t)box_pix, es,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for_bytes(box_c * 2),
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr,
+            "[gabril] cuTensorMapEncodeIm2col failed: %d (N%d H%d W%d C%d lo(%d,%d) up(%d,%d) "
+            "box_c %d box_pix %d stride %d)\n",
+            (int)r, N, H, W, C, lower_w, lower_h, upper_w, upper_h, box_c, box_pix, stride);
+    return GABRIL_ERR_DRIVER;
+  }
+  // Same driver quirk CUTLASS works around for im2col maps over tensors below 128 KiB.
+  if (g_driver_version <= 13010 && (size_t)N * H * W * C * 2 < 131072)
+    reinterpret_cast<uint64_t*>(m)[1] &= ~(1ull << 21);
+  return GABRIL_OK;
+}
+
+uint64_t desc_hi(uint32_t lbo_bytes, uint32_t sbo_bytes, int layout_type) {
+  uint64_t d = 0;
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
+  d |= (uint64_t)layout_type << 61;
+  return d;
+}
+
+uint32_t make_idesc(int a_mn, int b_mn, int M, int N) {
+  uint32_t d = 0;
+  d |= 1u << 4;   // D format fp32
+  d |= 1u << 7;   // A bf16
+  d |= 1u << 10;  // B bf16
+  d |= (uint32_t)(a_mn ? 1 : 0) << 15;
+  d |= (uint32_t)(b_mn ? 1 : 0) << 16;
+  d |= (uint32_t)(N >> 3) << 17;
+  d |= (uint32_t)(M >> 4) << 24;
+  return d;
+}
+
+uint32_t round_up(uint32_t v, uint32_t a) { return (v + a - 1) / a * a; }
+uint32_t pow2_cols(uint32_t c) {
+  uint32_t r = 32;
+  while (r < c) r <<= 1;
+  return r;
+}
+
+void zero_params(tc::Params& p) { memset(&p, 0, sizeof(p)); }
+
+void pick_stages(tc::Params& p, int kb_per_cta, size_t* smem_bytes) {
+  const uint32_t stage = p.a_stage_bytes + p.b_stage_bytes;
+  // keep two CTAs per SM resident when the tiles are small enough (epilogue/mainloop overlap)
+  const uint32_t budget = (p.tmem_cols <= 256 && stage * 3 <= 100 * 1024) ? 100 * 1024 : 200 * 1024;
+  int st = (int)(budget / stage);
+  st = std::max(2, std::min(st, tc::kMaxStages));
+  st = std::min(st, std::max(2, kb_per_cta));
+  p.stages = st;
+  *smem_bytes = (size_t)st * stage + 1024;
+}
+
+struct ActDims { int N, H, W, C; };
+
+// Common K-major / MN-major schedule helpers ---------------------------------------------------
+// FWD regime: A K-major with kc elements per k-block; B K-major or MN-major.
+void fwd_schedule(tc::Params& p, int kc, int block_n, int b_mn) {
+  const int a_sw = kc * 2;  // 128 or 64 byte swizzle span
+  p.kc = kc;
+  p.block_n = block_n;
+  p.n_acc = 1;
+  p.a_boxes = 1;
+  p.a_box_bytes = 128 * a_sw;
+  p.a_stage_bytes = round_up(p.a_box_bytes, 1024);
+  p.desc_a_hi = desc_hi(16, 8 * a_sw, layout_type_for_bytes(a_sw));
+  if (!b_mn) {
+    p.b_boxes = 1;
+    p.b_box_w = block_n;
+    p.b_box_bytes = block_n * a_sw;
+    p.desc_b_hi = desc_hi(16, 8 * a_sw, layout_type_for_bytes(a_sw));
+  } else {
+    const int bw = std::min(64, block_n);
+    const int b_sw = bw * 2;
+    p.b_boxes = block_n / bw;
+    p.b_box_w = bw;
+    p.b_box_bytes = kc * b_sw;
+    p.desc_b_hi = desc_hi(p.b_box_bytes, 8 * b_sw, layout_type_for_bytes(b_sw));
+  }
+  p.b_stage_bytes = round_up(p.b_boxes * p.b_box_bytes, 1024);
+  p.n_mma = kc / 16;
+  for (int j = 0; j < p.n_mma; ++j) {
+    p.mma_a_off[j] = (uint16_t)((j * 32) >> 4);
+    p.mma_b_off[j] =
+        (uint16_t)((b_mn ? j * 16 * (std::min(64, block_n) * 2) : j * 32) >> 4);
+    p.mma_dcol[j] = 0;
+    p.mma_acc[j] = 0;
+    p.mma_first[j] = (j == 0);
+  }
+  p.idesc = make_idesc(0, b_mn, 128, block_n);
+  p.tmem_cols = pow2_cols(block_n);
+}
+
+int weight_map(CUtensorMap* m, const void* w, int Cout, int T, int Cin, int b_mn, int kc,
+               int block_n) {
+  uint64_t dims[3] = {(uint64_t)Cin, (uint64_t)T, (uint64_t)Cout};
+  uint64_t strides[2] = {(uint64_t)Cin * 2, (uint64_t)T * Cin * 2};
+  if (!b_mn) {
+    uint32_t box[3] = {(uint32_t)kc, 1, (uint32_t)block_n};
+    return tiled_map(m, w, 3, dims, strides, box, kc * 2);
+  }
+  const int bw = std::min(64, block_n);
+  uint32_t box[3] = {(uint32_t)bw, 1, (uint32_t)kc};
+  return tiled_map(m, w, 3, dims, strides, box, bw * 2);
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------
+extern "C" {
+
+int gabril_tc_init(void) { return resolve_driver(); }
+
+int gabril_poll_error(void) {
+  if (!g_err_flag) return 0;
+  int v = 0;
+  if (cudaMemcpy(&v, g_err_flag, sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess)
+    return GABRIL_ERR_CUDA;
+  if (v) cudaMemset(g_err_flag, 0, sizeof(int));
+  return v;
+}
+
+// y[N,OH,OW,Cout] = act( conv(x[N,H,W,Cin], w[Cout][R*S][Cin]) + bias + resid ) * rowmask
+// Cin == 0 mod 32, Cout in {32, 64, 128, 256...} (multiple of 32).  R = S = 1 with H = W = 1 and
+// N = rows gives a plain linear layer (x[rows, Cin]).
+int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void* resid,
+                    const float* rowmask, void* y, int N, int H, int W, int Cin, int Cout, int R,
+                    int S, int stride, int pad, int relu, int out_f32_atomic, int splits,
+                    cudaStream_t stream) {
+  int rc = resolve_driver();
+  if (rc) return rc;
+  if (Cin % 32 || Cout % 32 || N <= 0) return GABRIL_ERR_BAD_SHAPE;
+  const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+  const int kc = (Cin % 64 == 0) ? 64 : 32;
+  const int block_n = std::min(Cout, 128);
+  tc::Params p;
+  zero_params(p);
+  p.kind = tc::KIND_FWD;
+  p.n_classes = 1;
+  p.b_mn = 0;
+  fwd_schedule(p, kc, block_n, 0);
+  const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
+  p.a_im2col = plain ? 0 : 1;
+  const long long M = (long long)N * OH * OW;
+  p.M_total[0] = (int)M;
+  p.N_total = Cout;
+  p.taps = R * S;
+  p.S = S;
+  p.chunks_per_tap = Cin / kc;
+  p.kb_total = p.taps * p.chunks_per_tap;
+  if (splits < 1) splits = 1;
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.OW[0] = OW; p.OHW[0] = OH * OW; p.lower_w[0] = -pad; p.lower_h[0] = -pad;
+  p.trav_stride = stride;
+  p.r_base[0] = 0; p.s_base[0] = 0; p.r_step = 1; p.s_step = 1; p.S_w = S;
+  if (plain) {
+    uint64_t dims[2] = {(uint64_t)Cin, (uint64_t)M};
+    uint64_t strides[1] = {(uint64_t)Cin * 2};
+    uint32_t box[2] = {(uint32_t)kc, 128};
+    rc = tiled_map(&p.mapA[0], x, 2, dims, strides, box, kc * 2);
+  } else {
+    rc = im2col_map(&p.mapA[0], x, N, H, W, Cin, -pad, -pad, pad - (S - 1), pad - (R - 1), kc, 128,
+                    stride);
+  }
+  if (rc) return rc;
+  rc = weight_map(&p.mapB, w, Cout, R * S, Cin, 0, kc, block_n);
+  if (rc) return rc;
+  p.out_mode = out_f32_atomic ? tc::OUT_F32_ATOMIC : tc::OUT_BF16;
+  p.out = y; p.ldo = Cout;
+  p.bias = bias; p.resid = (const bf16*)resid; p.gate = nullptr; p.rowmask = rowmask;
+  p.relu = relu;
+  p.err_flag = g_err_flag;
+  size_t smem;
+  pick_stages(p, p.kb_per_split, &smem);
+  dim3 grid((unsigned)((M + 127) / 128), (unsigned)(Cout / block_n), (unsigned)splits);
+  return tc::launch(p, grid, smem, stream);
+}
+
+// dx[N,H,W,Cin] = gate( conv_transpose(dy[N,OH,OW,Cout], w[Cout][R*S][Cin]) + addend )
+//   gate: dx = gate_tensor > 0 ? dx : 0 (ReLU backward of the layer below), rowmask: per-pixel
+//   multiplier (GMD).  stride 1 (any R,S,pad) and the k4/s2/p1 encoder convs are supported.
+int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const void* gate,
+                      const float* rowmask, void* dx, int N, int H, int W, int Cin, int Cout,
+                      int R, int S, int stride, int pad, cudaStream_t stream) {
+  int rc = resolve_driver();
+  if (rc) return rc;
+  if (Cin % 32 || Cout % 32 || N <= 0) return GABRIL_ERR_BAD_SHAPE;
+  const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+  const int kc = (Cout % 64 == 0) ? 64 : 32;  // contraction over Cout
+  const int block_n = std::min(Cin, 128);
+  tc::Params p;
+  zero_params(p);
+  p.kind = tc::KIND_FWD;
+  p.b_mn = 1;
+  fwd_schedule(p, kc, block_n, 1);
+  p.N_total = Cin;
+  p.chunks_per_tap = Cout / kc;
+  p.trav_stride = 1;
+  p.S_w = S;
+  const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
+  unsigned grid_x = 0;
+  if (stride == 1) {
+    p.n_classes = 1;
+    p.a_im2col = plain ? 0 : 1;
+    const long long M = (long long)N * H * W;
+    p.M_total[0] = (int)M;
+    p.taps = R * S;
+    p.S = S;
+    p.OW[0] = W; p.OHW[0] = H * W;
+    p.lower_w[0] = pad - (S - 1); p.lower_h[0] = pad - (R - 1);
+    p.r_base[0] = R - 1; p.s_base[0] = S - 1; p.r_step = -1; p.s_step = -1;
+    if (plain) {
+      uint64_t dims[2] = {(uint64_t)Cout, (uint64_t)M};
+      uint64_t strides[1] = {(uint64_t)Cout * 2};
+      uint32_t box[2] = {(uint32_t)kc, 128};
+      rc = tiled_map(&p.mapA[0], dy, 2, dims, strides, box, kc * 2);
+    } else {
+      rc = im2col_map(&p.mapA[0], dy, N, OH, OW, Cout, p.lower_w[0], p.lower_h[0], -pad, -pad, kc,
+                      128, 1);
+    }
+    if (rc) return rc;
+    grid_x = (unsigned)((M + 127) / 128);
+  } else if (stride == 2 && R == 4 && S == 4 && pad == 1) {
+    // Input pixel (ih, iw) of parity (a_h, a_w) receives exactly 2x2 taps: kh = 3 - a_h - 2 r',
+    // read from dy row j_h - 1 + a_h + r'  (j_h = ih / 2).  Four stride-1 sub-convolutions.
+    p.n_classes = 4;
+    p.a_im2col = 1;
+    p.remap = 1;
+    p.OHf = H; p.OWf = W;
+    p.taps = 4;
+    p.S = 2;
+    p.r_step = -2; p.s_step = -2;
+    int max_m = 0;
+    for (int c = 0; c < 4; ++c) {
+      const int ah = c >> 1, aw = c & 1;
+      const int Hs = (H - ah + 1) / 2, Ws = (W - aw + 1) / 2;
+      p.ah[c] = ah; p.aw[c] = aw; p.Hs[c] = Hs; p.Ws[c] = Ws;
+      p.M_total[c] = N * Hs * Ws;
+      max_m = std::max(max_m, p.M_total[c]);
+      p.OW[c] = Ws; p.OHW[c] = Hs * Ws;
+      p.lower_w[c] = aw - 1; p.lower_h[c] = ah - 1;
+      p.r_base[c] = 3 - ah; p.s_base[c] = 3 - aw;
+      const int upper_w = p.lower_w[c] + Ws - OW, upper_h = p.lower_h[c] + Hs - OH;
+      rc = im2col_map(&p.mapA[c], dy, N, OH, OW, Cout, p.lower_w[c], p.lower_h[c], upper_w,
+                      upper_h, kc, 128, 1);
+      if (rc) return rc;
+    }
+    grid_x = (unsigned)((max_m + 127) / 128);
+  } else {
+    return GABRIL_ERR_BAD_SHAPE;
+  }
+  p.kb_total = p.taps * p.chunks_per_tap;
+  p.kb_per_split = p.kb_total;
+  rc = weight_map(&p.mapB, w, Cout, R * S, Cin, 1, kc, block_n);
+  if (rc) return rc;
+  p.out_mode = tc::OUT_BF16;
+  p.out = dx; p.ldo = Cin;
+  p.bias = nullptr; p.resid = (const bf16*)addend; p.gate = (const bf16*)gate; p.rowmask = rowmask;
+  p.relu = 0;
+  p.err_flag = g_err_flag;
+  size_t smem;
+  pick_stages(p, p.kb_total, &smem);
+  dim3 grid(grid_x, (unsigned)(Cin / block_n), (unsigned)p.n_classes);
+  return tc::launch(p, grid, smem, stream);
+}
+
+// dw[Cout][R*S][Cin] (fp32) += sum_pixels dy[p, Cout]^T * im2col(x)[p, (tap, Cin)].
+// The caller zeroes dw (it lives in the flat gradient arena).  Also serves linear layers
+// (R = S = 1, H = W = 1, N = rows): dw[Cout][Cin] += dy[rows,Cout]^T x[rows,Cin].
+int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int Cin,
+                      int Cout, int R, int S, int stride, int pad, int direct_store,
+                      cudaStream_t stream) {
+  int rc = resolve_driver();
+  if (rc) return rc;
+  if (Cin % 32 || Cout % 32 || N <= 0) return GABRIL_ERR_BAD_SHAPE;
+  const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+  const long long P = (long long)N * OH * OW;  // contraction length (output pixels)
+  const int T = R * S;
+  const int KP = 64;
+  tc::Params p;
+  zero_params(p);
+  p.kind = tc::KIND_WGRAD;
+  p.n_classes = 1;
+  const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
+  p.a_im2col = plain ? 0 : 1;
+  p.kc = KP;
+  // A = dy^T: M = Cout rows padded to 128 with out-of-range (zero-filled) boxes.
+  const int aw = std::min(64, Cout), a_sw = aw * 2;
+  p.a_box_w = aw;
+  p.a_boxes = 128 / aw;
+  p.a_box_bytes = KP * a_sw;
+  p.a_stage_bytes = round_up(p.a_boxes * p.a_box_bytes, 1024);
+  p.desc_a_hi = desc_hi(p.a_box_bytes, 8 * a_sw, layout_type_for_bytes(a_sw));
+  // B = x (per tap): N = block_n channels.
+  const int block_n = std::min(Cin, 128);
+  const int bw = std::min(64, block_n), b_sw = bw * 2;
+  p.block_n = block_n;
+  p.b_box_w = bw;
+  p.b_boxes = block_n / bw;
+  p.b_box_bytes = KP * b_sw;
+  p.desc_b_hi = desc_hi(p.b_box_bytes, 8 * b_sw, layout_type_for_bytes(b_sw));
+  const uint32_t b_tap_bytes = p.b_boxes * p.b_box_bytes;
+  // accumulators: as many taps per CTA as TMEM (512 cols) and smem (2 stages in 200 KB) allow
+  int n_acc = std::min(T, 512 / block_n);
+  while (n_acc > 1 && 2 * (p.a_stage_bytes + n_acc * b_tap_bytes) > 200 * 1024) --n_acc;
+  n_acc = std::min(n_acc, tc::kMaxMma / (KP / 16));
+  p.n_acc = n_acc;
+  p.taps = T;
+  p.tap_groups = (T + n_acc - 1) / n_acc;
+  p.S = S;
+  p.b_stage_bytes = round_up(n_acc * b_tap_bytes, 1024);
+  p.n_mma = 0;
+  for (int t = 0; t < n_acc; ++t)
+    for (int j = 0; j < KP / 16; ++j) {
+      const int i = p.n_mma++;
+      p.mma_a_off[i] = (uint16_t)((j * 16 * a_sw) >> 4);
+      p.mma_b_off[i] = (uint16_t)((t * b_tap_bytes + j * 16 * b_sw) >> 4);
+      p.mma_dcol[i] = (uint16_t)(t * block_n);
+      p.mma_acc[i] = (uint8_t)t;
+      p.mma_first[i] = (j == 0);
+    }
+  p.idesc = make_idesc(1, 1, 128, block_n);
+  p.tmem_cols = pow2_cols(n_acc * block_n);
+  p.M_total[0] = Cout;
+  p.N_total = Cin;
+  p.kb_total = (int)((P + KP - 1) / KP);
+  p.OW[0] = OW; p.OHW[0] = OH * OW; p.lower_w[0] = -pad; p.lower_h[0] = -pad;
+  p.trav_stride = stride;
+  {
+    uint64_t dims[2] = {(uint64_t)Cout, (uint64_t)P};
+    uint64_t strides[1] = {(uint64_t)Cout * 2};
+    uint32_t box[2] = {(uint32_t)aw, (uint32_t)KP};
+    rc = tiled_map(&p.mapA[0], dy, 2, dims, strides, box, a_sw);
+    if (rc) return rc;
+  }
+  if (plain) {
+    uint64_t dims[2] = {(uint64_t)Cin, (uint64_t)P};
+    uint64_t strides[1] = {(uint64_t)Cin * 2};
+    uint32_t box[2] = {(uint32_t)bw, (uint32_t)KP};
+    rc = tiled_map(&p.mapB, x, 2, dims, strides, box, b_sw);
+  } else {
+    rc = im2col_map(&p.mapB, x, N, H, W, Cin, -pad, -pad, pad - (S - 1), pad - (R - 1), bw, KP,
+                    stride);
+  }
+  if (rc) return rc;
+  const int m_tiles = (Cout + 127) / 128, n_tiles = Cin / block_n;
+  int splits = 1;
+  if (!direct_store) {
+    const int base = m_tiles * n_tiles * p.tap_groups;
+    splits = std::max(1, std::min(p.kb_total, (2 * g_num_sms + base - 1) / base));
+  }
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.out_mode = direct_store ? tc::OUT_F32_STORE : tc::OUT_F32_ATOMIC;
+  p.out = dw;
+  p.ldo = (long long)T * Cin;
+  p.tap_stride = Cin;
+  p.err_flag = g_err_flag;
+  size_t smem;
+  pick_stages(p, p.kb_per_split, &smem);
+  dim3 grid((unsigned)m_tiles, (unsigned)(n_tiles * p.tap_groups), (unsigned)splits);
+  return tc::launch(p, grid, smem, stream);
+}
+
+}  // extern "C"
