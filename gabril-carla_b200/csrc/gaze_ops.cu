@@ -1,0 +1,948 @@
+// Memory-bound kernels of the GABRIL training step (sm_100a): frame formatting, gaze heat-map
+// synthesis, gaze-mask dropout and the activation-map regulariser (forward + backward).
+// Reference ops replaced (Gonglitian/GABRIL-CARLA, vlm_gaze/):
+//   data_utils/data_loader_robomimic.py:144-157  _gather_last_s_frames      (integer, bit-exact)
+//   data_utils/data_loader_robomimic.py:179-202  _format_obs_image          gabril_obs_format / _patches
+//   data_utils/data_loader_robomimic.py:85-139   GazePreprocessor.forward   gabril_gaze_splat
+//   data_utils/data_loader_robomimic.py:204-278  build_stack_heatmaps       gabril_gaze_splat
+//   data_utils/gaze_utils.py:7-30                get_gaze_mask              gabril_gaze_mask_fwd/_bwd
+//   data_utils/gaze_utils.py:33-52               apply_gmd_dropout          gabril_gmd_keep / _mask
+//   train/train_bc.py:145-171                    Reg/Teacher MSE loss       gabril_reg_mse
+// All of them are HBM-bound: one pass over the inputs, 16-byte accesses, per-sample tables in
+// shared memory, warp-shuffle reductions.
+#include <cfloat>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kMaxS = 8;     // frame-stack length supported by the splat kernel
+constexpr int kMaxPts = 16;  // gaze points per frame
+
+__device__ __forceinline__ int frame_index(int s, int S, int center, int L) {
+  // data_loader_robomimic.py:151-152: window [center-S+1, center], each index clamped to [0, L-1]
+  return min(max(center - S + 1 + s, 0), L - 1);
+}
+
+// ---- block reductions (all threads must call; result broadcast) --------------------------------
+__device__ __forceinline__ float block_sum(float v, float* scratch) {
+  v = warp_sum(v);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if (lane == 0) scratch[wid] = v;
+  __syncthreads();
+  float r = 0.f;
+  for (int i = 0; i < nw; ++i) r += scratch[i];  // fixed order: deterministic
+  return r;
+}
+__device__ __forceinline__ float block_max(float v, float* scratch) {
+  v = warp_max(v);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if (lane == 0) scratch[wid] = v;
+  __syncthreads();
+  float r = scratch[0];
+  for (int i = 1; i < nw; ++i) r = fmaxf(r, scratch[i]);
+  return r;
+}
+__device__ __forceinline__ float block_min(float v, float* scratch) {
+  v = warp_min(v);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if (lane == 0) scratch[wid] = v;
+  __syncthreads();
+  float r = scratch[0];
+  for (int i = 1; i < nw; ++i) r = fminf(r, scratch[i]);
+  return r;
+}
+
+// ---- PyTorch upsample_bicubic2d index math (fp32, A = -0.75, align_corners = False) -------------
+__device__ __forceinline__ float cubic1(float x) {
+  const float A = -0.75f;
+  return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f;
+}
+__device__ __forceinline__ float cubic2(float x) {
+  const float A = -0.75f;
+  return ((A * x - 5.f * A) * x + 8.f * A) * x - 4.f * A;
+}
+// taps i0-1 .. i0+2 clamped into [0, in-1]; weights in tap order.
+__device__ __forceinline__ void bicubic_taps(int dst, float scale, int in_size, int idx[4],
+                                             float w[4]) {
+  const float src = scale * ((float)dst + 0.5f) - 0.5f;
+  const float fl = floorf(src);
+  const int i0 = (int)fl;
+  const float t = src - fl;
+  w[0] = cubic2(t + 1.f);
+  w[1] = cubic1(t);
+  const float t2 = 1.f - t;
+  w[2] = cubic1(t2);
+  w[3] = cubic2(t2 + 1.f);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) idx[k] = min(max(i0 - 1 + k, 0), in_size - 1);
+}
+
+// =================================================================================================
+// K1a: uint8 NHWC frame stack -> fp32 NCHW (the reference-facing layout of _format_obs_image)
+// =================================================================================================
+__device__ __forceinline__ float u8_to_unit(uint32_t v) { return __fdiv_rn((float)v, 255.0f); }
+__device__ __forceinline__ float to_gray(float r, float g, float b) {
+  // ((0.299 R) + (0.587 G)) + (0.114 B), every op rounded separately like the reference's
+  // three torch multiplies and two adds (data_loader_robomimic.py:192-193)
+  return __fadd_rn(__fadd_rn(__fmul_rn(0.299f, r), __fmul_rn(0.587f, g)), __fmul_rn(0.114f, b));
+}
+
+template <bool GRAY>
+__global__ void __launch_bounds__(256)
+obs_format_kernel(const uint8_t* __restrict__ frames, float* __restrict__ out, int B, int L, int S,
+                  int center, int H, int W) {
+  const int W4 = W >> 2;
+  const long long total = (long long)B * S * H * W4;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int x4 = (int)(idx % W4);
+    long long t = idx / W4;
+    const int y = (int)(t % H);
+    t /= H;
+    const int s = (int)(t % S);
+    const int b = (int)(t / S);
+    const int f = frame_index(s, S, center, L);
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(
+        frames + ((((long long)b * L + f) * H + y) * W + x4 * 4) * 3);
+    const uint32_t w0 = __ldg(src), w1 = __ldg(src + 1), w2 = __ldg(src + 2);
+    const uint32_t by[12] = {w0 & 255u, (w0 >> 8) & 255u, (w0 >> 16) & 255u, w0 >> 24,
+                             w1 & 255u, (w1 >> 8) & 255u, (w1 >> 16) & 255u, w1 >> 24,
+                             w2 & 255u, (w2 >> 8) & 255u, (w2 >> 16) & 255u, w2 >> 24};
+    const long long plane = (long long)H * W;
+    if (GRAY) {
+      float4 o;
+      o.x = to_gray(u8_to_unit(by[0]), u8_to_unit(by[1]), u8_to_unit(by[2]));
+      o.y = to_gray(u8_to_unit(by[3]), u8_to_unit(by[4]), u8_to_unit(by[5]));
+      o.z = to_gray(u8_to_unit(by[6]), u8_to_unit(by[7]), u8_to_unit(by[8]));
+      o.w = to_gray(u8_to_unit(by[9]), u8_to_unit(by[10]), u8_to_unit(by[11]));
+      float* dst = out + ((long long)b * S + s) * plane + (long long)y * W + x4 * 4;
+      *reinterpret_cast<float4*>(dst) = o;
+    } else {
+      float* dst = out + (((long long)b * S + s) * 3) * plane + (long long)y * W + x4 * 4;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        float4 o = make_float4(u8_to_unit(by[c]), u8_to_unit(by[3 + c]), u8_to_unit(by[6 + c]),
+                               u8_to_unit(by[9 + c]));
+        *reinterpret_cast<float4*>(dst + c * plane) = o;
+      }
+    }
+  }
+}
+
+// =================================================================================================
+// K1b: uint8 NHWC frame stack -> bf16 patch matrix of conv_1 (k4 s2 p1), fused format + im2col.
+// Row = output pixel (b, oh, ow); column = (r*4 + s)*C0 + (frame*C' + c), zero padded to Kp.
+// One thread = one (pixel, filter row r): 4 taps x C0 values.
+// =================================================================================================
+template <int S_, bool GRAY>
+__global__ void __launch_bounds__(256)
+obs_patches_kernel(const uint8_t* __restrict__ frames, bf16* __restrict__ out, int B, int L,
+                   int center, int H, int W, int OH, int OW, int Kp) {
+  constexpr int CP = GRAY ? 1 : 3;
+  constexpr int C0 = S_ * CP;
+  const long long total = (long long)B * OH * OW * 4;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int r = (int)(idx & 3);
+    long long pix = idx >> 2;
+    const int ow = (int)(pix % OW);
+    long long t = pix / OW;
+    const int oh = (int)(t % OH);
+    const int b = (int)(t / OH);
+    const int ih = 2 * oh - 1 + r;
+    float v[4][C0];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const int iw = 2 * ow - 1 + s;
+      const bool ok = (ih >= 0) && (ih < H) && (iw >= 0) && (iw < W);
+#pragma unroll
+      for (int fs = 0; fs < S_; ++fs) {
+        float rr = 0.f, gg = 0.f, bb = 0.f;
+        if (ok) {
+          const int f = frame_index(fs, S_, center, L);
+          const uint8_t* src = frames + ((((long long)b * L + f) * H + ih) * W + iw) * 3;
+          rr = u8_to_unit(__ldg(src));
+          gg = u8_to_unit(__ldg(src + 1));
+          bb = u8_to_unit(__ldg(src + 2));
+        }
+        if (GRAY) {
+          v[s][fs] = ok ? to_gray(rr, gg, bb) : 0.f;
+        } else {
+          v[s][fs * 3 + 0] = rr;
+          v[s][fs * 3 + 1] = gg;
+          v[s][fs * 3 + 2] = bb;
+        }
+      }
+    }
+    bf16* dst = out + pix * Kp + r * (4 * C0);
+    const float* vf = &v[0][0];
+    if ((4 * C0) % 8 == 0) {
+#pragma unroll
+      for (int i = 0; i < (4 * C0) / 8; ++i) {
+        uint4 o;
+        o.x = pack_bf16x2(vf[8 * i + 0], vf[8 * i + 1]);
+        o.y = pack_bf16x2(vf[8 * i + 2], vf[8 * i + 3]);
+        o.z = pack_bf16x2(vf[8 * i + 4], vf[8 * i + 5]);
+        o.w = pack_bf16x2(vf[8 * i + 6], vf[8 * i + 7]);
+        *reinterpret_cast<uint4*>(dst + 8 * i) = o;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < (4 * C0) / 4; ++i) {
+        uint2 o;
+        o.x = pack_bf16x2(vf[4 * i + 0], vf[4 * i + 1]);
+        o.y = pack_bf16x2(vf[4 * i + 2], vf[4 * i + 3]);
+        *reinterpret_cast<uint2*>(dst + 4 * i) = o;
+      }
+    }
+    if (r == 3) {
+      for (int k = 16 * C0; k < Kp; k += 4)
+        *reinterpret_cast<uint2*>(out + pix * Kp + k) = make_uint2(0u, 0u);
+    }
+  }
+}
+
+// =================================================================================================
+// K2: gaze heat maps.  Closed form of the reference's scatter_add + separable blur (with its
+// row-band padding quirk) + per-frame min-max + causal aggregation + second min-max.
+//   raw_s(y,x) = coeff_s * sum_p  band_s(y) k_s[y_p - y + R_s] * k_s[x_p - x + R_s]
+// One CTA = one sample x one row slab; every CTA recomputes the (cheap) per-map extrema.
+// =================================================================================================
+struct SplatArgs {
+  const float* gaze;  // [B, L, P*2]
+  float* out;         // [B, S, H, W]
+  const float* ktab;  // [S][ktab_stride] fp32 taps of the per-step 1-D kernels
+  int Lk[kMaxS];
+  int ktab_stride;
+  float agg[kMaxS][kMaxS];  // agg[s][j], j <= s: causal aggregation coefficients
+  float step_coeff[kMaxS];  // multiscale: raw_s * coeff_s (1 otherwise)
+  int use_step_coeff;
+  int normalize_base;  // alpha_decay: per-frame min-max before aggregation
+  int aggregate;       // 0: out = base (gaze.temporal_flag = false)
+  int B, L, S, center, P, H, W, nsplit;
+};
+
+__global__ void __launch_bounds__(256) gaze_splat_kernel(const __grid_constant__ SplatArgs a) {
+  extern __shared__ float sm[];
+  const int S = a.S, P = a.P, H = a.H, W = a.W;
+  float* kyv = sm;               // [S*P][H]
+  float* kxv = kyv + S * P * H;  // [S*P][W]
+  __shared__ int s_xi[kMaxS * kMaxPts], s_yi[kMaxS * kMaxPts], s_ok[kMaxS * kMaxPts];
+  __shared__ float red_mn[8][kMaxS], red_mx[8][kMaxS];
+  __shared__ float s_mn[kMaxS], s_mx[kMaxS], s_amn[kMaxS], s_amx[kMaxS];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int b = blockIdx.x, split = blockIdx.y;
+
+  // ---- integer pixel indices (bit-exact: clamp, ONE fp32 multiply, truncate, clamp) ----
+  if (tid < S * P) {
+    const int s = tid / P, p = tid - s * P;
+    const int f = frame_index(s, S, a.center, a.L);
+    const float* gp = a.gaze + (((long long)b * a.L + f) * P + p) * 2;
+    const float gx = gp[0], gy = gp[1];
+    s_ok[tid] = (gx >= 0.f) && (gy >= 0.f);
+    const float cx = fminf(fmaxf(gx, 0.f), 1.f), cy = fminf(fmaxf(gy, 0.f), 1.f);
+    int xi = (int)__fmul_rn(cx, (float)(W - 1));
+    int yi = (int)__fmul_rn(cy, (float)(H - 1));
+    s_xi[tid] = min(max(xi, 0), W - 1);
+    s_yi[tid] = min(max(yi, 0), H - 1);
+  }
+  __syncthreads();
+  int ylo = H, yhi = 0;  // union of the per-step bands [R_s, H - R_s)
+  for (int s = 0; s < S; ++s) {
+    const int R = a.Lk[s] >> 1;
+    ylo = min(ylo, R);
+    yhi = max(yhi, H - R);
+  }
+  for (int i = tid; i < S * P * H; i += blockDim.x) {
+    const int sp = i / H, y = i - sp * H;
+    const int s = sp / P;
+    const int Lk = a.Lk[s], R = Lk >> 1;
+    const int d = s_yi[sp] - y + R;
+    const bool in = s_ok[sp] && d >= 0 && d < Lk && y >= R && y < H - R;
+    kyv[i] = in ? a.ktab[s * a.ktab_stride + d] : 0.f;
+  }
+  for (int i = tid; i < S * P * W; i += blockDim.x) {
+    const int sp = i / W, x = i - sp * W;
+    const int s = sp / P;
+    const int Lk = a.Lk[s], R = Lk >> 1;
+    const int d = s_xi[sp] - x + R;
+    const bool in = s_ok[sp] && d >= 0 && d < Lk;
+    kxv[i] = in ? a.ktab[s * a.ktab_stride + d] : 0.f;
+  }
+  __syncthreads();
+
+  auto raw_at = [&](int y, int x, float raw[kMaxS]) {
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s) {
+      if (s < S) {
+        float acc = 0.f;
+        for (int p = 0; p < P; ++p) acc = fmaf(kyv[(s * P + p) * H + y], kxv[(s * P + p) * W + x], acc);
+        raw[s] = a.use_step_coeff ? __fmul_rn(acc, a.step_coeff[s]) : acc;
+      }
+    }
+  };
+  const bool has_outside = (ylo > 0) || (yhi < H);  // rows where every raw_s is exactly 0
+  const int band_px = max(yhi - ylo, 0) * W;
+
+  // ---- pass A: per-frame extrema of the raw maps ----
+  float mn[kMaxS], mx[kMaxS];
+#pragma unroll
+  for (int s = 0; s < kMaxS; ++s) { mn[s] = 0.f; mx[s] = 1.f; }
+  if (a.normalize_base) {
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s) { mn[s] = has_outside ? 0.f : FLT_MAX; mx[s] = has_outside ? 0.f : -FLT_MAX; }
+    for (int i = tid; i < band_px; i += blockDim.x) {
+      const int y = ylo + i / W, x = i % W;
+      float raw[kMaxS];
+      raw_at(y, x, raw);
+#pragma unroll
+      for (int s = 0; s < kMaxS; ++s)
+        if (s < S) { mn[s] = fminf(mn[s], raw[s]); mx[s] = fmaxf(mx[s], raw[s]); }
+    }
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s)
+      if (s < S) {
+        const float lo = warp_min(mn[s]), hi = warp_max(mx[s]);
+        if (lane == 0) { red_mn[wid][s] = lo; red_mx[wid][s] = hi; }
+      }
+    __syncthreads();
+    if (tid < S) {
+      float lo = red_mn[0][tid], hi = red_mx[0][tid];
+      for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { lo = fminf(lo, red_mn[w][tid]); hi = fmaxf(hi, red_mx[w][tid]); }
+      s_mn[tid] = lo;
+      s_mx[tid] = hi;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s)
+      if (s < S) { mn[s] = s_mn[s]; mx[s] = s_mx[s]; }
+  }
+  // base_s = (raw - mn) / ((mx - mn) + 1e-8)   (data_loader_robomimic.py:134-136)
+  auto agg_at = [&](const float raw[kMaxS], float agg[kMaxS]) {
+    float base[kMaxS];
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s)
+      if (s < S)
+        base[s] = a.normalize_base
+                      ? __fdiv_rn(__fsub_rn(raw[s], mn[s]), __fadd_rn(__fsub_rn(mx[s], mn[s]), 1e-8f))
+                      : raw[s];
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s)
+      if (s < S) {
+        if (!a.aggregate || s == 0) {
+          agg[s] = base[s];
+        } else {
+          // (base[:, :s+1] * coeffs).sum(dim=1): products rounded, then summed j = 0..s (:265-274)
+          float acc = __fmul_rn(a.agg[s][0], base[0]);
+#pragma unroll
+          for (int j = 1; j < kMaxS; ++j)
+            if (j <= s) acc = __fadd_rn(acc, __fmul_rn(a.agg[s][j], base[j]));
+          agg[s] = acc;
+        }
+      }
+  };
+  float zero_raw[kMaxS];
+#pragma unroll
+  for (int s = 0; s < kMaxS; ++s) zero_raw[s] = 0.f;
+  float agg_out[kMaxS];  // value of every aggregated map on the all-zero rows
+  agg_at(zero_raw, agg_out);
+
+  // ---- pass B: extrema of the aggregated maps ----
+  float amn[kMaxS], amx[kMaxS];
+  const bool second_norm = a.aggregate != 0;
+  if (second_norm) {
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s) { amn[s] = has_outside ? agg_out[s] : FLT_MAX; amx[s] = has_outside ? agg_out[s] : -FLT_MAX; }
+    for (int i = tid; i < band_px; i += blockDim.x) {
+      const int y = ylo + i / W, x = i % W;
+      float raw[kMaxS], ag[kMaxS];
+      raw_at(y, x, raw);
+      agg_at(raw, ag);
+#pragma unroll
+      for (int s = 0; s < kMaxS; ++s)
+        if (s < S) { amn[s] = fminf(amn[s], ag[s]); amx[s] = fmaxf(amx[s], ag[s]); }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s)
+      if (s < S) {
+        const float lo = warp_min(amn[s]), hi = warp_max(amx[s]);
+        if (lane == 0) { red_mn[wid][s] = lo; red_mx[wid][s] = hi; }
+      }
+    __syncthreads();
+    if (tid < S) {
+      float lo = red_mn[0][tid], hi = red_mx[0][tid];
+      for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { lo = fminf(lo, red_mn[w][tid]); hi = fmaxf(hi, red_mx[w][tid]); }
+      s_amn[tid] = lo;
+      s_amx[tid] = hi;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s)
+      if (s < S) { amn[s] = s_amn[s]; amx[s] = s_amx[s]; }
+  }
+  auto finish = [&](float v, int s) {
+    return second_norm ? __fdiv_rn(__fsub_rn(v, amn[s]), __fadd_rn(__fsub_rn(amx[s], amn[s]), 1e-8f)) : v;
+  };
+
+  // ---- pass C: write this CTA's row slab of all S maps (float4 stores) ----
+  const int rows_per = (H + a.nsplit - 1) / a.nsplit;
+  const int y0 = split * rows_per, y1 = min(y0 + rows_per, H);
+  const int W4 = W >> 2;
+  float* outb = a.out + (long long)b * S * H * W;
+  for (int i = tid; i < (y1 - y0) * W4; i += blockDim.x) {
+    const int y = y0 + i / W4, x = (i % W4) * 4;
+    float o[kMaxS][4];
+    if (y < ylo || y >= yhi) {
+#pragma unroll
+      for (int s = 0; s < kMaxS; ++s)
+        if (s < S) { const float v = finish(agg_out[s], s); o[s][0] = o[s][1] = o[s][2] = o[s][3] = v; }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float raw[kMaxS], ag[kMaxS];
+        raw_at(y, x + k, raw);
+        agg_at(raw, ag);
+#pragma unroll
+        for (int s = 0; s < kMaxS; ++s)
+          if (s < S) o[s][k] = finish(ag[s], s);
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < kMaxS; ++s)
+      if (s < S)
+        *reinterpret_cast<float4*>(outb + ((long long)s * H + y) * W + x) =
+            make_float4(o[s][0], o[s][1], o[s][2], o[s][3]);
+  }
+}
+
+// =================================================================================================
+// K6: gaze-mask dropout.  gmd_keep: K[b, j] = mean_s bicubic_down(g[b, s])[j] + batch-global
+// min / max (ordered-uint atomics).  gmd_mask: rowmask[b, j] = (A < 0.7 Khat + 0.3) or the keep
+// probability itself in test mode.
+// =================================================================================================
+__global__ void __launch_bounds__(256)
+gmd_keep_kernel(const float* __restrict__ g, float* __restrict__ K, unsigned int* __restrict__ mnmx,
+                int B, int S, int H, int W, int h, int w) {
+  __shared__ float scratch[32];
+  const int n = h * w;
+  const long long total = (long long)B * n;
+  const float sy = (float)H / (float)h, sx = (float)W / (float)w;
+  float lo = FLT_MAX, hi = -FLT_MAX;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int j = (int)(idx % n);
+    const int b = (int)(idx / n);
+    const int oy = j / w, ox = j - oy * w;
+    int iy[4], ix[4];
+    float wy[4], wx[4];
+    bicubic_taps(oy, sy, H, iy, wy);
+    bicubic_taps(ox, sx, W, ix, wx);
+    float acc = 0.f;
+    for (int s = 0; s < S; ++s) {
+      const float* gp = g + ((long long)b * S + s) * H * W;
+      float rows[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const float* rp = gp + (long long)iy[r] * W;
+        rows[r] = __ldg(rp + ix[0]) * wx[0] + __ldg(rp + ix[1]) * wx[1] + __ldg(rp + ix[2]) * wx[2] +
+                  __ldg(rp + ix[3]) * wx[3];
+      }
+      const float v = rows[0] * wy[0] + rows[1] * wy[1] + rows[2] * wy[2] + rows[3] * wy[3];
+      acc = (s == 0) ? v : __fadd_rn(acc, v);
+    }
+    const float k = (S == 1) ? acc : __fdiv_rn(acc, (float)S);
+    K[idx] = k;
+    lo = fminf(lo, k);
+    hi = fmaxf(hi, k);
+  }
+  lo = block_min(lo, scratch);
+  hi = block_max(hi, scratch);
+  if (threadIdx.x == 0) {
+    atomicMin(&mnmx[0], f32_to_ordered(lo));
+    atomicMax(&mnmx[1], f32_to_ordered(hi));
+  }
+}
+
+__global__ void gmd_init_kernel(unsigned int* mnmx) {
+  mnmx[0] = 0xFFFFFFFFu;
+  mnmx[1] = 0u;
+}
+
+__global__ void __launch_bounds__(256)
+gmd_mask_kernel(const float* __restrict__ K, const float* __restrict__ A,
+                const unsigned int* __restrict__ mnmx, float* __restrict__ rowmask,
+                float* __restrict__ keep_out, long long total, float drop_p, int test_mode) {
+  const float mn = ordered_to_f32(mnmx[0]), mx = ordered_to_f32(mnmx[1]);
+  const float den = __fadd_rn(__fsub_rn(mx, mn), 1e-8f);
+  const float one_minus = (float)(1.0 - (double)drop_p);
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const float kh = __fdiv_rn(__fsub_rn(K[idx], mn), den);
+    const float kt = __fadd_rn(__fmul_rn(drop_p, kh), one_minus);
+    if (keep_out) keep_out[idx] = kt;
+    rowmask[idx] = test_mode ? kt : ((A[idx] < kt) ? 1.f : 0.f);
+  }
+}
+
+// z[B, C, n] fp32 (reference layout) times rowmask[B, n]
+__global__ void __launch_bounds__(256)
+rowmask_apply_nchw_kernel(const float* __restrict__ z, const float* __restrict__ rowmask,
+                          float* __restrict__ out, int B, int C, int n) {
+  const long long total = (long long)B * C * n;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int j = (int)(idx % n);
+    const int b = (int)(idx / ((long long)C * n));
+    out[idx] = z[idx] * rowmask[(long long)b * n + j];
+  }
+}
+
+// =================================================================================================
+// K5: get_gaze_mask forward / backward and the fused Reg-MSE loss + gradient.
+// One CTA = one sample; thread x owns output column x (blockDim = W rounded to a warp multiple).
+// Shared: p[n] softmax, t[h][W] row-interpolated map, sacc[h][W] y-adjoint accumulators,
+// bicubic tap tables for both axes, dp[n].
+// =================================================================================================
+enum { MODE_MSE = 0, MODE_MASK_FWD = 1, MODE_MASK_BWD = 2 };
+
+struct RegArgs {
+  const void* z;         // bf16 [B, n, C] (NHWC) or fp32 [B, C, n] (NCHW)
+  const float* g1;       // MODE_MSE: target plane of sample b at g1 + b * g1_bstride
+  long long g1_bstride;
+  const float* sel;      // optional [B]: 0 => sample skipped (gaze.ratio < 1)
+  float* mask_out;       // MODE_MASK_FWD: [B, H*W]
+  const float* grad_in;  // MODE_MASK_BWD: [B, H*W]
+  void* dz;              // gradient w.r.t. z, same layout as z (MODE_MSE / MODE_MASK_BWD)
+  float* loss_part;      // MODE_MSE: [B] per-sample sum of squared differences
+  float* stats;          // optional [B][4]: min, max, argmin, argmax of the up-sampled map
+  float beta, grad_scale;
+  int B, C, h, w, H, W;
+};
+
+template <bool NHWC_BF16, int MODE>
+__global__ void __launch_bounds__(1024) reg_kernel(const __grid_constant__ RegArgs a) {
+  extern __shared__ float sm[];
+  const int h = a.h, w = a.w, H = a.H, W = a.W, C = a.C, n = h * w;
+  float* p = sm;                                        // [n]
+  float* tmap = p + n;                                  // [h][W]
+  float* sacc = tmap + h * W;                           // [h][W]
+  float* wyt = sacc + h * W;                            // [H][4]
+  int* iyt = reinterpret_cast<int*>(wyt + 4 * H);       // [H][4]
+  float* wxt = reinterpret_cast<float*>(iyt + 4 * H);   // [W][4]
+  int* ixt = reinterpret_cast<int*>(wxt + 4 * W);       // [W][4]
+  float* dp = reinterpret_cast<float*>(ixt + 4 * W);    // [n]
+  int* xrange = reinterpret_cast<int*>(dp + n);         // [w][2]
+  __shared__ float scratch[32];
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarp = blockDim.x >> 5;
+  const int b = blockIdx.x;
+  const bool skip = (a.sel != nullptr) && (a.sel[b] <= 0.f);
+
+  const bf16* zb16 = reinterpret_cast<const bf16*>(a.z) + (long long)b * n * C;
+  const float* zf32 = reinterpret_cast<const float*>(a.z) + (long long)b * n * C;
+
+  if (MODE == MODE_MSE && skip) {
+    // sample not selected: zero gradient, zero loss
+    if (NHWC_BF16) {
+      uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(a.dz) + (long long)b * n * C);
+      for (int i = tid; i < n * C / 8; i += blockDim.x) d[i] = make_uint4(0, 0, 0, 0);
+    } else {
+      float* d = reinterpret_cast<float*>(a.dz) + (long long)b * n * C;
+      for (int i = tid; i < n * C; i += blockDim.x) d[i] = 0.f;
+    }
+    if (tid == 0) a.loss_part[b] = 0.f;
+    return;
+  }
+
+  // ---- tap tables ----
+  const float sy = (float)h / (float)H, sx = (float)w / (float)W;
+  for (int y = tid; y < H; y += blockDim.x) {
+    int id[4]; float wt[4];
+    bicubic_taps(y, sy, h, id, wt);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { iyt[4 * y + k] = id[k]; wyt[4 * y + k] = wt[k]; }
+  }
+  for (int x = tid; x < W; x += blockDim.x) {
+    int id[4]; float wt[4];
+    bicubic_taps(x, sx, w, id, wt);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { ixt[4 * x + k] = id[k]; wxt[4 * x + k] = wt[k]; }
+  }
+
+  // ---- s_j = sum_c |z| (fp32) ----
+  if (NHWC_BF16) {
+    // C/8 lanes per position, 16-byte loads, shuffle reduce inside the lane group
+    const int lpp = C >> 3;              // lanes per position (power of two <= 32)
+    const int ppw = 32 / lpp;            // positions per warp step
+    const int sub = lane % lpp, posl = lane / lpp;
+    for (int j0 = wid * ppw; j0 < n; j0 += nwarp * ppw) {
+      const int j = j0 + posl;
+      float acc = 0.f;
+      if (j < n) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(zb16 + (long long)j * C) + sub);
+        acc = fabsf(bf16lo(v.x)) + fabsf(bf16hi(v.x)) + fabsf(bf16lo(v.y)) + fabsf(bf16hi(v.y)) +
+              fabsf(bf16lo(v.z)) + fabsf(bf16hi(v.z)) + fabsf(bf16lo(v.w)) + fabsf(bf16hi(v.w));
+      }
+      for (int o = lpp >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (j < n && sub == 0) p[j] = acc;
+    }
+  } else {
+    for (int j = tid; j < n; j += blockDim.x) {
+      float acc = 0.f;
+      for (int c = 0; c < C; ++c) acc += fabsf(__ldg(zf32 + (long long)c * n + j));
+      p[j] = acc;
+    }
+  }
+  __syncthreads();
+
+  // ---- softmax(s / beta) over the n positions ----
+  float lmax = -FLT_MAX;
+  for (int j = tid; j < n; j += blockDim.x) { const float v = __fdiv_rn(p[j], a.beta); p[j] = v; lmax = fmaxf(lmax, v); }
+  const float smax = block_max(lmax, scratch);
+  float lsum = 0.f;
+  for (int j = tid; j < n; j += blockDim.x) { const float e = expf(p[j] - smax); p[j] = e; lsum += e; }
+  const float ssum = block_sum(lsum, scratch);
+  for (int j = tid; j < n; j += blockDim.x) p[j] = __fdiv_rn(p[j], ssum);
+  __syncthreads();
+
+  // ---- x interpolation of every source row: tmap[y'][x] ----
+  const int x = tid;
+  const bool col_ok = x < W;
+  if (col_ok) {
+    const int i0 = ixt[4 * x], i1 = ixt[4 * x + 1], i2 = ixt[4 * x + 2], i3 = ixt[4 * x + 3];
+    const float w0 = wxt[4 * x], w1 = wxt[4 * x + 1], w2 = wxt[4 * x + 2], w3 = wxt[4 * x + 3];
+    for (int yy = 0; yy < h; ++yy) {
+      const float* pr = p + yy * w;
+      tmap[yy * W + x] = pr[i0] * w0 + pr[i1] * w1 + pr[i2] * w2 + pr[i3] * w3;
+      if (MODE != MODE_MASK_FWD) sacc[yy * W + x] = 0.f;
+    }
+  }
+  __syncthreads();
+
+  auto u_at = [&](int y) {
+    const int* iy = iyt + 4 * y;
+    const float* wy = wyt + 4 * y;
+    return tmap[iy[0] * W + x] * wy[0] + tmap[iy[1] * W + x] * wy[1] + tmap[iy[2] * W + x] * wy[2] +
+           tmap[iy[3] * W + x] * wy[3];
+  };
+
+  // ---- pass 1: extrema (first occurrence wins ties, like torch's CPU max/min) ----
+  float vmin = FLT_MAX, vmax = -FLT_MAX;
+  int imin = 0x7fffffff, imax = 0x7fffffff;
+  if (col_ok) {
+    for (int y = 0; y < H; ++y) {
+      const float u = u_at(y);
+      if (u < vmin) { vmin = u; imin = y * W + x; }
+      if (u > vmax) { vmax = u; imax = y * W + x; }
+    }
+  }
+  // block arg-reduce
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, vmin, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, imin, o);
+    if (ov < vmin || (ov == vmin && oi < imin)) { vmin = ov; imin = oi; }
+    const float ov2 = __shfl_xor_sync(0xffffffffu, vmax, o);
+    const int oi2 = __shfl_xor_sync(0xffffffffu, imax, o);
+    if (ov2 > vmax || (ov2 == vmax && oi2 < imax)) { vmax = ov2; imax = oi2; }
+  }
+  __shared__ float r_min[32], r_max[32];
+  __shared__ int r_imin[32], r_imax[32];
+  if (lane == 0) { r_min[wid] = vmin; r_imin[wid] = imin; r_max[wid] = vmax; r_imax[wid] = imax; }
+  __syncthreads();
+  vmin = r_min[0]; imin = r_imin[0]; vmax = r_max[0]; imax = r_imax[0];
+  for (int i = 1; i < nwarp; ++i) {
+    if (r_min[i] < vmin || (r_min[i] == vmin && r_imin[i] < imin)) { vmin = r_min[i]; imin = r_imin[i]; }
+    if (r_max[i] > vmax || (r_max[i] == vmax && r_imax[i] < imax)) { vmax = r_max[i]; imax = r_imax[i]; }
+  }
+  if (imin >= H * W) imin = 0;  // all-NaN map: keep the indices addressable, values stay NaN
+  if (imax >= H * W) imax = 0;
+  const float mn = vmin, mx = vmax;
+  const float rng = __fsub_rn(mx, mn);
+  if (a.stats && tid == 0) {
+    a.stats[4 * b + 0] = mn; a.stats[4 * b + 1] = mx;
+    a.stats[4 * b + 2] = (float)imin; a.stats[4 * b + 3] = (float)imax;
+  }
+
+  if (MODE == MODE_MASK_FWD) {
+    if (col_ok) {
+      float* mo = a.mask_out + (long long)b * H * W;
+      for (int y = 0; y < H; ++y) mo[y * W + x] = __fdiv_rn(__fsub_rn(u_at(y), mn), rng);
+    }
+    return;
+  }
+
+  // ---- pass 2: g2, loss, d(loss)/du accumulated through the y-adjoint into sacc ----
+  float sq = 0.f, E = 0.f, F = 0.f;
+  if (col_ok) {
+    const float* g1 = (MODE == MODE_MSE) ? a.g1 + (long long)b * a.g1_bstride : nullptr;
+    const float* gi = (MODE == MODE_MASK_BWD) ? a.grad_in + (long long)b * H * W : nullptr;
+    for (int y = 0; y < H; ++y) {
+      const float u = u_at(y);
+      const float g2 = __fdiv_rn(__fsub_rn(u, mn), rng);
+      float e;
+      if (MODE == MODE_MSE) {
+        const float d = g2 - __ldg(g1 + y * W + x);
+        sq = fmaf(d, d, sq);
+        e = 2.f * d * a.grad_scale;
+      } else {
+        e = __ldg(gi + y * W + x);
+      }
+      E += e;
+      F = fmaf(e, g2, F);
+      const float du = e / rng;
+      const int* iy = iyt + 4 * y;
+      const float* wy = wyt + 4 * y;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) sacc[iy[k] * W + x] += wy[k] * du;  // column-private: no race
+    }
+  }
+  const float Esum = block_sum(E, scratch);
+  const float Fsum = block_sum(F, scratch);
+  if (MODE == MODE_MSE) {
+    const float sqsum = block_sum(sq, scratch);
+    if (tid == 0) a.loss_part[b] = sqsum;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    // max/min backward: the whole -sum term goes to the single arg index
+    const int ymin = imin / W, xmin = imin - ymin * W;
+    const int ymax = imax / W, xmax = imax - ymax * W;
+    const float dmin = -(Esum - Fsum) / rng, dmax = -Fsum / rng;
+    for (int k = 0; k < 4; ++k) sacc[iyt[4 * ymin + k] * W + xmin] += wyt[4 * ymin + k] * dmin;
+    for (int k = 0; k < 4; ++k) sacc[iyt[4 * ymax + k] * W + xmax] += wyt[4 * ymax + k] * dmax;
+  }
+  // columns that feed each source column x' (contiguous range; verified tap by tap below)
+  if (tid < w) {
+    int lo = W, hi = -1;
+    for (int xx = 0; xx < W; ++xx)
+      for (int k = 0; k < 4; ++k)
+        if (ixt[4 * xx + k] == tid) { lo = min(lo, xx); hi = max(hi, xx); }
+    xrange[2 * tid] = lo;
+    xrange[2 * tid + 1] = hi;
+  }
+  __syncthreads();
+  // ---- x-adjoint: dp[y'][x'] = sum_x sum_k [ix[x][k] == x'] wx[x][k] sacc[y'][x] ----
+  for (int j = tid; j < n; j += blockDim.x) {
+    const int yy = j / w, xs = j - yy * w;
+    float acc = 0.f;
+    for (int xx = xrange[2 * xs]; xx <= xrange[2 * xs + 1]; ++xx) {
+      const float sv = sacc[yy * W + xx];
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (ixt[4 * xx + k] == xs) acc = fmaf(wxt[4 * xx + k], sv, acc);
+    }
+    dp[j] = acc;
+  }
+  __syncthreads();
+  // ---- softmax backward: ds_j = p_j (dp_j - sum_k p_k dp_k) / beta ----
+  float ldot = 0.f;
+  for (int j = tid; j < n; j += blockDim.x) ldot = fmaf(p[j], dp[j], ldot);
+  const float dot = block_sum(ldot, scratch);
+  for (int j = tid; j < n; j += blockDim.x) dp[j] = p[j] * (dp[j] - dot) / a.beta;
+  __syncthreads();
+  // ---- dz = sign(z) ds ----
+  if (NHWC_BF16) {
+    bf16* dzb = reinterpret_cast<bf16*>(a.dz) + (long long)b * n * C;
+    const int vec_per_pos = C >> 3;
+    for (int i = tid; i < n * vec_per_pos; i += blockDim.x) {
+      const int j = i / vec_per_pos;
+      const float ds = dp[j];
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(zb16) + i);
+      auto sg = [&](float zv) { return zv > 0.f ? ds : (zv < 0.f ? -ds : 0.f); };
+      uint4 o;
+      o.x = pack_bf16x2(sg(bf16lo(v.x)), sg(bf16hi(v.x)));
+      o.y = pack_bf16x2(sg(bf16lo(v.y)), sg(bf16hi(v.y)));
+      o.z = pack_bf16x2(sg(bf16lo(v.z)), sg(bf16hi(v.z)));
+      o.w = pack_bf16x2(sg(bf16lo(v.w)), sg(bf16hi(v.w)));
+      reinterpret_cast<uint4*>(dzb)[i] = o;
+    }
+  } else {
+    float* dzf = reinterpret_cast<float*>(a.dz) + (long long)b * n * C;
+    for (int i = tid; i < n * C; i += blockDim.x) {
+      const int j = i % n;
+      const float zv = __ldg(zf32 + i), ds = dp[j];
+      dzf[i] = zv > 0.f ? ds : (zv < 0.f ? -ds : 0.f);
+    }
+  }
+}
+
+size_t reg_smem_bytes(int h, int w, int H, int W) {
+  const size_t n = (size_t)h * w;
+  return sizeof(float) * (n + 2 * (size_t)h * W + 8 * (size_t)H + 8 * (size_t)W + n + 2 * (size_t)w);
+}
+
+template <bool NHWC, int MODE>
+int launch_reg(const RegArgs& a, cudaStream_t stream) {
+  if (a.B <= 0 || a.W > 1024 || a.W < 1 || a.h < 1 || a.w < 1) return GABRIL_ERR_BAD_SHAPE;
+  if (NHWC) {
+    const int lpp = a.C / 8;
+    if (a.C % 8 || lpp > 32 || (lpp & (lpp - 1))) return GABRIL_ERR_BAD_SHAPE;
+  }
+  const size_t smem = reg_smem_bytes(a.h, a.w, a.H, a.W);
+  if (smem > 200 * 1024) return GABRIL_ERR_BAD_SHAPE;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(reg_kernel<NHWC, MODE>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return gabril_set_cuda_error(e);
+    attr_done = true;
+  }
+  const int threads = ((a.W + 31) / 32) * 32;
+  reg_kernel<NHWC, MODE><<<a.B, threads, smem, stream>>>(a);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int grid_for(long long total, int threads, int max_blocks = 148 * 16) {
+  long long blocks = (total + threads - 1) / threads;
+  if (blocks > max_blocks) blocks = max_blocks;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gabril_obs_format(const uint8_t* frames, float* out, int B, int L, int S, int center, int H,
+                      int W, int grayscale, cudaStream_t stream) {
+  if (!frames || !out) return GABRIL_ERR_NULL;
+  if (B <= 0 || S <= 0 || L <= 0 || W % 4) return GABRIL_ERR_BAD_SHAPE;
+  const long long total = (long long)B * S * H * (W / 4);
+  const int grid = grid_for(total, 256, 148 * 32);
+  if (grayscale)
+    obs_format_kernel<true><<<grid, 256, 0, stream>>>(frames, out, B, L, S, center, H, W);
+  else
+    obs_format_kernel<false><<<grid, 256, 0, stream>>>(frames, out, B, L, S, center, H, W);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_obs_patches(const uint8_t* frames, void* patches, int B, int L, int S, int center, int H,
+                       int W, int grayscale, int Kp, cudaStream_t stream) {
+  if (!frames || !patches) return GABRIL_ERR_NULL;
+  const int C0 = S * (grayscale ? 1 : 3);
+  if (B <= 0 || S < 1 || S > 4 || Kp < 16 * C0 || Kp % 4) return GABRIL_ERR_BAD_SHAPE;
+  const int OH = (H + 2 - 4) / 2 + 1, OW = (W + 2 - 4) / 2 + 1;
+  const long long total = (long long)B * OH * OW * 4;
+  const int grid = grid_for(total, 256, 148 * 32);
+  bf16* out = reinterpret_cast<bf16*>(patches);
+#define GABRIL_PATCH_CASE(SS, GG)                                                              \
+  obs_patches_kernel<SS, GG><<<grid, 256, 0, stream>>>(frames, out, B, L, center, H, W, OH, OW, Kp)
+  if (grayscale) {
+    switch (S) {
+      case 1: GABRIL_PATCH_CASE(1, true); break;
+      case 2: GABRIL_PATCH_CASE(2, true); break;
+      case 3: GABRIL_PATCH_CASE(3, true); break;
+      default: GABRIL_PATCH_CASE(4, true); break;
+    }
+  } else {
+    switch (S) {
+      case 1: GABRIL_PATCH_CASE(1, false); break;
+      case 2: GABRIL_PATCH_CASE(2, false); break;
+      case 3: GABRIL_PATCH_CASE(3, false); break;
+      default: GABRIL_PATCH_CASE(4, false); break;
+    }
+  }
+#undef GABRIL_PATCH_CASE
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_gaze_splat(const float* gaze, float* out, const float* ktab, const int* Lk,
+                      int ktab_stride, const float* agg_coeff, const float* step_coeff,
+                      int normalize_base, int aggregate, int B, int L, int S, int center, int P,
+                      int H, int W, cudaStream_t stream) {
+  if (!gaze || !out || !ktab || !Lk) return GABRIL_ERR_NULL;
+  if (B <= 0 || S < 1 || S > kMaxS || P < 1 || P > kMaxPts || W % 4 || S * P > 256)
+    return GABRIL_ERR_BAD_SHAPE;
+  SplatArgs a;
+  a.gaze = gaze; a.out = out; a.ktab = ktab; a.ktab_stride = ktab_stride;
+  for (int s = 0; s < kMaxS; ++s) {
+    a.Lk[s] = s < S ? Lk[s] : 1;
+    a.step_coeff[s] = (step_coeff && s < S) ? step_coeff[s] : 1.f;
+    for (int j = 0; j < kMaxS; ++j)
+      a.agg[s][j] = (agg_coeff && s < S && j <= s) ? agg_coeff[s * S + j] : (j <= s ? 1.f : 0.f);
+    // the reference's conv2d needs H >= kernel size (valid vertical pass)
+    if (s < S && (Lk[s] > H || Lk[s] < 1 || Lk[s] > ktab_stride || (Lk[s] & 1) == 0))
+      return GABRIL_ERR_BAD_SHAPE;
+  }
+  a.use_step_coeff = step_coeff != nullptr;
+  a.normalize_base = normalize_base; a.aggregate = aggregate;
+  a.B = B; a.L = L; a.S = S; a.center = center; a.P = P; a.H = H; a.W = W;
+  int nsplit = 1;
+  while ((long long)B * nsplit < 2 * 148 && nsplit < 8 && nsplit * 2 <= H) nsplit *= 2;
+  a.nsplit = nsplit;
+  const size_t smem = sizeof(float) * (size_t)S * P * (H + W);
+  if (smem > 160 * 1024) return GABRIL_ERR_BAD_SHAPE;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(gaze_splat_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+    if (e != cudaSuccess) return gabril_set_cuda_error(e);
+    attr_done = true;
+  }
+  gaze_splat_kernel<<<dim3(B, nsplit), 256, smem, stream>>>(a);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_gmd_mask(const float* g, const float* A, float* K_ws, unsigned int* mnmx_ws,
+                    float* rowmask, float* keep_out, int B, int S, int H, int W, int h, int w,
+                    float drop_p, int test_mode, cudaStream_t stream) {
+  if (!g || !K_ws || !mnmx_ws || !rowmask || (!A && !test_mode)) return GABRIL_ERR_NULL;
+  if (B <= 0 || S < 1) return GABRIL_ERR_BAD_SHAPE;
+  const long long total = (long long)B * h * w;
+  gmd_init_kernel<<<1, 1, 0, stream>>>(mnmx_ws);
+  gmd_keep_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(g, K_ws, mnmx_ws, B, S, H, W, h, w);
+  gmd_mask_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(K_ws, A, mnmx_ws, rowmask, keep_out,
+                                                                     total, drop_p, test_mode);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_rowmask_apply_nchw(const float* z, const float* rowmask, float* out, int B, int C, int n,
+                              cudaStream_t stream) {
+  if (!z || !rowmask || !out) return GABRIL_ERR_NULL;
+  const long long total = (long long)B * C * n;
+  rowmask_apply_nchw_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, stream>>>(z, rowmask, out, B, C, n);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_gaze_mask_fwd(const void* z, int z_nhwc_bf16, float* mask_out, float* stats, int B, int C,
+                         int h, int w, int H, int W, float beta, cudaStream_t stream) {
+  if (!z || !mask_out) return GABRIL_ERR_NULL;
+  RegArgs a = {};
+  a.z = z; a.mask_out = mask_out; a.stats = stats; a.beta = beta;
+  a.B = B; a.C = C; a.h = h; a.w = w; a.H = H; a.W = W;
+  return z_nhwc_bf16 ? launch_reg<true, MODE_MASK_FWD>(a, stream)
+                     : launch_reg<false, MODE_MASK_FWD>(a, stream);
+}
+
+int gabril_gaze_mask_bwd(const void* z, int z_nhwc_bf16, const float* grad_mask, void* dz, int B,
+                         int C, int h, int w, int H, int W, float beta, cudaStream_t stream) {
+  if (!z || !grad_mask || !dz) return GABRIL_ERR_NULL;
+  RegArgs a = {};
+  a.z = z; a.grad_in = grad_mask; a.dz = dz; a.beta = beta;
+  a.B = B; a.C = C; a.h = h; a.w = w; a.H = H; a.W = W;
+  return z_nhwc_bf16 ? launch_reg<true, MODE_MASK_BWD>(a, stream)
+                     : launch_reg<false, MODE_MASK_BWD>(a, stream);
+}
+
+int gabril_reg_mse(const void* z, int z_nhwc_bf16, const float* g1, long long g1_bstride,
+                   const float* sel, void* dz, float* loss_part, float* stats, int B, int C, int h,
+                   int w, int H, int W, float beta, float grad_scale, cudaStream_t stream) {
+  if (!z || !g1 || !dz || !loss_part) return GABRIL_ERR_NULL;
+  RegArgs a = {};
+  a.z = z; a.g1 = g1; a.g1_bstride = g1_bstride; a.sel = sel; a.dz = dz; a.loss_part = loss_part;
+  a.stats = stats; a.beta = beta; a.grad_scale = grad_scale;
+  a.B = B; a.C = C; a.h = h; a.w = w; a.H = H; a.W = W;
+  return z_nhwc_bf16 ? launch_reg<true, MODE_MSE>(a, stream) : launch_reg<false, MODE_MSE>(a, stream);
+}
+
+}  // extern "C"

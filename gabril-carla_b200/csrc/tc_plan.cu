@@ -137,6 +137,11 @@ uint32_t pow2_cols(uint32_t c) {
   return r;
 }
 
+// N-side channel counts the MN-major box split supports: 32, 64, or a multiple of 128.
+bool mn_ok(int c) { return c == 32 || c == 64 || (c >= 128 && c % 128 == 0); }
+// Output-column counts of the K-major forward: a multiple of 32 up to 128, or a multiple of 128.
+bool fwd_cout_ok(int c) { return c % 32 == 0 && (c <= 128 || c % 128 == 0); }
+
 void zero_params(tc::Params& p) { memset(&p, 0, sizeof(p)); }
 
 void pick_stages(tc::Params& p, int kb_per_cta, size_t* smem_bytes) {
@@ -230,7 +235,7 @@ int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void*
                     cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
-  if (Cin % 32 || Cout % 32 || N <= 0) return GABRIL_ERR_BAD_SHAPE;
+  if (Cin % 32 || !fwd_cout_ok(Cout) || N <= 0) return GABRIL_ERR_BAD_SHAPE;
   const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
   const int kc = (Cin % 64 == 0) ? 64 : 32;
   const int block_n = std::min(Cout, 128);
@@ -286,7 +291,7 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
                       int R, int S, int stride, int pad, cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
-  if (Cin % 32 || Cout % 32 || N <= 0) return GABRIL_ERR_BAD_SHAPE;
+  if (!mn_ok(Cin) || Cout % 32 || N <= 0) return GABRIL_ERR_BAD_SHAPE;
   const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
   const int kc = (Cout % 64 == 0) ? 64 : 32;  // contraction over Cout
   const int block_n = std::min(Cin, 128);
@@ -374,7 +379,7 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
                       cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
-  if (Cin % 32 || Cout % 32 || N <= 0) return GABRIL_ERR_BAD_SHAPE;
+  if (!mn_ok(Cin) || Cout % 32 || N <= 0) return GABRIL_ERR_BAD_SHAPE;
   const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
   const long long P = (long long)N * OH * OW;  // contraction length (output pixels)
   const int T = R * S;

@@ -1,0 +1,246 @@
+"""The fused GABRIL / GABRIL+GMD training step on one B200.
+
+Mirrors BCTrainer.compute_loss (vlm_gaze/train/train_bc.py:203-299) + loss.backward() +
+optimizer.step() (vlm_gaze/train/common/base_trainer.py:129-149) as an explicit kernel schedule:
+every arithmetic operation below is one of libgabril_b200's sm_100a kernels; PyTorch only owns the
+buffers, the stream and the RNG draw of GMD's uniform tensor.
+
+Activation layout: NHWC bf16.  Saved-for-backward tensors are the post-ReLU activations
+themselves (ReLU backward is a `gate > 0` predicate in the dgrad epilogue).  Quirks reproduced
+(SURVEY F6-F8): Residual's in-place ReLU (skip branch sees relu(x)), conv_4 activated by the first
+Residual, the regulariser reading the post-dropout z under GMD.
+"""
+from typing import Dict, Optional
+
+import torch
+
+from . import _lib, ops
+from .gaze import GazePreprocessor
+from .model import ParamArena, PolicySpec
+
+
+class StepEngine:
+    def __init__(self, spec: PolicySpec, arena: ParamArena, gaze_pre: GazePreprocessor, *,
+                 gaze_method: str = "Reg", dp_method: str = "None", grayscale: bool = True,
+                 frame_stack: int = 2, beta: float = 50.0, lam: float = 10.0,
+                 aggregate: bool = True, grad_accum: int = 1, seed: int = 0):
+        if gaze_method not in ("None", "Reg", "Teacher"):
+            raise NotImplementedError(f"gaze.method={gaze_method} is outside the B200 hot path "
+                                      "(supported: None, Reg, Teacher)")
+        if dp_method not in ("None", "GMD"):
+            raise NotImplementedError(f"dropout.method={dp_method} is outside the B200 hot path "
+                                      "(supported: None, GMD)")
+        _lib.init()
+        self.spec, self.arena, self.gaze_pre = spec, arena, gaze_pre
+        self.use_reg = gaze_method in ("Reg", "Teacher")
+        self.use_gmd = dp_method == "GMD"
+        self.grayscale, self.S = grayscale, frame_stack
+        self.beta, self.lam, self.aggregate = float(beta), float(lam), aggregate
+        self.grad_accum = max(1, int(grad_accum))
+        self.device = arena.device
+        self.B = 0
+        self.buf: Dict[str, torch.Tensor] = {}
+        self.rng = torch.Generator(device=self.device)
+        self.rng.manual_seed(seed)
+        self.injected_A: Optional[torch.Tensor] = None  # parity tests inject GMD's uniform draw
+        self.gaze_ratio = 1.0
+        self._accum_count = 0
+        self.on_heads_grads_ready = None   # hooks for the data-parallel bucket all-reduce
+        self.on_all_grads_ready = None
+
+    # ------------------------------------------------------------------------------------------
+    def _alloc(self, B):
+        s, dev = self.spec, self.device
+        bf, f32 = torch.bfloat16, torch.float32
+
+        def act(h, w, c):
+            return torch.empty(B, h, w, c, device=dev, dtype=bf)
+        b = {}
+        b["patches"] = torch.empty(B * s.H1 * s.W1, s.K1p, device=dev, dtype=bf)
+        b["a1"], b["a2"], b["a3"] = act(s.H1, s.W1, s.C1), act(s.H2, s.W2, s.C2), act(s.H3, s.W3, s.NH)
+        b["r-1"] = act(s.h, s.w, s.NH)  # relu(conv_4): the input of the first Residual
+        for i in range(s.NR):
+            b[f"h{i}"] = act(s.h, s.w, s.RH)
+            b[f"r{i}"] = act(s.h, s.w, s.NH)
+        b["a5"], b["z"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.E)
+        b["heat"] = torch.empty(B, self.S, s.H, s.W, device=dev, dtype=f32)
+        b["rowmask"] = torch.empty(B, s.n, device=dev, dtype=f32)
+        b["K"] = torch.empty(B, s.n, device=dev, dtype=f32)
+        b["mnmx"] = torch.empty(2, device=dev, dtype=torch.int32)
+        b["zf_raw"] = torch.empty(B, s.Z, device=dev, dtype=f32)
+        b["zf"] = torch.empty(B, s.Z, device=dev, dtype=bf)
+        b["act1"] = torch.empty(B, s.Z, device=dev, dtype=bf)
+        b["lg_raw"] = torch.empty(B, s.AP, device=dev, dtype=f32)
+        b["logits"] = torch.empty(B, s.A, device=dev, dtype=f32)
+        b["dlog"] = torch.empty(B, s.AP, device=dev, dtype=bf)
+        b["actor_part"] = torch.empty(B, device=dev, dtype=f32)
+        b["reg_part"] = torch.zeros(B, device=dev, dtype=f32)
+        b["losses"] = torch.zeros(3, device=dev, dtype=f32)
+        b["stats"] = torch.empty(B, 4, device=dev, dtype=f32)
+        # gradients (same shapes as the activations they belong to)
+        b["dact1"] = torch.empty(B, s.Z, device=dev, dtype=bf)
+        b["dzf"] = torch.empty(B, s.Z, device=dev, dtype=bf)
+        b["dz_reg"] = act(s.h, s.w, s.E)
+        b["dz"] = act(s.h, s.w, s.E)
+        b["da5"] = act(s.h, s.w, s.NH)
+        b["dt_a"], b["dt_b"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.NH)
+        b["dh"] = act(s.h, s.w, s.RH)
+        b["da3"], b["da2"], b["da1"] = act(s.H3, s.W3, s.NH), act(s.H2, s.W2, s.C2), act(s.H1, s.W1, s.C1)
+        self.buf, self.B = b, B
+        # split-K for the pre_actor GEMM: enough CTAs to cover the machine
+        m_tiles = (B + 127) // 128
+        n_tiles = s.Z // 128 if s.Z >= 128 else 1
+        self.pre_splits = max(1, min(s.flat // 64, (2 * 148) // max(1, m_tiles * n_tiles)))
+
+    # ------------------------------------------------------------------------------------------
+    def zero_grad(self):
+        self.arena.g.zero_()
+        self._accum_count = 0
+
+    def forward(self, frames: torch.Tensor, gaze: torch.Tensor, actions: torch.Tensor):
+        """frames u8 [B,L,H,W,3], gaze f32 [B,L,P*2], actions f32 [B,L,A] or [B,A] (all on device).
+        Runs the forward pass, the losses and the loss-side gradient seeds.  Returns the device
+        tensor losses = [actor, reg, total]."""
+        s, a = self.spec, self.arena
+        B, L = frames.shape[0], frames.shape[1]
+        if B != self.B:
+            self._alloc(B)
+        b = self.buf
+        center = L - 1
+        # ---- preprocessing (prepare_for_bc, data_loader_robomimic.py:318-360) ----
+        ops.obs_patches(frames, self.S, center, self.grayscale, out=b["patches"])
+        if self.use_reg or self.use_gmd:
+            self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
+        rowmask = None
+        if self.use_gmd:
+            # A is drawn before the interpolation, like gaze_utils.py:36
+            A = self.injected_A if self.injected_A is not None else torch.rand(
+                B, s.n, device=self.device, dtype=torch.float32, generator=self.rng)
+            ops.gmd_mask(b["heat"], A.reshape(B, s.n), s.h, s.w, 0.7, False, rowmask=b["rowmask"],
+                         ws=(b["K"], b["mnmx"]))
+            rowmask = b["rowmask"]
+        # ---- encoder (linear_models.py:191-207) ----
+        M1 = B * s.H1 * s.W1
+        ops.conv_fwd(b["patches"].view(M1, 1, 1, s.K1p), a.WB("enc.conv1.w"), a.P("enc.conv1.b"),
+                     b["a1"], 1, 1, 1, 0, relu=True)
+        ops.conv_fwd(b["a1"], a.WB("enc.conv2.w"), a.P("enc.conv2.b"), b["a2"], 4, 4, 2, 1, relu=True)
+        ops.conv_fwd(b["a2"], a.WB("enc.conv3.w"), a.P("enc.conv3.b"), b["a3"], 4, 4, 2, 1, relu=True)
+        # conv_4 has no activation of its own; the first Residual's in-place ReLU rectifies it (F7)
+        ops.conv_fwd(b["a3"], a.WB("enc.conv4.w"), a.P("enc.conv4.b"), b["r-1"], 3, 3, 1, 0, relu=True)
+        for i in range(s.NR):
+            prev = b[f"r{i - 1}"]
+            ops.conv_fwd(prev, a.WB(f"enc.res{i}.c3.w"), None, b[f"h{i}"], 3, 3, 1, 1, relu=True)
+            # relu(x) + block(x); the next consumer (next Residual / the stack's final ReLU)
+            # rectifies it again, so the rectified value is what gets stored
+            ops.conv_fwd(b[f"h{i}"], a.WB(f"enc.res{i}.c1.w"), None, b[f"r{i}"], 1, 1, 1, 0, relu=True,
+                         resid=prev)
+        last = b[f"r{s.NR - 1}"]
+        ops.conv_fwd(last, a.WB("enc.conv5.w"), a.P("enc.conv5.b"), b["a5"], 5, 5, 1, 2, relu=True)
+        ops.conv_fwd(b["a5"], a.WB("enc.conv6.w"), a.P("enc.conv6.b"), b["z"], 5, 5, 1, 2, relu=False,
+                     rowmask=rowmask.view(-1) if rowmask is not None else None)
+        # ---- heads (train_bc.py:290-292) ----
+        b["zf_raw"].zero_()
+        ops.conv_fwd(b["z"].view(B, 1, 1, s.flat), a.WB("pre.w"), None, b["zf_raw"], 1, 1, 1, 0,
+                     out_f32_atomic=True, splits=self.pre_splits)
+        ops.bias_act_cast(b["zf_raw"], a.P("pre.b"), b["zf"], relu=False)
+        ops.conv_fwd(b["zf"].view(B, 1, 1, s.Z), a.WB("act.0.w"), a.P("act.0.b"), b["act1"], 1, 1, 1, 0,
+                     relu=True)
+        b["lg_raw"].zero_()
+        ops.conv_fwd(b["act1"].view(B, 1, 1, s.Z), a.WB("act.2.w"), None, b["lg_raw"], 1, 1, 1, 0,
+                     out_f32_atomic=True, splits=1)
+        if actions.dim() == 3:
+            act_view = actions[:, center if center < actions.shape[1] else -1, :]
+        else:
+            act_view = actions
+        assert act_view.stride(-1) == 1 and act_view.dtype == torch.float32
+        scale = 1.0 / self.grad_accum
+        ops.mse_head(b["lg_raw"], a.P("act.2.b"), act_view, s.A, b["actor_part"],
+                     scale / (B * s.A), dlogits=b["dlog"], dbias=a.G("act.2.b"), logits_out=b["logits"])
+        # ---- regulariser (train_bc.py:145-150,168-169) on the (post-dropout) z ----
+        reg_scale = 0.0
+        if self.use_reg:
+            n_sel = B  # gaze.ratio = 1
+            reg_scale = 1.0 / (n_sel * s.H * s.W)
+            g1 = b["heat"][:, self.S - 1]
+            ops.reg_mse(b["z"], g1, b["heat"].stride(0), s.H, s.W, self.beta,
+                        self.lam * scale * reg_scale, b["dz_reg"], b["reg_part"], stats=b["stats"])
+        ops.finalize_losses(b["actor_part"], b["reg_part"] if self.use_reg else None, B,
+                            1.0 / (B * s.A), reg_scale, self.lam, b["losses"])
+        return b["losses"]
+
+    # ------------------------------------------------------------------------------------------
+    def backward(self):
+        """The rest of loss.backward(): every weight / bias gradient accumulated into arena.g."""
+        s, a, b = self.spec, self.arena, self.buf
+        B = self.B
+        direct = self.grad_accum == 1  # pre_actor dW: plain stores when nothing accumulates
+        rowmask = b["rowmask"].view(-1) if self.use_gmd else None
+        # actor.2
+        ops.conv_wgrad(b["dlog"].view(B, 1, 1, s.AP), b["act1"].view(B, 1, 1, s.Z), a.G("act.2.w"), 1, 1, 1, 0)
+        ops.conv_dgrad(b["dlog"].view(B, 1, 1, s.AP), a.WB("act.2.w"), b["dact1"].view(B, 1, 1, s.Z),
+                       1, 1, 1, 0, gate=b["act1"].view(B, 1, 1, s.Z))
+        # actor.0
+        ops.colsum_bf16(b["dact1"], a.G("act.0.b"))
+        ops.conv_wgrad(b["dact1"].view(B, 1, 1, s.Z), b["zf"].view(B, 1, 1, s.Z), a.G("act.0.w"), 1, 1, 1, 0)
+        ops.conv_dgrad(b["dact1"].view(B, 1, 1, s.Z), a.WB("act.0.w"), b["dzf"].view(B, 1, 1, s.Z), 1, 1, 1, 0)
+        # pre_actor
+        ops.colsum_bf16(b["dzf"], a.G("pre.b"))
+        ops.conv_wgrad(b["dzf"].view(B, 1, 1, s.Z), b["z"].view(B, 1, 1, s.flat), a.G("pre.w"), 1, 1, 1, 0,
+                       direct_store=direct)
+        ops.conv_dgrad(b["dzf"].view(B, 1, 1, s.Z), a.WB("pre.w"), b["dz"].view(B, 1, 1, s.flat), 1, 1, 1, 0,
+                       addend=b["dz_reg"].view(B, 1, 1, s.flat) if self.use_reg else None)
+        if rowmask is not None:
+            # z' = z * M  =>  dz = dz' * M (the regulariser part is already zero where z' == 0)
+            self._mask_rows(b["dz"], rowmask)
+        if self.on_heads_grads_ready is not None:
+            self.on_heads_grads_ready()
+        # conv_6 / conv_5
+        last = b[f"r{s.NR - 1}"]
+        ops.colsum_bf16(b["dz"], a.G("enc.conv6.b"))
+        ops.conv_wgrad(b["dz"], b["a5"], a.G("enc.conv6.w"), 5, 5, 1, 2)
+        ops.conv_dgrad(b["dz"], a.WB("enc.conv6.w"), b["da5"], 5, 5, 1, 2, gate=b["a5"])
+        ops.colsum_bf16(b["da5"], a.G("enc.conv5.b"))
+        ops.conv_wgrad(b["da5"], last, a.G("enc.conv5.w"), 5, 5, 1, 2)
+        dt, other = b["dt_a"], b["dt_b"]
+        ops.conv_dgrad(b["da5"], a.WB("enc.conv5.w"), dt, 5, 5, 1, 2, gate=last)
+        # residual stack, last block first
+        for i in reversed(range(s.NR)):
+            prev = b[f"r{i - 1}"]
+            ops.conv_wgrad(dt, b[f"h{i}"], a.G(f"enc.res{i}.c1.w"), 1, 1, 1, 0)
+            ops.conv_dgrad(dt, a.WB(f"enc.res{i}.c1.w"), b["dh"], 1, 1, 1, 0, gate=b[f"h{i}"])
+            ops.conv_wgrad(b["dh"], prev, a.G(f"enc.res{i}.c3.w"), 3, 3, 1, 1)
+            ops.conv_dgrad(b["dh"], a.WB(f"enc.res{i}.c3.w"), other, 3, 3, 1, 1, addend=dt, gate=prev)
+            dt, other = other, dt
+        # conv_4 .. conv_1
+        ops.colsum_bf16(dt, a.G("enc.conv4.b"))
+        ops.conv_wgrad(dt, b["a3"], a.G("enc.conv4.w"), 3, 3, 1, 0)
+        ops.conv_dgrad(dt, a.WB("enc.conv4.w"), b["da3"], 3, 3, 1, 0, gate=b["a3"])
+        ops.colsum_bf16(b["da3"], a.G("enc.conv3.b"))
+        ops.conv_wgrad(b["da3"], b["a2"], a.G("enc.conv3.w"), 4, 4, 2, 1)
+        ops.conv_dgrad(b["da3"], a.WB("enc.conv3.w"), b["da2"], 4, 4, 2, 1, gate=b["a2"])
+        ops.colsum_bf16(b["da2"], a.G("enc.conv2.b"))
+        ops.conv_wgrad(b["da2"], b["a1"], a.G("enc.conv2.w"), 4, 4, 2, 1)
+        ops.conv_dgrad(b["da2"], a.WB("enc.conv2.w"), b["da1"], 4, 4, 2, 1, gate=b["a1"])
+        M1 = B * s.H1 * s.W1
+        ops.colsum_bf16(b["da1"], a.G("enc.conv1.b"))
+        ops.conv_wgrad(b["da1"].view(M1, 1, 1, s.C1), b["patches"].view(M1, 1, 1, s.K1p),
+                       a.G("enc.conv1.w"), 1, 1, 1, 0)
+        self._accum_count += 1
+        if self.on_all_grads_ready is not None:
+            self.on_all_grads_ready()
+
+    def _mask_rows(self, t, rowmask):
+        # dz * M as a 1x1 "identity-free" epilogue: reuse the dgrad rowmask path would need a second
+        # GEMM; a dedicated vectorised kernel is cheaper
+        ops.rowscale_bf16(t, rowmask)
+
+    # ------------------------------------------------------------------------------------------
+    def adam_step(self, step: int, lr: float, *, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0,
+                  decoupled=False, grad_scale=1.0):
+        a = self.arena
+        ops.adam(a.p, a.g, a.m, a.v, a.wb, step, lr, beta1, beta2, eps, weight_decay, decoupled, grad_scale)
+
+    def losses_host(self):
+        """One device->host read: (actor, reg, total)."""
+        v = self.buf["losses"].tolist()
+        return v[0], v[1], v[2]

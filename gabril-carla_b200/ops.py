@@ -88,3 +88,186 @@ def w_oihw_to_internal(w_oihw: torch.Tensor) -> torch.Tensor:
 def w_internal_to_oihw(w: torch.Tensor, R: int, S: int) -> torch.Tensor:
     Co, T, Ci = w.shape
     return w.reshape(Co, R, S, Ci).permute(0, 3, 1, 2).contiguous()
+
+
+# ---- memory-bound kernels (gaze_ops.cu / train_ops.cu) ---------------------------------------
+from ._lib import c_float, c_ll  # noqa: E402
+
+
+def _chk(t, dtype, name):
+    if t is None:
+        return
+    if t.dtype != dtype or not t.is_cuda or not t.is_contiguous():
+        raise ValueError(f"{name}: expected contiguous CUDA {dtype} tensor, got {t.dtype} on {t.device}"
+                         f" contiguous={t.is_contiguous()}")
+
+
+def _call(name, *args):
+    lib = _lib.init()
+    _lib.check(getattr(lib, name)(*args), name)
+
+
+def obs_format(frames, S, center, grayscale, out=None):
+    """uint8 [B,L,H,W,3] -> fp32 [B,S*C',H,W] (data_loader_robomimic.py:144-157,179-202)."""
+    _chk(frames, torch.uint8, "frames")
+    B, L, H, W, C = frames.shape
+    assert C == 3
+    Cp = 1 if grayscale else 3
+    if out is None:
+        out = torch.empty(B, S * Cp, H, W, device=frames.device, dtype=torch.float32)
+    _call("gabril_obs_format", ptr(frames), ptr(out), c_int(B), c_int(L), c_int(S), c_int(center),
+          c_int(H), c_int(W), c_int(int(grayscale)), stream())
+    return out
+
+
+def conv1_kp(S, grayscale):
+    k = 16 * S * (1 if grayscale else 3)
+    # the patch GEMM's K is the N side of its wgrad: 32, 64 or a multiple of 128
+    return 32 if k <= 32 else 64 if k <= 64 else (k + 127) // 128 * 128
+
+
+def obs_patches(frames, S, center, grayscale, out=None):
+    """uint8 [B,L,H,W,3] -> bf16 [B*OH*OW, Kp] conv_1 patch matrix (format + im2col fused)."""
+    _chk(frames, torch.uint8, "frames")
+    B, L, H, W, C = frames.shape
+    OH, OW = conv_out_hw(H, W, 4, 4, 2, 1)
+    Kp = conv1_kp(S, grayscale)
+    if out is None:
+        out = torch.empty(B * OH * OW, Kp, device=frames.device, dtype=torch.bfloat16)
+    _call("gabril_obs_patches", ptr(frames), ptr(out), c_int(B), c_int(L), c_int(S), c_int(center),
+          c_int(H), c_int(W), c_int(int(grayscale)), c_int(Kp), stream())
+    return out
+
+
+def gaze_splat(gaze, out, ktab, Lk_host, agg_coeff, step_coeff, normalize_base, aggregate, S, center,
+               P, H, W):
+    """gaze fp32 [B,L,P*2] -> out fp32 [B,S,H,W]; ktab fp32 [S,stride] (device), Lk_host: ints."""
+    import ctypes
+    _chk(gaze, torch.float32, "gaze"); _chk(out, torch.float32, "out"); _chk(ktab, torch.float32, "ktab")
+    B, L = gaze.shape[0], gaze.shape[1]
+    Lk = (ctypes.c_int * S)(*[int(v) for v in Lk_host])
+    agg = (ctypes.c_float * (S * S))(*[float(v) for v in agg_coeff]) if agg_coeff is not None else None
+    stc = (ctypes.c_float * S)(*[float(v) for v in step_coeff]) if step_coeff is not None else None
+    _call("gabril_gaze_splat", ptr(gaze), ptr(out), ptr(ktab), Lk, c_int(ktab.shape[1]), agg, stc,
+          c_int(int(normalize_base)), c_int(int(aggregate)), c_int(B), c_int(L), c_int(S),
+          c_int(center), c_int(P), c_int(H), c_int(W), stream())
+    return out
+
+
+def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=None, ws=None):
+    """g fp32 [B,S,H,W], A fp32 [B,h*w] -> rowmask fp32 [B,h*w] (gaze_utils.py:33-52)."""
+    _chk(g, torch.float32, "g"); _chk(A, torch.float32, "A")
+    B, S, H, W = g.shape
+    if rowmask is None:
+        rowmask = torch.empty(B, h * w, device=g.device, dtype=torch.float32)
+    if ws is None:
+        ws = (torch.empty(B, h * w, device=g.device, dtype=torch.float32),
+              torch.empty(2, device=g.device, dtype=torch.int32))
+    _call("gabril_gmd_mask", ptr(g), ptr(A), ptr(ws[0]), ptr(ws[1]), ptr(rowmask), ptr(keep_out),
+          c_int(B), c_int(S), c_int(H), c_int(W), c_int(h), c_int(w), c_float(drop_p),
+          c_int(int(test_mode)), stream())
+    return rowmask
+
+
+def rowmask_apply_nchw(z, rowmask, out=None):
+    _chk(z, torch.float32, "z"); _chk(rowmask, torch.float32, "rowmask")
+    B, C = z.shape[0], z.shape[1]
+    n = z.numel() // (B * C)
+    if out is None:
+        out = torch.empty_like(z)
+    _call("gabril_rowmask_apply_nchw", ptr(z), ptr(rowmask), ptr(out), c_int(B), c_int(C), c_int(n),
+          stream())
+    return out
+
+
+def _z_layout(z):
+    if z.dtype == torch.bfloat16:
+        return 1
+    if z.dtype == torch.float32:
+        return 0
+    raise ValueError("z must be bf16 NHWC [B,h,w,C] or fp32 NCHW [B,C,h,w]")
+
+
+def _z_dims(z):
+    if z.dtype == torch.bfloat16:
+        B, h, w, C = z.shape
+    else:
+        B, C, h, w = z.shape
+    return B, C, h, w
+
+
+def gaze_mask_fwd(z, H, W, beta, out=None, stats=None):
+    assert z.is_cuda and z.is_contiguous()
+    B, C, h, w = _z_dims(z)
+    if out is None:
+        out = torch.empty(B, 1, H, W, device=z.device, dtype=torch.float32)
+    _call("gabril_gaze_mask_fwd", ptr(z), c_int(_z_layout(z)), ptr(out), ptr(stats), c_int(B), c_int(C),
+          c_int(h), c_int(w), c_int(H), c_int(W), c_float(beta), stream())
+    return out
+
+
+def gaze_mask_bwd(z, grad_mask, H, W, beta, dz=None):
+    assert z.is_cuda and z.is_contiguous()
+    _chk(grad_mask, torch.float32, "grad_mask")
+    B, C, h, w = _z_dims(z)
+    if dz is None:
+        dz = torch.empty_like(z)
+    _call("gabril_gaze_mask_bwd", ptr(z), c_int(_z_layout(z)), ptr(grad_mask), ptr(dz), c_int(B),
+          c_int(C), c_int(h), c_int(w), c_int(H), c_int(W), c_float(beta), stream())
+    return dz
+
+
+def reg_mse(z, g1_base, g1_bstride, H, W, beta, grad_scale, dz, loss_part, sel=None, stats=None):
+    """Fused Reg-MSE forward+backward; g1_base: fp32 tensor whose data_ptr is sample 0's plane."""
+    assert z.is_cuda and z.is_contiguous()
+    B, C, h, w = _z_dims(z)
+    _call("gabril_reg_mse", ptr(z), c_int(_z_layout(z)), ptr(g1_base), c_ll(g1_bstride), ptr(sel),
+          ptr(dz), ptr(loss_part), ptr(stats), c_int(B), c_int(C), c_int(h), c_int(w), c_int(H),
+          c_int(W), c_float(beta), c_float(grad_scale), stream())
+
+
+def colsum_bf16(dy, db):
+    _chk(dy, torch.bfloat16, "dy"); _chk(db, torch.float32, "db")
+    C = db.numel()
+    M = dy.numel() // C
+    _call("gabril_colsum_bf16", ptr(dy), ptr(db), c_ll(M), c_int(C), stream())
+
+
+def bias_act_cast(x, bias, y_bf16, relu=False, y_f32=None):
+    _chk(x, torch.float32, "x"); _chk(y_bf16, torch.bfloat16, "y")
+    M, C = x.shape
+    _call("gabril_bias_act_cast", ptr(x), ptr(bias), ptr(y_bf16), ptr(y_f32), c_ll(M), c_int(C),
+          c_int(int(relu)), stream())
+
+
+def mse_head(raw, bias, actions_view, A, part, gscale, dlogits=None, dbias=None, logits_out=None):
+    """raw fp32 [B, ld]; actions_view: fp32 view whose row b starts at data_ptr + b*stride(0)."""
+    B, ld = raw.shape
+    ld_d = dlogits.shape[1] if dlogits is not None else 0
+    _call("gabril_mse_head", ptr(raw), c_int(ld), ptr(bias), ptr(actions_view),
+          c_ll(actions_view.stride(0)), c_int(A), ptr(logits_out), ptr(dlogits), c_int(ld_d),
+          ptr(dbias), ptr(part), c_int(B), c_float(gscale), stream())
+
+
+def finalize_losses(actor_part, reg_part, B, actor_scale, reg_scale, lam, losses):
+    _call("gabril_finalize_losses", ptr(actor_part), ptr(reg_part), c_int(B), c_float(actor_scale),
+          c_float(reg_scale), c_float(lam), ptr(losses), stream())
+
+
+def adam(p, g, m, v, shadow, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0,
+         decoupled=False, grad_scale=1.0):
+    n = p.numel()
+    _call("gabril_adam", ptr(p), ptr(g), ptr(m), ptr(v), ptr(shadow), c_ll(n), c_float(lr),
+          c_float(beta1), c_float(beta2), c_float(eps), c_float(weight_decay), c_int(int(decoupled)),
+          c_int(step), c_float(grad_scale), stream())
+
+
+def cast_f32_bf16(x, y):
+    _call("gabril_cast_f32_bf16", ptr(x), ptr(y), c_ll(x.numel()), stream())
+
+
+def rowscale_bf16(t, scale):
+    _chk(t, torch.bfloat16, "t"); _chk(scale, torch.float32, "scale")
+    rows = scale.numel()
+    C = t.numel() // rows
+    _call("gabril_rowscale_bf16", ptr(t), ptr(scale), c_ll(rows), c_int(C), stream())

@@ -76,6 +76,81 @@ int gabril_conv_wgrad_naive(const void* dy, const void* x, float* dw, int N, int
                             int Cout, int R, int S, int stride, int pad, int direct_store,
                             cudaStream_t stream);
 
+/* ---- frame formatting: data_loader_robomimic.py:144-157 (_gather_last_s_frames) + :179-202
+ * (_format_obs_image).  frames: uint8 [B, L, H, W, 3]; the S frames ending at `center` are taken
+ * (indices clamped into [0, L-1], bit-exact integer gather). ---------------------------------- */
+/* -> fp32 [B, S*C', H, W] (C' = 1 gray / 3 RGB), u8/255 then the reference's left-to-right gray
+ * sum, every operation rounded separately (bit-exact vs the reference's fp32 result). W % 4 == 0. */
+int gabril_obs_format(const uint8_t* frames, float* out, int B, int L, int S, int center, int H,
+                      int W, int grayscale, cudaStream_t stream);
+/* -> bf16 patch matrix [B*OH*OW, Kp] of the k4/s2/p1 conv_1 (linear_models.py:141-146), column
+ * (r*4+s)*S*C' + frame*C' + c, zero padded to Kp: formatting and im2col fused in one pass. */
+int gabril_obs_patches(const uint8_t* frames, void* patches_bf16, int B, int L, int S, int center,
+                       int H, int W, int grayscale, int Kp, cudaStream_t stream);
+
+/* ---- gaze heat maps: GazePreprocessor.forward (data_loader_robomimic.py:85-139) and
+ * build_stack_heatmaps (:204-278) in one kernel.  gaze: fp32 [B, L, P*2] ((x, y) in [0,1], negative
+ * = padding).  ktab: [S][ktab_stride] taps of the 1-D Gaussian per stack step (Lk[s] taps, odd);
+ * agg_coeff: [S][S] lower-triangular causal coefficients (NULL = ones); step_coeff: [S] per-step
+ * multipliers of the multiscale mode (NULL = none); normalize_base: per-frame min-max before the
+ * aggregation (alpha_decay mode); aggregate = 0 returns the per-frame maps (gaze.temporal_flag =
+ * false).  out: fp32 [B, S, H, W].  Pixel indices are bit-exact; the row-band quirk of the
+ * reference's padding is reproduced. */
+int gabril_gaze_splat(const float* gaze, float* out, const float* ktab, const int* Lk,
+                      int ktab_stride, const float* agg_coeff, const float* step_coeff,
+                      int normalize_base, int aggregate, int B, int L, int S, int center, int P,
+                      int H, int W, cudaStream_t stream);
+
+/* ---- gaze-mask dropout: apply_gmd_dropout (gaze_utils.py:33-52).  g: fp32 [B, S, H, W];
+ * A: the uniform draw fp32 [B, h*w]; K_ws: fp32 [B, h*w] workspace; mnmx_ws: 2 x uint32 workspace.
+ * rowmask[b, j] = (A < 0.7 Khat + 0.3) (train) or the keep value itself (test_mode); keep_out
+ * (optional) receives 0.7 Khat + 0.3.  min / max are global over the local batch. */
+int gabril_gmd_mask(const float* g, const float* A, float* K_ws, unsigned int* mnmx_ws,
+                    float* rowmask, float* keep_out, int B, int S, int H, int W, int h, int w,
+                    float drop_p, int test_mode, cudaStream_t stream);
+/* out[b, c, j] = z[b, c, j] * rowmask[b, j] on the reference's fp32 NCHW layout. */
+int gabril_rowmask_apply_nchw(const float* z, const float* rowmask, float* out, int B, int C, int n,
+                              cudaStream_t stream);
+
+/* ---- get_gaze_mask (gaze_utils.py:7-30): |z| channel sum -> softmax(./beta) -> bicubic up-sample
+ * (fp32 index math, A = -0.75) -> per-sample min-max without eps.  z is bf16 [B, h*w, C]
+ * (z_nhwc_bf16 = 1) or fp32 [B, C, h*w].  stats (optional): [B][4] = min, max, argmin, argmax. */
+int gabril_gaze_mask_fwd(const void* z, int z_nhwc_bf16, float* mask_out, float* stats, int B, int C,
+                         int h, int w, int H, int W, float beta, cudaStream_t stream);
+/* autograd of the above: grad_mask fp32 [B, H*W] -> dz in the layout of z. */
+int gabril_gaze_mask_bwd(const void* z, int z_nhwc_bf16, const float* grad_mask, void* dz, int B,
+                         int C, int h, int w, int H, int W, float beta, cudaStream_t stream);
+/* Reg/Teacher MSE regulariser (train_bc.py:145-150,168-169) forward + backward in one pass:
+ * loss_part[b] = sum_i (g1 - get_gaze_mask(z))^2, dz = grad_scale * d(sum)/dz.  g1 plane of sample b
+ * at g1 + b * g1_bstride floats; sel (optional) [B]: samples with sel <= 0 are skipped. */
+int gabril_reg_mse(const void* z, int z_nhwc_bf16, const float* g1, long long g1_bstride,
+                   const float* sel, void* dz, float* loss_part, float* stats, int B, int C, int h,
+                   int w, int H, int W, float beta, float grad_scale, cudaStream_t stream);
+
+/* ---- heads, losses, optimiser ------------------------------------------------------------- */
+/* db[c] += sum_rows dy[row][c]  (bias gradient of nn.Conv2d / nn.Linear); dy bf16 [M, C]. */
+int gabril_colsum_bf16(const void* dy, float* db, long long M, int C, cudaStream_t stream);
+/* y = act(x + bias) cast to bf16 (and optionally kept in fp32); x fp32 [M, C]. */
+int gabril_bias_act_cast(const float* x, const float* bias, void* y_bf16, float* y_f32, long long M,
+                         int C, int relu, cudaStream_t stream);
+/* nn.MSELoss on the action head (train_bc.py:292): logits = raw[:, :A] + bias;
+ * part[b] = sum_k (logits - actions)^2; dlogits (bf16 [B, ld_d], zero padded) = 2 (l - a) gscale;
+ * dbias[k] += sum_b dlogits. */
+int gabril_mse_head(const float* raw, int ld_raw, const float* bias, const float* actions,
+                    long long act_bstride, int A, float* logits_out, void* dlogits_bf16, int ld_d,
+                    float* dbias, float* part, int B, float gscale, cudaStream_t stream);
+/* losses[0] = actor, [1] = reg, [2] = lambda * reg + actor (train_bc.py:297); deterministic. */
+int gabril_finalize_losses(const float* actor_part, const float* reg_part, int B, float actor_scale,
+                           float reg_scale, float lambda, float* losses, cudaStream_t stream);
+/* torch.optim.Adam (decoupled = 0) / AdamW (1) step `step` (1-based) over a flat fp32 arena
+ * (optim.py:11-28); grads are multiplied by grad_scale first; the bf16 shadow is refreshed. */
+int gabril_adam(float* p, const float* g, float* m, float* v, void* shadow_bf16, long long n,
+                float lr, float beta1, float beta2, float eps, float weight_decay, int decoupled,
+                int step, float grad_scale, cudaStream_t stream);
+int gabril_cast_f32_bf16(const float* x, void* y_bf16, long long n, cudaStream_t stream);
+/* t[row][c] *= scale[row] in place; t bf16 [rows, C] (GMD backward, gaze_utils.py:51: dz = dz' * M). */
+int gabril_rowscale_bf16(void* t, const float* scale, long long rows, int C, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
