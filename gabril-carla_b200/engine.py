@@ -244,3 +244,43 @@ class StepEngine:
         """One device->host read: (actor, reg, total)."""
         v = self.buf["losses"].tolist()
         return v[0], v[1], v[2]
+
+
+class HostFeeder:
+    """Pinned-host -> device staging of one batch on a side stream (the DataLoader(pin_memory) +
+    `.to(device, non_blocking=True)` boundary of train_bc.py:204-207), double buffered so the copy
+    of batch i+1 overlaps the kernels of batch i."""
+
+    def __init__(self, device, depth: int = 2):
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(device=self.device)
+        self.depth = depth
+        self.slots = [None] * depth
+        self.events = [torch.cuda.Event() for _ in range(depth)]
+        self.free_events = [None] * depth
+        self.i = 0
+
+    def stage(self, frames: torch.Tensor, gaze: torch.Tensor, actions: torch.Tensor):
+        """Start the H2D copies of one host batch; returns a ticket for `wait`."""
+        k = self.i % self.depth
+        self.i += 1
+        if self.slots[k] is None or self.slots[k][0].shape != frames.shape:
+            self.slots[k] = tuple(torch.empty(t.shape, dtype=t.dtype, device=self.device)
+                                  for t in (frames, gaze, actions))
+        with torch.cuda.stream(self.stream):
+            if self.free_events[k] is not None:
+                self.stream.wait_event(self.free_events[k])  # previous consumer of this slot done
+            for dst, src in zip(self.slots[k], (frames, gaze, actions)):
+                dst.copy_(src, non_blocking=True)
+            self.events[k].record(self.stream)
+        return k
+
+    def wait(self, k):
+        """Make the compute stream wait for slot k; returns the device tensors."""
+        torch.cuda.current_stream(self.device).wait_event(self.events[k])
+        return self.slots[k]
+
+    def release(self, k):
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self.free_events[k] = ev

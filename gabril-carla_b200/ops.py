@@ -19,6 +19,47 @@ def _fn(name):
     return getattr(lib, name + ("_naive" if _NAIVE else ""))
 
 
+# ---- optional per-launch tracing (bench.py's roofline leg): CUDA events around every call ----
+_TRACE = None
+
+
+class trace:
+    """with ops.trace() as t: ...; t.rows() -> [(kernel, label, work, unit, ms)] after a sync."""
+
+    def __init__(self):
+        self.items = []
+
+    def __enter__(self):
+        global _TRACE
+        _TRACE = self
+        return self
+
+    def __exit__(self, *exc):
+        global _TRACE
+        _TRACE = None
+
+    def rows(self):
+        torch.cuda.synchronize()
+        return [(k, lab, work, unit, e0.elapsed_time(e1)) for k, lab, work, unit, e0, e1 in self.items]
+
+
+class _span:
+    def __init__(self, kernel, label, work, unit):
+        self.args = (kernel, label, work, unit)
+
+    def __enter__(self):
+        if _TRACE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if _TRACE is not None:
+            self.e1.record()
+            _TRACE.items.append(self.args + (self.e0, self.e1))
+
+
 def _chk_bf16(t, name):
     if t is None:
         return
@@ -40,10 +81,11 @@ def conv_fwd(x, w, bias, y, R, S, stride, pad, relu=False, resid=None, rowmask=N
     OH, OW = conv_out_hw(H, W, R, S, stride, pad)
     assert y.numel() == N * OH * OW * Cout, (y.shape, N, OH, OW, Cout)
     assert y.dtype == (torch.float32 if out_f32_atomic else torch.bfloat16)
-    st = _fn("gabril_conv_fwd")(ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(rowmask), ptr(y),
-                                c_int(N), c_int(H), c_int(W), c_int(Cin), c_int(Cout), c_int(R),
-                                c_int(S), c_int(stride), c_int(pad), c_int(int(relu)),
-                                c_int(int(out_f32_atomic)), c_int(splits), stream())
+    with _span("tc_gemm_kernel", f"fwd {Cin}->{Cout} k{R}s{stride}", 2.0 * N * OH * OW * Cout * R * S * Cin, "flop"):
+        st = _fn("gabril_conv_fwd")(ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(rowmask), ptr(y),
+                                    c_int(N), c_int(H), c_int(W), c_int(Cin), c_int(Cout), c_int(R),
+                                    c_int(S), c_int(stride), c_int(pad), c_int(int(relu)),
+                                    c_int(int(out_f32_atomic)), c_int(splits), stream())
     _lib.check(st, "gabril_conv_fwd")
     return y
 
@@ -56,9 +98,10 @@ def conv_dgrad(dy, w, dx, R, S, stride, pad, addend=None, gate=None, rowmask=Non
     Cout = w.shape[0]
     OH, OW = conv_out_hw(H, W, R, S, stride, pad)
     assert dy.numel() == N * OH * OW * Cout, (dy.shape, N, OH, OW, Cout)
-    st = _fn("gabril_conv_dgrad")(ptr(dy), ptr(w), ptr(addend), ptr(gate), ptr(rowmask), ptr(dx),
-                                  c_int(N), c_int(H), c_int(W), c_int(Cin), c_int(Cout), c_int(R),
-                                  c_int(S), c_int(stride), c_int(pad), stream())
+    with _span("tc_gemm_kernel", f"dgrad {Cin}<-{Cout} k{R}s{stride}", 2.0 * N * OH * OW * Cout * R * S * Cin, "flop"):
+        st = _fn("gabril_conv_dgrad")(ptr(dy), ptr(w), ptr(addend), ptr(gate), ptr(rowmask), ptr(dx),
+                                      c_int(N), c_int(H), c_int(W), c_int(Cin), c_int(Cout), c_int(R),
+                                      c_int(S), c_int(stride), c_int(pad), stream())
     _lib.check(st, "gabril_conv_dgrad")
     return dx
 
@@ -71,9 +114,10 @@ def conv_wgrad(dy, x, dw, R, S, stride, pad, direct_store=False):
     assert dw.dtype == torch.float32 and dw.numel() == Cout * R * S * Cin
     OH, OW = conv_out_hw(H, W, R, S, stride, pad)
     assert dy.numel() == N * OH * OW * Cout, (dy.shape, N, OH, OW, Cout)
-    st = _fn("gabril_conv_wgrad")(ptr(dy), ptr(x), ptr(dw), c_int(N), c_int(H), c_int(W),
-                                  c_int(Cin), c_int(Cout), c_int(R), c_int(S), c_int(stride),
-                                  c_int(pad), c_int(int(direct_store)), stream())
+    with _span("tc_gemm_kernel", f"wgrad {Cin}x{Cout} k{R}s{stride}", 2.0 * N * OH * OW * Cout * R * S * Cin, "flop"):
+        st = _fn("gabril_conv_wgrad")(ptr(dy), ptr(x), ptr(dw), c_int(N), c_int(H), c_int(W),
+                                      c_int(Cin), c_int(Cout), c_int(R), c_int(S), c_int(stride),
+                                      c_int(pad), c_int(int(direct_store)), stream())
     _lib.check(st, "gabril_conv_wgrad")
     return dw
 
@@ -102,9 +146,11 @@ def _chk(t, dtype, name):
                          f" contiguous={t.is_contiguous()}")
 
 
-def _call(name, *args):
+def _call(name, *args, work=0.0):
     lib = _lib.init()
-    _lib.check(getattr(lib, name)(*args), name)
+    with _span(name, "", work, "byte"):
+        st = getattr(lib, name)(*args)
+    _lib.check(st, name)
 
 
 def obs_format(frames, S, center, grayscale, out=None):
@@ -135,7 +181,8 @@ def obs_patches(frames, S, center, grayscale, out=None):
     if out is None:
         out = torch.empty(B * OH * OW, Kp, device=frames.device, dtype=torch.bfloat16)
     _call("gabril_obs_patches", ptr(frames), ptr(out), c_int(B), c_int(L), c_int(S), c_int(center),
-          c_int(H), c_int(W), c_int(int(grayscale)), c_int(Kp), stream())
+          c_int(H), c_int(W), c_int(int(grayscale)), c_int(Kp), stream(),
+          work=float(B * S * H * W * 3 + out.numel() * 2))
     return out
 
 
@@ -150,7 +197,8 @@ def gaze_splat(gaze, out, ktab, Lk_host, agg_coeff, step_coeff, normalize_base, 
     stc = (ctypes.c_float * S)(*[float(v) for v in step_coeff]) if step_coeff is not None else None
     _call("gabril_gaze_splat", ptr(gaze), ptr(out), ptr(ktab), Lk, c_int(ktab.shape[1]), agg, stc,
           c_int(int(normalize_base)), c_int(int(aggregate)), c_int(B), c_int(L), c_int(S),
-          c_int(center), c_int(P), c_int(H), c_int(W), stream())
+          c_int(center), c_int(P), c_int(H), c_int(W), stream(),
+          work=float(B * S * P * 8 + out.numel() * 4))
     return out
 
 
@@ -165,7 +213,7 @@ def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=Non
               torch.empty(2, device=g.device, dtype=torch.int32))
     _call("gabril_gmd_mask", ptr(g), ptr(A), ptr(ws[0]), ptr(ws[1]), ptr(rowmask), ptr(keep_out),
           c_int(B), c_int(S), c_int(H), c_int(W), c_int(h), c_int(w), c_float(drop_p),
-          c_int(int(test_mode)), stream())
+          c_int(int(test_mode)), stream(), work=float(B * h * w * (16 * S * 4 + 16)))
     return rowmask
 
 
@@ -223,14 +271,15 @@ def reg_mse(z, g1_base, g1_bstride, H, W, beta, grad_scale, dz, loss_part, sel=N
     B, C, h, w = _z_dims(z)
     _call("gabril_reg_mse", ptr(z), c_int(_z_layout(z)), ptr(g1_base), c_ll(g1_bstride), ptr(sel),
           ptr(dz), ptr(loss_part), ptr(stats), c_int(B), c_int(C), c_int(h), c_int(w), c_int(H),
-          c_int(W), c_float(beta), c_float(grad_scale), stream())
+          c_int(W), c_float(beta), c_float(grad_scale), stream(),
+          work=float(B * (2 * z.element_size() * C * h * w + 4 * H * W)))
 
 
 def colsum_bf16(dy, db):
     _chk(dy, torch.bfloat16, "dy"); _chk(db, torch.float32, "db")
     C = db.numel()
     M = dy.numel() // C
-    _call("gabril_colsum_bf16", ptr(dy), ptr(db), c_ll(M), c_int(C), stream())
+    _call("gabril_colsum_bf16", ptr(dy), ptr(db), c_ll(M), c_int(C), stream(), work=float(M * C * 2))
 
 
 def bias_act_cast(x, bias, y_bf16, relu=False, y_f32=None):
@@ -259,7 +308,7 @@ def adam(p, g, m, v, shadow, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_
     n = p.numel()
     _call("gabril_adam", ptr(p), ptr(g), ptr(m), ptr(v), ptr(shadow), c_ll(n), c_float(lr),
           c_float(beta1), c_float(beta2), c_float(eps), c_float(weight_decay), c_int(int(decoupled)),
-          c_int(step), c_float(grad_scale), stream())
+          c_int(step), c_float(grad_scale), stream(), work=float(n * (28 + (2 if shadow is not None else 0))))
 
 
 def cast_f32_bf16(x, y):
@@ -270,4 +319,5 @@ def rowscale_bf16(t, scale):
     _chk(t, torch.bfloat16, "t"); _chk(scale, torch.float32, "scale")
     rows = scale.numel()
     C = t.numel() // rows
-    _call("gabril_rowscale_bf16", ptr(t), ptr(scale), c_ll(rows), c_int(C), stream())
+    _call("gabril_rowscale_bf16", ptr(t), ptr(scale), c_ll(rows), c_int(C), stream(),
+          work=float(rows * (4 * C + 4)))
