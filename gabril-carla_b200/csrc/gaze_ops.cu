@@ -207,220 +207,6 @@ obs_patches_kernel(const uint8_t* __restrict__ frames, bf16* __restrict__ out, i
 }
 
 // =================================================================================================
-// K2: gaze heat maps.  Closed form of the reference's scatter_add + separable blur (with its
-// row-band padding quirk) + per-frame min-max + causal aggregation + second min-max.
-//   raw_s(y,x) = coeff_s * sum_p  band_s(y) k_s[y_p - y + R_s] * k_s[x_p - x + R_s]
-// One CTA = one sample x one row slab; every CTA recomputes the (cheap) per-map extrema.
-// =================================================================================================
-struct SplatArgs {
-  const float* gaze;  // [B, L, P*2]
-  float* out;         // [B, S, H, W]
-  const float* ktab;  // [S][ktab_stride] fp32 taps of the per-step 1-D kernels
-  int Lk[kMaxS];
-  int ktab_stride;
-  float agg[kMaxS][kMaxS];  // agg[s][j], j <= s: causal aggregation coefficients
-  float step_coeff[kMaxS];  // multiscale: raw_s * coeff_s (1 otherwise)
-  int use_step_coeff;
-  int normalize_base;  // alpha_decay: per-frame min-max before aggregation
-  int aggregate;       // 0: out = base (gaze.temporal_flag = false)
-  int B, L, S, center, P, H, W, nsplit;
-};
-
-__global__ void __launch_bounds__(256) gaze_splat_kernel(const __grid_constant__ SplatArgs a) {
-  extern __shared__ float sm[];
-  const int S = a.S, P = a.P, H = a.H, W = a.W;
-  float* kyv = sm;               // [S*P][H]
-  float* kxv = kyv + S * P * H;  // [S*P][W]
-  __shared__ int s_xi[kMaxS * kMaxPts], s_yi[kMaxS * kMaxPts], s_ok[kMaxS * kMaxPts];
-  __shared__ float red_mn[8][kMaxS], red_mx[8][kMaxS];
-  __shared__ float s_mn[kMaxS], s_mx[kMaxS], s_amn[kMaxS], s_amx[kMaxS];
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int b = blockIdx.x, split = blockIdx.y;
-
-  // ---- integer pixel indices (bit-exact: clamp, ONE fp32 multiply, truncate, clamp) ----
-  if (tid < S * P) {
-    const int s = tid / P, p = tid - s * P;
-    const int f = frame_index(s, S, a.center, a.L);
-    const float* gp = a.gaze + (((long long)b * a.L + f) * P + p) * 2;
-    const float gx = gp[0], gy = gp[1];
-    s_ok[tid] = (gx >= 0.f) && (gy >= 0.f);
-    const float cx = fminf(fmaxf(gx, 0.f), 1.f), cy = fminf(fmaxf(gy, 0.f), 1.f);
-    int xi = (int)__fmul_rn(cx, (float)(W - 1));
-    int yi = (int)__fmul_rn(cy, (float)(H - 1));
-    s_xi[tid] = min(max(xi, 0), W - 1);
-    s_yi[tid] = min(max(yi, 0), H - 1);
-  }
-  __syncthreads();
-  int ylo = H, yhi = 0;  // union of the per-step bands [R_s, H - R_s)
-  for (int s = 0; s < S; ++s) {
-    const int R = a.Lk[s] >> 1;
-    ylo = min(ylo, R);
-    yhi = max(yhi, H - R);
-  }
-  for (int i = tid; i < S * P * H; i += blockDim.x) {
-    const int sp = i / H, y = i - sp * H;
-    const int s = sp / P;
-    const int Lk = a.Lk[s], R = Lk >> 1;
-    const int d = s_yi[sp] - y + R;
-    const bool in = s_ok[sp] && d >= 0 && d < Lk && y >= R && y < H - R;
-    kyv[i] = in ? a.ktab[s * a.ktab_stride + d] : 0.f;
-  }
-  for (int i = tid; i < S * P * W; i += blockDim.x) {
-    const int sp = i / W, x = i - sp * W;
-    const int s = sp / P;
-    const int Lk = a.Lk[s], R = Lk >> 1;
-    const int d = s_xi[sp] - x + R;
-    const bool in = s_ok[sp] && d >= 0 && d < Lk;
-    kxv[i] = in ? a.ktab[s * a.ktab_stride + d] : 0.f;
-  }
-  __syncthreads();
-
-  auto raw_at = [&](int y, int x, float raw[kMaxS]) {
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s) {
-      if (s < S) {
-        float acc = 0.f;
-        for (int p = 0; p < P; ++p) acc = fmaf(kyv[(s * P + p) * H + y], kxv[(s * P + p) * W + x], acc);
-        raw[s] = a.use_step_coeff ? __fmul_rn(acc, a.step_coeff[s]) : acc;
-      }
-    }
-  };
-  const bool has_outside = (ylo > 0) || (yhi < H);  // rows where every raw_s is exactly 0
-  const int band_px = max(yhi - ylo, 0) * W;
-
-  // ---- pass A: per-frame extrema of the raw maps ----
-  float mn[kMaxS], mx[kMaxS];
-#pragma unroll
-  for (int s = 0; s < kMaxS; ++s) { mn[s] = 0.f; mx[s] = 1.f; }
-  if (a.normalize_base) {
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s) { mn[s] = has_outside ? 0.f : FLT_MAX; mx[s] = has_outside ? 0.f : -FLT_MAX; }
-    for (int i = tid; i < band_px; i += blockDim.x) {
-      const int y = ylo + i / W, x = i % W;
-      float raw[kMaxS];
-      raw_at(y, x, raw);
-#pragma unroll
-      for (int s = 0; s < kMaxS; ++s)
-        if (s < S) { mn[s] = fminf(mn[s], raw[s]); mx[s] = fmaxf(mx[s], raw[s]); }
-    }
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s)
-      if (s < S) {
-        const float lo = warp_min(mn[s]), hi = warp_max(mx[s]);
-        if (lane == 0) { red_mn[wid][s] = lo; red_mx[wid][s] = hi; }
-      }
-    __syncthreads();
-    if (tid < S) {
-      float lo = red_mn[0][tid], hi = red_mx[0][tid];
-      for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { lo = fminf(lo, red_mn[w][tid]); hi = fmaxf(hi, red_mx[w][tid]); }
-      s_mn[tid] = lo;
-      s_mx[tid] = hi;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s)
-      if (s < S) { mn[s] = s_mn[s]; mx[s] = s_mx[s]; }
-  }
-  // base_s = (raw - mn) / ((mx - mn) + 1e-8)   (data_loader_robomimic.py:134-136)
-  auto agg_at = [&](const float raw[kMaxS], float agg[kMaxS]) {
-    float base[kMaxS];
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s)
-      if (s < S)
-        base[s] = a.normalize_base
-                      ? __fdiv_rn(__fsub_rn(raw[s], mn[s]), __fadd_rn(__fsub_rn(mx[s], mn[s]), 1e-8f))
-                      : raw[s];
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s)
-      if (s < S) {
-        if (!a.aggregate || s == 0) {
-          agg[s] = base[s];
-        } else {
-          // (base[:, :s+1] * coeffs).sum(dim=1): products rounded, then summed j = 0..s (:265-274)
-          float acc = __fmul_rn(a.agg[s][0], base[0]);
-#pragma unroll
-          for (int j = 1; j < kMaxS; ++j)
-            if (j <= s) acc = __fadd_rn(acc, __fmul_rn(a.agg[s][j], base[j]));
-          agg[s] = acc;
-        }
-      }
-  };
-  float zero_raw[kMaxS];
-#pragma unroll
-  for (int s = 0; s < kMaxS; ++s) zero_raw[s] = 0.f;
-  float agg_out[kMaxS];  // value of every aggregated map on the all-zero rows
-  agg_at(zero_raw, agg_out);
-
-  // ---- pass B: extrema of the aggregated maps ----
-  float amn[kMaxS], amx[kMaxS];
-  const bool second_norm = a.aggregate != 0;
-  if (second_norm) {
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s) { amn[s] = has_outside ? agg_out[s] : FLT_MAX; amx[s] = has_outside ? agg_out[s] : -FLT_MAX; }
-    for (int i = tid; i < band_px; i += blockDim.x) {
-      const int y = ylo + i / W, x = i % W;
-      float raw[kMaxS], ag[kMaxS];
-      raw_at(y, x, raw);
-      agg_at(raw, ag);
-#pragma unroll
-      for (int s = 0; s < kMaxS; ++s)
-        if (s < S) { amn[s] = fminf(amn[s], ag[s]); amx[s] = fmaxf(amx[s], ag[s]); }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s)
-      if (s < S) {
-        const float lo = warp_min(amn[s]), hi = warp_max(amx[s]);
-        if (lane == 0) { red_mn[wid][s] = lo; red_mx[wid][s] = hi; }
-      }
-    __syncthreads();
-    if (tid < S) {
-      float lo = red_mn[0][tid], hi = red_mx[0][tid];
-      for (int w = 1; w < (int)(blockDim.x >> 5); ++w) { lo = fminf(lo, red_mn[w][tid]); hi = fmaxf(hi, red_mx[w][tid]); }
-      s_amn[tid] = lo;
-      s_amx[tid] = hi;
-    }
-    __syncthreads();
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s)
-      if (s < S) { amn[s] = s_amn[s]; amx[s] = s_amx[s]; }
-  }
-  auto finish = [&](float v, int s) {
-    return second_norm ? __fdiv_rn(__fsub_rn(v, amn[s]), __fadd_rn(__fsub_rn(amx[s], amn[s]), 1e-8f)) : v;
-  };
-
-  // ---- pass C: write this CTA's row slab of all S maps (float4 stores) ----
-  const int rows_per = (H + a.nsplit - 1) / a.nsplit;
-  const int y0 = split * rows_per, y1 = min(y0 + rows_per, H);
-  const int W4 = W >> 2;
-  float* outb = a.out + (long long)b * S * H * W;
-  for (int i = tid; i < (y1 - y0) * W4; i += blockDim.x) {
-    const int y = y0 + i / W4, x = (i % W4) * 4;
-    float o[kMaxS][4];
-    if (y < ylo || y >= yhi) {
-#pragma unroll
-      for (int s = 0; s < kMaxS; ++s)
-        if (s < S) { const float v = finish(agg_out[s], s); o[s][0] = o[s][1] = o[s][2] = o[s][3] = v; }
-    } else {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        float raw[kMaxS], ag[kMaxS];
-        raw_at(y, x + k, raw);
-        agg_at(raw, ag);
-#pragma unroll
-        for (int s = 0; s < kMaxS; ++s)
-          if (s < S) o[s][k] = finish(ag[s], s);
-      }
-    }
-#pragma unroll
-    for (int s = 0; s < kMaxS; ++s)
-      if (s < S)
-        *reinterpret_cast<float4*>(outb + ((long long)s * H + y) * W + x) =
-            make_float4(o[s][0], o[s][1], o[s][2], o[s][3]);
-  }
-}
-
-// =================================================================================================
 // K6: gaze-mask dropout.  gmd_keep: K[b, j] = mean_s bicubic_down(g[b, s])[j] + batch-global
 // min / max (ordered-uint atomics).  gmd_mask: rowmask[b, j] = (A < 0.7 Khat + 0.3) or the keep
 // probability itself in test mode.
@@ -849,44 +635,6 @@ int gabril_obs_patches(const uint8_t* frames, void* patches, int B, int L, int S
     }
   }
 #undef GABRIL_PATCH_CASE
-  GABRIL_CHECK_LAUNCH();
-  return GABRIL_OK;
-}
-
-int gabril_gaze_splat(const float* gaze, float* out, const float* ktab, const int* Lk,
-                      int ktab_stride, const float* agg_coeff, const float* step_coeff,
-                      int normalize_base, int aggregate, int B, int L, int S, int center, int P,
-                      int H, int W, cudaStream_t stream) {
-  if (!gaze || !out || !ktab || !Lk) return GABRIL_ERR_NULL;
-  if (B <= 0 || S < 1 || S > kMaxS || P < 1 || P > kMaxPts || W % 4 || S * P > 256)
-    return GABRIL_ERR_BAD_SHAPE;
-  SplatArgs a;
-  a.gaze = gaze; a.out = out; a.ktab = ktab; a.ktab_stride = ktab_stride;
-  for (int s = 0; s < kMaxS; ++s) {
-    a.Lk[s] = s < S ? Lk[s] : 1;
-    a.step_coeff[s] = (step_coeff && s < S) ? step_coeff[s] : 1.f;
-    for (int j = 0; j < kMaxS; ++j)
-      a.agg[s][j] = (agg_coeff && s < S && j <= s) ? agg_coeff[s * S + j] : (j <= s ? 1.f : 0.f);
-    // the reference's conv2d needs H >= kernel size (valid vertical pass)
-    if (s < S && (Lk[s] > H || Lk[s] < 1 || Lk[s] > ktab_stride || (Lk[s] & 1) == 0))
-      return GABRIL_ERR_BAD_SHAPE;
-  }
-  a.use_step_coeff = step_coeff != nullptr;
-  a.normalize_base = normalize_base; a.aggregate = aggregate;
-  a.B = B; a.L = L; a.S = S; a.center = center; a.P = P; a.H = H; a.W = W;
-  int nsplit = 1;
-  while ((long long)B * nsplit < 2 * 148 && nsplit < 8 && nsplit * 2 <= H) nsplit *= 2;
-  a.nsplit = nsplit;
-  const size_t smem = sizeof(float) * (size_t)S * P * (H + W);
-  if (smem > 160 * 1024) return GABRIL_ERR_BAD_SHAPE;
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(gaze_splat_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    if (e != cudaSuccess) return gabril_set_cuda_error(e);
-    attr_done = true;
-  }
-  gaze_splat_kernel<<<dim3(B, nsplit), 256, smem, stream>>>(a);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
 }

@@ -410,14 +410,18 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
   // accumulators: as many taps per CTA as TMEM (512 cols) and smem (2 stages in 200 KB) allow
   int n_acc = std::min(T, 512 / block_n);
   while (n_acc > 1 && 2 * (p.a_stage_bytes + n_acc * b_tap_bytes) > 200 * 1024) --n_acc;
-  n_acc = std::min(n_acc, tc::kMaxMma / (KP / 16));
+  // One UMMA covers G consecutive taps: their MN-major B tiles sit b_tap_bytes apart, which is a
+  // whole number of swizzle atoms, so N = G * block_n (<= 256) is a single instruction.
+  const int G = std::max(1, std::min(n_acc, 256 / block_n));
+  if (n_acc > G) n_acc = n_acc / G * G;
+  n_acc = std::min(n_acc, G * (tc::kMaxMma / (KP / 16)));
   p.n_acc = n_acc;
   p.taps = T;
   p.tap_groups = (T + n_acc - 1) / n_acc;
   p.S = S;
   p.b_stage_bytes = round_up(n_acc * b_tap_bytes, 1024);
   p.n_mma = 0;
-  for (int t = 0; t < n_acc; ++t)
+  for (int t = 0; t < n_acc; t += G)
     for (int j = 0; j < KP / 16; ++j) {
       const int i = p.n_mma++;
       p.mma_a_off[i] = (uint16_t)((j * 16 * a_sw) >> 4);
@@ -426,7 +430,7 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
       p.mma_acc[i] = (uint8_t)t;
       p.mma_first[i] = (j == 0);
     }
-  p.idesc = make_idesc(1, 1, 128, block_n);
+  p.idesc = make_idesc(1, 1, 128, G * block_n);
   p.tmem_cols = pow2_cols(n_acc * block_n);
   p.M_total[0] = Cout;
   p.N_total = Cin;

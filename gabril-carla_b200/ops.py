@@ -186,8 +186,11 @@ def obs_patches(frames, S, center, grayscale, out=None):
     return out
 
 
+_splat_ws = {}
+
+
 def gaze_splat(gaze, out, ktab, Lk_host, agg_coeff, step_coeff, normalize_base, aggregate, S, center,
-               P, H, W):
+               P, H, W, ws=None):
     """gaze fp32 [B,L,P*2] -> out fp32 [B,S,H,W]; ktab fp32 [S,stride] (device), Lk_host: ints."""
     import ctypes
     _chk(gaze, torch.float32, "gaze"); _chk(out, torch.float32, "out"); _chk(ktab, torch.float32, "ktab")
@@ -195,7 +198,12 @@ def gaze_splat(gaze, out, ktab, Lk_host, agg_coeff, step_coeff, normalize_base, 
     Lk = (ctypes.c_int * S)(*[int(v) for v in Lk_host])
     agg = (ctypes.c_float * (S * S))(*[float(v) for v in agg_coeff]) if agg_coeff is not None else None
     stc = (ctypes.c_float * S)(*[float(v) for v in step_coeff]) if step_coeff is not None else None
-    _call("gabril_gaze_splat", ptr(gaze), ptr(out), ptr(ktab), Lk, c_int(ktab.shape[1]), agg, stc,
+    if ws is None:  # per-(device, B) extrema workspace, reused across calls (stream ordered)
+        key = (gaze.device, B)
+        ws = _splat_ws.get(key)
+        if ws is None:
+            ws = _splat_ws[key] = torch.empty(B, 32, device=gaze.device, dtype=torch.float32)
+    _call("gabril_gaze_splat", ptr(gaze), ptr(out), ptr(ws), ptr(ktab), Lk, c_int(ktab.shape[1]), agg, stc,
           c_int(int(normalize_base)), c_int(int(aggregate)), c_int(B), c_int(L), c_int(S),
           c_int(center), c_int(P), c_int(H), c_int(W), stream(),
           work=float(B * S * P * 8 + out.numel() * 4))

@@ -96,7 +96,8 @@ int gabril_obs_patches(const uint8_t* frames, void* patches_bf16, int B, int L, 
  * aggregation (alpha_decay mode); aggregate = 0 returns the per-frame maps (gaze.temporal_flag =
  * false).  out: fp32 [B, S, H, W].  Pixel indices are bit-exact; the row-band quirk of the
  * reference's padding is reproduced. */
-int gabril_gaze_splat(const float* gaze, float* out, const float* ktab, const int* Lk,
+int gabril_gaze_splat(const float* gaze, float* out, float* ext_ws /* [B][32] fp32 workspace */,
+                      const float* ktab, const int* Lk,
                       int ktab_stride, const float* agg_coeff, const float* step_coeff,
                       int normalize_base, int aggregate, int B, int L, int S, int center, int P,
                       int H, int W, cudaStream_t stream);

@@ -1,0 +1,103 @@
+"""-m gpu: every dense contraction of the encoder / heads (fwd, dgrad, wgrad) through the tcgen05
+path (C ABI via ctypes) against fp64 CPU convolution of the same bf16-rounded operands."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+# (name, H, W, Cin, Cout, R, S, stride, pad)
+LAYERS = [
+    ("conv1_gemm_gray", 1, 1, 32, 32, 1, 1, 1, 0),
+    ("conv1_gemm_rgb", 1, 1, 128, 32, 1, 1, 1, 0),
+    ("conv2", 90, 160, 32, 64, 4, 4, 2, 1),
+    ("conv3", 45, 80, 64, 128, 4, 4, 2, 1),
+    ("conv4", 22, 40, 128, 128, 3, 3, 1, 0),
+    ("res3x3", 20, 38, 128, 32, 3, 3, 1, 1),
+    ("res1x1", 20, 38, 32, 128, 1, 1, 1, 0),
+    ("conv5", 20, 38, 128, 128, 5, 5, 1, 2),
+    ("conv6", 20, 38, 128, 64, 5, 5, 1, 2),
+    ("actor0", 1, 1, 256, 256, 1, 1, 1, 0),
+    ("actor2", 1, 1, 256, 32, 1, 1, 1, 0),
+]
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import gabril_carla_b200  # noqa: F401
+    from gabril_carla_b200 import _lib, ops
+    _lib.init()
+    return ops
+
+
+def rel(a, b):
+    return ((a.double() - b).norm() / (b.norm() + 1e-30)).item()
+
+
+@pytest.mark.parametrize("N", [3, 40])
+@pytest.mark.parametrize("layer", LAYERS, ids=[l[0] for l in LAYERS])
+def test_conv_fwd_dgrad_wgrad(ops, layer, N):
+    name, H, W, Cin, Cout, R, S, stride, pad = layer
+    if H == 1:
+        N = N * 700 + 13  # linear layers: rows
+    from gabril_carla_b200 import _lib
+    g = torch.Generator().manual_seed(len(name) * 7 + N)
+    OH, OW = ops.conv_out_hw(H, W, R, S, stride, pad)
+    x = (torch.randn(N, H, W, Cin, generator=g) * 0.5).to(torch.bfloat16)
+    w = (torch.randn(Cout, Cin, R, S, generator=g) / (Cin * R * S) ** 0.5).to(torch.bfloat16)
+    bias = torch.randn(Cout, generator=g)
+    resid = torch.randn(N, OH, OW, Cout, generator=g).to(torch.bfloat16)
+    rowmask = (torch.rand(N * OH * OW, generator=g) > 0.3).float()
+    dy = (torch.randn(N, OH, OW, Cout, generator=g) * 0.5).to(torch.bfloat16)
+    addend = torch.randn(N, H, W, Cin, generator=g).to(torch.bfloat16)
+    gate = torch.randn(N, H, W, Cin, generator=g).to(torch.bfloat16)
+    xd, wd = x.to(DEV), ops.w_oihw_to_internal(w).to(DEV)
+    x64, w64, dy64 = x.double().permute(0, 3, 1, 2), w.double(), dy.double().permute(0, 3, 1, 2)
+    # forward: bias + residual + ReLU + row mask epilogue
+    y = torch.full((N, OH, OW, Cout), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.conv_fwd(xd, wd, bias.to(DEV), y, R, S, stride, pad, relu=True, resid=resid.to(DEV),
+                 rowmask=rowmask.to(DEV))
+    ref = F.relu(F.conv2d(x64, w64, bias.double(), stride=stride, padding=pad).permute(0, 2, 3, 1)
+                 + resid.double()) * rowmask.double().view(N, OH, OW, 1)
+    assert rel(y.cpu(), ref) <= 4e-3  # bf16 output rounding (2^-9)
+    # dgrad: + addend, gated
+    dx = torch.full((N, H, W, Cin), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.conv_dgrad(dy.to(DEV), wd, dx, R, S, stride, pad, addend=addend.to(DEV), gate=gate.to(DEV))
+    dref = torch.nn.grad.conv2d_input((N, Cin, H, W), w64, dy64, stride=stride, padding=pad).permute(0, 2, 3, 1)
+    dref = (dref + addend.double()) * (gate.double() > 0)
+    assert rel(dx.cpu(), dref) <= 4e-3
+    # wgrad: fp32 accumulate (split over CTAs with fp32 atomics), and direct store for linears
+    dw = torch.zeros(Cout, R * S, Cin, device=DEV, dtype=torch.float32)
+    ops.conv_wgrad(dy.to(DEV), xd, dw, R, S, stride, pad)
+    wref = ops.w_oihw_to_internal(torch.nn.grad.conv2d_weight(x64, (Cout, Cin, R, S), dy64, stride=stride, padding=pad))
+    assert rel(dw.cpu(), wref) <= 2e-5
+    _lib.poll_error()
+
+
+def test_pre_actor_shapes(ops):
+    from gabril_carla_b200 import _lib
+    g = torch.Generator().manual_seed(7)
+    Bn, K, Nf = 96, 48640, 256
+    z = (torch.randn(Bn, K, generator=g) * 0.5).to(torch.bfloat16)
+    wp = (torch.randn(Nf, K, generator=g) / K ** 0.5).to(torch.bfloat16)
+    dzf = torch.randn(Bn, Nf, generator=g).to(torch.bfloat16)
+    zd, wd, dd = z.to(DEV), wp.to(DEV), dzf.to(DEV)
+    out = torch.zeros(Bn, Nf, device=DEV, dtype=torch.float32)
+    ops.conv_fwd(zd.view(Bn, 1, 1, K), wd.view(Nf, 1, K), None, out, 1, 1, 1, 0, out_f32_atomic=True, splits=19)
+    assert rel(out.cpu(), z.double() @ wp.double().t()) <= 1e-5
+    dz = torch.full((Bn, 1, 1, K), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.conv_dgrad(dd.view(Bn, 1, 1, Nf), wd.view(Nf, 1, K), dz, 1, 1, 1, 0)
+    assert rel(dz.view(Bn, K).cpu(), dzf.double() @ wp.double()) <= 4e-3
+    dwp = torch.full((Nf, 1, K), float("nan"), device=DEV, dtype=torch.float32)
+    ops.conv_wgrad(dd.view(Bn, 1, 1, Nf), zd.view(Bn, 1, 1, K), dwp, 1, 1, 1, 0, direct_store=True)
+    assert rel(dwp.view(Nf, K).cpu(), dzf.double().t() @ z.double()) <= 1e-5
+    _lib.poll_error()
+
+
+def test_unsupported_shapes_fail_loudly(ops):
+    x = torch.zeros(2, 4, 4, 96, device=DEV, dtype=torch.bfloat16)
+    dy = torch.zeros(2, 4, 4, 32, device=DEV, dtype=torch.bfloat16)
+    dw = torch.zeros(32, 1, 96, device=DEV)
+    with pytest.raises(RuntimeError):
+        ops.conv_wgrad(dy, x, dw, 1, 1, 1, 0)  # Cin = 96 is not 32 / 64 / k*128
