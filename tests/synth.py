@@ -27,3 +27,41 @@ def make_batch(B, L=2, H=180, W=320, P=5, A=7, seed=0, smooth=True, edge_cases=T
         gaze[3, -1, 0] = torch.tensor([-1.0, 0.4])  # negative on one axis only => invalid
     actions = torch.rand(B, L, A, generator=g)
     return img.contiguous(), gaze.reshape(B, L, P * 2).contiguous(), actions.contiguous()
+
+
+# reference state_dict layout: key -> shape, c = encoder input channels
+def reference_shapes(c_in, action_dim=7):
+    enc = {"_conv_1.weight": (32, c_in, 4, 4), "_conv_1.bias": (32,),
+           "_conv_2.weight": (64, 32, 4, 4), "_conv_2.bias": (64,),
+           "_conv_3.weight": (128, 64, 4, 4), "_conv_3.bias": (128,),
+           "_conv_4.weight": (128, 128, 3, 3), "_conv_4.bias": (128,),
+           "_residual_stack._layers.0._block.1.weight": (32, 128, 3, 3),
+           "_residual_stack._layers.0._block.3.weight": (128, 32, 1, 1),
+           "_residual_stack._layers.1._block.1.weight": (32, 128, 3, 3),
+           "_residual_stack._layers.1._block.3.weight": (128, 32, 1, 1),
+           "_conv_5.weight": (128, 128, 5, 5), "_conv_5.bias": (128,),
+           "_conv_6.weight": (64, 128, 5, 5), "_conv_6.bias": (64,)}
+    pre = {"1.weight": (256, 48640), "1.bias": (256,)}
+    act = {"0.weight": (256, 256), "0.bias": (256,), "2.weight": (action_dim, 256), "2.bias": (action_dim,)}
+    return {"encoder": enc, "pre_actor": pre, "actor": act}
+
+
+def make_weights(c_in, seed=7, action_dim=7):
+    """Deterministic (torch CPU generator) He-scaled weights and small non-zero biases in the
+    reference's state_dict layout — independent of LAPACK (orthogonal_) so that the committed
+    golden vectors can be regenerated bit-identically anywhere."""
+    g = torch.Generator().manual_seed(seed)
+    out = {}
+    for mod, shapes in reference_shapes(c_in, action_dim).items():
+        sd = {}
+        for k, shp in shapes.items():
+            if k.endswith("bias"):
+                sd[k] = (torch.rand(shp, generator=g) - 0.5) * 0.1
+            else:
+                fan_in = 1
+                for d in shp[1:]:
+                    fan_in *= d
+                gain = 2.0 ** 0.5 if len(shp) == 4 else 1.0
+                sd[k] = torch.randn(shp, generator=g) * (gain / fan_in ** 0.5)
+        out[mod] = sd
+    return out
