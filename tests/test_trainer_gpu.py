@@ -1,0 +1,89 @@
+"""-m gpu: the drop-in trainer surface (BCTrainer hooks, reference-style loop, checkpoint layout)."""
+import json
+import os
+
+import pytest
+import torch
+
+from oracle import gabril_oracle as O
+from tests.synth import reference_shapes
+
+pytestmark = pytest.mark.gpu
+
+
+def make_cfg(tmp_path, *extra):
+    import gabril_carla_b200  # noqa: F401
+    from gabril_carla_b200.config import load_config
+    return load_config(["data.hdf5_path=synthetic:96", "data.batch_size=32", "training.epochs=2",
+                        "training.save_interval=1", "scheduler.type=none", "optimizer.lr=1e-4",
+                        f"logging.checkpoint_dir={tmp_path}", f"logging.log_dir={tmp_path}", *extra])
+
+
+def test_compute_loss_matches_oracle_and_reference_loop_style(tmp_path):
+    from gabril_carla_b200.trainer import BCTrainer
+    tr = BCTrainer(make_cfg(tmp_path, "dropout.method=GMD"))
+    tr.set_train_mode()
+    batch = next(iter(tr.train_loader))
+    A = torch.rand(32, 1, 20, 38, generator=torch.Generator().manual_seed(4))
+    tr.engine.injected_A = A.to(tr.device)
+    sds = {m: {k: v.cpu() for k, v in sd.items()} for m, sd in tr.arena.state_dicts().items()}
+    tr.zero_grad()
+    loss, bs, metrics = tr.compute_loss(batch)           # the reference's hook signature
+    assert bs == 32 and isinstance(metrics["Loss/actor"], float) and loss.dim() == 0
+    (loss / 1).backward()                                # the reference's loop statement
+    tr.optimizer_step()
+    torch.cuda.synchronize()
+    cpu = lambda t: t.cpu()
+    total, actor, reg, _ = O.bc_losses(sds["encoder"], sds["pre_actor"], sds["actor"],
+                                       cpu(batch["obs"]["image"]), cpu(batch["obs"]["gaze_coords"]),
+                                       cpu(batch["actions"]), gaze_method="Reg", dp_method="GMD", gmd_A=A)
+    # bf16 activations vs the fp32 oracle: losses rel 1e-3 x safety 5 (north_star tolerance family)
+    assert abs(metrics["Loss/actor"] - actor.item()) <= 5e-3 * abs(actor.item())
+    assert abs(metrics["Loss/reg"] - reg.item()) <= 5e-3 * abs(reg.item())
+    assert abs(loss.item() - total.item()) <= 5e-3 * abs(total.item())
+    # parameters moved
+    new = tr.arena.state_dicts()["actor"]["2.weight"].cpu()
+    assert (new - sds["actor"]["2.weight"]).abs().max() > 0
+
+
+def test_train_two_epochs_and_checkpoint_layout(tmp_path):
+    from gabril_carla_b200.trainer import BCTrainer
+    tr = BCTrainer(make_cfg(tmp_path))
+    first = {}
+    tr.train()
+    d = tr.checkpoint_dir
+    assert d.parent.name == "Mixed_"
+    for ep in (1, 2):
+        for mod in ("encoder", "pre_actor", "actor"):
+            assert (d / f"ep{ep}_{mod}.pth").exists()
+    params = json.load(open(d / "params.json"))
+    for k in ("gaze_method", "dp_method", "grayscale", "stack", "embedding_dim", "num_embeddings", "num_hiddens",
+              "num_residual_layers", "num_residual_hiddens", "z_dim", "gaze_predictor_path", "models_path",
+              "epochs", "action_dim"):
+        assert k in params, k
+    assert params["epochs"] == 2 and params["stack"] == 2 and params["models_path"] == str(d)
+    # the reference loader (bc_agent.py:96-128): torch.load(weights_only=True), strict key/shape match
+    shapes = reference_shapes(2)
+    sds = {}
+    for mod in ("encoder", "pre_actor", "actor"):
+        sd = torch.load(d / f"ep2_{mod}.pth", weights_only=True)
+        assert list(sd.keys()) == list(shapes[mod].keys())
+        for k, v in sd.items():
+            assert tuple(v.shape) == shapes[mod][k] and v.dtype == torch.float32 and v.device.type == "cpu"
+            assert torch.isfinite(v).all()
+        sds[mod] = sd
+    # the saved weights drive the reference forward (oracle restatement) to finite actions
+    batch = next(iter(tr.train_loader))
+    obs, heat, c = O.prepare_for_bc(batch["obs"]["image"].cpu()[:2], batch["obs"]["gaze_coords"].cpu()[:2], 2, True)
+    z = O.encoder_forward(sds["encoder"], obs)
+    _, logits = O.heads_forward(sds["pre_actor"], sds["actor"], z)
+    assert logits.shape == (2, 7) and torch.isfinite(logits).all()
+    assert tr.last_epoch_loss == tr.last_epoch_loss  # not NaN
+
+
+def test_unsupported_methods_raise(tmp_path):
+    from gabril_carla_b200.trainer import BCTrainer
+    with pytest.raises(NotImplementedError):
+        BCTrainer(make_cfg(tmp_path, "gaze.method=AGIL"))
+    with pytest.raises(NotImplementedError):
+        BCTrainer(make_cfg(tmp_path, "dropout.method=Oreo"))
