@@ -17,41 +17,54 @@ namespace tc {
 // ---------------------------------------------------------------------------------------------
 // device
 // ---------------------------------------------------------------------------------------------
+__device__ unsigned long long g_prof[8];
+
 __device__ __forceinline__ void report_timeout(const Params& p, int code) {
   if (p.err_flag) atomicExch(p.err_flag, code);
 }
 
-__global__ void __launch_bounds__(kThreads) tc_gemm_kernel(const __grid_constant__ Params p) {
+struct Tile {
+  int cls, m0, n0, tap0, ntaps, kb_begin, kb_end;
+};
+
+// tile id -> (m tile over the concatenated classes, n tile [x tap group], split)
+__device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
+  Tile r;
+  int mi = t % p.tiles_m_total;
+  const int rest = t / p.tiles_m_total;
+  const int y = rest % p.n_tiles;
+  const int split = rest / p.n_tiles;
+  int cls = 0;
+  while (cls + 1 < p.n_classes && mi >= p.tiles_m[cls]) { mi -= p.tiles_m[cls]; ++cls; }
+  r.cls = cls;
+  r.m0 = mi * 128;
+  int n_tile = y, tg = 0;
+  if (p.kind == KIND_WGRAD) {
+    n_tile = y / p.tap_groups;
+    tg = y - n_tile * p.tap_groups;
+  }
+  r.n0 = n_tile * p.block_n;
+  r.tap0 = tg * p.n_acc;
+  r.ntaps = (p.kind == KIND_WGRAD) ? min(p.n_acc, p.taps - r.tap0) : 1;
+  r.kb_begin = split * p.kb_per_split;
+  r.kb_end = min(r.kb_begin + p.kb_per_split, p.kb_total);
+  return r;
+}
+
+// Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ...  The smem stage ring runs across
+// tile boundaries and the accumulator lives in a ring of acc_bufs TMEM buffers, so the producer
+// and the MMA issuer work on tile i+1 while the epilogue warps drain tile i.
+__global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_constant__ Params p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 1];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int cls = p.n_classes > 1 ? (int)blockIdx.z : 0;
-  const int split = p.n_classes > 1 ? 0 : (int)blockIdx.z;
-  const int M_total = p.M_total[cls];
-  const int m0 = blockIdx.x * 128;
-  if (m0 >= M_total) return;
-  const int kb_begin = split * p.kb_per_split;
-  const int kb_end = min(kb_begin + p.kb_per_split, p.kb_total);
-  if (kb_begin >= kb_end) return;
-
-  int n_tile, tg;
-  if (p.kind == KIND_WGRAD) {
-    n_tile = blockIdx.y / p.tap_groups;
-    tg = blockIdx.y - n_tile * p.tap_groups;
-  } else {
-    n_tile = blockIdx.y;
-    tg = 0;
-  }
-  const int n0 = n_tile * p.block_n;
-  const int tap0 = tg * p.n_acc;
-  const int ntaps = (p.kind == KIND_WGRAD) ? min(p.n_acc, p.taps - tap0) : 1;
-
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t full0 = ptx::smem_u32(&bars[0]);
   const uint32_t empty0 = ptx::smem_u32(&bars[kMaxStages]);
-  const uint32_t tfull = ptx::smem_u32(&bars[2 * kMaxStages]);
+  const uint32_t tfull0 = ptx::smem_u32(&bars[2 * kMaxStages]);
+  const uint32_t tempty0 = ptx::smem_u32(&bars[2 * kMaxStages + 2]);
   const uint32_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
 
   if (threadIdx.x == 0) {
@@ -59,10 +72,13 @@ __global__ void __launch_bounds__(kThreads) tc_gemm_kernel(const __grid_constant
       ptx::mbar_init(full0 + 8 * s, 1);
       ptx::mbar_init(empty0 + 8 * s, 1);
     }
-    ptx::mbar_init(tfull, 1);
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(tfull0 + 8 * b, 1);
+      ptx::mbar_init(tempty0 + 8 * b, 4);  // one arrival per epilogue warp
+    }
     ptx::fence_mbar_init();
   }
-  if (warp == 1) {
+  if (warp == kMmaWarp) {
     ptx::tmem_alloc(ptx::smem_u32(&tmem_base_s), p.tmem_cols);
     ptx::tmem_relinquish();
   }
@@ -71,118 +87,171 @@ __global__ void __launch_bounds__(kThreads) tc_gemm_kernel(const __grid_constant
   ptx::tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
-  if (warp == 0) {
-    // ===================== TMA producer (one thread) =====================
+  if (warp >= kFirstProducerWarp) {
+    // ===================== TMA producers (one thread per warp) =====================
+    // Issuing a tensor-map copy costs the issuing thread hundreds of cycles, so the smem stages
+    // are dealt round-robin to kProducers threads in different warps.  A stage is always served
+    // by the same thread (in iteration order), which keeps the parity waits unambiguous.
     if (lane == 0) {
-      ptx::tma_prefetch_desc(&p.mapA[cls]);
+      const int me = warp - kFirstProducerWarp;
+      ptx::tma_prefetch_desc(&p.mapA[0]);
       ptx::tma_prefetch_desc(&p.mapB);
-      const int ohw = p.OHW[cls], oww = p.OW[cls];
-      int it = 0;
-      if (p.kind == KIND_FWD) {
-        int w_base = 0, h_base = 0, n_img = 0;
-        if (p.a_im2col) {
-          n_img = m0 / ohw;
-          const int rem = m0 - n_img * ohw;
-          const int oh = rem / oww;
-          const int ow = rem - oh * oww;
-          w_base = ow * p.trav_stride + p.lower_w[cls];
-          h_base = oh * p.trav_stride + p.lower_h[cls];
-        }
-        const uint32_t tx = p.a_boxes * p.a_box_bytes + p.b_boxes * p.b_box_bytes;
-        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
-          const int s = it % p.stages;
-          const uint32_t ph = (it / p.stages) & 1;
-          if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { report_timeout(p, 101); break; }
-          const uint32_t a_dst = smem_base + s * stage_bytes;
-          const uint32_t b_dst = a_dst + p.a_stage_bytes;
-          const uint32_t full = full0 + 8 * s;
-          ptx::mbar_arrive_expect_tx(full, tx);
-          const int tap = kb / p.chunks_per_tap;
-          const int chunk = kb - tap * p.chunks_per_tap;
-          const int rp = tap / p.S, sp = tap - rp * p.S;
-          if (p.a_im2col)
-            ptx::tma_load_im2col_4d(a_dst, &p.mapA[cls], full, chunk * p.kc, w_base, h_base, n_img,
-                                    (uint16_t)sp, (uint16_t)rp);
-          else
-            ptx::tma_load_2d(a_dst, &p.mapA[0], full, kb * p.kc, m0);
-          const int wtap =
-              (p.r_base[cls] + p.r_step * rp) * p.S_w + p.s_base[cls] + p.s_step * sp;
-          if (!p.b_mn) {
-            ptx::tma_load_3d(b_dst, &p.mapB, full, chunk * p.kc, wtap, n0);
-          } else {
-            for (int i = 0; i < p.b_boxes; ++i)
-              ptx::tma_load_3d(b_dst + i * p.b_box_bytes, &p.mapB, full, n0 + i * p.b_box_w, wtap,
-                               chunk * p.kc);
-          }
-        }
-      } else {
-        const uint32_t tx = p.a_boxes * p.a_box_bytes + ntaps * p.b_boxes * p.b_box_bytes;
-        for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
-          const int s = it % p.stages;
-          const uint32_t ph = (it / p.stages) & 1;
-          if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { report_timeout(p, 102); break; }
-          const uint32_t a_dst = smem_base + s * stage_bytes;
-          const uint32_t b_dst = a_dst + p.a_stage_bytes;
-          const uint32_t full = full0 + 8 * s;
-          ptx::mbar_arrive_expect_tx(full, tx);
-          const int p0 = kb * p.kc;
-          for (int i = 0; i < p.a_boxes; ++i)
-            ptx::tma_load_2d(a_dst + i * p.a_box_bytes, &p.mapA[0], full, m0 + i * p.a_box_w, p0);
+      int st = 0;
+      uint32_t st_ph = 0;
+      bool ok = true;
+      for (int t = blockIdx.x; t < p.total_tiles && ok; t += gridDim.x) {
+        const Tile tl = decode_tile(p, t);
+        const int cls = tl.cls, m0 = tl.m0, n0 = tl.n0;
+        const int ohw = p.OHW[cls], oww = p.OW[cls];
+        if (p.kind == KIND_FWD) {
+          int w_base = 0, h_base = 0, n_img = 0;
           if (p.a_im2col) {
-            const int n_img = p0 / ohw;
-            const int rem = p0 - n_img * ohw;
+            n_img = m0 / ohw;
+            const int rem = m0 - n_img * ohw;
             const int oh = rem / oww;
             const int ow = rem - oh * oww;
-            const int w_base = ow * p.trav_stride + p.lower_w[0];
-            const int h_base = oh * p.trav_stride + p.lower_h[0];
-            for (int t = 0; t < ntaps; ++t) {
-              const int tap = tap0 + t;
-              const int rp = tap / p.S, sp = tap - rp * p.S;
+            w_base = ow * p.trav_stride_w + p.lower_w[cls];
+            h_base = oh * p.trav_stride_h + p.lower_h[cls];
+          }
+          const uint32_t tx = p.a_boxes * p.a_box_bytes + p.b_boxes * p.b_box_bytes;
+          int tap = tl.kb_begin / p.chunks_per_tap;
+          int chunk = tl.kb_begin - tap * p.chunks_per_tap;
+          int rp = tap / p.S, sp = tap - rp * p.S;
+          for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+            const int s = st;
+            const uint32_t ph = st_ph;
+            const int chunk_c = chunk, rp_c = rp, sp_c = sp;
+            if (++st == p.stages) { st = 0; st_ph ^= 1; }
+            if (++chunk == p.chunks_per_tap) { chunk = 0; if (++sp == p.S) { sp = 0; ++rp; } }
+            if (s % kProducers != me) continue;  // a stage always belongs to the same producer
+            if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { report_timeout(p, 101); ok = false; break; }
+            const uint32_t a_dst = smem_base + s * stage_bytes;
+            const uint32_t b_dst = a_dst + p.a_stage_bytes;
+            const uint32_t full = full0 + 8 * s;
+            if (p.debug & 1) { ptx::mbar_arrive(full); continue; }
+            ptx::mbar_arrive_expect_tx(full, tx);
+            if (p.a_im2col)
+              ptx::tma_load_im2col_4d(a_dst, &p.mapA[cls], full, chunk_c * p.kc, w_base, h_base,
+                                      n_img, (uint16_t)sp_c, (uint16_t)rp_c);
+            else
+              ptx::tma_load_2d(a_dst, &p.mapA[0], full, kb * p.kc, m0);
+            const int wtap =
+                (p.r_base[cls] + p.r_step * rp_c) * p.S_w + p.s_base[cls] + p.s_step * sp_c;
+            if (!p.b_mn) {
+              ptx::tma_load_3d(b_dst, &p.mapB, full, chunk_c * p.kc, wtap, n0);
+            } else {
               for (int i = 0; i < p.b_boxes; ++i)
-                ptx::tma_load_im2col_4d(b_dst + (t * p.b_boxes + i) * p.b_box_bytes, &p.mapB, full,
-                                        n0 + i * p.b_box_w, w_base, h_base, n_img, (uint16_t)sp,
-                                        (uint16_t)rp);
+                ptx::tma_load_3d(b_dst + i * p.b_box_bytes, &p.mapB, full, n0 + i * p.b_box_w,
+                                 wtap, chunk_c * p.kc);
             }
-          } else {
-            for (int i = 0; i < p.b_boxes; ++i)
-              ptx::tma_load_2d(b_dst + i * p.b_box_bytes, &p.mapB, full, n0 + i * p.b_box_w, p0);
+          }
+        } else {
+          const uint32_t tx = p.a_boxes * p.a_box_bytes + tl.ntaps * p.b_boxes * p.b_box_bytes;
+          for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+            const int s = st;
+            const uint32_t ph = st_ph;
+            if (++st == p.stages) { st = 0; st_ph ^= 1; }
+            if (s % kProducers != me) continue;  // a stage always belongs to the same producer
+            if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { report_timeout(p, 102); ok = false; break; }
+            const uint32_t a_dst = smem_base + s * stage_bytes;
+            const uint32_t b_dst = a_dst + p.a_stage_bytes;
+            const uint32_t full = full0 + 8 * s;
+            ptx::mbar_arrive_expect_tx(full, tx);
+            const int p0 = kb * p.kc;
+            for (int i = 0; i < p.a_boxes; ++i)
+              ptx::tma_load_2d(a_dst + i * p.a_box_bytes, &p.mapA[0], full, m0 + i * p.a_box_w, p0);
+            if (p.a_im2col) {
+              const int n_img = p0 / ohw;
+              const int rem = p0 - n_img * ohw;
+              const int oh = rem / oww;
+              const int ow = rem - oh * oww;
+              const int w_base = ow * p.trav_stride_w + p.lower_w[0];
+              const int h_base = oh * p.trav_stride_h + p.lower_h[0];
+              for (int tt = 0; tt < tl.ntaps; ++tt) {
+                const int tap = tl.tap0 + tt;
+                const int rp = tap / p.S, sp = tap - rp * p.S;
+                for (int i = 0; i < p.b_boxes; ++i)
+                  ptx::tma_load_im2col_4d(b_dst + (tt * p.b_boxes + i) * p.b_box_bytes, &p.mapB,
+                                          full, n0 + i * p.b_box_w, w_base, h_base, n_img,
+                                          (uint16_t)sp, (uint16_t)rp);
+              }
+            } else {
+              for (int i = 0; i < p.b_boxes; ++i)
+                ptx::tma_load_2d(b_dst + i * p.b_box_bytes, &p.mapB, full, n0 + i * p.b_box_w, p0);
+            }
           }
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     // ===================== MMA issuer (one thread) =====================
     if (lane == 0) {
-      int it = 0;
+      int it = 0, tcount = 0;
       bool ok = true;
-      for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
-        const int s = it % p.stages;
-        const uint32_t ph = (it / p.stages) & 1;
-        if (!ptx::mbar_wait(full0 + 8 * s, ph)) { report_timeout(p, 103); ok = false; break; }
+      const int mma_k = p.mma_k, mma_groups = p.mma_groups, g_taps = p.g_taps;
+      const uint32_t a_kstep = p.a_kstep, b_kstep = p.b_kstep, b_gstep = p.b_gstep, d_gstep = p.d_gstep;
+      const uint64_t desc_a_hi = p.desc_a_hi, desc_b_hi = p.desc_b_hi;
+      const uint32_t idesc = p.idesc, a_stage16 = p.a_stage_bytes >> 4;
+      const int stages = p.stages;
+      const bool dbg_skip = (p.debug & 2) != 0;
+      int s = 0;
+      uint32_t ph = 0;
+      long long pw = 0, pi = 0, pc = 0, pt = 0, pn = 0;
+      const bool prof = (p.debug & 4) != 0;
+      for (int t = blockIdx.x; t < p.total_tiles && ok; t += gridDim.x, ++tcount) {
+        const long long c0 = prof ? clock64() : 0;
+        const Tile tl = decode_tile(p, t);
+        const int buf = (p.acc_bufs == 2) ? (tcount & 1) : 0;
+        const int use = (p.acc_bufs == 2) ? (tcount >> 1) : tcount;
+        // the epilogue must have drained this accumulator buffer
+        if (!ptx::mbar_wait(tempty0 + 8 * buf, (use & 1) ^ 1)) { report_timeout(p, 105); break; }
         ptx::tc_fence_after();
-        const uint32_t a_base = (smem_base + s * stage_bytes) >> 4;
-        const uint32_t b_base = a_base + (p.a_stage_bytes >> 4);
-        for (int j = 0; j < p.n_mma; ++j) {
-          if (p.mma_acc[j] >= ntaps) continue;
-          const uint64_t a_desc = p.desc_a_hi | (uint64_t)((a_base + p.mma_a_off[j]) & 0x3FFFu);
-          const uint64_t b_desc = p.desc_b_hi | (uint64_t)((b_base + p.mma_b_off[j]) & 0x3FFFu);
-          const uint32_t accumulate = (it > 0 || !p.mma_first[j]) ? 1u : 0u;
-          ptx::umma_bf16(tmem_base + p.mma_dcol[j], a_desc, b_desc, p.idesc, accumulate);
+        if (prof) pt += clock64() - c0;
+        const uint32_t d_base = tmem_base + buf * p.acc_stride;
+        for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb, ++it) {
+          const long long c1 = prof ? clock64() : 0;
+          if (!ptx::mbar_wait(full0 + 8 * s, ph)) { report_timeout(p, 103); ok = false; break; }
+          ptx::tc_fence_after();
+          const long long c2 = prof ? clock64() : 0;
+          const uint32_t a_base = (smem_base + s * stage_bytes) >> 4;
+          const uint32_t b_base = a_base + a_stage16;
+          for (int g = 0; g < mma_groups; ++g) {
+            if (g * g_taps >= tl.ntaps) break;
+            const uint32_t ag = a_base, bg = b_base + g * b_gstep, dg = d_base + g * d_gstep;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (j < mma_k) {
+                const uint64_t a_desc = desc_a_hi | (uint64_t)((ag + j * a_kstep) & 0x3FFFu);
+                const uint64_t b_desc = desc_b_hi | (uint64_t)((bg + j * b_kstep) & 0x3FFFu);
+                const uint32_t accumulate = (kb > tl.kb_begin || j > 0) ? 1u : 0u;
+                if (!dbg_skip) ptx::umma_bf16(dg, a_desc, b_desc, idesc, accumulate);
+              }
+            }
+          }
+          const long long c3 = prof ? clock64() : 0;
+          ptx::umma_commit(empty0 + 8 * s);
+          if (prof) { const long long c4 = clock64(); pw += c2 - c1; pi += c3 - c2; pc += c4 - c3; ++pn; }
+          if (++s == stages) { s = 0; ph ^= 1; }
         }
-        ptx::umma_commit(empty0 + 8 * s);
+        if (ok) ptx::umma_commit(tfull0 + 8 * buf);
       }
-      if (ok) ptx::umma_commit(tfull);
+      if (prof) {
+        atomicAdd(&g_prof[0], (unsigned long long)pw); atomicAdd(&g_prof[1], (unsigned long long)pi);
+        atomicAdd(&g_prof[2], (unsigned long long)pc); atomicAdd(&g_prof[3], (unsigned long long)pt);
+        atomicAdd(&g_prof[4], (unsigned long long)pn);
+      }
     }
   } else {
     // ===================== epilogue (4 warps, one TMEM lane quarter each) =====================
     const int q = warp & 3;
-    const int row = m0 + q * 32 + lane;
-    const bool row_ok = row < M_total;
-    bool ok = ptx::mbar_wait(tfull, 0);
-    if (!ok) report_timeout(p, 104);
-    ok = __all_sync(0xffffffffu, ok);
-    if (ok) {
-      ptx::tc_fence_after();
+    int tcount = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tcount) {
+      const Tile tl = decode_tile(p, t);
+      const int cls = tl.cls, n0 = tl.n0;
+      const int buf = (p.acc_bufs == 2) ? (tcount & 1) : 0;
+      const int use = (p.acc_bufs == 2) ? (tcount >> 1) : tcount;
+      const int row = tl.m0 + q * 32 + lane;
+      const bool row_ok = row < p.M_total[cls];
       long long orow = row;
       if (p.remap && row_ok) {
         const int hw = p.Hs[cls] * p.Ws[cls];
@@ -190,95 +259,136 @@ __global__ void __launch_bounds__(kThreads) tc_gemm_kernel(const __grid_constant
         const int rem = row - n * hw;
         const int jh = rem / p.Ws[cls];
         const int jw = rem - jh * p.Ws[cls];
-        orow = ((long long)n * p.OHf + (2 * jh + p.ah[cls])) * p.OWf + (2 * jw + p.aw[cls]);
+        orow = ((long long)n * p.OHf + (jh * p.remap_sh + p.ah[cls])) * p.OWf +
+               (jw * p.remap_sw + p.aw[cls]);
+      }
+      bool zero_row = false;
+      if (p.border_h > 0 && row_ok) {
+        const int hw = p.border_h * p.border_w;
+        const int rem = row % hw;
+        const int y = rem / p.border_w;
+        const int x = rem - y * p.border_w;
+        zero_row = (y == 0) || (y == p.border_h - 1) || (x == 0) || (x == p.border_w - 1);
       }
       const float rmask = (p.rowmask && row_ok) ? p.rowmask[orow] : 1.0f;
-      for (int a = 0; a < ntaps; ++a) {
-        for (int c = 0; c < p.block_n; c += 32) {
-          uint32_t v[32];
-          ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + a * p.block_n + c, v);
-          ptx::tmem_ld_wait();
-          const int col0 = n0 + c;
-          if (!row_ok || col0 >= p.N_total) continue;
-          float f[32];
+      const long long off0 = orow * p.ldo + n0;
+      bool ok = ptx::mbar_wait(tfull0 + 8 * buf, use & 1);
+      if (!ok) report_timeout(p, 104);
+      ok = __all_sync(0xffffffffu, ok);
+      if (!ok) break;
+      ptx::tc_fence_after();
+      const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + buf * p.acc_stride;
+      for (int a = 0; a < tl.ntaps; ++a) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-          if (p.out_mode == OUT_BF16) {
-            const long long off = orow * p.ldo + col0;
-            if (p.bias) {
-              const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
+        for (int ci = 0; ci < 4; ++ci) {
+          const int c = ci * 32;
+          if (c < p.block_n) {
+            uint32_t v[32];
+            uint4 gpre[4], rpre[4];
+            if (p.out_mode == OUT_BF16 && row_ok) {  // issued before the TMEM load: latencies overlap
+              if (p.gate) {
+                const uint4* g4 = reinterpret_cast<const uint4*>(p.gate + off0 + c);
 #pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                const float4 b = __ldg(b4 + i);
-                f[4 * i + 0] += b.x; f[4 * i + 1] += b.y; f[4 * i + 2] += b.z; f[4 * i + 3] += b.w;
+                for (int i = 0; i < 4; ++i) gpre[i] = __ldg(g4 + i);
+              }
+              if (p.resid) {
+                const uint4* r4 = reinterpret_cast<const uint4*>(p.resid + off0 + c);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) rpre[i] = __ldg(r4 + i);
               }
             }
-            if (p.resid) {
-              const uint4* r4 = reinterpret_cast<const uint4*>(p.resid + off);
+            __syncwarp();
+            ptx::tmem_ld_32x32(t_lane + a * p.block_n + c, v);
+            ptx::tmem_ld_wait();
+            const int col0 = n0 + c;
+            if (row_ok && col0 < p.N_total) {
+              float f[32];
 #pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint4 r = __ldg(r4 + i);
-                f[8 * i + 0] += bf16lo(r.x); f[8 * i + 1] += bf16hi(r.x);
-                f[8 * i + 2] += bf16lo(r.y); f[8 * i + 3] += bf16hi(r.y);
-                f[8 * i + 4] += bf16lo(r.z); f[8 * i + 5] += bf16hi(r.z);
-                f[8 * i + 6] += bf16lo(r.w); f[8 * i + 7] += bf16hi(r.w);
+              for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
+              if (p.out_mode == OUT_BF16) {
+                const long long off = off0 + c;
+                if (p.bias) {
+                  const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) {
+                    const float4 b = __ldg(b4 + i);
+                    f[4 * i + 0] += b.x; f[4 * i + 1] += b.y; f[4 * i + 2] += b.z; f[4 * i + 3] += b.w;
+                  }
+                }
+                if (p.resid) {
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    const uint4 r = rpre[i];
+                    f[8 * i + 0] += bf16lo(r.x); f[8 * i + 1] += bf16hi(r.x);
+                    f[8 * i + 2] += bf16lo(r.y); f[8 * i + 3] += bf16hi(r.y);
+                    f[8 * i + 4] += bf16lo(r.z); f[8 * i + 5] += bf16hi(r.z);
+                    f[8 * i + 6] += bf16lo(r.w); f[8 * i + 7] += bf16hi(r.w);
+                  }
+                }
+                if (p.relu) {
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.0f);
+                }
+                if (p.gate) {
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    const uint4 g = gpre[i];
+                    f[8 * i + 0] = bf16lo(g.x) > 0.f ? f[8 * i + 0] : 0.f;
+                    f[8 * i + 1] = bf16hi(g.x) > 0.f ? f[8 * i + 1] : 0.f;
+                    f[8 * i + 2] = bf16lo(g.y) > 0.f ? f[8 * i + 2] : 0.f;
+                    f[8 * i + 3] = bf16hi(g.y) > 0.f ? f[8 * i + 3] : 0.f;
+                    f[8 * i + 4] = bf16lo(g.z) > 0.f ? f[8 * i + 4] : 0.f;
+                    f[8 * i + 5] = bf16hi(g.z) > 0.f ? f[8 * i + 5] : 0.f;
+                    f[8 * i + 6] = bf16lo(g.w) > 0.f ? f[8 * i + 6] : 0.f;
+                    f[8 * i + 7] = bf16hi(g.w) > 0.f ? f[8 * i + 7] : 0.f;
+                  }
+                }
+                if (p.rowmask) {
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) f[i] *= rmask;
+                }
+                if (zero_row) {
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) f[i] = 0.f;
+                }
+                uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + off);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  uint4 o;
+                  o.x = pack_bf16x2(f[8 * i + 0], f[8 * i + 1]);
+                  o.y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
+                  o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]);
+                  o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
+                  o4[i] = o;
+                }
+              } else {
+                float* o = reinterpret_cast<float*>(p.out) + orow * p.ldo +
+                           (long long)(tl.tap0 + a) * p.tap_stride + col0;
+                if (p.out_mode == OUT_F32_STORE) {
+                  float4* o4 = reinterpret_cast<float4*>(o);
+#pragma unroll
+                  for (int i = 0; i < 8; ++i)
+                    o4[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                } else {
+#pragma unroll
+                  for (int i = 0; i < 8; ++i)
+                    ptx::red_add_v4_f32(o + 4 * i, f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                }
               }
-            }
-            if (p.relu) {
-#pragma unroll
-              for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.0f);
-            }
-            if (p.gate) {
-              const uint4* g4 = reinterpret_cast<const uint4*>(p.gate + off);
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const uint4 g = __ldg(g4 + i);
-                f[8 * i + 0] = bf16lo(g.x) > 0.f ? f[8 * i + 0] : 0.f;
-                f[8 * i + 1] = bf16hi(g.x) > 0.f ? f[8 * i + 1] : 0.f;
-                f[8 * i + 2] = bf16lo(g.y) > 0.f ? f[8 * i + 2] : 0.f;
-                f[8 * i + 3] = bf16hi(g.y) > 0.f ? f[8 * i + 3] : 0.f;
-                f[8 * i + 4] = bf16lo(g.z) > 0.f ? f[8 * i + 4] : 0.f;
-                f[8 * i + 5] = bf16hi(g.z) > 0.f ? f[8 * i + 5] : 0.f;
-                f[8 * i + 6] = bf16lo(g.w) > 0.f ? f[8 * i + 6] : 0.f;
-                f[8 * i + 7] = bf16hi(g.w) > 0.f ? f[8 * i + 7] : 0.f;
-              }
-            }
-            if (p.rowmask) {
-#pragma unroll
-              for (int i = 0; i < 32; ++i) f[i] *= rmask;
-            }
-            uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + off);
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              uint4 o;
-              o.x = pack_bf16x2(f[8 * i + 0], f[8 * i + 1]);
-              o.y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
-              o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]);
-              o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
-              o4[i] = o;
-            }
-          } else {
-            float* o = reinterpret_cast<float*>(p.out) + orow * p.ldo +
-                       (long long)(tap0 + a) * p.tap_stride + col0;
-            if (p.out_mode == OUT_F32_STORE) {
-              float4* o4 = reinterpret_cast<float4*>(o);
-#pragma unroll
-              for (int i = 0; i < 8; ++i)
-                o4[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
-            } else {
-#pragma unroll
-              for (int i = 0; i < 8; ++i)
-                ptx::red_add_v4_f32(o + 4 * i, f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
             }
           }
         }
       }
+      // accumulator buffer drained: hand it back to the MMA issuer
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(tempty0 + 8 * buf);
     }
   }
 
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 1) ptx::tmem_dealloc(tmem_base, p.tmem_cols);
+  if (warp == kMmaWarp) ptx::tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -286,16 +396,25 @@ __global__ void __launch_bounds__(kThreads) tc_gemm_kernel(const __grid_constant
 // ---------------------------------------------------------------------------------------------
 static std::once_flag g_attr_once;
 
-int launch(const Params& p, dim3 grid, size_t smem_bytes, cudaStream_t stream) {
+int launch(const Params& p, int num_sms, size_t smem_bytes, cudaStream_t stream) {
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(g_attr_once, [] {
     attr_err = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     227 * 1024 - 256);
   });
   if (attr_err != cudaSuccess) return gabril_set_cuda_error(attr_err);
+  if (p.total_tiles <= 0) return GABRIL_OK;
+  // one persistent CTA per SM (smem / TMEM are sized for single occupancy)
+  const unsigned grid = (unsigned)std::min(p.total_tiles, num_sms);
   tc_gemm_kernel<<<grid, kThreads, smem_bytes, stream>>>(p);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
 }
 
 }  // namespace tc
+
+extern "C" int gabril_tc_prof(unsigned long long* out8, int reset) {
+  if (cudaMemcpyFromSymbol(out8, tc::g_prof, 8 * sizeof(unsigned long long)) != cudaSuccess) return -1;
+  if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(tc::g_prof, z, sizeof(z)); }
+  return 0;
+}

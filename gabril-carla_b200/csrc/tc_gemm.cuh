@@ -7,8 +7,8 @@
 //              (forward conv, dgrad as a conv over dY, linear)     B K-major or MN-major weight tile
 //   KIND_WGRAD D[Cout, Cin]    = dY[pixels, Cout]^T * X[pixels, Cin]   both MN-major, contraction
 //              (one accumulator per filter tap, several per CTA)       over pixels, split over CTAs
-// Warp roles (192 threads): warp0 = TMA producer, warp1 = TMEM owner + single-thread MMA issuer,
-// warps2..5 = epilogue (tcgen05.ld -> fused bias/residual/ReLU/gate/mask -> global).
+// Warp roles (256 threads): warp0 = TMEM owner + single-thread MMA issuer, warps1..4 = epilogue,
+// warps5..7 = TMA producers (tcgen05.ld -> fused bias/residual/ReLU/gate/mask -> global).
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -18,8 +18,11 @@
 namespace tc {
 
 constexpr int kMaxStages = 8;
-constexpr int kMaxMma = 32;
-constexpr int kThreads = 192;
+constexpr int kProducers = 3;          // TMA-issuing warps
+constexpr int kMmaWarp = 0;            // TMEM owner + single-thread MMA issuer
+constexpr int kFirstEpilogueWarp = 1;  // 4 epilogue warps (TMEM lane quarter = warp % 4)
+constexpr int kFirstProducerWarp = 5;
+constexpr int kThreads = 32 * (kFirstProducerWarp + kProducers);
 
 enum Kind { KIND_FWD = 0, KIND_WGRAD = 1 };
 enum OutMode { OUT_BF16 = 0, OUT_F32_STORE = 1, OUT_F32_ATOMIC = 2 };
@@ -45,18 +48,17 @@ struct Params {
   int a_box_w, b_box_w;  // elements one box covers along the MN dimension
   // im2col traversal geometry (per parity class)
   int OW[4], OHW[4], lower_w[4], lower_h[4];
-  int trav_stride;
+  int trav_stride_w, trav_stride_h;
   int S;  // traversal filter width: tap -> (r', s') = (tap / S, tap % S)
   int chunks_per_tap;
   // weight tap mapping r = r_base + r_step*r', s = s_base + s_step*s', wtap = r*S_w + s
   int r_base[4], s_base[4], r_step, s_step, S_w;
   // MMA schedule of one k-block
-  int n_mma;
-  uint16_t mma_a_off[kMaxMma];  // byte offset >> 4 from the stage's A base
-  uint16_t mma_b_off[kMaxMma];  // byte offset >> 4 from the stage's B base
-  uint16_t mma_dcol[kMaxMma];   // TMEM column of the accumulator
-  uint8_t mma_acc[kMaxMma];     // accumulator index
-  uint8_t mma_first[kMaxMma];   // first MMA of its accumulator inside the k-block
+  // MMA schedule of one k-block: mma_groups accumulator groups x mma_k K-steps of 16.
+  //   A start = stage A base + j*a_kstep;  B start = stage B base + g*b_gstep + j*b_kstep
+  //   (16-byte units);  accumulator column = g*d_gstep;  group g covers taps [g*g_taps, ...)
+  int mma_k, mma_groups, g_taps;
+  uint32_t a_kstep, b_kstep, b_gstep, d_gstep;
   uint64_t desc_a_hi, desc_b_hi;  // smem descriptors with the start-address field zero
   uint32_t idesc;
   uint32_t tmem_cols;
@@ -69,13 +71,22 @@ struct Params {
   const __nv_bfloat16* gate;    // out = gate > 0 ? out : 0 (ReLU backward), or null
   const float* rowmask;         // per output row multiplier (GMD mask), or null
   int relu;
-  int remap;  // strided-dgrad: tile row -> (n, 2*jh+ah, 2*jw+aw) of the full-resolution grid
+  // remap: tile row (n, jh, jw) over the Hs x Ws grid of its class -> row
+  //        (n*OHf + jh*remap_sh + ah)*OWf + jw*remap_sw + aw of the output tensor
+  //        (strided-dgrad parity classes; writes into the interior of a pre-padded tensor)
+  int remap, remap_sh, remap_sw;
   int Hs[4], Ws[4], ah[4], aw[4], OHf, OWf;
+  // border_h/w > 0: rows are pixels of a border_h x border_w padded grid; border pixels store 0
+  int border_h, border_w;
+  // persistent tile schedule: tile -> (m tile [classes concatenated], n tile, split)
+  int tiles_m[4], tiles_m_total, n_tiles, n_splits, total_tiles;
+  int acc_bufs, acc_stride;  // TMEM accumulator ring (1 or 2 buffers of acc_stride columns)
   long long tap_stride;  // WGRAD: element (m, tap, n) at out + m*ldo + tap*tap_stride + n
   int* err_flag;
+  int debug;  // perf experiments only: bit0 = producer skips the TMA copies, bit1 = issuer skips the MMAs
 };
 
 // Fills the launch geometry and launches; returns a negative gabril status on failure.
-int launch(const Params& p, dim3 grid, size_t smem_bytes, cudaStream_t stream);
+int launch(const Params& p, int num_sms, size_t smem_bytes, cudaStream_t stream);
 
 }  // namespace tc

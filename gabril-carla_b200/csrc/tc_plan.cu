@@ -5,6 +5,7 @@
 // weight gradients are fp32 in the same [Cout][R*S][Cin] order.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -142,17 +143,44 @@ bool mn_ok(int c) { return c == 32 || c == 64 || (c >= 128 && c % 128 == 0); }
 // Output-column counts of the K-major forward: a multiple of 32 up to 128, or a multiple of 128.
 bool fwd_cout_ok(int c) { return c % 32 == 0 && (c <= 128 || c % 128 == 0); }
 
-void zero_params(tc::Params& p) { memset(&p, 0, sizeof(p)); }
+void zero_params(tc::Params& p) {
+  memset(&p, 0, sizeof(p));
+  static int dbg = -1;
+  if (dbg < 0) { const char* e = getenv("GABRIL_TC_DEBUG"); dbg = e ? atoi(e) : 0; }
+  p.debug = dbg;
+}
 
-void pick_stages(tc::Params& p, int kb_per_cta, size_t* smem_bytes) {
+// Persistent single-occupancy CTA: the stage ring takes what shared memory allows (ring runs
+// across tiles, so even one-k-block tiles benefit from depth).
+int g_occ = 0;  // CTAs per SM the FWD-regime launches are sized for (GABRIL_TC_OCC, default 2)
+int occ_setting() {
+  if (!g_occ) {
+    const char* e = getenv("GABRIL_TC_OCC");
+    g_occ = (e && atoi(e) == 1) ? 1 : 2;
+  }
+  return g_occ;
+}
+
+void pick_stages(tc::Params& p, size_t* smem_bytes, int occ) {
   const uint32_t stage = p.a_stage_bytes + p.b_stage_bytes;
-  // keep two CTAs per SM resident when the tiles are small enough (epilogue/mainloop overlap)
-  const uint32_t budget = (p.tmem_cols <= 256 && stage * 3 <= 100 * 1024) ? 100 * 1024 : 200 * 1024;
-  int st = (int)(budget / stage);
+  int st = (int)(((occ == 2 ? 104u : 208u) * 1024u) / stage);
   st = std::max(2, std::min(st, tc::kMaxStages));
-  st = std::min(st, std::max(2, kb_per_cta));
   p.stages = st;
   *smem_bytes = (size_t)st * stage + 1024;
+}
+
+// Tile schedule + TMEM accumulator ring.  m_tiles[c] = 128-row tiles of class c; n_tiles_y = n
+// tiles (x tap groups for WGRAD); splits = split-K factor.
+void finalize_schedule(tc::Params& p, const int* m_tiles, int n_tiles_y, int splits, int acc_cols,
+                       int occ) {
+  p.tiles_m_total = 0;
+  for (int c = 0; c < p.n_classes; ++c) { p.tiles_m[c] = m_tiles[c]; p.tiles_m_total += m_tiles[c]; }
+  p.n_tiles = n_tiles_y;
+  p.n_splits = splits;
+  p.total_tiles = p.tiles_m_total * n_tiles_y * splits;
+  p.acc_stride = (int)pow2_cols((uint32_t)acc_cols);
+  p.acc_bufs = (p.acc_stride * 2 <= 512 / occ) ? 2 : 1;
+  p.tmem_cols = (uint32_t)(p.acc_stride * p.acc_bufs);
 }
 
 struct ActDims { int N, H, W, C; };
@@ -182,17 +210,14 @@ void fwd_schedule(tc::Params& p, int kc, int block_n, int b_mn) {
     p.desc_b_hi = desc_hi(p.b_box_bytes, 8 * b_sw, layout_type_for_bytes(b_sw));
   }
   p.b_stage_bytes = round_up(p.b_boxes * p.b_box_bytes, 1024);
-  p.n_mma = kc / 16;
-  for (int j = 0; j < p.n_mma; ++j) {
-    p.mma_a_off[j] = (uint16_t)((j * 32) >> 4);
-    p.mma_b_off[j] =
-        (uint16_t)((b_mn ? j * 16 * (std::min(64, block_n) * 2) : j * 32) >> 4);
-    p.mma_dcol[j] = 0;
-    p.mma_acc[j] = 0;
-    p.mma_first[j] = (j == 0);
-  }
+  p.mma_k = kc / 16;
+  p.mma_groups = 1;
+  p.g_taps = 1;
+  p.a_kstep = 32 >> 4;
+  p.b_kstep = (uint32_t)((b_mn ? 16 * (std::min(64, block_n) * 2) : 32) >> 4);
+  p.b_gstep = 0;
+  p.d_gstep = 0;
   p.idesc = make_idesc(0, b_mn, 128, block_n);
-  p.tmem_cols = pow2_cols(block_n);
 }
 
 int weight_map(CUtensorMap* m, const void* w, int Cout, int T, int Cin, int b_mn, int kc,
@@ -258,7 +283,7 @@ int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void*
   p.kb_per_split = (p.kb_total + splits - 1) / splits;
   splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
   p.OW[0] = OW; p.OHW[0] = OH * OW; p.lower_w[0] = -pad; p.lower_h[0] = -pad;
-  p.trav_stride = stride;
+  p.trav_stride_w = stride; p.trav_stride_h = stride;
   p.r_base[0] = 0; p.s_base[0] = 0; p.r_step = 1; p.s_step = 1; p.S_w = S;
   if (plain) {
     uint64_t dims[2] = {(uint64_t)Cin, (uint64_t)M};
@@ -278,9 +303,11 @@ int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void*
   p.relu = relu;
   p.err_flag = g_err_flag;
   size_t smem;
-  pick_stages(p, p.kb_per_split, &smem);
-  dim3 grid((unsigned)((M + 127) / 128), (unsigned)(Cout / block_n), (unsigned)splits);
-  return tc::launch(p, grid, smem, stream);
+  const int occ = occ_setting();
+  pick_stages(p, &smem, occ);
+  const int mt[1] = {(int)((M + 127) / 128)};
+  finalize_schedule(p, mt, Cout / block_n, splits, block_n, occ);
+  return tc::launch(p, g_num_sms * occ, smem, stream);
 }
 
 // dx[N,H,W,Cin] = gate( conv_transpose(dy[N,OH,OW,Cout], w[Cout][R*S][Cin]) + addend )
@@ -302,10 +329,9 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
   fwd_schedule(p, kc, block_n, 1);
   p.N_total = Cin;
   p.chunks_per_tap = Cout / kc;
-  p.trav_stride = 1;
+  p.trav_stride_w = 1; p.trav_stride_h = 1;
   p.S_w = S;
   const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
-  unsigned grid_x = 0;
   if (stride == 1) {
     p.n_classes = 1;
     p.a_im2col = plain ? 0 : 1;
@@ -326,24 +352,21 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
                       128, 1);
     }
     if (rc) return rc;
-    grid_x = (unsigned)((M + 127) / 128);
   } else if (stride == 2 && R == 4 && S == 4 && pad == 1) {
     // Input pixel (ih, iw) of parity (a_h, a_w) receives exactly 2x2 taps: kh = 3 - a_h - 2 r',
     // read from dy row j_h - 1 + a_h + r'  (j_h = ih / 2).  Four stride-1 sub-convolutions.
     p.n_classes = 4;
     p.a_im2col = 1;
-    p.remap = 1;
+    p.remap = 1; p.remap_sh = 2; p.remap_sw = 2;
     p.OHf = H; p.OWf = W;
     p.taps = 4;
     p.S = 2;
     p.r_step = -2; p.s_step = -2;
-    int max_m = 0;
     for (int c = 0; c < 4; ++c) {
       const int ah = c >> 1, aw = c & 1;
       const int Hs = (H - ah + 1) / 2, Ws = (W - aw + 1) / 2;
       p.ah[c] = ah; p.aw[c] = aw; p.Hs[c] = Hs; p.Ws[c] = Ws;
       p.M_total[c] = N * Hs * Ws;
-      max_m = std::max(max_m, p.M_total[c]);
       p.OW[c] = Ws; p.OHW[c] = Hs * Ws;
       p.lower_w[c] = aw - 1; p.lower_h[c] = ah - 1;
       p.r_base[c] = 3 - ah; p.s_base[c] = 3 - aw;
@@ -352,7 +375,6 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
                       upper_h, kc, 128, 1);
       if (rc) return rc;
     }
-    grid_x = (unsigned)((max_m + 127) / 128);
   } else {
     return GABRIL_ERR_BAD_SHAPE;
   }
@@ -366,9 +388,12 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
   p.relu = 0;
   p.err_flag = g_err_flag;
   size_t smem;
-  pick_stages(p, p.kb_total, &smem);
-  dim3 grid(grid_x, (unsigned)(Cin / block_n), (unsigned)p.n_classes);
-  return tc::launch(p, grid, smem, stream);
+  const int occ = occ_setting();
+  pick_stages(p, &smem, occ);
+  int mt[4] = {0, 0, 0, 0};
+  for (int c = 0; c < p.n_classes; ++c) mt[c] = (p.M_total[c] + 127) / 128;
+  finalize_schedule(p, mt, Cin / block_n, 1, block_n, occ);
+  return tc::launch(p, g_num_sms * occ, smem, stream);
 }
 
 // dw[Cout][R*S][Cin] (fp32) += sum_pixels dy[p, Cout]^T * im2col(x)[p, (tap, Cin)].
@@ -414,29 +439,24 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
   // whole number of swizzle atoms, so N = G * block_n (<= 256) is a single instruction.
   const int G = std::max(1, std::min(n_acc, 256 / block_n));
   if (n_acc > G) n_acc = n_acc / G * G;
-  n_acc = std::min(n_acc, G * (tc::kMaxMma / (KP / 16)));
   p.n_acc = n_acc;
   p.taps = T;
   p.tap_groups = (T + n_acc - 1) / n_acc;
   p.S = S;
   p.b_stage_bytes = round_up(n_acc * b_tap_bytes, 1024);
-  p.n_mma = 0;
-  for (int t = 0; t < n_acc; t += G)
-    for (int j = 0; j < KP / 16; ++j) {
-      const int i = p.n_mma++;
-      p.mma_a_off[i] = (uint16_t)((j * 16 * a_sw) >> 4);
-      p.mma_b_off[i] = (uint16_t)((t * b_tap_bytes + j * 16 * b_sw) >> 4);
-      p.mma_dcol[i] = (uint16_t)(t * block_n);
-      p.mma_acc[i] = (uint8_t)t;
-      p.mma_first[i] = (j == 0);
-    }
+  p.mma_k = KP / 16;
+  p.mma_groups = (n_acc + G - 1) / G;
+  p.g_taps = G;
+  p.a_kstep = (uint32_t)((16 * a_sw) >> 4);
+  p.b_kstep = (uint32_t)((16 * b_sw) >> 4);
+  p.b_gstep = (uint32_t)((G * b_tap_bytes) >> 4);
+  p.d_gstep = (uint32_t)(G * block_n);
   p.idesc = make_idesc(1, 1, 128, G * block_n);
-  p.tmem_cols = pow2_cols(n_acc * block_n);
   p.M_total[0] = Cout;
   p.N_total = Cin;
   p.kb_total = (int)((P + KP - 1) / KP);
   p.OW[0] = OW; p.OHW[0] = OH * OW; p.lower_w[0] = -pad; p.lower_h[0] = -pad;
-  p.trav_stride = stride;
+  p.trav_stride_w = stride; p.trav_stride_h = stride;
   {
     uint64_t dims[2] = {(uint64_t)Cout, (uint64_t)P};
     uint64_t strides[1] = {(uint64_t)Cout * 2};
@@ -468,9 +488,14 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
   p.tap_stride = Cin;
   p.err_flag = g_err_flag;
   size_t smem;
-  pick_stages(p, p.kb_per_split, &smem);
-  dim3 grid((unsigned)m_tiles, (unsigned)(n_tiles * p.tap_groups), (unsigned)splits);
-  return tc::launch(p, grid, smem, stream);
+  // every tile is its own CTA here (long split-K loops, up to 512 TMEM columns)
+  const int occ = (n_acc * block_n <= 256 && 2 * (p.a_stage_bytes + p.b_stage_bytes) <= 100 * 1024) ? 2 : 1;
+  pick_stages(p, &smem, occ);
+  const int mt[1] = {m_tiles};
+  finalize_schedule(p, mt, n_tiles * p.tap_groups, splits, n_acc * block_n, occ);
+  p.acc_bufs = 1;
+  p.tmem_cols = (uint32_t)p.acc_stride;
+  return tc::launch(p, 1 << 30, smem, stream);
 }
 
 }  // extern "C"
