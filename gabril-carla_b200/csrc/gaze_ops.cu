@@ -206,6 +206,115 @@ obs_patches_kernel(const uint8_t* __restrict__ frames, bf16* __restrict__ out, i
   }
 }
 
+// Tiled variant (even C0, W*3 a multiple of 16): one CTA = one sample x kPatchRows output rows.
+// Phase 1 copies the 2*kPatchRows+2 input rows of every stacked frame into shared memory with
+// 16-byte loads, phase 2 converts each input pixel ONCE (u8 -> /255 -> gray -> bf16) into a
+// zero-padded [row][x+1][C0] image, phase 3 emits the patch rows: the 4*C0 values of one
+// (pixel, filter row) are contiguous in that image, so they leave as 16-byte stores, four
+// consecutive threads filling one 64/128-byte patch row.
+constexpr int kPatchRows = 6;
+
+template <int S_, bool GRAY>
+__global__ void __launch_bounds__(256)
+obs_patches_tiled_kernel(const uint8_t* __restrict__ frames, bf16* __restrict__ out, int L,
+                         int center, int H, int W, int OH, int OW, int Kp) {
+  constexpr int CP = GRAY ? 1 : 3;
+  constexpr int C0 = S_ * CP;
+  constexpr int NR = 2 * kPatchRows + 2;
+  extern __shared__ __align__(16) uint8_t psm[];
+  const int row_bytes = W * 3;
+  const int img_row = (W + 2) * C0;  // bf16 elements
+  uint8_t* raw = psm;                                        // [NR][S_][row_bytes]
+  bf16* img = reinterpret_cast<bf16*>(psm + ((NR * S_ * row_bytes + 15) & ~15));  // [NR][img_row]
+  const int tiles = (OH + kPatchRows - 1) / kPatchRows;
+  const int b = blockIdx.x / tiles;
+  const int oh0 = (blockIdx.x - b * tiles) * kPatchRows;
+  const int ih0 = 2 * oh0 - 1;
+  __shared__ float lut[256];
+  lut[threadIdx.x & 255] = u8_to_unit(threadIdx.x & 255);
+  // ---- phase 1 ----
+  const int vec_per_row = row_bytes / 16;
+  for (int i = threadIdx.x; i < NR * S_ * vec_per_row; i += blockDim.x) {
+    const int v = i % vec_per_row;
+    const int rs = i / vec_per_row;
+    const int fs = rs % S_, r = rs / S_;
+    const int ih = ih0 + r;
+    if (ih >= 0 && ih < H) {
+      const int f = frame_index(fs, S_, center, L);
+      const uint4* src = reinterpret_cast<const uint4*>(
+          frames + (((long long)b * L + f) * H + ih) * (long long)row_bytes);
+      reinterpret_cast<uint4*>(raw + (size_t)rs * row_bytes)[v] = __ldg(src + v);
+    }
+  }
+  __syncthreads();
+  // ---- phase 2: four pixels per thread (12 raw bytes = three 32-bit words per frame); u8/255 comes
+  //      from a 256-entry table of the correctly rounded quotients (same bits as the division) ----
+  const int quads = W >> 2;
+  for (int i = threadIdx.x; i < NR * (quads + 1); i += blockDim.x) {
+    const int qd = i % (quads + 1);
+    const int r = i / (quads + 1);
+    bf16* drow = img + r * img_row;
+    if (qd == quads) {  // the two zero-padding columns x = -1 and x = W
+#pragma unroll
+      for (int c = 0; c < C0; ++c) { drow[c] = __float2bfloat16(0.f); drow[(W + 1) * C0 + c] = __float2bfloat16(0.f); }
+      continue;
+    }
+    const int ih = ih0 + r;
+    const bool ok = (ih >= 0) && (ih < H);
+    float px[4][C0];
+#pragma unroll
+    for (int fs = 0; fs < S_; ++fs) {
+      uint32_t wv[3] = {0u, 0u, 0u};
+      if (ok) {
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(raw + (size_t)(r * S_ + fs) * row_bytes) + 3 * qd;
+        wv[0] = src[0]; wv[1] = src[1]; wv[2] = src[2];
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float ch[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const int byte = 3 * k + c;
+          ch[c] = lut[(wv[byte >> 2] >> (8 * (byte & 3))) & 0xffu];
+        }
+        if (GRAY) {
+          px[k][fs] = ok ? to_gray(ch[0], ch[1], ch[2]) : 0.f;
+        } else {
+          px[k][fs * 3 + 0] = ok ? ch[0] : 0.f;
+          px[k][fs * 3 + 1] = ok ? ch[1] : 0.f;
+          px[k][fs * 3 + 2] = ok ? ch[2] : 0.f;
+        }
+      }
+    }
+    // 4 pixels x C0 bf16 = 2*C0 words, contiguous from column (4*qd + 1)
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(drow + (4 * qd + 1) * C0);
+    const float* pf = &px[0][0];
+#pragma unroll
+    for (int k = 0; k < 2 * C0; ++k) d32[k] = pack_bf16x2(pf[2 * k], pf[2 * k + 1]);
+  }
+  __syncthreads();
+  // ---- phase 3 ----
+  const int rows_here = min(kPatchRows, OH - oh0);
+  for (int i = threadIdx.x; i < rows_here * OW * 4; i += blockDim.x) {
+    const int r4 = i & 3;
+    const int pl = i >> 2;
+    const int ow = pl % OW;
+    const int ohl = pl / OW;
+    const long long pix = ((long long)b * OH + oh0 + ohl) * OW + ow;
+    const uint2* src = reinterpret_cast<const uint2*>(img + (2 * ohl + r4) * img_row + 2 * ow * C0);
+    uint4* dst = reinterpret_cast<uint4*>(out + pix * Kp + r4 * (4 * C0));
+#pragma unroll
+    for (int k = 0; k < C0 / 2; ++k) {
+      const uint2 lo = src[2 * k], hi = src[2 * k + 1];
+      dst[k] = make_uint4(lo.x, lo.y, hi.x, hi.y);
+    }
+    if (r4 == 3) {
+      uint4* z = reinterpret_cast<uint4*>(out + pix * Kp + 16 * C0);
+      for (int k = 0; k < (Kp - 16 * C0) / 8; ++k) z[k] = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+}
+
 // =================================================================================================
 // K6: gaze-mask dropout.  gmd_keep: K[b, j] = mean_s bicubic_down(g[b, s])[j] + batch-global
 // min / max (ordered-uint atomics).  gmd_mask: rowmask[b, j] = (A < 0.7 Khat + 0.3) or the keep
@@ -617,6 +726,31 @@ int gabril_obs_patches(const uint8_t* frames, void* patches, int B, int L, int S
   const long long total = (long long)B * OH * OW * 4;
   const int grid = grid_for(total, 256, 148 * 32);
   bf16* out = reinterpret_cast<bf16*>(patches);
+  if (C0 % 2 == 0 && (W * 3) % 16 == 0 && W % 4 == 0 && (Kp - 16 * C0) % 8 == 0) {
+    constexpr int NR = 2 * kPatchRows + 2;
+    const size_t smem = (size_t)((NR * S * W * 3 + 15) & ~15) + (size_t)NR * (W + 2) * C0 * 2;
+    const int tgrid = B * ((OH + kPatchRows - 1) / kPatchRows);
+    if (smem <= 160 * 1024) {
+#define GABRIL_TILED_CASE(SS, GG)                                                                  \
+  do {                                                                                             \
+    static bool attr_done = false;                                                                 \
+    if (!attr_done) {                                                                              \
+      cudaFuncSetAttribute(obs_patches_tiled_kernel<SS, GG>,                                       \
+                           cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);               \
+      attr_done = true;                                                                            \
+    }                                                                                              \
+    obs_patches_tiled_kernel<SS, GG><<<tgrid, 256, smem, stream>>>(frames, out, L, center, H, W,   \
+                                                                   OH, OW, Kp);                    \
+  } while (0)
+      if (grayscale && S == 2) GABRIL_TILED_CASE(2, true);
+      else if (grayscale && S == 4) GABRIL_TILED_CASE(4, true);
+      else if (!grayscale && S == 2) GABRIL_TILED_CASE(2, false);
+      else GABRIL_TILED_CASE(4, false);
+#undef GABRIL_TILED_CASE
+      GABRIL_CHECK_LAUNCH();
+      return GABRIL_OK;
+    }
+  }
 #define GABRIL_PATCH_CASE(SS, GG)                                                              \
   obs_patches_kernel<SS, GG><<<grid, 256, 0, stream>>>(frames, out, B, L, center, H, W, OH, OW, Kp)
   if (grayscale) {

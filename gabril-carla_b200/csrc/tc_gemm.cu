@@ -190,8 +190,11 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       bool ok = true;
       const int mma_k = p.mma_k, mma_groups = p.mma_groups, g_taps = p.g_taps;
       const uint32_t a_kstep = p.a_kstep, b_kstep = p.b_kstep, b_gstep = p.b_gstep, d_gstep = p.d_gstep;
-      const uint64_t desc_a_hi = p.desc_a_hi, desc_b_hi = p.desc_b_hi;
-      const uint32_t idesc = p.idesc, a_stage16 = p.a_stage_bytes >> 4;
+      const uint32_t a_hi32 = (uint32_t)(p.desc_a_hi >> 32), b_hi32 = (uint32_t)(p.desc_b_hi >> 32);
+      const uint32_t stage16 = stage_bytes >> 4;
+      const uint32_t a_lo_const = (uint32_t)p.desc_a_hi + (smem_base >> 4);
+      const uint32_t b_lo_const = (uint32_t)p.desc_b_hi + ((smem_base + p.a_stage_bytes) >> 4);
+      const uint32_t idesc = p.idesc;
       const int stages = p.stages;
       const bool dbg_skip = (p.debug & 2) != 0;
       int s = 0;
@@ -213,16 +216,18 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
           if (!ptx::mbar_wait(full0 + 8 * s, ph)) { report_timeout(p, 103); ok = false; break; }
           ptx::tc_fence_after();
           const long long c2 = prof ? clock64() : 0;
-          const uint32_t a_base = (smem_base + s * stage_bytes) >> 4;
-          const uint32_t b_base = a_base + a_stage16;
+          // descriptors differ only in their low word (14-bit address field; smem addresses >> 4
+          // stay below 2^14, so plain adds never carry into the LBO field)
+          const uint32_t a_lo = a_lo_const + (uint32_t)s * stage16;
+          const uint32_t b_lo = b_lo_const + (uint32_t)s * stage16;
           for (int g = 0; g < mma_groups; ++g) {
             if (g * g_taps >= tl.ntaps) break;
-            const uint32_t ag = a_base, bg = b_base + g * b_gstep, dg = d_base + g * d_gstep;
+            const uint32_t bg = b_lo + g * b_gstep, dg = d_base + g * d_gstep;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               if (j < mma_k) {
-                const uint64_t a_desc = desc_a_hi | (uint64_t)((ag + j * a_kstep) & 0x3FFFu);
-                const uint64_t b_desc = desc_b_hi | (uint64_t)((bg + j * b_kstep) & 0x3FFFu);
+                const uint64_t a_desc = ((uint64_t)a_hi32 << 32) | (uint64_t)(a_lo + j * a_kstep);
+                const uint64_t b_desc = ((uint64_t)b_hi32 << 32) | (uint64_t)(bg + j * b_kstep);
                 const uint32_t accumulate = (kb > tl.kb_begin || j > 0) ? 1u : 0u;
                 if (!dbg_skip) ptx::umma_bf16(dg, a_desc, b_desc, idesc, accumulate);
               }
@@ -272,6 +277,21 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       }
       const float rmask = (p.rowmask && row_ok) ? p.rowmask[orow] : 1.0f;
       const long long off0 = orow * p.ldo + n0;
+      // gate / residual operands of the first 32 columns are fetched BEFORE waiting for the MMAs:
+      // their global-memory latency hides behind the main loop of this tile
+      uint4 gpre[4], rpre[4];
+      if (p.out_mode == OUT_BF16 && row_ok) {
+        if (p.gate) {
+          const uint4* g4 = reinterpret_cast<const uint4*>(p.gate + off0);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) gpre[i] = __ldg(g4 + i);
+        }
+        if (p.resid) {
+          const uint4* r4 = reinterpret_cast<const uint4*>(p.resid + off0);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) rpre[i] = __ldg(r4 + i);
+        }
+      }
       bool ok = ptx::mbar_wait(tfull0 + 8 * buf, use & 1);
       if (!ok) report_timeout(p, 104);
       ok = __all_sync(0xffffffffu, ok);
@@ -284,8 +304,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
           const int c = ci * 32;
           if (c < p.block_n) {
             uint32_t v[32];
-            uint4 gpre[4], rpre[4];
-            if (p.out_mode == OUT_BF16 && row_ok) {  // issued before the TMEM load: latencies overlap
+            if (p.out_mode == OUT_BF16 && row_ok && (ci > 0 || a > 0)) {  // chunk 0 was fetched before the wait
               if (p.gate) {
                 const uint4* g4 = reinterpret_cast<const uint4*>(p.gate + off0 + c);
 #pragma unroll
