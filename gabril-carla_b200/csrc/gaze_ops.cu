@@ -419,23 +419,31 @@ struct RegArgs {
   int B, C, h, w, H, W;
 };
 
-template <bool NHWC_BF16, int MODE>
-__global__ void __launch_bounds__(1024) reg_kernel(const __grid_constant__ RegArgs a) {
-  extern __shared__ float sm[];
-  const int h = a.h, w = a.w, H = a.H, W = a.W, C = a.C, n = h * w;
-  float* p = sm;                                        // [n]
-  float* tmap = p + n;                                  // [h][W]
+// blockDim = Wr * YS (Wr = W rounded up to a warp multiple): thread (x, yq) owns output column x
+// and the row slab yq of YS.  Walking down a column the four source rows of the bicubic y-taps change
+// only every H/h rows, so their tmap values (and, in the backward pass, the four y-adjoint
+// accumulators) live in registers and shared memory is touched only when the tap window moves.
+template <bool NHWC_BF16, int MODE, int MAXT>
+__global__ void __launch_bounds__(MAXT, MAXT <= 704 ? 2 : 1) reg_kernel(const __grid_constant__ RegArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  const int h = a.h, w = a.w, H = a.H, W = a.W, C = a.C, n = h * w, n4 = (n + 3) & ~3;
+  float* p = sm;                                        // [n4]
+  float* tmap = p + n4;                                 // [h][W]
   float* sacc = tmap + h * W;                           // [h][W]
   float* wyt = sacc + h * W;                            // [H][4]
   int* iyt = reinterpret_cast<int*>(wyt + 4 * H);       // [H][4]
   float* wxt = reinterpret_cast<float*>(iyt + 4 * H);   // [W][4]
   int* ixt = reinterpret_cast<int*>(wxt + 4 * W);       // [W][4]
-  float* dp = reinterpret_cast<float*>(ixt + 4 * W);    // [n]
-  int* xrange = reinterpret_cast<int*>(dp + n);         // [w][2]
+  float* dp = reinterpret_cast<float*>(ixt + 4 * W);    // [n4]
+  int* xrange = reinterpret_cast<int*>(dp + n4);        // [w][2]
   __shared__ float scratch[32];
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarp = blockDim.x >> 5;
   const int b = blockIdx.x;
   const bool skip = (a.sel != nullptr) && (a.sel[b] <= 0.f);
+  const int Wr = (W + 31) & ~31, YS = blockDim.x / Wr;
+  const int x = tid % Wr, yq = tid / Wr;
+  const int Hq = (H + YS - 1) / YS;
+  const int ya = min(yq * Hq, H), yb = min(ya + Hq, H);
 
   const bf16* zb16 = reinterpret_cast<const bf16*>(a.z) + (long long)b * n * C;
   const float* zf32 = reinterpret_cast<const float*>(a.z) + (long long)b * n * C;
@@ -461,12 +469,13 @@ __global__ void __launch_bounds__(1024) reg_kernel(const __grid_constant__ RegAr
 #pragma unroll
     for (int k = 0; k < 4; ++k) { iyt[4 * y + k] = id[k]; wyt[4 * y + k] = wt[k]; }
   }
-  for (int x = tid; x < W; x += blockDim.x) {
+  for (int xx = tid; xx < W; xx += blockDim.x) {
     int id[4]; float wt[4];
-    bicubic_taps(x, sx, w, id, wt);
+    bicubic_taps(xx, sx, w, id, wt);
 #pragma unroll
-    for (int k = 0; k < 4; ++k) { ixt[4 * x + k] = id[k]; wxt[4 * x + k] = wt[k]; }
+    for (int k = 0; k < 4; ++k) { ixt[4 * xx + k] = id[k]; wxt[4 * xx + k] = wt[k]; }
   }
+  if (tid < w) { xrange[2 * tid] = W; xrange[2 * tid + 1] = -1; }
 
   // ---- s_j = sum_c |z| (fp32) ----
   if (NHWC_BF16) {
@@ -494,6 +503,15 @@ __global__ void __launch_bounds__(1024) reg_kernel(const __grid_constant__ RegAr
   }
   __syncthreads();
 
+  // source columns x' <- the contiguous range of output columns whose taps touch it
+  if (MODE != MODE_MASK_FWD && tid < W) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      atomicMin(&xrange[2 * ixt[4 * tid + k]], tid);
+      atomicMax(&xrange[2 * ixt[4 * tid + k] + 1], tid);
+    }
+  }
+
   // ---- softmax(s / beta) over the n positions ----
   float lmax = -FLT_MAX;
   for (int j = tid; j < n; j += blockDim.x) { const float v = __fdiv_rn(p[j], a.beta); p[j] = v; lmax = fmaxf(lmax, v); }
@@ -504,33 +522,39 @@ __global__ void __launch_bounds__(1024) reg_kernel(const __grid_constant__ RegAr
   for (int j = tid; j < n; j += blockDim.x) p[j] = __fdiv_rn(p[j], ssum);
   __syncthreads();
 
-  // ---- x interpolation of every source row: tmap[y'][x] ----
-  const int x = tid;
-  const bool col_ok = x < W;
+  // ---- x interpolation of every source row: tmap[y'][x] (rows dealt over the YS slabs) ----
+  const bool col_ok = x < W && yq < YS;
   if (col_ok) {
-    const int i0 = ixt[4 * x], i1 = ixt[4 * x + 1], i2 = ixt[4 * x + 2], i3 = ixt[4 * x + 3];
-    const float w0 = wxt[4 * x], w1 = wxt[4 * x + 1], w2 = wxt[4 * x + 2], w3 = wxt[4 * x + 3];
-    for (int yy = 0; yy < h; ++yy) {
+    const int4 ii = *reinterpret_cast<const int4*>(ixt + 4 * x);
+    const float4 ww = *reinterpret_cast<const float4*>(wxt + 4 * x);
+    for (int yy = yq; yy < h; yy += YS) {
       const float* pr = p + yy * w;
-      tmap[yy * W + x] = pr[i0] * w0 + pr[i1] * w1 + pr[i2] * w2 + pr[i3] * w3;
+      tmap[yy * W + x] = pr[ii.x] * ww.x + pr[ii.y] * ww.y + pr[ii.z] * ww.z + pr[ii.w] * ww.w;
       if (MODE != MODE_MASK_FWD) sacc[yy * W + x] = 0.f;
     }
   }
   __syncthreads();
 
-  auto u_at = [&](int y) {
-    const int* iy = iyt + 4 * y;
-    const float* wy = wyt + 4 * y;
-    return tmap[iy[0] * W + x] * wy[0] + tmap[iy[1] * W + x] * wy[1] + tmap[iy[2] * W + x] * wy[2] +
-           tmap[iy[3] * W + x] * wy[3];
+  const int4* iy4 = reinterpret_cast<const int4*>(iyt);
+  const float4* wy4 = reinterpret_cast<const float4*>(wyt);
+  // register window over the four source rows of the current y
+  int4 cur = make_int4(-1, -1, -1, -1);
+  float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
+  auto load_window = [&](const int4& id) {
+    cur = id;
+    t0 = tmap[id.x * W + x]; t1 = tmap[id.y * W + x]; t2 = tmap[id.z * W + x]; t3 = tmap[id.w * W + x];
   };
+  auto moved = [&](const int4& id) { return id.x != cur.x || id.w != cur.w; };
 
   // ---- pass 1: extrema (first occurrence wins ties, like torch's CPU max/min) ----
   float vmin = FLT_MAX, vmax = -FLT_MAX;
   int imin = 0x7fffffff, imax = 0x7fffffff;
   if (col_ok) {
-    for (int y = 0; y < H; ++y) {
-      const float u = u_at(y);
+    for (int y = ya; y < yb; ++y) {
+      const int4 id = iy4[y];
+      const float4 wv = wy4[y];
+      if (moved(id)) load_window(id);
+      const float u = t0 * wv.x + t1 * wv.y + t2 * wv.z + t3 * wv.w;
       if (u < vmin) { vmin = u; imin = y * W + x; }
       if (u > vmax) { vmax = u; imax = y * W + x; }
     }
@@ -565,19 +589,42 @@ __global__ void __launch_bounds__(1024) reg_kernel(const __grid_constant__ RegAr
   if (MODE == MODE_MASK_FWD) {
     if (col_ok) {
       float* mo = a.mask_out + (long long)b * H * W;
-      for (int y = 0; y < H; ++y) mo[y * W + x] = __fdiv_rn(__fsub_rn(u_at(y), mn), rng);
+      for (int y = ya; y < yb; ++y) {
+        const int4 id = iy4[y];
+        const float4 wv = wy4[y];
+        if (moved(id)) load_window(id);
+        const float u = t0 * wv.x + t1 * wv.y + t2 * wv.z + t3 * wv.w;
+        mo[y * W + x] = __fdiv_rn(__fsub_rn(u, mn), rng);  // reference-facing op: exact division
+      }
     }
     return;
   }
 
   // ---- pass 2: g2, loss, d(loss)/du accumulated through the y-adjoint into sacc ----
+  // (training path: the two divisions by rng are multiplications by 1/rng; 0/0 still gives NaN)
+  const float inv_rng = __fdiv_rn(1.f, rng);
   float sq = 0.f, E = 0.f, F = 0.f;
   if (col_ok) {
     const float* g1 = (MODE == MODE_MSE) ? a.g1 + (long long)b * a.g1_bstride : nullptr;
     const float* gi = (MODE == MODE_MASK_BWD) ? a.grad_in + (long long)b * H * W : nullptr;
-    for (int y = 0; y < H; ++y) {
-      const float u = u_at(y);
-      const float g2 = __fdiv_rn(__fsub_rn(u, mn), rng);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    auto flush = [&]() {
+      if (cur.x < 0) return;
+      if (YS == 1) {  // column-private
+        sacc[cur.x * W + x] += a0; sacc[cur.y * W + x] += a1; sacc[cur.z * W + x] += a2; sacc[cur.w * W + x] += a3;
+      } else {
+        atomicAdd(&sacc[cur.x * W + x], a0); atomicAdd(&sacc[cur.y * W + x], a1);
+        atomicAdd(&sacc[cur.z * W + x], a2); atomicAdd(&sacc[cur.w * W + x], a3);
+      }
+      a0 = a1 = a2 = a3 = 0.f;
+    };
+    cur = make_int4(-1, -1, -1, -1);
+    for (int y = ya; y < yb; ++y) {
+      const int4 id = iy4[y];
+      const float4 wv = wy4[y];
+      if (moved(id)) { flush(); load_window(id); }
+      const float u = t0 * wv.x + t1 * wv.y + t2 * wv.z + t3 * wv.w;
+      const float g2 = __fsub_rn(u, mn) * inv_rng;
       float e;
       if (MODE == MODE_MSE) {
         const float d = g2 - __ldg(g1 + y * W + x);
@@ -588,12 +635,10 @@ __global__ void __launch_bounds__(1024) reg_kernel(const __grid_constant__ RegAr
       }
       E += e;
       F = fmaf(e, g2, F);
-      const float du = e / rng;
-      const int* iy = iyt + 4 * y;
-      const float* wy = wyt + 4 * y;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) sacc[iy[k] * W + x] += wy[k] * du;  // column-private: no race
+      const float du = e * inv_rng;
+      a0 = fmaf(wv.x, du, a0); a1 = fmaf(wv.y, du, a1); a2 = fmaf(wv.z, du, a2); a3 = fmaf(wv.w, du, a3);
     }
+    flush();
   }
   const float Esum = block_sum(E, scratch);
   const float Fsum = block_sum(F, scratch);
@@ -606,18 +651,9 @@ __global__ void __launch_bounds__(1024) reg_kernel(const __grid_constant__ RegAr
     // max/min backward: the whole -sum term goes to the single arg index
     const int ymin = imin / W, xmin = imin - ymin * W;
     const int ymax = imax / W, xmax = imax - ymax * W;
-    const float dmin = -(Esum - Fsum) / rng, dmax = -Fsum / rng;
+    const float dmin = -(Esum - Fsum) * inv_rng, dmax = -Fsum * inv_rng;
     for (int k = 0; k < 4; ++k) sacc[iyt[4 * ymin + k] * W + xmin] += wyt[4 * ymin + k] * dmin;
     for (int k = 0; k < 4; ++k) sacc[iyt[4 * ymax + k] * W + xmax] += wyt[4 * ymax + k] * dmax;
-  }
-  // columns that feed each source column x' (contiguous range; verified tap by tap below)
-  if (tid < w) {
-    int lo = W, hi = -1;
-    for (int xx = 0; xx < W; ++xx)
-      for (int k = 0; k < 4; ++k)
-        if (ixt[4 * xx + k] == tid) { lo = min(lo, xx); hi = max(hi, xx); }
-    xrange[2 * tid] = lo;
-    xrange[2 * tid + 1] = hi;
   }
   __syncthreads();
   // ---- x-adjoint: dp[y'][x'] = sum_x sum_k [ix[x][k] == x'] wx[x][k] sacc[y'][x] ----
@@ -666,30 +702,38 @@ __global__ void __launch_bounds__(1024) reg_kernel(const __grid_constant__ RegAr
 }
 
 size_t reg_smem_bytes(int h, int w, int H, int W) {
-  const size_t n = (size_t)h * w;
-  return sizeof(float) * (n + 2 * (size_t)h * W + 8 * (size_t)H + 8 * (size_t)W + n + 2 * (size_t)w);
+  const size_t n4 = ((size_t)h * w + 3) & ~(size_t)3;
+  return sizeof(float) * (n4 + 2 * (size_t)h * W + 8 * (size_t)H + 8 * (size_t)W + n4 + 2 * (size_t)w);
+}
+
+template <bool NHWC, int MODE, int MAXT>
+int launch_reg_t(const RegArgs& a, int threads, size_t smem, cudaStream_t stream) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(reg_kernel<NHWC, MODE, MAXT>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return gabril_set_cuda_error(e);
+    attr_done = true;
+  }
+  reg_kernel<NHWC, MODE, MAXT><<<a.B, threads, smem, stream>>>(a);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
 }
 
 template <bool NHWC, int MODE>
 int launch_reg(const RegArgs& a, cudaStream_t stream) {
-  if (a.B <= 0 || a.W > 1024 || a.W < 1 || a.h < 1 || a.w < 1) return GABRIL_ERR_BAD_SHAPE;
+  if (a.B <= 0 || a.W > 1024 || a.W < 1 || a.h < 1 || a.w < 1 || (a.W & 3)) return GABRIL_ERR_BAD_SHAPE;
   if (NHWC) {
     const int lpp = a.C / 8;
     if (a.C % 8 || lpp > 32 || (lpp & (lpp - 1))) return GABRIL_ERR_BAD_SHAPE;
   }
   const size_t smem = reg_smem_bytes(a.h, a.w, a.H, a.W);
   if (smem > 200 * 1024) return GABRIL_ERR_BAD_SHAPE;
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(reg_kernel<NHWC, MODE>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e != cudaSuccess) return gabril_set_cuda_error(e);
-    attr_done = true;
-  }
-  const int threads = ((a.W + 31) / 32) * 32;
-  reg_kernel<NHWC, MODE><<<a.B, threads, smem, stream>>>(a);
-  GABRIL_CHECK_LAUNCH();
-  return GABRIL_OK;
+  const int Wr = ((a.W + 31) / 32) * 32;
+  // two row slabs per column when the block still fits twice on an SM
+  if (2 * Wr <= 704) return launch_reg_t<NHWC, MODE, 704>(a, 2 * Wr, smem, stream);
+  if (Wr <= 704) return launch_reg_t<NHWC, MODE, 704>(a, Wr, smem, stream);
+  return launch_reg_t<NHWC, MODE, 1024>(a, Wr, smem, stream);
 }
 
 int grid_for(long long total, int threads, int max_blocks = 148 * 16) {

@@ -62,8 +62,9 @@ __device__ __forceinline__ void load_points(const SplatArgs& a, int b, Tables<S>
     t.yi[threadIdx.x] = min(max((int)__fmul_rn(cy, (float)(H - 1)), 0), H - 1);
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < S * P * H; i += blockDim.x) {
-    const int sp = i / H, y = i - sp * H;
+  const int Hs = (H + 3) & ~3;  // row stride: four consecutive rows are one aligned float4
+  for (int i = threadIdx.x; i < S * P * Hs; i += blockDim.x) {
+    const int sp = i / Hs, y = i - sp * Hs;
     const int s = sp / P;
     const int Lk = a.Lk[s], R = Lk >> 1;
     const int d = t.yi[sp] - y + R;
@@ -95,28 +96,51 @@ __device__ __forceinline__ void column_factors(const SplatArgs& a, const Tables<
 template <int S, int PMAX>
 __device__ __forceinline__ void raw_at(const SplatArgs& a, const float* ky, const float (&kx)[S][PMAX],
                                        int y, float (&raw)[S]) {
-  const int P = a.P, H = a.H;
+  const int P = a.P, Hs = (a.H + 3) & ~3;
 #pragma unroll
   for (int s = 0; s < S; ++s) {
     float acc = 0.f;
 #pragma unroll
     for (int p = 0; p < PMAX; ++p)
-      if (p < P) acc = fmaf(ky[(s * P + p) * H + y], kx[s][p], acc);
+      if (p < P) acc = fmaf(ky[(s * P + p) * Hs + y], kx[s][p], acc);
     raw[s] = a.use_step_coeff ? __fmul_rn(acc, a.step_coeff[s]) : acc;
+  }
+}
+
+// four consecutive rows y4 .. y4+3 (y4 % 4 == 0): one 16-byte broadcast read per (s, p)
+template <int S, int PMAX>
+__device__ __forceinline__ void raw_at4(const SplatArgs& a, const float* ky, const float (&kx)[S][PMAX],
+                                        int y4, float (&raw)[S][4]) {
+  const int P = a.P, Hs = (a.H + 3) & ~3;
+#pragma unroll
+  for (int s = 0; s < S; ++s) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+    for (int p = 0; p < PMAX; ++p)
+      if (p < P) {
+        const float4 k4 = *reinterpret_cast<const float4*>(ky + (s * P + p) * Hs + y4);
+        a0 = fmaf(k4.x, kx[s][p], a0); a1 = fmaf(k4.y, kx[s][p], a1);
+        a2 = fmaf(k4.z, kx[s][p], a2); a3 = fmaf(k4.w, kx[s][p], a3);
+      }
+    if (a.use_step_coeff) {
+      const float c = a.step_coeff[s];
+      a0 = __fmul_rn(a0, c); a1 = __fmul_rn(a1, c); a2 = __fmul_rn(a2, c); a3 = __fmul_rn(a3, c);
+    }
+    raw[s][0] = a0; raw[s][1] = a1; raw[s][2] = a2; raw[s][3] = a3;
   }
 }
 
 // base_s = (raw - mn) / ((mx - mn) + 1e-8) (:134-136); agg_s = sum_{j<=s} c[s][j] base_j with every
 // product and sum rounded separately, j ascending (:265-274)
+// The two min-max divisions are multiplications by the per-(sample, frame) reciprocal
+// inv = 1 / ((mx - mn) + 1e-8): <= 1 ulp away from the reference's division (heat-map tolerance 1e-6).
 template <int S>
 __device__ __forceinline__ void agg_at(const SplatArgs& a, const float (&raw)[S], const float (&mn)[S],
-                                       const float (&mx)[S], float (&agg)[S]) {
+                                       const float (&inv)[S], float (&agg)[S]) {
   float base[S];
 #pragma unroll
   for (int s = 0; s < S; ++s)
-    base[s] = a.normalize_base
-                  ? __fdiv_rn(__fsub_rn(raw[s], mn[s]), __fadd_rn(__fsub_rn(mx[s], mn[s]), 1e-8f))
-                  : raw[s];
+    base[s] = a.normalize_base ? __fmul_rn(__fsub_rn(raw[s], mn[s]), inv[s]) : raw[s];
 #pragma unroll
   for (int s = 0; s < S; ++s) {
     if (!a.aggregate || s == 0) {
@@ -161,9 +185,17 @@ __device__ __forceinline__ void band_of(const SplatArgs& a, int& ylo, int& yhi) 
   }
 }
 
+template <int S>
+__device__ __forceinline__ void make_inv(const SplatArgs& a, const float (&mn)[S], const float (&mx)[S],
+                                         float (&inv)[S]) {
+#pragma unroll
+  for (int s = 0; s < S; ++s)
+    inv[s] = a.normalize_base ? __fdiv_rn(1.f, __fadd_rn(__fsub_rn(mx[s], mn[s]), 1e-8f)) : 1.f;
+}
+
 template <int S, int PMAX>
 __global__ void __launch_bounds__(kThreads) splat_extrema_kernel(const __grid_constant__ SplatArgs a) {
-  extern __shared__ float ky[];  // [S*P][H]
+  extern __shared__ __align__(16) float ky[];  // [S*P][Hs]
   __shared__ Tables<S> t;
   __shared__ float red[kThreads / 32][2][kMaxS];
   const int b = blockIdx.x, H = a.H, W = a.W;
@@ -171,6 +203,8 @@ __global__ void __launch_bounds__(kThreads) splat_extrema_kernel(const __grid_co
   int ylo, yhi;
   band_of<S>(a, ylo, yhi);
   const bool has_outside = (ylo > 0) || (yhi < H);  // rows where every raw_s is exactly 0
+  // fast path: the band is a whole number of 4-row groups (sigma 30 / 20 at H = 180: [60,120), [40,140))
+  const bool quad = has_outside && ((ylo | yhi) & 3) == 0;
 
   float mn[S], mx[S];
 #pragma unroll
@@ -179,11 +213,23 @@ __global__ void __launch_bounds__(kThreads) splat_extrema_kernel(const __grid_co
     for (int x = threadIdx.x; x < W; x += blockDim.x) {
       float kx[S][PMAX];
       column_factors<S, PMAX>(a, t, x, kx);
-      for (int y = ylo; y < yhi; ++y) {
-        float raw[S];
-        raw_at<S, PMAX>(a, ky, kx, y, raw);
+      if (quad) {
+        for (int y = ylo; y < yhi; y += 4) {
+          float raw[S][4];
+          raw_at4<S, PMAX>(a, ky, kx, y, raw);
 #pragma unroll
-        for (int s = 0; s < S; ++s) { mn[s] = fminf(mn[s], raw[s]); mx[s] = fmaxf(mx[s], raw[s]); }
+          for (int s = 0; s < S; ++s) {
+            mn[s] = fminf(fminf(mn[s], fminf(raw[s][0], raw[s][1])), fminf(raw[s][2], raw[s][3]));
+            mx[s] = fmaxf(fmaxf(mx[s], fmaxf(raw[s][0], raw[s][1])), fmaxf(raw[s][2], raw[s][3]));
+          }
+        }
+      } else {
+        for (int y = ylo; y < yhi; ++y) {
+          float raw[S];
+          raw_at<S, PMAX>(a, ky, kx, y, raw);
+#pragma unroll
+          for (int s = 0; s < S; ++s) { mn[s] = fminf(mn[s], raw[s]); mx[s] = fmaxf(mx[s], raw[s]); }
+        }
       }
     }
     block_minmax<S>(mn, mx, red);
@@ -191,23 +237,41 @@ __global__ void __launch_bounds__(kThreads) splat_extrema_kernel(const __grid_co
 #pragma unroll
     for (int s = 0; s < S; ++s) { mn[s] = 0.f; mx[s] = 1.f; }
   }
+  float inv[S];
+  make_inv<S>(a, mn, mx, inv);
   float amn[S], amx[S];
   float zero_raw[S], agg0[S];
 #pragma unroll
   for (int s = 0; s < S; ++s) zero_raw[s] = 0.f;
-  agg_at<S>(a, zero_raw, mn, mx, agg0);
+  agg_at<S>(a, zero_raw, mn, inv, agg0);
 #pragma unroll
   for (int s = 0; s < S; ++s) { amn[s] = has_outside ? agg0[s] : FLT_MAX; amx[s] = has_outside ? agg0[s] : -FLT_MAX; }
   if (a.aggregate) {
     for (int x = threadIdx.x; x < W; x += blockDim.x) {
       float kx[S][PMAX];
       column_factors<S, PMAX>(a, t, x, kx);
-      for (int y = ylo; y < yhi; ++y) {
-        float raw[S], ag[S];
-        raw_at<S, PMAX>(a, ky, kx, y, raw);
-        agg_at<S>(a, raw, mn, mx, ag);
+      if (quad) {
+        for (int y = ylo; y < yhi; y += 4) {
+          float raw4[S][4];
+          raw_at4<S, PMAX>(a, ky, kx, y, raw4);
 #pragma unroll
-        for (int s = 0; s < S; ++s) { amn[s] = fminf(amn[s], ag[s]); amx[s] = fmaxf(amx[s], ag[s]); }
+          for (int r = 0; r < 4; ++r) {
+            float raw[S], ag[S];
+#pragma unroll
+            for (int s = 0; s < S; ++s) raw[s] = raw4[s][r];
+            agg_at<S>(a, raw, mn, inv, ag);
+#pragma unroll
+            for (int s = 0; s < S; ++s) { amn[s] = fminf(amn[s], ag[s]); amx[s] = fmaxf(amx[s], ag[s]); }
+          }
+        }
+      } else {
+        for (int y = ylo; y < yhi; ++y) {
+          float raw[S], ag[S];
+          raw_at<S, PMAX>(a, ky, kx, y, raw);
+          agg_at<S>(a, raw, mn, inv, ag);
+#pragma unroll
+          for (int s = 0; s < S; ++s) { amn[s] = fminf(amn[s], ag[s]); amx[s] = fmaxf(amx[s], ag[s]); }
+        }
       }
     }
     block_minmax<S>(amn, amx, red);
@@ -221,44 +285,61 @@ __global__ void __launch_bounds__(kThreads) splat_extrema_kernel(const __grid_co
   }
 }
 
+// grid (B, nsplit): CTA (b, split) streams the 4-row groups [g0, g1) of sample b
 template <int S, int PMAX>
 __global__ void __launch_bounds__(kThreads) splat_write_kernel(const __grid_constant__ SplatArgs a) {
-  extern __shared__ float ky[];
+  extern __shared__ __align__(16) float ky[];
   __shared__ Tables<S> t;
   const int b = blockIdx.x, split = blockIdx.y, H = a.H, W = a.W;
   load_points<S>(a, b, t, ky);
   int ylo, yhi;
   band_of<S>(a, ylo, yhi);
-  float mn[S], mx[S], amn[S], amx[S];
+  float mn[S], mx[S], amn[S], ainv[S], inv[S];
   const float* e = a.ext + (long long)b * 4 * kMaxS;
 #pragma unroll
-  for (int s = 0; s < S; ++s) { mn[s] = e[s]; mx[s] = e[kMaxS + s]; amn[s] = e[2 * kMaxS + s]; amx[s] = e[3 * kMaxS + s]; }
+  for (int s = 0; s < S; ++s) {
+    mn[s] = e[s]; mx[s] = e[kMaxS + s]; amn[s] = e[2 * kMaxS + s];
+    ainv[s] = __fdiv_rn(1.f, __fadd_rn(__fsub_rn(e[3 * kMaxS + s], amn[s]), 1e-8f));
+  }
+  make_inv<S>(a, mn, mx, inv);
   auto finish = [&](float v, int s) {
-    return a.aggregate ? __fdiv_rn(__fsub_rn(v, amn[s]), __fadd_rn(__fsub_rn(amx[s], amn[s]), 1e-8f)) : v;
+    return a.aggregate ? __fmul_rn(__fsub_rn(v, amn[s]), ainv[s]) : v;
   };
   float zero_raw[S], agg0[S], out0[S];
 #pragma unroll
   for (int s = 0; s < S; ++s) zero_raw[s] = 0.f;
-  agg_at<S>(a, zero_raw, mn, mx, agg0);
+  agg_at<S>(a, zero_raw, mn, inv, agg0);
 #pragma unroll
   for (int s = 0; s < S; ++s) out0[s] = finish(agg0[s], s);
 
-  const int rows_per = (H + a.nsplit - 1) / a.nsplit;
-  const int y0 = split * rows_per, y1 = min(y0 + rows_per, H);
+  const int groups = (H + 3) >> 2;
+  const int per = (groups + a.nsplit - 1) / a.nsplit;
+  const int y0 = split * per * 4, y1 = min(y0 + per * 4, H);
   float* outb = a.out + (long long)b * S * H * W;
   for (int x = threadIdx.x; x < W; x += blockDim.x) {
     float kx[S][PMAX];
     column_factors<S, PMAX>(a, t, x, kx);
-    for (int y = y0; y < y1; ++y) {
-      if (y < ylo || y >= yhi) {
+    for (int y = y0; y < y1; y += 4) {
+      const int nr = min(4, y1 - y);
+      if (y + 4 <= ylo || y >= yhi) {  // whole group outside the band: constant rows
+        for (int r = 0; r < nr; ++r)
 #pragma unroll
-        for (int s = 0; s < S; ++s) outb[((long long)s * H + y) * W + x] = out0[s];
+          for (int s = 0; s < S; ++s) outb[((long long)s * H + y + r) * W + x] = out0[s];
       } else {
-        float raw[S], ag[S];
-        raw_at<S, PMAX>(a, ky, kx, y, raw);
-        agg_at<S>(a, raw, mn, mx, ag);
+        // ky is zero outside the band, so the closed form covers partially covered groups too
+        float raw4[S][4];
+        raw_at4<S, PMAX>(a, ky, kx, y, raw4);
 #pragma unroll
-        for (int s = 0; s < S; ++s) outb[((long long)s * H + y) * W + x] = finish(ag[s], s);
+        for (int r = 0; r < 4; ++r) {
+          if (r < nr) {
+            float raw[S], ag[S];
+#pragma unroll
+            for (int s = 0; s < S; ++s) raw[s] = raw4[s][r];
+            agg_at<S>(a, raw, mn, inv, ag);
+#pragma unroll
+            for (int s = 0; s < S; ++s) outb[((long long)s * H + y + r) * W + x] = finish(ag[s], s);
+          }
+        }
       }
     }
   }
@@ -266,7 +347,7 @@ __global__ void __launch_bounds__(kThreads) splat_write_kernel(const __grid_cons
 
 template <int S, int PMAX>
 int launch_splat(const SplatArgs& a, cudaStream_t stream) {
-  const size_t smem = sizeof(float) * (size_t)S * a.P * a.H;
+  const size_t smem = sizeof(float) * (size_t)S * a.P * ((a.H + 3) & ~3);
   if (smem > 96 * 1024) return GABRIL_ERR_BAD_SHAPE;
   static bool attr_done = false;
   if (!attr_done) {
@@ -310,7 +391,7 @@ extern "C" int gabril_gaze_splat(const float* gaze, float* out, float* ext_ws, c
   a.normalize_base = normalize_base; a.aggregate = aggregate;
   a.B = B; a.L = L; a.S = S; a.center = center; a.P = P; a.H = H; a.W = W;
   int nsplit = 1;  // row slabs per sample: enough CTAs to keep every SM streaming stores
-  while ((long long)B * nsplit < 8 * 148 && nsplit < 16 && nsplit * 2 <= H) nsplit *= 2;
+  while ((long long)B * nsplit < 8 * 148 && nsplit < 16 && nsplit * 8 <= H) nsplit *= 2;
   a.nsplit = nsplit;
 #define GABRIL_SPLAT_CASE(SS)                                                     \
   case SS: return P <= 8 ? launch_splat<SS, 8>(a, stream) : launch_splat<SS, 16>(a, stream)
