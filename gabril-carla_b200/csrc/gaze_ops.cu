@@ -424,19 +424,21 @@ struct RegArgs {
 // only every H/h rows, so their tmap values (and, in the backward pass, the four y-adjoint
 // accumulators) live in registers and shared memory is touched only when the tap window moves.
 template <bool NHWC_BF16, int MODE, int MAXT>
-__global__ void __launch_bounds__(MAXT, MAXT <= 704 ? 2 : 1) reg_kernel(const __grid_constant__ RegArgs a) {
+__global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __grid_constant__ RegArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int h = a.h, w = a.w, H = a.H, W = a.W, C = a.C, n = h * w, n4 = (n + 3) & ~3;
   float* p = sm;                                        // [n4]
   float* tmap = p + n4;                                 // [h][W]
-  float* sacc = tmap + h * W;                           // [h][W]
-  float* wyt = sacc + h * W;                            // [H][4]
+  float* sacc = tmap + h * W;                           // [2][h][W] (one copy per row slab)
+  float* wyt = sacc + 2 * h * W;                        // [H][4]
   int* iyt = reinterpret_cast<int*>(wyt + 4 * H);       // [H][4]
   float* wxt = reinterpret_cast<float*>(iyt + 4 * H);   // [W][4]
   int* ixt = reinterpret_cast<int*>(wxt + 4 * W);       // [W][4]
   float* dp = reinterpret_cast<float*>(ixt + 4 * W);    // [n4]
   int* xrange = reinterpret_cast<int*>(dp + n4);        // [w][2]
+  int* ystart = xrange + 2 * w;                         // [runs + 1] first row of every tap-window run
   __shared__ float scratch[32];
+  __shared__ int nruns_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarp = blockDim.x >> 5;
   const int b = blockIdx.x;
   const bool skip = (a.sel != nullptr) && (a.sel[b] <= 0.f);
@@ -512,6 +514,20 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 704 ? 2 : 1) reg_kernel(const __
     }
   }
 
+  // runs of consecutive output rows that share one y-tap window (H / h rows each)
+  if (wid == 0) {
+    int base = 0;
+    for (int c = 0; c < H; c += 32) {
+      const int y = c + lane;
+      bool f = false;
+      if (y < H) f = (y == 0) || iyt[4 * y] != iyt[4 * y - 4] || iyt[4 * y + 3] != iyt[4 * y - 1];
+      const unsigned m = __ballot_sync(0xffffffffu, f);
+      if (f) ystart[base + __popc(m & ((2u << lane) - 1u)) - 1] = y;
+      base += __popc(m);
+    }
+    if (lane == 0) { ystart[base] = H; nruns_s = base; }
+  }
+
   // ---- softmax(s / beta) over the n positions ----
   float lmax = -FLT_MAX;
   for (int j = tid; j < n; j += blockDim.x) { const float v = __fdiv_rn(p[j], a.beta); p[j] = v; lmax = fmaxf(lmax, v); }
@@ -530,34 +546,40 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 704 ? 2 : 1) reg_kernel(const __
     for (int yy = yq; yy < h; yy += YS) {
       const float* pr = p + yy * w;
       tmap[yy * W + x] = pr[ii.x] * ww.x + pr[ii.y] * ww.y + pr[ii.z] * ww.z + pr[ii.w] * ww.w;
-      if (MODE != MODE_MASK_FWD) sacc[yy * W + x] = 0.f;
+      if (MODE != MODE_MASK_FWD) { sacc[yy * W + x] = 0.f; sacc[(h + yy) * W + x] = 0.f; }
     }
   }
   __syncthreads();
 
   const int4* iy4 = reinterpret_cast<const int4*>(iyt);
   const float4* wy4 = reinterpret_cast<const float4*>(wyt);
-  // register window over the four source rows of the current y
-  int4 cur = make_int4(-1, -1, -1, -1);
+  const int nruns = nruns_s;
+  // register window over the four source rows of the current run
+  int4 cur = make_int4(0, 0, 0, 0);
   float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
-  auto load_window = [&](const int4& id) {
-    cur = id;
-    t0 = tmap[id.x * W + x]; t1 = tmap[id.y * W + x]; t2 = tmap[id.z * W + x]; t3 = tmap[id.w * W + x];
+  auto load_window = [&](int y) {
+    cur = iy4[y];
+    t0 = tmap[cur.x * W + x]; t1 = tmap[cur.y * W + x]; t2 = tmap[cur.z * W + x]; t3 = tmap[cur.w * W + x];
   };
-  auto moved = [&](const int4& id) { return id.x != cur.x || id.w != cur.w; };
+  auto u_of = [&](const float4& wv) { return t0 * wv.x + t1 * wv.y + t2 * wv.z + t3 * wv.w; };
 
   // ---- pass 1: extrema (first occurrence wins ties, like torch's CPU max/min) ----
   float vmin = FLT_MAX, vmax = -FLT_MAX;
   int imin = 0x7fffffff, imax = 0x7fffffff;
   if (col_ok) {
-    for (int y = ya; y < yb; ++y) {
-      const int4 id = iy4[y];
-      const float4 wv = wy4[y];
-      if (moved(id)) load_window(id);
-      const float u = t0 * wv.x + t1 * wv.y + t2 * wv.z + t3 * wv.w;
-      if (u < vmin) { vmin = u; imin = y * W + x; }
-      if (u > vmax) { vmax = u; imax = y * W + x; }
+    for (int r = 0; r < nruns; ++r) {
+      const int y0 = max(ya, ystart[r]), y1 = min(yb, ystart[r + 1]);
+      if (y0 >= y1) continue;
+      load_window(y0);
+#pragma unroll 4
+      for (int y = y0; y < y1; ++y) {
+        const float u = u_of(wy4[y]);
+        if (u < vmin) { vmin = u; imin = y; }
+        if (u > vmax) { vmax = u; imax = y; }
+      }
     }
+    if (imin != 0x7fffffff) imin = imin * W + x;
+    if (imax != 0x7fffffff) imax = imax * W + x;
   }
   // block arg-reduce
   for (int o = 16; o > 0; o >>= 1) {
@@ -589,12 +611,12 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 704 ? 2 : 1) reg_kernel(const __
   if (MODE == MODE_MASK_FWD) {
     if (col_ok) {
       float* mo = a.mask_out + (long long)b * H * W;
-      for (int y = ya; y < yb; ++y) {
-        const int4 id = iy4[y];
-        const float4 wv = wy4[y];
-        if (moved(id)) load_window(id);
-        const float u = t0 * wv.x + t1 * wv.y + t2 * wv.z + t3 * wv.w;
-        mo[y * W + x] = __fdiv_rn(__fsub_rn(u, mn), rng);  // reference-facing op: exact division
+      for (int r = 0; r < nruns; ++r) {
+        const int y0 = max(ya, ystart[r]), y1 = min(yb, ystart[r + 1]);
+        if (y0 >= y1) continue;
+        load_window(y0);
+        for (int y = y0; y < y1; ++y)  // reference-facing op: exact division
+          mo[y * W + x] = __fdiv_rn(__fsub_rn(u_of(wy4[y]), mn), rng);
       }
     }
     return;
@@ -605,40 +627,42 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 704 ? 2 : 1) reg_kernel(const __
   const float inv_rng = __fdiv_rn(1.f, rng);
   float sq = 0.f, E = 0.f, F = 0.f;
   if (col_ok) {
-    const float* g1 = (MODE == MODE_MSE) ? a.g1 + (long long)b * a.g1_bstride : nullptr;
-    const float* gi = (MODE == MODE_MASK_BWD) ? a.grad_in + (long long)b * H * W : nullptr;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    auto flush = [&]() {
-      if (cur.x < 0) return;
-      if (YS == 1) {  // column-private
-        sacc[cur.x * W + x] += a0; sacc[cur.y * W + x] += a1; sacc[cur.z * W + x] += a2; sacc[cur.w * W + x] += a3;
-      } else {
-        atomicAdd(&sacc[cur.x * W + x], a0); atomicAdd(&sacc[cur.y * W + x], a1);
-        atomicAdd(&sacc[cur.z * W + x], a2); atomicAdd(&sacc[cur.w * W + x], a3);
+    const float* gsrc = (MODE == MODE_MSE) ? a.g1 + (long long)b * a.g1_bstride
+                                           : a.grad_in + (long long)b * H * W;
+    gsrc += x;
+    for (int r = 0; r < nruns; ++r) {
+      const int y0 = max(ya, ystart[r]), y1 = min(yb, ystart[r + 1]);
+      if (y0 >= y1) continue;
+      load_window(y0);
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+      for (int yc = y0; yc < y1; yc += 8) {
+        float gv[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) gv[k] = (yc + k < y1) ? __ldg(gsrc + (yc + k) * W) : 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          if (yc + k < y1) {
+            const float4 wv = wy4[yc + k];
+            const float g2 = __fsub_rn(u_of(wv), mn) * inv_rng;
+            float e;
+            if (MODE == MODE_MSE) {
+              const float d = g2 - gv[k];
+              sq = fmaf(d, d, sq);
+              e = 2.f * d * a.grad_scale;
+            } else {
+              e = gv[k];
+            }
+            E += e;
+            F = fmaf(e, g2, F);
+            const float du = e * inv_rng;
+            a0 = fmaf(wv.x, du, a0); a1 = fmaf(wv.y, du, a1); a2 = fmaf(wv.z, du, a2); a3 = fmaf(wv.w, du, a3);
+          }
+        }
       }
-      a0 = a1 = a2 = a3 = 0.f;
-    };
-    cur = make_int4(-1, -1, -1, -1);
-    for (int y = ya; y < yb; ++y) {
-      const int4 id = iy4[y];
-      const float4 wv = wy4[y];
-      if (moved(id)) { flush(); load_window(id); }
-      const float u = t0 * wv.x + t1 * wv.y + t2 * wv.z + t3 * wv.w;
-      const float g2 = __fsub_rn(u, mn) * inv_rng;
-      float e;
-      if (MODE == MODE_MSE) {
-        const float d = g2 - __ldg(g1 + y * W + x);
-        sq = fmaf(d, d, sq);
-        e = 2.f * d * a.grad_scale;
-      } else {
-        e = __ldg(gi + y * W + x);
-      }
-      E += e;
-      F = fmaf(e, g2, F);
-      const float du = e * inv_rng;
-      a0 = fmaf(wv.x, du, a0); a1 = fmaf(wv.y, du, a1); a2 = fmaf(wv.z, du, a2); a3 = fmaf(wv.w, du, a3);
+      // slab-private copy of the accumulators: plain read-modify-write, no atomics
+      float* sa = sacc + (yq & 1) * h * W + x;
+      sa[cur.x * W] += a0; sa[cur.y * W] += a1; sa[cur.z * W] += a2; sa[cur.w * W] += a3;
     }
-    flush();
   }
   const float Esum = block_sum(E, scratch);
   const float Fsum = block_sum(F, scratch);
@@ -661,7 +685,7 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 704 ? 2 : 1) reg_kernel(const __
     const int yy = j / w, xs = j - yy * w;
     float acc = 0.f;
     for (int xx = xrange[2 * xs]; xx <= xrange[2 * xs + 1]; ++xx) {
-      const float sv = sacc[yy * W + xx];
+      const float sv = sacc[yy * W + xx] + sacc[(h + yy) * W + xx];
 #pragma unroll
       for (int k = 0; k < 4; ++k)
         if (ixt[4 * xx + k] == xs) acc = fmaf(wxt[4 * xx + k], sv, acc);
@@ -703,7 +727,7 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 704 ? 2 : 1) reg_kernel(const __
 
 size_t reg_smem_bytes(int h, int w, int H, int W) {
   const size_t n4 = ((size_t)h * w + 3) & ~(size_t)3;
-  return sizeof(float) * (n4 + 2 * (size_t)h * W + 8 * (size_t)H + 8 * (size_t)W + n4 + 2 * (size_t)w);
+  return sizeof(float) * (n4 + 3 * (size_t)h * W + 8 * (size_t)H + 8 * (size_t)W + n4 + 2 * (size_t)w + (size_t)H + 1);
 }
 
 template <bool NHWC, int MODE, int MAXT>
@@ -731,8 +755,8 @@ int launch_reg(const RegArgs& a, cudaStream_t stream) {
   if (smem > 200 * 1024) return GABRIL_ERR_BAD_SHAPE;
   const int Wr = ((a.W + 31) / 32) * 32;
   // two row slabs per column when the block still fits twice on an SM
-  if (2 * Wr <= 704) return launch_reg_t<NHWC, MODE, 704>(a, 2 * Wr, smem, stream);
-  if (Wr <= 704) return launch_reg_t<NHWC, MODE, 704>(a, Wr, smem, stream);
+  if (2 * Wr <= 640) return launch_reg_t<NHWC, MODE, 640>(a, 2 * Wr, smem, stream);
+  if (Wr <= 640) return launch_reg_t<NHWC, MODE, 640>(a, Wr, smem, stream);
   return launch_reg_t<NHWC, MODE, 1024>(a, Wr, smem, stream);
 }
 
