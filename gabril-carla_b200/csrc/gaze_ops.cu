@@ -217,7 +217,7 @@ constexpr int kPatchRows = 6;
 template <int S_, bool GRAY>
 __global__ void __launch_bounds__(256)
 obs_patches_tiled_kernel(const uint8_t* __restrict__ frames, bf16* __restrict__ out, int L,
-                         int center, int H, int W, int OH, int OW, int Kp) {
+                         int center, int H, int W, int OH, int OW, int Kp, int SH, int SW) {
   constexpr int CP = GRAY ? 1 : 3;
   constexpr int C0 = S_ * CP;
   constexpr int NR = 2 * kPatchRows + 2;
@@ -300,7 +300,13 @@ obs_patches_tiled_kernel(const uint8_t* __restrict__ frames, bf16* __restrict__ 
     const int pl = i >> 2;
     const int ow = pl % OW;
     const int ohl = pl / OW;
-    const long long pix = ((long long)b * OH + oh0 + ohl) * OW + ow;
+    long long pix = ((long long)b * OH + oh0 + ohl) * OW + ow;
+    if (SH > 0) {
+      // space-to-depth row order over the one-pixel-padded output: pixel (oh, ow) is quadrant
+      // ((oh+1)&1, (ow+1)&1) of super-pixel ((oh+1)>>1, (ow+1)>>1) of an SH x SW grid
+      const int ph = oh0 + ohl + 1, pw = ow + 1;
+      pix = ((((long long)b * SH + (ph >> 1)) * SW + (pw >> 1)) << 2) + ((ph & 1) << 1) + (pw & 1);
+    }
     const uint2* src = reinterpret_cast<const uint2*>(img + (2 * ohl + r4) * img_row + 2 * ow * C0);
     uint4* dst = reinterpret_cast<uint4*>(out + pix * Kp + r4 * (4 * C0));
 #pragma unroll
@@ -785,8 +791,8 @@ int gabril_obs_format(const uint8_t* frames, float* out, int B, int L, int S, in
   return GABRIL_OK;
 }
 
-int gabril_obs_patches(const uint8_t* frames, void* patches, int B, int L, int S, int center, int H,
-                       int W, int grayscale, int Kp, cudaStream_t stream) {
+static int obs_patches_impl(const uint8_t* frames, void* patches, int B, int L, int S, int center,
+                            int H, int W, int grayscale, int Kp, int SH, int SW, cudaStream_t stream) {
   if (!frames || !patches) return GABRIL_ERR_NULL;
   const int C0 = S * (grayscale ? 1 : 3);
   if (B <= 0 || S < 1 || S > 4 || Kp < 16 * C0 || Kp % 4) return GABRIL_ERR_BAD_SHAPE;
@@ -808,7 +814,7 @@ int gabril_obs_patches(const uint8_t* frames, void* patches, int B, int L, int S
       attr_done = true;                                                                            \
     }                                                                                              \
     obs_patches_tiled_kernel<SS, GG><<<tgrid, 256, smem, stream>>>(frames, out, L, center, H, W,   \
-                                                                   OH, OW, Kp);                    \
+                                                                   OH, OW, Kp, SH, SW);            \
   } while (0)
       if (grayscale && S == 2) GABRIL_TILED_CASE(2, true);
       else if (grayscale && S == 4) GABRIL_TILED_CASE(4, true);
@@ -819,6 +825,7 @@ int gabril_obs_patches(const uint8_t* frames, void* patches, int B, int L, int S
       return GABRIL_OK;
     }
   }
+  if (SH > 0) return GABRIL_ERR_BAD_SHAPE;  // the space-to-depth row order needs the tiled kernel
 #define GABRIL_PATCH_CASE(SS, GG)                                                              \
   obs_patches_kernel<SS, GG><<<grid, 256, 0, stream>>>(frames, out, B, L, center, H, W, OH, OW, Kp)
   if (grayscale) {
@@ -839,6 +846,18 @@ int gabril_obs_patches(const uint8_t* frames, void* patches, int B, int L, int S
 #undef GABRIL_PATCH_CASE
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
+}
+
+int gabril_obs_patches(const uint8_t* frames, void* patches, int B, int L, int S, int center, int H,
+                       int W, int grayscale, int Kp, cudaStream_t stream) {
+  return obs_patches_impl(frames, patches, B, L, S, center, H, W, grayscale, Kp, 0, 0, stream);
+}
+
+int gabril_obs_patches_s2d(const uint8_t* frames, void* patches, int B, int L, int S, int center,
+                           int H, int W, int grayscale, int Kp, int SH, int SW, cudaStream_t stream) {
+  const int OH = (H + 2 - 4) / 2 + 1, OW = (W + 2 - 4) / 2 + 1;
+  if (SH < (OH + 2) / 2 || SW < (OW + 2) / 2) return GABRIL_ERR_BAD_SHAPE;
+  return obs_patches_impl(frames, patches, B, L, S, center, H, W, grayscale, Kp, SH, SW, stream);
 }
 
 int gabril_gmd_mask(const float* g, const float* A, float* K_ws, unsigned int* mnmx_ws,

@@ -56,7 +56,7 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
 // and the MMA issuer work on tile i+1 while the epilogue warps drain tile i.
 __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_constant__ Params p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 4];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 5];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -65,6 +65,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
   const uint32_t empty0 = ptx::smem_u32(&bars[kMaxStages]);
   const uint32_t tfull0 = ptx::smem_u32(&bars[2 * kMaxStages]);
   const uint32_t tempty0 = ptx::smem_u32(&bars[2 * kMaxStages + 2]);
+  const uint32_t wfull = ptx::smem_u32(&bars[2 * kMaxStages + 4]);  // resident weights landed
   const uint32_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
 
   if (threadIdx.x == 0) {
@@ -76,6 +77,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       ptx::mbar_init(tfull0 + 8 * b, 1);
       ptx::mbar_init(tempty0 + 8 * b, 4);  // one arrival per epilogue warp
     }
+    ptx::mbar_init(wfull, 1);
     ptx::fence_mbar_init();
   }
   if (warp == kMmaWarp) {
@@ -99,11 +101,84 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       int st = 0;
       uint32_t st_ph = 0;
       bool ok = true;
+      if (p.a_flat && p.kind == KIND_FWD && p.b_resident && me == 0) {
+        // every weight tile of the layer, once per CTA, in traversal order (r, s, chunk)
+        const int chunks = p.chunks_per_tap;
+        ptx::mbar_arrive_expect_tx(wfull, (uint32_t)(p.flat_R * p.flat_S * chunks) * p.b_tap_bytes);
+        for (int r = 0; r < p.flat_R; ++r)
+          for (int sx = 0; sx < p.flat_S; ++sx) {
+            const int wtap = (p.r_base[0] + p.r_step * r) * p.S_w + p.s_base[0] + p.s_step * sx;
+            for (int ch = 0; ch < chunks; ++ch) {
+              const uint32_t dst =
+                  smem_base + p.resident_off + (uint32_t)((r * p.flat_S + sx) * chunks + ch) * p.b_tap_bytes;
+              if (!p.b_mn) {
+                ptx::tma_load_3d(dst, &p.mapB, wfull, ch * p.kc, wtap, 0);
+              } else {
+                for (int i = 0; i < p.b_boxes; ++i)
+                  ptx::tma_load_3d(dst + i * p.b_box_bytes, &p.mapB, wfull, i * p.b_box_w, wtap, ch * p.kc);
+              }
+            }
+          }
+      }
       for (int t = blockIdx.x; t < p.total_tiles && ok; t += gridDim.x) {
         const Tile tl = decode_tile(p, t);
         const int cls = tl.cls, m0 = tl.m0, n0 = tl.n0;
         const int ohw = p.OHW[cls], oww = p.OW[cls];
-        if (p.kind == KIND_FWD) {
+        if (p.a_flat && p.kind == KIND_FWD) {
+          const int chunks = p.chunks_per_tap;
+          const uint32_t tx = p.slab_tx_bytes + (p.b_resident ? 0u : (uint32_t)p.flat_S * p.b_tap_bytes);
+          int r = tl.kb_begin / chunks, chunk = tl.kb_begin - (tl.kb_begin / chunks) * chunks;
+          for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+            const int s = st;
+            const uint32_t ph = st_ph;
+            const int chunk_c = chunk, r_c = r;
+            if (++st == p.stages) { st = 0; st_ph ^= 1; }
+            if (++chunk == chunks) { chunk = 0; ++r; }
+            if (s % kProducers != me) continue;
+            if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { report_timeout(p, 106); ok = false; break; }
+            const uint32_t a_dst = smem_base + s * stage_bytes;
+            const uint32_t b_dst = a_dst + p.a_stage_bytes;
+            const uint32_t full = full0 + 8 * s;
+            ptx::mbar_arrive_expect_tx(full, tx);
+            ptx::tma_load_2d(a_dst, &p.mapA[0], full, chunk_c * p.kc, m0 + r_c * p.flat_pitch);
+            if (!p.b_resident) {
+              for (int sx = 0; sx < p.flat_S; ++sx) {
+                const int wtap = (p.r_base[0] + p.r_step * r_c) * p.S_w + p.s_base[0] + p.s_step * sx;
+                const uint32_t dst = b_dst + sx * p.b_tap_bytes;
+                if (!p.b_mn) {
+                  ptx::tma_load_3d(dst, &p.mapB, full, chunk_c * p.kc, wtap, n0);
+                } else {
+                  for (int i = 0; i < p.b_boxes; ++i)
+                    ptx::tma_load_3d(dst + i * p.b_box_bytes, &p.mapB, full, n0 + i * p.b_box_w, wtap,
+                                     chunk_c * p.kc);
+                }
+              }
+            }
+          }
+        } else if (p.a_flat) {
+          // WGRAD flat: A = dY rows of the k-block, B = one pixel slab per filter row of the group
+          const int r0 = tl.tap0 / p.flat_S, nrows = tl.ntaps / p.flat_S;
+          const uint32_t tx = p.a_boxes * p.a_box_bytes + (uint32_t)(nrows * p.b_boxes) * p.slab_tx_bytes;
+          for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+            const int s = st;
+            const uint32_t ph = st_ph;
+            if (++st == p.stages) { st = 0; st_ph ^= 1; }
+            if (s % kProducers != me) continue;
+            if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { report_timeout(p, 107); ok = false; break; }
+            const uint32_t a_dst = smem_base + s * stage_bytes;
+            const uint32_t b_dst = a_dst + p.a_stage_bytes;
+            const uint32_t full = full0 + 8 * s;
+            ptx::mbar_arrive_expect_tx(full, tx);
+            const int p0 = kb * p.kc;
+            for (int i = 0; i < p.a_boxes; ++i)
+              ptx::tma_load_2d(a_dst + i * p.a_box_bytes, &p.mapA[0], full, m0 + i * p.a_box_w,
+                               p0 + p.dy_row_off);
+            for (int rr = 0; rr < nrows; ++rr)
+              for (int i = 0; i < p.b_boxes; ++i)
+                ptx::tma_load_2d(b_dst + (uint32_t)(rr * p.b_boxes + i) * p.b_tap_bytes, &p.mapB, full,
+                                 n0 + i * p.b_box_w, p0 + (r0 + rr) * p.flat_pitch);
+          }
+        } else if (p.kind == KIND_FWD) {
           int w_base = 0, h_base = 0, n_img = 0;
           if (p.a_im2col) {
             n_img = m0 / ohw;
@@ -211,6 +286,61 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
         ptx::tc_fence_after();
         if (prof) pt += clock64() - c0;
         const uint32_t d_base = tmem_base + buf * p.acc_stride;
+        if (p.a_flat) {
+          const int chunks = p.chunks_per_tap, FS = p.flat_S;
+          const uint32_t tap16 = p.b_tap_bytes >> 4;
+          if (p.kind == KIND_FWD) {
+            if (p.b_resident && tcount == 0) {
+              if (!ptx::mbar_wait(wfull, 0)) { report_timeout(p, 108); break; }
+              ptx::tc_fence_after();
+            }
+            const uint32_t w_lo = (uint32_t)p.desc_b_hi + ((smem_base + p.resident_off) >> 4);
+            int r = tl.kb_begin / chunks, chunk = tl.kb_begin - (tl.kb_begin / chunks) * chunks;
+            for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+              if (!ptx::mbar_wait(full0 + 8 * s, ph)) { report_timeout(p, 103); ok = false; break; }
+              ptx::tc_fence_after();
+              const uint32_t a_lo = a_lo_const + (uint32_t)s * stage16;
+              const uint32_t b_lo = b_lo_const + (uint32_t)s * stage16;
+              for (int sx = 0; sx < FS; ++sx) {
+                const uint32_t as = a_lo + sx * 8u;  // view of the slab from pixel row sx on
+                const uint32_t bb = p.b_resident ? w_lo + (uint32_t)((r * FS + sx) * chunks + chunk) * tap16
+                                                 : b_lo + sx * tap16;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const uint64_t a_desc = ((uint64_t)a_hi32 << 32) | (uint64_t)(as + j * a_kstep);
+                  const uint64_t b_desc = ((uint64_t)b_hi32 << 32) | (uint64_t)(bb + j * b_kstep);
+                  ptx::umma_bf16(d_base, a_desc, b_desc, idesc, (kb > tl.kb_begin || sx > 0 || j > 0) ? 1u : 0u);
+                }
+              }
+              ptx::umma_commit(empty0 + 8 * s);
+              if (++s == stages) { s = 0; ph ^= 1; }
+              if (++chunk == chunks) { chunk = 0; ++r; }
+            }
+          } else {
+            const int nrows = tl.ntaps / FS;
+            for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+              if (!ptx::mbar_wait(full0 + 8 * s, ph)) { report_timeout(p, 103); ok = false; break; }
+              ptx::tc_fence_after();
+              const uint32_t a_lo = a_lo_const + (uint32_t)s * stage16;
+              const uint32_t b_lo = b_lo_const + (uint32_t)s * stage16;
+              for (int rr = 0; rr < nrows; ++rr)
+                for (int sx = 0; sx < FS; ++sx) {
+                  const uint32_t bb = b_lo + (uint32_t)(rr * p.b_boxes) * tap16 + sx * 8u;
+                  const uint32_t dcol = d_base + (uint32_t)((rr * FS + sx) * p.block_n);
+#pragma unroll
+                  for (int j = 0; j < 4; ++j) {
+                    const uint64_t a_desc = ((uint64_t)a_hi32 << 32) | (uint64_t)(a_lo + j * a_kstep);
+                    const uint64_t b_desc = ((uint64_t)b_hi32 << 32) | (uint64_t)(bb + j * b_kstep);
+                    ptx::umma_bf16(dcol, a_desc, b_desc, idesc, (kb > tl.kb_begin || j > 0) ? 1u : 0u);
+                  }
+                }
+              ptx::umma_commit(empty0 + 8 * s);
+              if (++s == stages) { s = 0; ph ^= 1; }
+            }
+          }
+          if (ok) ptx::umma_commit(tfull0 + 8 * buf);
+          continue;
+        }
         for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb, ++it) {
           const long long c1 = prof ? clock64() : 0;
           if (!ptx::mbar_wait(full0 + 8 * s, ph)) { report_timeout(p, 103); ok = false; break; }
@@ -256,7 +386,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       const int buf = (p.acc_bufs == 2) ? (tcount & 1) : 0;
       const int use = (p.acc_bufs == 2) ? (tcount >> 1) : tcount;
       const int row = tl.m0 + q * 32 + lane;
-      const bool row_ok = row < p.M_total[cls];
+      bool row_ok = row < p.M_total[cls];
       long long orow = row;
       if (p.remap && row_ok) {
         const int hw = p.Hs[cls] * p.Ws[cls];
@@ -266,9 +396,15 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
         const int jw = rem - jh * p.Ws[cls];
         orow = ((long long)n * p.OHf + (jh * p.remap_sh + p.ah[cls])) * p.OWf +
                (jw * p.remap_sw + p.aw[cls]);
+        if (p.valid_h > 0 && (jh >= p.valid_h || jw >= p.valid_w)) row_ok = false;
       }
       bool zero_row = false;
-      if (p.border_h > 0 && row_ok) {
+      if (p.s2d_H > 0 && row_ok) {
+        const int qd = row & 3, sp = row >> 2;
+        const int sw = sp % p.border_w, sh = (sp / p.border_w) % p.border_h;
+        const int ih = 2 * sh + (qd >> 1) - 1, iw = 2 * sw + (qd & 1) - 1;
+        zero_row = ih < 0 || ih >= p.s2d_H || iw < 0 || iw >= p.s2d_W;
+      } else if (p.border_h > 0 && row_ok) {
         const int hw = p.border_h * p.border_w;
         const int rem = row % hw;
         const int y = rem / p.border_w;

@@ -76,8 +76,24 @@ struct Params {
   //        (strided-dgrad parity classes; writes into the interior of a pre-padded tensor)
   int remap, remap_sh, remap_sw;
   int Hs[4], Ws[4], ah[4], aw[4], OHf, OWf;
-  // border_h/w > 0: rows are pixels of a border_h x border_w padded grid; border pixels store 0
-  int border_h, border_w;
+  // border_h/w > 0: rows are pixels of a border_h x border_w padded grid; border pixels store 0.
+  // s2d_H/W > 0 instead: rows are (super-pixel, quadrant) of a border_h x border_w space-to-depth
+  // grid over an s2d_H x s2d_W image padded by one pixel; rows of padding pixels store 0.
+  int border_h, border_w, s2d_H, s2d_W;
+  // remap validity: rows with jh >= valid_h or jw >= valid_w are not stored (0 = no check)
+  int valid_h, valid_w;
+  // flat-slab mode: the A rows (FWD) / B rows (WGRAD) are the flat pixels of a zero-bordered
+  // tensor.  Filter row r is ONE 2-D TMA slab of (tile rows + flat_S - 1) pixels starting at
+  // row0 + r * flat_pitch; tap (r, s) is that slab viewed from row s on (descriptor start
+  // address + s * 128 bytes: the 128-byte swizzle is a function of the absolute shared-memory
+  // address, so whole-row shifts of the start address are legal).
+  int a_flat, flat_pitch, flat_R, flat_S;
+  int dy_row_off;           // WGRAD flat: dY row of contraction index q is q + dy_row_off
+  int rows_per_group;       // WGRAD flat: filter rows per CTA (taps per CTA = rows_per_group * flat_S)
+  int b_resident;           // FWD flat: all weight tiles are loaded once per CTA
+  uint32_t b_tap_bytes;     // bytes of one weight tap tile (FWD flat) / one slab (WGRAD flat)
+  uint32_t slab_tx_bytes;   // bytes one slab load transfers
+  uint32_t resident_off;    // offset of the resident weight region from the aligned smem base
   // persistent tile schedule: tile -> (m tile [classes concatenated], n tile, split)
   int tiles_m[4], tiles_m_total, n_tiles, n_splits, total_tiles;
   int acc_bufs, acc_stride;  // TMEM accumulator ring (1 or 2 buffers of acc_stride columns)

@@ -498,4 +498,220 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
   return tc::launch(p, 1 << 30, smem, stream);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Flat-slab convolutions over zero-bordered tensors (see Params::a_flat).
+// ---------------------------------------------------------------------------------------------
+// out(q) = sum_{r,s} x_flat[q + r*Wg + s] . W(r, s) for every flat pixel q of x[N, Hg, Wg, Cx]
+// (stride 1; the zero border of x supplies the padding).  Pixel q = (n, i, j) is stored at
+// y[(n*o_rows + i + o_off_h)*o_pitch + j + o_off_w][:] when i < valid_h and j < valid_w
+// (valid_h == 0: every pixel is stored at its own index).
+//   transpose_w == 0 (forward):  w[Cy][R*S][Cx], tap (r, s)           -> Cy output channels
+//   transpose_w == 1 (dgrad):    w[Cx][R*S][Cy], tap (R-1-r, S-1-s)   -> Cy output channels,
+//                                contraction over w's leading dimension
+// epilogue: + bias[Cy], + resid (indexed like y), ReLU, gate (y = gate > 0 ? y : 0, indexed like y).
+int gabril_conv_flat(const void* x, const void* w, const float* bias, const void* resid,
+                     const void* gate, void* y, int N, int Hg, int Wg, int Cx, int Cy, int R, int S,
+                     int valid_h, int valid_w, int o_rows, int o_pitch, int o_off_h, int o_off_w,
+                     int relu, int transpose_w, cudaStream_t stream) {
+  int rc = resolve_driver();
+  if (rc) return rc;
+  if (Cx % 64 || N <= 0 || R < 1 || S < 1 || S > 8) return GABRIL_ERR_BAD_SHAPE;
+  if (transpose_w ? !mn_ok(Cy) : !fwd_cout_ok(Cy)) return GABRIL_ERR_BAD_SHAPE;
+  const int kc = 64;
+  const int block_n = std::min(Cy, 128);
+  tc::Params p;
+  zero_params(p);
+  p.kind = tc::KIND_FWD;
+  p.n_classes = 1;
+  p.b_mn = transpose_w ? 1 : 0;
+  fwd_schedule(p, kc, block_n, p.b_mn);
+  p.a_flat = 1;
+  p.flat_pitch = Wg; p.flat_R = R; p.flat_S = S;
+  const long long M = (long long)N * Hg * Wg;
+  if (M >= (1ll << 31)) return GABRIL_ERR_BAD_SHAPE;
+  p.M_total[0] = (int)M;
+  p.N_total = Cy;
+  p.taps = R * S; p.S = S; p.S_w = S;
+  p.chunks_per_tap = Cx / kc;
+  p.kb_total = R * p.chunks_per_tap;  // one k-block = one (filter row, channel chunk) slab
+  p.kb_per_split = p.kb_total;
+  if (transpose_w) { p.r_base[0] = R - 1; p.s_base[0] = S - 1; p.r_step = -1; p.s_step = -1; }
+  else { p.r_base[0] = 0; p.s_base[0] = 0; p.r_step = 1; p.s_step = 1; }
+  // A: the activation as [rows][Cx]; a slab = 128 + S - 1 rows of one 64-channel chunk
+  const int slab_rows = 128 + S - 1;
+  {
+    uint64_t dims[2] = {(uint64_t)Cx, (uint64_t)M};
+    uint64_t strides[1] = {(uint64_t)Cx * 2};
+    uint32_t box[2] = {(uint32_t)kc, (uint32_t)slab_rows};
+    rc = tiled_map(&p.mapA[0], x, 2, dims, strides, box, kc * 2);
+    if (rc) return rc;
+  }
+  p.slab_tx_bytes = (uint32_t)slab_rows * 128u;
+  p.a_box_bytes = p.slab_tx_bytes;
+  p.a_stage_bytes = round_up(p.slab_tx_bytes, 1024);
+  // B: weight tap tiles
+  if (!transpose_w) rc = weight_map(&p.mapB, w, Cy, R * S, Cx, 0, kc, block_n);
+  else rc = weight_map(&p.mapB, w, Cx, R * S, Cy, 1, kc, block_n);
+  if (rc) return rc;
+  p.b_tap_bytes = (uint32_t)p.b_boxes * p.b_box_bytes;
+  const int n_tiles = Cy / block_n;
+  const uint32_t resident_bytes = (uint32_t)(R * S * p.chunks_per_tap) * p.b_tap_bytes;
+  p.b_resident = (n_tiles == 1 && resident_bytes <= 96u * 1024u) ? 1 : 0;
+  p.b_stage_bytes = p.b_resident ? 0u : (uint32_t)S * p.b_tap_bytes;
+  const uint32_t stage = p.a_stage_bytes + p.b_stage_bytes;
+  const uint32_t budget = 224u * 1024u - 2048u - (p.b_resident ? resident_bytes : 0u);
+  int st = (int)(budget / stage);
+  st = std::min(st, tc::kMaxStages);
+  if (st < 2) return GABRIL_ERR_BAD_SHAPE;
+  p.stages = st;
+  p.resident_off = (uint32_t)st * stage;
+  const size_t smem = (size_t)st * stage + (p.b_resident ? resident_bytes : 0u) + 1024;
+  // epilogue
+  p.out_mode = tc::OUT_BF16;
+  p.out = y; p.ldo = Cy;
+  p.bias = bias; p.resid = (const bf16*)resid; p.gate = (const bf16*)gate; p.rowmask = nullptr;
+  p.relu = relu;
+  if (valid_h > 0) {
+    p.remap = 1; p.remap_sh = 1; p.remap_sw = 1;
+    p.Hs[0] = Hg; p.Ws[0] = Wg; p.OHf = o_rows; p.OWf = o_pitch; p.ah[0] = o_off_h; p.aw[0] = o_off_w;
+    p.valid_h = valid_h; p.valid_w = valid_w;
+  }
+  p.err_flag = g_err_flag;
+  const int mt[1] = {(int)((M + 127) / 128)};
+  finalize_schedule(p, mt, n_tiles, 1, block_n, 1);
+  return tc::launch(p, g_num_sms, smem, stream);
+}
+
+// dw[Cy][R*S][Cx] (fp32) += sum_q dy_flat[q + dy_row_off, Cy]^T . x_flat[q + r*Wg + s, Cx]
+// over every flat pixel q of the [N, Hg, Wg] grid; dy and x are zero-bordered tensors with that
+// same grid (rows past the end read as zero).  The caller zeroes dw.
+int gabril_conv_wgrad_flat(const void* dy, const void* x, float* dw, int N, int Hg, int Wg, int Cx,
+                           int Cy, int R, int S, int dy_row_off, cudaStream_t stream) {
+  int rc = resolve_driver();
+  if (rc) return rc;
+  if (!mn_ok(Cx) || Cx < 64 || Cy % 32 || N <= 0 || S > 8) return GABRIL_ERR_BAD_SHAPE;
+  const long long P = (long long)N * Hg * Wg;
+  if (P >= (1ll << 31)) return GABRIL_ERR_BAD_SHAPE;
+  const int KP = 64, T = R * S;
+  tc::Params p;
+  zero_params(p);
+  p.kind = tc::KIND_WGRAD;
+  p.n_classes = 1;
+  p.a_flat = 1;
+  p.flat_pitch = Wg; p.flat_R = R; p.flat_S = S;
+  p.dy_row_off = dy_row_off;
+  p.kc = KP;
+  // A = dy^T: M = Cy rows padded to 128 with out-of-range (zero-filled) boxes
+  const int aw = std::min(64, Cy), a_sw = aw * 2;
+  p.a_box_w = aw;
+  p.a_boxes = 128 / aw;
+  p.a_box_bytes = KP * a_sw;
+  p.a_stage_bytes = round_up(p.a_boxes * p.a_box_bytes, 1024);
+  p.desc_a_hi = desc_hi(p.a_box_bytes, 8 * a_sw, layout_type_for_bytes(a_sw));
+  // B = x slabs: 64-channel boxes of KP + S - 1 pixel rows
+  int block_n = std::min(Cx, 128);
+  while (S * block_n > 512) block_n >>= 1;
+  if (block_n < 64) return GABRIL_ERR_BAD_SHAPE;
+  const int slab_rows = KP + S - 1;
+  p.block_n = block_n;
+  p.b_box_w = 64;
+  p.b_boxes = block_n / 64;
+  p.slab_tx_bytes = (uint32_t)slab_rows * 128u;
+  p.b_tap_bytes = round_up(p.slab_tx_bytes, 1024);  // one slab box
+  p.b_box_bytes = p.b_tap_bytes;
+  p.desc_b_hi = desc_hi(p.b_tap_bytes, 1024, 2);
+  int rpg = std::max(1, std::min(R, 512 / (S * block_n)));  // filter rows per CTA
+  while (rpg > 1 && 2 * (p.a_stage_bytes + (uint32_t)(rpg * p.b_boxes) * p.b_tap_bytes) > 200u * 1024u) --rpg;
+  p.rows_per_group = rpg;
+  p.n_acc = rpg * S;
+  p.taps = T;
+  p.tap_groups = (R + rpg - 1) / rpg;
+  p.S = S;
+  p.b_stage_bytes = (uint32_t)(rpg * p.b_boxes) * p.b_tap_bytes;
+  p.mma_k = KP / 16; p.mma_groups = 1; p.g_taps = 1;
+  p.a_kstep = (uint32_t)((16 * a_sw) >> 4);
+  p.b_kstep = (uint32_t)((16 * 128) >> 4);
+  p.idesc = make_idesc(1, 1, 128, block_n);
+  p.M_total[0] = Cy;
+  p.N_total = Cx;
+  p.kb_total = (int)((P + KP - 1) / KP);
+  {
+    uint64_t dims[2] = {(uint64_t)Cy, (uint64_t)P};
+    uint64_t strides[1] = {(uint64_t)Cy * 2};
+    uint32_t box[2] = {(uint32_t)aw, (uint32_t)KP};
+    rc = tiled_map(&p.mapA[0], dy, 2, dims, strides, box, a_sw);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)Cx, (uint64_t)P};
+    uint64_t strides[1] = {(uint64_t)Cx * 2};
+    uint32_t box[2] = {64u, (uint32_t)slab_rows};
+    rc = tiled_map(&p.mapB, x, 2, dims, strides, box, 128);
+    if (rc) return rc;
+  }
+  const int m_tiles = (Cy + 127) / 128, n_tiles = Cx / block_n;
+  const int base = m_tiles * n_tiles * p.tap_groups;
+  int splits = std::max(1, std::min(p.kb_total, (g_num_sms + base - 1) / base));
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.out_mode = tc::OUT_F32_ATOMIC;
+  p.out = dw;
+  p.ldo = (long long)T * Cx;
+  p.tap_stride = Cx;
+  p.err_flag = g_err_flag;
+  size_t smem;
+  pick_stages(p, &smem, 1);
+  const int mt[1] = {m_tiles};
+  finalize_schedule(p, mt, n_tiles * p.tap_groups, splits, p.n_acc * block_n, 1);
+  p.acc_bufs = 1;
+  p.tmem_cols = (uint32_t)p.acc_stride;
+  return tc::launch(p, 1 << 30, smem, stream);
+}
+
+// conv_1 as a patch GEMM whose rows are in space-to-depth order: row = ((n*SH + sh)*SW + sw)*4 + q
+// is pixel (2*sh + q/2 - 1, 2*sw + q%2 - 1) of the img_h x img_w output; rows of padding pixels
+// store exact zeros (they are the zero border the next layer's flat-slab convolution reads).
+int gabril_conv1_s2d_fwd(const void* patches, const void* w, const float* bias, void* y, int N,
+                         int SH, int SW, int img_h, int img_w, int Kp, int Cout, int relu,
+                         cudaStream_t stream) {
+  int rc = resolve_driver();
+  if (rc) return rc;
+  if (Kp % 32 || !fwd_cout_ok(Cout) || N <= 0) return GABRIL_ERR_BAD_SHAPE;
+  const int kc = (Kp % 64 == 0) ? 64 : 32;
+  const int block_n = std::min(Cout, 128);
+  tc::Params p;
+  zero_params(p);
+  p.kind = tc::KIND_FWD;
+  p.n_classes = 1;
+  fwd_schedule(p, kc, block_n, 0);
+  const long long M = (long long)N * SH * SW * 4;
+  if (M >= (1ll << 31)) return GABRIL_ERR_BAD_SHAPE;
+  p.M_total[0] = (int)M;
+  p.N_total = Cout;
+  p.taps = 1; p.S = 1; p.S_w = 1; p.r_step = 1; p.s_step = 1;
+  p.chunks_per_tap = Kp / kc;
+  p.kb_total = p.chunks_per_tap;
+  p.kb_per_split = p.kb_total;
+  p.OW[0] = 1; p.OHW[0] = 1;
+  p.trav_stride_w = 1; p.trav_stride_h = 1;
+  uint64_t dims[2] = {(uint64_t)Kp, (uint64_t)M};
+  uint64_t strides[1] = {(uint64_t)Kp * 2};
+  uint32_t box[2] = {(uint32_t)kc, 128};
+  rc = tiled_map(&p.mapA[0], patches, 2, dims, strides, box, kc * 2);
+  if (rc) return rc;
+  rc = weight_map(&p.mapB, w, Cout, 1, Kp, 0, kc, block_n);
+  if (rc) return rc;
+  p.out_mode = tc::OUT_BF16;
+  p.out = y; p.ldo = Cout;
+  p.bias = bias; p.relu = relu;
+  p.border_h = SH; p.border_w = SW; p.s2d_H = img_h; p.s2d_W = img_w;
+  p.err_flag = g_err_flag;
+  size_t smem;
+  const int occ = occ_setting();
+  pick_stages(p, &smem, occ);
+  const int mt[1] = {(int)((M + 127) / 128)};
+  finalize_schedule(p, mt, Cout / block_n, 1, block_n, occ);
+  return tc::launch(p, g_num_sms * occ, smem, stream);
+}
+
 }  // extern "C"

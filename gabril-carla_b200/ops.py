@@ -122,6 +122,83 @@ def conv_wgrad(dy, x, dw, R, S, stride, pad, direct_store=False):
     return dw
 
 
+
+# ---- flat-slab convolutions over zero-bordered tensors (csrc/tc_plan.cu) ----------------------
+def conv_flat(x, w, y, R, S, *, bias=None, resid=None, gate=None, valid=None, out_geom=None, relu=False,
+              transpose_w=False):
+    """x [N,Hg,Wg,Cx] bf16 zero-bordered; out(q) = sum_{r,s} x_flat[q + r*Wg + s] . W(r,s) for every
+    flat pixel q.  valid=(vh, vw), out_geom=(o_rows, o_pitch, off_h, off_w): pixel (n,i,j) with
+    i<vh, j<vw is stored at y row (n*o_rows + i+off_h)*o_pitch + j+off_w; valid=None stores every
+    pixel at its own index.  transpose_w: w is [Cx,R*S,Cy] and taps are flipped (dgrad)."""
+    _chk_bf16(x, "x"); _chk_bf16(w, "w"); _chk_bf16(y, "y"); _chk_bf16(resid, "resid"); _chk_bf16(gate, "gate")
+    N, Hg, Wg, Cx = x.shape
+    Cy = w.shape[2] if transpose_w else w.shape[0]
+    assert w.shape[1] == R * S and (w.shape[0] if transpose_w else w.shape[2]) == Cx, (w.shape, R, S, Cx)
+    vh, vw = valid if valid is not None else (0, 0)
+    o_rows, o_pitch, off_h, off_w = out_geom if out_geom is not None else (Hg, Wg, 0, 0)
+    if valid is None:
+        assert y.numel() == N * Hg * Wg * Cy, (y.shape, N, Hg, Wg, Cy)
+    else:
+        assert y.numel() == N * o_rows * o_pitch * Cy, (y.shape, N, o_rows, o_pitch, Cy)
+        assert vh + off_h <= o_rows and vw + off_w <= o_pitch
+    with _span("tc_gemm_kernel", f"{'dgrad' if transpose_w else 'fwd'}-flat {Cx}->{Cy} k{R}x{S}",
+               2.0 * N * (vh or Hg) * (vw or Wg) * Cy * R * S * Cx, "flop"):
+        st = _fn("gabril_conv_flat")(ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(gate), ptr(y), c_int(N),
+                                     c_int(Hg), c_int(Wg), c_int(Cx), c_int(Cy), c_int(R), c_int(S),
+                                     c_int(vh), c_int(vw), c_int(o_rows), c_int(o_pitch), c_int(off_h),
+                                     c_int(off_w), c_int(int(relu)), c_int(int(transpose_w)), stream())
+    _lib.check(st, "gabril_conv_flat")
+    return y
+
+
+def conv_wgrad_flat(dy, x, dw, R, S, dy_row_off, flop_pixels=None):
+    """dw [Cy,R*S,Cx] fp32 += sum_q dy_flat[q + dy_row_off]^T x_flat[q + r*Wg + s]; dy [N,Hg,Wg,Cy] and
+    x [N,Hg,Wg,Cx] share one zero-bordered grid."""
+    _chk_bf16(dy, "dy"); _chk_bf16(x, "x")
+    N, Hg, Wg, Cx = x.shape
+    Cy = dy.shape[-1]
+    assert dy.numel() == N * Hg * Wg * Cy and dw.dtype == torch.float32 and dw.numel() == Cy * R * S * Cx
+    px = flop_pixels if flop_pixels is not None else N * Hg * Wg
+    with _span("tc_gemm_kernel", f"wgrad-flat {Cx}x{Cy} k{R}x{S}", 2.0 * px * Cy * R * S * Cx, "flop"):
+        st = _fn("gabril_conv_wgrad_flat")(ptr(dy), ptr(x), ptr(dw), c_int(N), c_int(Hg), c_int(Wg), c_int(Cx),
+                                           c_int(Cy), c_int(R), c_int(S), c_int(dy_row_off), stream())
+    _lib.check(st, "gabril_conv_wgrad_flat")
+    return dw
+
+
+def conv1_s2d_fwd(patches, w, bias, y, N, SH, SW, img_h, img_w, relu=True):
+    """patches bf16 [N*SH*SW*4, Kp] (space-to-depth row order), w [Cout,1,Kp] -> y [N,SH,SW,4*Cout];
+    rows of padding pixels are stored as exact zeros."""
+    _chk_bf16(patches, "patches"); _chk_bf16(w, "w"); _chk_bf16(y, "y")
+    Kp = patches.shape[1]
+    Cout = w.shape[0]
+    assert patches.shape[0] == N * SH * SW * 4 and y.numel() == N * SH * SW * 4 * Cout
+    with _span("tc_gemm_kernel", f"fwd {Kp}->{Cout} k1s1", 2.0 * N * img_h * img_w * Cout * Kp, "flop"):
+        st = _fn("gabril_conv1_s2d_fwd")(ptr(patches), ptr(w), ptr(bias), ptr(y), c_int(N), c_int(SH), c_int(SW),
+                                         c_int(img_h), c_int(img_w), c_int(Kp), c_int(Cout), c_int(int(relu)),
+                                         stream())
+    _lib.check(st, "gabril_conv1_s2d_fwd")
+    return y
+
+
+def obs_patches_s2d(frames, S, center, grayscale, SH, SW, out):
+    """uint8 [B,L,H,W,3] -> bf16 patch rows in space-to-depth order (out must start zeroed: rows of
+    padding pixels are never written)."""
+    _chk(frames, torch.uint8, "frames")
+    B, L, H, W, C = frames.shape
+    Kp = conv1_kp(S, grayscale)
+    assert out.shape == (B * SH * SW * 4, Kp) and out.dtype == torch.bfloat16
+    _call("gabril_obs_patches_s2d", ptr(frames), ptr(out), c_int(B), c_int(L), c_int(S), c_int(center),
+          c_int(H), c_int(W), c_int(int(grayscale)), c_int(Kp), c_int(SH), c_int(SW), stream(),
+          work=float(B * S * H * W * 3 + B * (H // 2) * (W // 2) * Kp * 2))
+    return out
+
+
+def s2d_weight_taps():
+    """Permutation of the 16 taps of a k4/s2 filter into (r', s', qh, qw) order: the 2x2 stride-1
+    filter over the space-to-depth input has tap (r', s') = [W(2r'+qh, 2s'+qw) for qh, qw]."""
+    return [(2 * r + qh) * 4 + (2 * s + qw) for r in range(2) for s in range(2) for qh in range(2) for qw in range(2)]
+
 # ---- layout helpers (host-side plumbing, torch ops) ------------------------------------------
 def w_oihw_to_internal(w_oihw: torch.Tensor) -> torch.Tensor:
     """[Cout,Cin,R,S] -> [Cout,R*S,Cin] (same dtype)."""

@@ -87,6 +87,11 @@ int gabril_obs_format(const uint8_t* frames, float* out, int B, int L, int S, in
  * (r*4+s)*S*C' + frame*C' + c, zero padded to Kp: formatting and im2col fused in one pass. */
 int gabril_obs_patches(const uint8_t* frames, void* patches_bf16, int B, int L, int S, int center,
                        int H, int W, int grayscale, int Kp, cudaStream_t stream);
+/* Same patches, rows in space-to-depth order over the one-pixel-padded conv_1 output: row
+ * ((b*SH + sh)*SW + sw)*4 + q holds output pixel (2*sh + q/2 - 1, 2*sw + q%2 - 1); rows of padding
+ * pixels are left untouched (allocate the matrix zeroed).  Feeds gabril_conv1_s2d_fwd. */
+int gabril_obs_patches_s2d(const uint8_t* frames, void* patches_bf16, int B, int L, int S, int center,
+                           int H, int W, int grayscale, int Kp, int SH, int SW, cudaStream_t stream);
 
 /* ---- gaze heat maps: GazePreprocessor.forward (data_loader_robomimic.py:85-139) and
  * build_stack_heatmaps (:204-278) in one kernel.  gaze: fp32 [B, L, P*2] ((x, y) in [0,1], negative
@@ -151,6 +156,21 @@ int gabril_adam(float* p, const float* g, float* m, float* v, void* shadow_bf16,
 int gabril_cast_f32_bf16(const float* x, void* y_bf16, long long n, cudaStream_t stream);
 /* t[row][c] *= scale[row] in place; t bf16 [rows, C] (GMD backward, gaze_utils.py:51: dz = dz' * M). */
 int gabril_rowscale_bf16(void* t, const float* scale, long long rows, int C, cudaStream_t stream);
+
+/* ---- flat-slab convolutions (stride 1) over zero-bordered NHWC tensors: one TMA slab per filter
+ * row, the S taps of the row are descriptor views shifted by whole pixel rows.  Replaces the same
+ * nn.Conv2d forward / backward (linear_models.py:141-207) as gabril_conv_fwd/_dgrad/_wgrad; the
+ * k4/s2/p1 conv_2 runs through it as a 2x2 stride-1 convolution over the space-to-depth conv_1
+ * output.  See csrc/tc_plan.cu for the exact index conventions. ------------------------------- */
+int gabril_conv_flat(const void* x, const void* w, const float* bias, const void* resid,
+                     const void* gate, void* y, int N, int Hg, int Wg, int Cx, int Cy, int R, int S,
+                     int valid_h, int valid_w, int o_rows, int o_pitch, int o_off_h, int o_off_w,
+                     int relu, int transpose_w, cudaStream_t stream);
+int gabril_conv_wgrad_flat(const void* dy, const void* x, float* dw, int N, int Hg, int Wg, int Cx,
+                           int Cy, int R, int S, int dy_row_off, cudaStream_t stream);
+int gabril_conv1_s2d_fwd(const void* patches, const void* w, const float* bias, void* y, int N,
+                         int SH, int SW, int img_h, int img_w, int Kp, int Cout, int relu,
+                         cudaStream_t stream);
 
 #ifdef __cplusplus
 }

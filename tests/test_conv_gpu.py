@@ -101,3 +101,56 @@ def test_unsupported_shapes_fail_loudly(ops):
     dw = torch.zeros(32, 1, 96, device=DEV)
     with pytest.raises(RuntimeError):
         ops.conv_wgrad(dy, x, dw, 1, 1, 1, 0)  # Cin = 96 is not 32 / 64 / k*128
+
+
+# ---- flat-slab convolutions (one TMA slab per filter row, taps as shifted descriptor views) ----
+FLAT = [
+    # name, H, W, Cin, Cout, R, pad  (stride-1 'same'/valid convs on a zero-bordered grid)
+    ("res3x3", 20, 38, 128, 32, 3, 1),
+    ("conv4", 22, 40, 128, 128, 3, 0),
+    ("conv6", 20, 38, 128, 64, 5, 2),
+    ("dec1", 20, 38, 64, 128, 3, 1),
+]
+
+
+@pytest.mark.parametrize("N", [2, 37])
+@pytest.mark.parametrize("layer", FLAT, ids=[l[0] for l in FLAT])
+def test_conv_flat_fwd_dgrad_wgrad(ops, layer, N):
+    from gabril_carla_b200 import _lib
+    name, H, W, Cin, Cout, R, pad = layer
+    g = torch.Generator().manual_seed(len(name) * 11 + N)
+    Hg, Wg = H + 2 * pad, W + 2 * pad
+    OH, OW = Hg - R + 1, Wg - R + 1
+    x = (torch.randn(N, H, W, Cin, generator=g) * 0.5).to(torch.bfloat16)
+    w = (torch.randn(Cout, Cin, R, R, generator=g) / (Cin * R * R) ** 0.5).to(torch.bfloat16)
+    bias = torch.randn(Cout, generator=g)
+    dy = (torch.randn(N, OH, OW, Cout, generator=g) * 0.5).to(torch.bfloat16)
+    xp = torch.zeros(N, Hg, Wg, Cin, dtype=torch.bfloat16)
+    xp[:, pad:pad + H, pad:pad + W] = x
+    xd, wd = xp.to(DEV), ops.w_oihw_to_internal(w).to(DEV)
+    x64, w64, dy64 = x.double().permute(0, 3, 1, 2), w.double(), dy.double().permute(0, 3, 1, 2)
+    # forward into a tensor with a 1-pixel border (borders must stay untouched)
+    y = torch.full((N, OH + 2, OW + 2, Cout), 7.0, device=DEV, dtype=torch.bfloat16)
+    ops.conv_flat(xd, wd, y, R, R, bias=bias.to(DEV), valid=(OH, OW), out_geom=(OH + 2, OW + 2, 1, 1), relu=True)
+    ref = F.relu(F.conv2d(x64, w64, bias.double(), padding=pad).permute(0, 2, 3, 1))
+    yc = y.cpu()
+    assert rel(yc[:, 1:-1, 1:-1], ref) <= 4e-3
+    assert (yc[:, 0] == 7).all() and (yc[:, -1] == 7).all() and (yc[:, :, 0] == 7).all() and (yc[:, :, -1] == 7).all()
+    # dgrad: dy zero-bordered by R-1 on the x grid; every pixel of the x grid is produced, gated
+    dyp = torch.zeros(N, Hg + R - 1, Wg + R - 1, Cout, dtype=torch.bfloat16)
+    dyp[:, R - 1:R - 1 + OH, R - 1:R - 1 + OW] = dy
+    gate = torch.randn(N, Hg, Wg, Cin, generator=g).to(torch.bfloat16)
+    if Cout % 64 == 0:  # the slab contraction runs over 64-channel chunks
+        dx = torch.full((N, Hg, Wg, Cin), float("nan"), device=DEV, dtype=torch.bfloat16)
+        ops.conv_flat(dyp.to(DEV), wd, dx, R, R, gate=gate.to(DEV), valid=(Hg, Wg), out_geom=(Hg, Wg, 0, 0),
+                      transpose_w=True)
+        dref = torch.nn.grad.conv2d_input((N, Cin, Hg, Wg), w64, dy64).permute(0, 2, 3, 1) * (gate.double() > 0)
+        assert rel(dx.cpu(), dref) <= 4e-3
+    # wgrad on the x grid: dy stored at the top-left of a zero tensor with x's geometry
+    dyg = torch.zeros(N, Hg, Wg, Cout, dtype=torch.bfloat16)
+    dyg[:, :OH, :OW] = dy
+    dw = torch.zeros(Cout, R * R, Cin, device=DEV, dtype=torch.float32)
+    ops.conv_wgrad_flat(dyg.to(DEV), xd, dw, R, R, 0)
+    wref = ops.w_oihw_to_internal(torch.nn.grad.conv2d_weight(x64, (Cout, Cin, R, R), dy64, padding=pad))
+    assert rel(dw.cpu(), wref) <= 2e-5
+    _lib.poll_error()
