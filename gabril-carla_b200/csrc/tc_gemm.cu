@@ -94,7 +94,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
     // Issuing a tensor-map copy costs the issuing thread hundreds of cycles, so the smem stages
     // are dealt round-robin to kProducers threads in different warps.  A stage is always served
     // by the same thread (in iteration order), which keeps the parity waits unambiguous.
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       const int me = warp - kFirstProducerWarp;
       ptx::tma_prefetch_desc(&p.mapA[0]);
       ptx::tma_prefetch_desc(&p.mapB);
@@ -260,7 +260,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
     }
   } else if (warp == kMmaWarp) {
     // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       int it = 0, tcount = 0;
       bool ok = true;
       const int mma_k = p.mma_k, mma_groups = p.mma_groups, g_taps = p.g_taps;
