@@ -352,9 +352,10 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
                       128, 1);
     }
     if (rc) return rc;
-  } else if (stride == 2 && R == 4 && S == 4 && pad == 1) {
-    // Input pixel (ih, iw) of parity (a_h, a_w) receives exactly 2x2 taps: kh = 3 - a_h - 2 r',
-    // read from dy row j_h - 1 + a_h + r'  (j_h = ih / 2).  Four stride-1 sub-convolutions.
+  } else if (stride == 2 && R == 4 && S == 4 && (pad == 1 || pad == 0)) {
+    // Input pixel ih = 2*jh + a_h receives exactly two filter rows: kh = b_h + 2 - 2r' with
+    // b_h = (a_h + pad) & 1, read from dy row jh + c_h - 1 + r', c_h = (a_h + pad - b_h) / 2
+    // (same along w).  Four stride-1 sub-convolutions, one per input parity class.
     p.n_classes = 4;
     p.a_im2col = 1;
     p.remap = 1; p.remap_sh = 2; p.remap_sw = 2;
@@ -364,12 +365,14 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
     p.r_step = -2; p.s_step = -2;
     for (int c = 0; c < 4; ++c) {
       const int ah = c >> 1, aw = c & 1;
+      const int bh = (ah + pad) & 1, bw_ = (aw + pad) & 1;
+      const int ch = (ah + pad - bh) / 2, cw = (aw + pad - bw_) / 2;
       const int Hs = (H - ah + 1) / 2, Ws = (W - aw + 1) / 2;
       p.ah[c] = ah; p.aw[c] = aw; p.Hs[c] = Hs; p.Ws[c] = Ws;
       p.M_total[c] = N * Hs * Ws;
       p.OW[c] = Ws; p.OHW[c] = Hs * Ws;
-      p.lower_w[c] = aw - 1; p.lower_h[c] = ah - 1;
-      p.r_base[c] = 3 - ah; p.s_base[c] = 3 - aw;
+      p.lower_w[c] = cw - 1; p.lower_h[c] = ch - 1;
+      p.r_base[c] = bh + 2; p.s_base[c] = bw_ + 2;
       const int upper_w = p.lower_w[c] + Ws - OW, upper_h = p.lower_h[c] + Hs - OH;
       rc = im2col_map(&p.mapA[c], dy, N, OH, OW, Cout, p.lower_w[c], p.lower_h[c], upper_w,
                       upper_h, kc, 128, 1);

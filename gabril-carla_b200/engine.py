@@ -56,8 +56,16 @@ class StepEngine:
         def act(h, w, c):
             return torch.empty(B, h, w, c, device=dev, dtype=bf)
         b = {}
-        b["patches"] = torch.empty(B * s.H1 * s.W1, s.K1p, device=dev, dtype=bf)
-        b["a1"], b["a2"], b["a3"] = act(s.H1, s.W1, s.C1), act(s.H2, s.W2, s.C2), act(s.H3, s.W3, s.NH)
+        # conv_1 / conv_2 live on a space-to-depth grid: a1s[B,SH,SW,(qh,qw,C1)] holds conv_1 output
+        # pixel (2*sh+qh-1, 2*sw+qw-1) (a one-pixel zero border included), so that the k4/s2/p1
+        # conv_2 is a 2x2 stride-1 flat-slab convolution; a2p / da2p are conv_2's output and its
+        # gradient with a one-pixel zero border on the same [SH, SW] grid (conv_3 reads them with pad 0).
+        self.SH, self.SW = s.H2 + 2, s.W2 + 2
+        assert s.H1 % 2 == 0 and s.W1 % 2 == 0 and (4 * s.C1) % 64 == 0 and s.C2 % 64 == 0
+        zact = lambda h, w, c: torch.zeros(B, h, w, c, device=dev, dtype=bf)  # noqa: E731
+        b["patches"] = torch.zeros(B * self.SH * self.SW * 4, s.K1p, device=dev, dtype=bf)
+        b["a1s"], b["a2p"] = zact(self.SH, self.SW, 4 * s.C1), zact(self.SH, self.SW, s.C2)
+        b["a3"] = act(s.H3, s.W3, s.NH)
         b["r-1"] = act(s.h, s.w, s.NH)  # relu(conv_4): the input of the first Residual
         for i in range(s.NR):
             b[f"h{i}"] = act(s.h, s.w, s.RH)
@@ -85,7 +93,8 @@ class StepEngine:
         b["da5"] = act(s.h, s.w, s.NH)
         b["dt_a"], b["dt_b"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.NH)
         b["dh"] = act(s.h, s.w, s.RH)
-        b["da3"], b["da2"], b["da1"] = act(s.H3, s.W3, s.NH), act(s.H2, s.W2, s.C2), act(s.H1, s.W1, s.C1)
+        b["da3"] = act(s.H3, s.W3, s.NH)
+        b["da2p"], b["da1s"] = zact(self.SH, self.SW, s.C2), zact(self.SH, self.SW, 4 * s.C1)
         self.buf, self.B = b, B
         # split-K for the pre_actor GEMM: enough CTAs to cover the machine
         m_tiles = (B + 127) // 128
@@ -108,7 +117,7 @@ class StepEngine:
         b = self.buf
         center = L - 1
         # ---- preprocessing (prepare_for_bc, data_loader_robomimic.py:318-360) ----
-        ops.obs_patches(frames, self.S, center, self.grayscale, out=b["patches"])
+        ops.obs_patches_s2d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["patches"])
         if self.use_reg or self.use_gmd:
             self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
         rowmask = None
@@ -120,11 +129,11 @@ class StepEngine:
                          ws=(b["K"], b["mnmx"]))
             rowmask = b["rowmask"]
         # ---- encoder (linear_models.py:191-207) ----
-        M1 = B * s.H1 * s.W1
-        ops.conv_fwd(b["patches"].view(M1, 1, 1, s.K1p), a.WB("enc.conv1.w"), a.P("enc.conv1.b"),
-                     b["a1"], 1, 1, 1, 0, relu=True)
-        ops.conv_fwd(b["a1"], a.WB("enc.conv2.w"), a.P("enc.conv2.b"), b["a2"], 4, 4, 2, 1, relu=True)
-        ops.conv_fwd(b["a2"], a.WB("enc.conv3.w"), a.P("enc.conv3.b"), b["a3"], 4, 4, 2, 1, relu=True)
+        ops.conv1_s2d_fwd(b["patches"], a.WB("enc.conv1.w"), a.P("enc.conv1.b"), b["a1s"], B, self.SH,
+                          self.SW, s.H1, s.W1, relu=True)
+        ops.conv_flat(b["a1s"], a.WB("enc.conv2.w"), b["a2p"], 2, 2, bias=a.P("enc.conv2.b"),
+                      valid=(s.H2, s.W2), out_geom=(self.SH, self.SW, 1, 1), relu=True)
+        ops.conv_fwd(b["a2p"], a.WB("enc.conv3.w"), a.P("enc.conv3.b"), b["a3"], 4, 4, 2, 0, relu=True)
         # conv_4 has no activation of its own; the first Residual's in-place ReLU rectifies it (F7)
         ops.conv_fwd(b["a3"], a.WB("enc.conv4.w"), a.P("enc.conv4.b"), b["r-1"], 3, 3, 1, 0, relu=True)
         for i in range(s.NR):
@@ -216,18 +225,33 @@ class StepEngine:
         ops.conv_wgrad(dt, b["a3"], a.G("enc.conv4.w"), 3, 3, 1, 0)
         ops.conv_dgrad(dt, a.WB("enc.conv4.w"), b["da3"], 3, 3, 1, 0, gate=b["a3"])
         ops.colsum_bf16(b["da3"], a.G("enc.conv3.b"))
-        ops.conv_wgrad(b["da3"], b["a2"], a.G("enc.conv3.w"), 4, 4, 2, 1)
-        ops.conv_dgrad(b["da3"], a.WB("enc.conv3.w"), b["da2"], 4, 4, 2, 1, gate=b["a2"])
-        ops.colsum_bf16(b["da2"], a.G("enc.conv2.b"))
-        ops.conv_wgrad(b["da2"], b["a1"], a.G("enc.conv2.w"), 4, 4, 2, 1)
-        ops.conv_dgrad(b["da2"], a.WB("enc.conv2.w"), b["da1"], 4, 4, 2, 1, gate=b["a1"])
-        M1 = B * s.H1 * s.W1
-        ops.colsum_bf16(b["da1"], a.G("enc.conv1.b"))
-        ops.conv_wgrad(b["da1"].view(M1, 1, 1, s.C1), b["patches"].view(M1, 1, 1, s.K1p),
+        # conv_3 over the zero-bordered a2p (pad 0): the border gradients are gated to zero by a2p itself
+        ops.conv_wgrad(b["da3"], b["a2p"], a.G("enc.conv3.w"), 4, 4, 2, 0)
+        ops.conv_dgrad(b["da3"], a.WB("enc.conv3.w"), b["da2p"], 4, 4, 2, 0, gate=b["a2p"])
+        ops.colsum_bf16(b["da2p"], a.G("enc.conv2.b"))
+        # conv_2 on the space-to-depth grid: dY pixel (i, j) sits at flat row q + SW + 1
+        ops.conv_wgrad_flat(b["da2p"], b["a1s"], a.G("enc.conv2.w"), 2, 2, self.SW + 1,
+                            flop_pixels=B * s.H2 * s.W2)
+        ops.conv_flat(b["da2p"], a.WB("enc.conv2.w"), b["da1s"], 2, 2, gate=b["a1s"], transpose_w=True,
+                      flop_pixels=B * s.H2 * s.W2)  # algorithmic FLOPs of the k4/s2 dgrad
+        M1 = B * self.SH * self.SW * 4
+        ops.colsum_bf16(b["da1s"].view(M1, s.C1), a.G("enc.conv1.b"))
+        ops.conv_wgrad(b["da1s"].view(M1, 1, 1, s.C1), b["patches"].view(M1, 1, 1, s.K1p),
                        a.G("enc.conv1.w"), 1, 1, 1, 0)
         self._accum_count += 1
         if self.on_all_grads_ready is not None:
             self.on_all_grads_ready()
+
+    def activation(self, name: str) -> torch.Tensor:
+        """Stored activation `name` as a plain NHWC tensor (tests / debugging): undoes the
+        space-to-depth / zero-border storage of conv_1 and conv_2 outputs."""
+        s, b = self.spec, self.buf
+        if name == "a1":
+            t = b["a1s"].view(self.B, self.SH, self.SW, 2, 2, s.C1).permute(0, 1, 3, 2, 4, 5)
+            return t.reshape(self.B, 2 * self.SH, 2 * self.SW, s.C1)[:, 1:1 + s.H1, 1:1 + s.W1].contiguous()
+        if name == "a2":
+            return b["a2p"][:, 1:1 + s.H2, 1:1 + s.W2].contiguous()
+        return b[name]
 
     def _mask_rows(self, t, rowmask):
         # dz * M as a 1x1 "identity-free" epilogue: reuse the dgrad rowmask path would need a second

@@ -93,7 +93,11 @@ class PolicySpec:
             conv(f"res{i}.c3", f"_residual_stack._layers.{i}._block.1", s.RH, s.NH, 3)
         conv("conv4", "_conv_4", s.NH, s.NH, 3); bias("conv4", "_conv_4", s.NH)
         conv("conv3", "_conv_3", s.NH, s.C2, 4); bias("conv3", "_conv_3", s.NH)
-        conv("conv2", "_conv_2", s.C2, s.C1, 4); bias("conv2", "_conv_2", s.C2)
+        # conv_2 (k4/s2/p1) runs as a 2x2 stride-1 convolution over the space-to-depth conv_1 output:
+        # its 16 taps are stored as [Cout][(r',s')][(qh,qw,cin)] with (kh, kw) = (2r'+qh, 2s'+qw)
+        e.append(Entry("enc.conv2.w", "encoder", "_conv_2.weight", "conv_s2d", (s.C2, s.C1, 4, 4),
+                       (s.C2, 4, 4 * s.C1)))
+        bias("conv2", "_conv_2", s.C2)
         e.append(Entry("enc.conv1.w", "encoder", "_conv_1.weight", "conv1", (s.C1, s.C0, 4, 4), (s.C1, 1, s.K1p)))
         bias("conv1", "_conv_1", s.C1)
         off = 0
@@ -110,6 +114,10 @@ def to_internal(ent: Entry, t: torch.Tensor, spec: PolicySpec) -> torch.Tensor:
     if ent.kind == "conv":
         co, ci, r, s_ = t.shape
         return t.permute(0, 2, 3, 1).reshape(co, r * s_, ci).contiguous()
+    if ent.kind == "conv_s2d":
+        co, ci, r, s_ = t.shape  # r = s_ = 4
+        w = t.permute(0, 2, 3, 1).reshape(co, 2, 2, 2, 2, ci)       # [co, r', qh, s', qw, ci]
+        return w.permute(0, 1, 3, 2, 4, 5).reshape(co, 4, 4 * ci).contiguous()
     if ent.kind == "conv1":
         co, ci, r, s_ = t.shape
         flat = t.permute(0, 2, 3, 1).reshape(co, r * s_ * ci)
@@ -139,6 +147,10 @@ def to_reference(ent: Entry, t: torch.Tensor, spec: PolicySpec) -> torch.Tensor:
     if ent.kind == "conv":
         co, ci, r, s_ = ent.ref_shape
         return t.reshape(co, r, s_, ci).permute(0, 3, 1, 2).contiguous()
+    if ent.kind == "conv_s2d":
+        co, ci, r, s_ = ent.ref_shape
+        w = t.reshape(co, 2, 2, 2, 2, ci).permute(0, 1, 3, 2, 4, 5)  # [co, r', qh, s', qw, ci]
+        return w.reshape(co, 4, 4, ci).permute(0, 3, 1, 2).contiguous()
     if ent.kind == "conv1":
         co, ci, r, s_ = ent.ref_shape
         return t[:, 0, :spec.K1].reshape(co, r, s_, ci).permute(0, 3, 1, 2).contiguous()
@@ -235,7 +247,7 @@ class ParamArena:
         gain = nn.init.calculate_gain("relu")
         for e in reversed(self.entries):
             t = torch.zeros(e.ref_shape)
-            if e.kind in ("conv", "conv1"):
+            if e.kind in ("conv", "conv1", "conv_s2d"):
                 nn.init.orthogonal_(t, gain)
             elif e.kind in ("linear", "pre_actor", "head"):
                 nn.init.orthogonal_(t)

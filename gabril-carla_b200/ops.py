@@ -125,7 +125,7 @@ def conv_wgrad(dy, x, dw, R, S, stride, pad, direct_store=False):
 
 # ---- flat-slab convolutions over zero-bordered tensors (csrc/tc_plan.cu) ----------------------
 def conv_flat(x, w, y, R, S, *, bias=None, resid=None, gate=None, valid=None, out_geom=None, relu=False,
-              transpose_w=False):
+              transpose_w=False, flop_pixels=None):
     """x [N,Hg,Wg,Cx] bf16 zero-bordered; out(q) = sum_{r,s} x_flat[q + r*Wg + s] . W(r,s) for every
     flat pixel q.  valid=(vh, vw), out_geom=(o_rows, o_pitch, off_h, off_w): pixel (n,i,j) with
     i<vh, j<vw is stored at y row (n*o_rows + i+off_h)*o_pitch + j+off_w; valid=None stores every
@@ -142,7 +142,8 @@ def conv_flat(x, w, y, R, S, *, bias=None, resid=None, gate=None, valid=None, ou
         assert y.numel() == N * o_rows * o_pitch * Cy, (y.shape, N, o_rows, o_pitch, Cy)
         assert vh + off_h <= o_rows and vw + off_w <= o_pitch
     with _span("tc_gemm_kernel", f"{'dgrad' if transpose_w else 'fwd'}-flat {Cx}->{Cy} k{R}x{S}",
-               2.0 * N * (vh or Hg) * (vw or Wg) * Cy * R * S * Cx, "flop"):
+               2.0 * (flop_pixels if flop_pixels is not None else N * (vh or Hg) * (vw or Wg)) * Cy * R * S * Cx,
+               "flop"):
         st = _fn("gabril_conv_flat")(ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(gate), ptr(y), c_int(N),
                                      c_int(Hg), c_int(Wg), c_int(Cx), c_int(Cy), c_int(R), c_int(S),
                                      c_int(vh), c_int(vw), c_int(o_rows), c_int(o_pitch), c_int(off_h),

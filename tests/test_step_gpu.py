@@ -29,7 +29,7 @@ def our_activations(eng):
     """Stored activations of the CUDA path as reference-layout (NCHW fp32, CPU) tensors."""
     out = {}
     for k in ["a1", "a2", "a3", "r-1", "a5", "z"] + [f"{p}{i}" for i in range(eng.spec.NR) for p in "hr"]:
-        out[k] = eng.buf[k].float().cpu().permute(0, 3, 1, 2).contiguous()
+        out[k] = eng.activation(k).float().cpu().permute(0, 3, 1, 2).contiguous()
     out["zf"] = eng.buf["zf"].float().cpu()
     out["act1"] = eng.buf["act1"].float().cpu()
     return out
