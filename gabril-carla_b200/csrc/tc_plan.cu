@@ -478,10 +478,13 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
   }
   if (rc) return rc;
   const int m_tiles = (Cout + 127) / 128, n_tiles = Cin / block_n;
+  // every tile is its own CTA here (long split-K loops, up to 512 TMEM columns)
+  const int occ = (n_acc * block_n <= 256 && 2 * (p.a_stage_bytes + p.b_stage_bytes) <= 100 * 1024) ? 2 : 1;
   int splits = 1;
   if (!direct_store) {
+    // whole waves only: the CTA count never exceeds what is resident at once
     const int base = m_tiles * n_tiles * p.tap_groups;
-    splits = std::max(1, std::min(p.kb_total, (2 * g_num_sms + base - 1) / base));
+    splits = std::max(1, std::min(p.kb_total, (occ * g_num_sms) / base));
   }
   p.kb_per_split = (p.kb_total + splits - 1) / splits;
   splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
@@ -491,8 +494,6 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
   p.tap_stride = Cin;
   p.err_flag = g_err_flag;
   size_t smem;
-  // every tile is its own CTA here (long split-K loops, up to 512 TMEM columns)
-  const int occ = (n_acc * block_n <= 256 && 2 * (p.a_stage_bytes + p.b_stage_bytes) <= 100 * 1024) ? 2 : 1;
   pick_stages(p, &smem, occ);
   const int mt[1] = {m_tiles};
   finalize_schedule(p, mt, n_tiles * p.tap_groups, splits, n_acc * block_n, occ);
@@ -654,7 +655,7 @@ int gabril_conv_wgrad_flat(const void* dy, const void* x, float* dw, int N, int 
   }
   const int m_tiles = (Cy + 127) / 128, n_tiles = Cx / block_n;
   const int base = m_tiles * n_tiles * p.tap_groups;
-  int splits = std::max(1, std::min(p.kb_total, (g_num_sms + base - 1) / base));
+  int splits = std::max(1, std::min(p.kb_total, g_num_sms / base));  // one whole wave
   p.kb_per_split = (p.kb_total + splits - 1) / splits;
   splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
   p.out_mode = tc::OUT_F32_ATOMIC;
