@@ -152,6 +152,19 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows), "power_w_max": max(float(r[2]) for r in self.rows)}
 
 
+def load_tc_traffic(args, B):
+    """dram__bytes_read.sum + dram__bytes_write.sum of every tc_gemm_kernel launch of ONE step, from the
+    committed ncu pass (profiles/r1_tc_traffic.json); only quoted for the configuration it was taken on."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_tc_traffic.json")) as f:
+            t = json.load(f)
+        if B == 1024 and not args.rgb and args.gaze_method == "Reg" and args.dp_method == "None":
+            return t["dram_bytes_per_step"], t["source"]
+    except Exception:
+        pass
+    return None, None
+
+
 def load_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -273,6 +286,7 @@ def main_ours(args):
     hbm, tf_burst, tf_sust, how = load_peaks()
     total = B * world
     achieved = tc_flop / (tc_ms * 1e-3) / 1e12 if tc_ms > 0 else 0.0
+    traffic, traffic_src = load_tc_traffic(args, B)
     line = {
         "metric": "GABRIL train samples/sec (320x180 stack, fwd+bwd+gaze reg)",
         "value": total / (ms * 1e-3), "unit": "samples/s", "n_gpus": world, "steps": args.steps,
@@ -286,7 +300,9 @@ def main_ours(args):
                 "note": "pinned host batch -> double-buffered H2D on a copy stream -> step -> losses D2H, per rank"},
         "roofline": {"bound": "tensor", "kernel": "tc_gemm_kernel (every conv / linear fwd, dgrad, wgrad launch of one step)",
                      "achieved": achieved, "peak": tf_sust, "unit": "TFLOP/s", "frac": achieved / tf_sust,
-                     "peak_source": f"bf16_tflops_sustained, {how}", "traffic": None,
+                     "peak_source": f"bf16_tflops_sustained, {how}", "traffic": traffic,
+                     "traffic_unit": "bytes per step (all tc_gemm_kernel launches), like achieved", "traffic_source": traffic_src,
+                     "algorithmic_flop_per_step": tc_flop,
                      "tc_ms_per_step": tc_ms, "all_traced_ms_per_step": traced_ms,
                      "step_flop_frac_of_peak": FLOP_PER_SAMPLE[gray] * B / (ms * 1e-3) / 1e12 / tf_sust},
         "losses_last_step": {"actor": losses[0], "reg": losses[1], "total": losses[2]},
