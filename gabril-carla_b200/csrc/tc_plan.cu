@@ -254,10 +254,10 @@ int gabril_poll_error(void) {
 // y[N,OH,OW,Cout] = act( conv(x[N,H,W,Cin], w[Cout][R*S][Cin]) + bias + resid ) * rowmask
 // Cin == 0 mod 32, Cout in {32, 64, 128, 256...} (multiple of 32).  R = S = 1 with H = W = 1 and
 // N = rows gives a plain linear layer (x[rows, Cin]).
-int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void* resid,
-                    const float* rowmask, void* y, int N, int H, int W, int Cin, int Cout, int R,
-                    int S, int stride, int pad, int relu, int out_f32_atomic, int splits,
-                    cudaStream_t stream) {
+static int conv_fwd_impl(const void* x, const void* w, const float* bias, const void* resid,
+                         const void* gate, const float* rowmask, void* y, int N, int H, int W, int Cin,
+                         int Cout, int R, int S, int stride, int pad, int relu, int out_f32_atomic,
+                         int splits, cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
   if (Cin % 32 || !fwd_cout_ok(Cout) || N <= 0) return GABRIL_ERR_BAD_SHAPE;
@@ -299,7 +299,7 @@ int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void*
   if (rc) return rc;
   p.out_mode = out_f32_atomic ? tc::OUT_F32_ATOMIC : tc::OUT_BF16;
   p.out = y; p.ldo = Cout;
-  p.bias = bias; p.resid = (const bf16*)resid; p.gate = nullptr; p.rowmask = rowmask;
+  p.bias = bias; p.resid = (const bf16*)resid; p.gate = (const bf16*)gate; p.rowmask = rowmask;
   p.relu = relu;
   p.err_flag = g_err_flag;
   size_t smem;
@@ -310,12 +310,20 @@ int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void*
   return tc::launch(p, g_num_sms * occ, smem, stream);
 }
 
+int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void* resid,
+                    const float* rowmask, void* y, int N, int H, int W, int Cin, int Cout, int R,
+                    int S, int stride, int pad, int relu, int out_f32_atomic, int splits,
+                    cudaStream_t stream) {
+  return conv_fwd_impl(x, w, bias, resid, nullptr, rowmask, y, N, H, W, Cin, Cout, R, S, stride, pad, relu,
+                       out_f32_atomic, splits, stream);
+}
+
 // dx[N,H,W,Cin] = gate( conv_transpose(dy[N,OH,OW,Cout], w[Cout][R*S][Cin]) + addend )
 //   gate: dx = gate_tensor > 0 ? dx : 0 (ReLU backward of the layer below), rowmask: per-pixel
 //   multiplier (GMD).  stride 1 (any R,S,pad) and the k4/s2/p1 encoder convs are supported.
-int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const void* gate,
-                      const float* rowmask, void* dx, int N, int H, int W, int Cin, int Cout,
-                      int R, int S, int stride, int pad, cudaStream_t stream) {
+static int conv_dgrad_impl(const void* dy, const void* w, const float* bias, int relu, const void* addend,
+                           const void* gate, const float* rowmask, void* dx, int N, int H, int W, int Cin,
+                           int Cout, int R, int S, int stride, int pad, cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
   if (!mn_ok(Cin) || Cout % 32 || N <= 0) return GABRIL_ERR_BAD_SHAPE;
@@ -387,8 +395,8 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
   if (rc) return rc;
   p.out_mode = tc::OUT_BF16;
   p.out = dx; p.ldo = Cin;
-  p.bias = nullptr; p.resid = (const bf16*)addend; p.gate = (const bf16*)gate; p.rowmask = rowmask;
-  p.relu = 0;
+  p.bias = bias; p.resid = (const bf16*)addend; p.gate = (const bf16*)gate; p.rowmask = rowmask;
+  p.relu = relu;
   p.err_flag = g_err_flag;
   size_t smem;
   const int occ = occ_setting();
@@ -397,6 +405,32 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
   for (int c = 0; c < p.n_classes; ++c) mt[c] = (p.M_total[c] + 127) / 128;
   finalize_schedule(p, mt, Cin / block_n, 1, block_n, occ);
   return tc::launch(p, g_num_sms * occ, smem, stream);
+}
+
+int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const void* gate,
+                      const float* rowmask, void* dx, int N, int H, int W, int Cin, int Cout,
+                      int R, int S, int stride, int pad, cudaStream_t stream) {
+  return conv_dgrad_impl(dy, w, nullptr, 0, addend, gate, rowmask, dx, N, H, W, Cin, Cout, R, S, stride, pad,
+                         stream);
+}
+
+// nn.ConvTranspose2d (Decoder, linear_models.py:236-263) on the same kernels.  A transposed
+// convolution with weight Wt[Cin_t][Cout_t][R][S] is the data gradient of the convolution
+// Cout_t -> Cin_t whose internal weight is w[Cin_t][R*S][Cout_t] (= the "conv" layout of Wt):
+//   forward   y[N,H,W,Cout_t]  = act(dgrad(x[N,OH,OW,Cin_t]) + bias)   (H, W: output size, so
+//             output_padding needs no special case: it only changes which H, W the caller asks for)
+//   backward  dx[N,OH,OW,Cin_t] = gate(conv_fwd(dy[N,H,W,Cout_t]))
+//   weights   dw = gabril_conv_wgrad(dy := x, x := dy)
+int gabril_convt_fwd(const void* x, const void* w, const float* bias, void* y, int N, int H, int W,
+                     int Cout_t, int Cin_t, int R, int S, int stride, int pad, int relu,
+                     cudaStream_t stream) {
+  return conv_dgrad_impl(x, w, bias, relu, nullptr, nullptr, nullptr, y, N, H, W, Cout_t, Cin_t, R, S, stride,
+                         pad, stream);
+}
+int gabril_convt_dgrad(const void* dy, const void* w, const void* gate, void* dx, int N, int H, int W,
+                       int Cout_t, int Cin_t, int R, int S, int stride, int pad, cudaStream_t stream) {
+  return conv_fwd_impl(dy, w, nullptr, nullptr, gate, nullptr, dx, N, H, W, Cout_t, Cin_t, R, S, stride, pad, 0,
+                       0, 1, stream);
 }
 
 // dw[Cout][R*S][Cin] (fp32) += sum_pixels dy[p, Cout]^T * im2col(x)[p, (tap, Cin)].

@@ -128,7 +128,13 @@ class StepEngine:
             ops.gmd_mask(b["heat"], A.reshape(B, s.n), s.h, s.w, 0.7, False, rowmask=b["rowmask"],
                          ws=(b["K"], b["mnmx"]))
             rowmask = b["rowmask"]
-        # ---- encoder (linear_models.py:191-207) ----
+        self._encoder_fwd(rowmask)
+        self._heads_fwd(actions, center)
+        return b["losses"]
+
+    def _encoder_fwd(self, rowmask=None):
+        """Encoder.forward (linear_models.py:191-207) from the patch matrix to z."""
+        s, a, b, B = self.spec, self.arena, self.buf, self.B
         ops.conv1_s2d_fwd(b["patches"], a.WB("enc.conv1.w"), a.P("enc.conv1.b"), b["a1s"], B, self.SH,
                           self.SW, s.H1, s.W1, relu=True)
         ops.conv_flat(b["a1s"], a.WB("enc.conv2.w"), b["a2p"], 2, 2, bias=a.P("enc.conv2.b"),
@@ -147,6 +153,9 @@ class StepEngine:
         ops.conv_fwd(last, a.WB("enc.conv5.w"), a.P("enc.conv5.b"), b["a5"], 5, 5, 1, 2, relu=True)
         ops.conv_fwd(b["a5"], a.WB("enc.conv6.w"), a.P("enc.conv6.b"), b["z"], 5, 5, 1, 2, relu=False,
                      rowmask=rowmask.view(-1) if rowmask is not None else None)
+
+    def _heads_fwd(self, actions, center):
+        s, a, b, B = self.spec, self.arena, self.buf, self.B
         # ---- heads (train_bc.py:290-292) ----
         b["zf_raw"].zero_()
         ops.conv_fwd(b["z"].view(B, 1, 1, s.flat), a.WB("pre.w"), None, b["zf_raw"], 1, 1, 1, 0,
@@ -203,6 +212,14 @@ class StepEngine:
             self._mask_rows(b["dz"], rowmask)
         if self.on_heads_grads_ready is not None:
             self.on_heads_grads_ready()
+        self._encoder_bwd()
+        self._accum_count += 1
+        if self.on_all_grads_ready is not None:
+            self.on_all_grads_ready()
+
+    def _encoder_bwd(self):
+        """Backward of the encoder from b["dz"] (gradient w.r.t. z) to every encoder weight gradient."""
+        s, a, b, B = self.spec, self.arena, self.buf, self.B
         # conv_6 / conv_5
         last = b[f"r{s.NR - 1}"]
         ops.colsum_bf16(b["dz"], a.G("enc.conv6.b"))
@@ -238,9 +255,6 @@ class StepEngine:
         ops.colsum_bf16(b["da1s"].view(M1, s.C1), a.G("enc.conv1.b"))
         ops.conv_wgrad(b["da1s"].view(M1, 1, 1, s.C1), b["patches"].view(M1, 1, 1, s.K1p),
                        a.G("enc.conv1.w"), 1, 1, 1, 0)
-        self._accum_count += 1
-        if self.on_all_grads_ready is not None:
-            self.on_all_grads_ready()
 
     def activation(self, name: str) -> torch.Tensor:
         """Stored activation `name` as a plain NHWC tensor (tests / debugging): undoes the

@@ -86,6 +86,16 @@ class PolicySpec:
 
         def bias(name, key, co):
             e.append(Entry(f"enc.{name}.b", "encoder", f"{key}.bias", "bias", (co,), (co,)))
+        self._encoder_entries(e, conv, bias)
+        off = 0
+        for ent in e:
+            ent.offset = off
+            off += (ent.numel + ALIGN - 1) // ALIGN * ALIGN
+        self.total = off
+        return e
+
+    def _encoder_entries(self, e, conv, bias):
+        s = self
         conv("conv6", "_conv_6", s.E, s.NH, 5); bias("conv6", "_conv_6", s.E)
         conv("conv5", "_conv_5", s.NH, s.NH, 5); bias("conv5", "_conv_5", s.NH)
         for i in reversed(range(s.NR)):
@@ -100,6 +110,41 @@ class PolicySpec:
         bias("conv2", "_conv_2", s.C2)
         e.append(Entry("enc.conv1.w", "encoder", "_conv_1.weight", "conv1", (s.C1, s.C0, 4, 4), (s.C1, 1, s.K1p)))
         bias("conv1", "_conv_1", s.C1)
+
+
+class GazePredictorSpec(PolicySpec):
+    """AutoEncoder(Encoder, Decoder(out_channels=1)) of train_gaze_predictor.py:50-64
+    (Decoder: vlm_gaze/models/linear_models.py:210-282).  Entries in reverse execution order:
+    decoder (conv_trans_4 ... conv_1) first, then the encoder."""
+
+    def entries(self) -> List[Entry]:
+        s = self
+        e: List[Entry] = []
+
+        def dconv(name, key, shape_ref, kind="conv"):
+            o, i, k, _ = shape_ref
+            int_shape = (o, 1, 32) if kind == "patch16" else (o, k * k, i)
+            e.append(Entry(f"dec.{name}.w", "decoder", f"{key}.weight", kind, shape_ref, int_shape))
+
+        def dbias(name, key, co):
+            e.append(Entry(f"dec.{name}.b", "decoder", f"{key}.bias", "bias", (co,), (co,)))
+        # nn.ConvTranspose2d weights are [in, out, k, k]: the "conv" layout of that tensor is exactly the
+        # internal weight of the convolution whose data gradient the transposed convolution is
+        dconv("ct4", "_conv_trans_4", (s.C1, 1, 4, 4), "patch16"); dbias("ct4", "_conv_trans_4", 1)
+        dconv("ct3", "_conv_trans_3", (s.C2, s.C1, 4, 4)); dbias("ct3", "_conv_trans_3", s.C1)
+        dconv("ct2", "_conv_trans_2", (s.NH, s.C2, 4, 4)); dbias("ct2", "_conv_trans_2", s.C2)
+        dconv("ct1", "_conv_trans_1", (s.NH, s.NH, 3, 3)); dbias("ct1", "_conv_trans_1", s.NH)
+        for i in reversed(range(s.NR)):
+            dconv(f"res{i}.c1", f"_residual_stack._layers.{i}._block.3", (s.NH, s.RH, 1, 1))
+            dconv(f"res{i}.c3", f"_residual_stack._layers.{i}._block.1", (s.RH, s.NH, 3, 3))
+        dconv("conv1", "_conv_1", (s.NH, s.E, 3, 3)); dbias("conv1", "_conv_1", s.NH)
+
+        def conv(name, key, co, ci, k):
+            e.append(Entry(f"enc.{name}.w", "encoder", f"{key}.weight", "conv", (co, ci, k, k), (co, k * k, ci)))
+
+        def bias(name, key, co):
+            e.append(Entry(f"enc.{name}.b", "encoder", f"{key}.bias", "bias", (co,), (co,)))
+        self._encoder_entries(e, conv, bias)
         off = 0
         for ent in e:
             ent.offset = off
@@ -123,6 +168,11 @@ def to_internal(ent: Entry, t: torch.Tensor, spec: PolicySpec) -> torch.Tensor:
         flat = t.permute(0, 2, 3, 1).reshape(co, r * s_ * ci)
         out = t.new_zeros(co, 1, spec.K1p)
         out[:, 0, :flat.shape[1]] = flat
+        return out
+    if ent.kind == "patch16":  # ConvTranspose2d(C, 1, 4, 2, 1) weight [C,1,4,4] -> patch-GEMM matrix [C][1][32]
+        co = t.shape[0]
+        out = t.new_zeros(co, 1, ent.int_shape[2])
+        out[:, 0, :16] = t.reshape(co, 16)
         return out
     if ent.kind == "linear":
         return t.reshape(t.shape[0], 1, t.shape[1]).contiguous()
@@ -154,6 +204,8 @@ def to_reference(ent: Entry, t: torch.Tensor, spec: PolicySpec) -> torch.Tensor:
     if ent.kind == "conv1":
         co, ci, r, s_ = ent.ref_shape
         return t[:, 0, :spec.K1].reshape(co, r, s_, ci).permute(0, 3, 1, 2).contiguous()
+    if ent.kind == "patch16":
+        return t[:, 0, :16].reshape(ent.ref_shape).contiguous()
     if ent.kind == "linear":
         return t.reshape(ent.ref_shape).contiguous()
     if ent.kind == "pre_actor":
@@ -219,7 +271,7 @@ class ParamArena:
         self.refresh_shadow()
 
     def _export(self, flat) -> Dict[str, "OrderedDict[str, torch.Tensor]"]:
-        out = {"encoder": OrderedDict(), "pre_actor": OrderedDict(), "actor": OrderedDict()}
+        out = OrderedDict((m, OrderedDict()) for m in self.modules())
         # reference key order = forward order
         for e in reversed(self.entries):
             out[e.module][e.key] = to_reference(e, self._view(flat, e.name), self.spec)
@@ -229,6 +281,14 @@ class ParamArena:
             keys.sort(key=lambda k: (_layer_rank(mod, k), 0 if k.endswith("weight") else 1))
             out[mod] = OrderedDict((k, out[mod][k]) for k in keys)
         return out
+
+    def modules(self):
+        """Module names in forward order (entries are stored in reverse execution order)."""
+        seen = []
+        for e in reversed(self.entries):
+            if e.module not in seen:
+                seen.append(e.module)
+        return seen
 
     def state_dicts(self):
         return self._export(self.p)
@@ -243,12 +303,12 @@ class ParamArena:
         import torch.nn as nn
         if seed is not None:
             torch.manual_seed(seed)
-        sds = {"encoder": OrderedDict(), "pre_actor": OrderedDict(), "actor": OrderedDict()}
+        sds = {m: OrderedDict() for m in self.modules()}
         gain = nn.init.calculate_gain("relu")
         for e in reversed(self.entries):
             t = torch.zeros(e.ref_shape)
-            if e.kind in ("conv", "conv1", "conv_s2d"):
-                nn.init.orthogonal_(t, gain)
+            if e.kind in ("conv", "conv1", "conv_s2d", "patch16"):
+                nn.init.orthogonal_(t, gain)  # weight_init also covers nn.ConvTranspose2d (linear_models.py:13)
             elif e.kind in ("linear", "pre_actor", "head"):
                 nn.init.orthogonal_(t)
             sds[e.module][e.key] = t
@@ -256,8 +316,10 @@ class ParamArena:
 
 
 def _layer_rank(mod, key):
-    if mod != "encoder":
+    if mod not in ("encoder", "decoder"):
         return int(key.split(".")[0])
+    if key.startswith("_conv_trans_"):
+        return 200 + int(key.split(".")[0].split("_")[-1])
     if key.startswith("_conv_"):
         i = int(key.split(".")[0].split("_")[-1])
         return i if i <= 4 else i + 100

@@ -200,6 +200,56 @@ def s2d_weight_taps():
     filter over the space-to-depth input has tap (r', s') = [W(2r'+qh, 2s'+qw) for qh, qw]."""
     return [(2 * r + qh) * 4 + (2 * s + qw) for r in range(2) for s in range(2) for qh in range(2) for qw in range(2)]
 
+
+# ---- nn.ConvTranspose2d on the convolution kernels + the gaze-predictor head --------------------
+def convt_fwd(x, w, bias, y, R, S, stride, pad, relu=False):
+    """x [N,OH,OW,Cin_t] bf16, w [Cin_t,R*S,Cout_t] bf16 -> y [N,H,W,Cout_t] (H, W taken from y)."""
+    _chk_bf16(x, "x"); _chk_bf16(w, "w"); _chk_bf16(y, "y")
+    N, H, W, Cout_t = y.shape
+    Cin_t = w.shape[0]
+    OH, OW = conv_out_hw(H, W, R, S, stride, pad)
+    assert w.shape[1] == R * S and w.shape[2] == Cout_t and x.numel() == N * OH * OW * Cin_t, (x.shape, w.shape, y.shape)
+    with _span("tc_gemm_kernel", f"convT fwd {Cin_t}->{Cout_t} k{R}s{stride}", 2.0 * N * OH * OW * Cin_t * R * S * Cout_t, "flop"):
+        st = _fn("gabril_convt_fwd")(ptr(x), ptr(w), ptr(bias), ptr(y), c_int(N), c_int(H), c_int(W), c_int(Cout_t),
+                                     c_int(Cin_t), c_int(R), c_int(S), c_int(stride), c_int(pad), c_int(int(relu)),
+                                     stream())
+    _lib.check(st, "gabril_convt_fwd")
+    return y
+
+
+def convt_dgrad(dy, w, dx, R, S, stride, pad, gate=None):
+    """dy [N,H,W,Cout_t] -> dx [N,OH,OW,Cin_t] (gated by `gate`, same shape as dx)."""
+    _chk_bf16(dy, "dy"); _chk_bf16(w, "w"); _chk_bf16(dx, "dx"); _chk_bf16(gate, "gate")
+    N, H, W, Cout_t = dy.shape
+    Cin_t = w.shape[0]
+    OH, OW = conv_out_hw(H, W, R, S, stride, pad)
+    assert w.shape[1] == R * S and w.shape[2] == Cout_t and dx.numel() == N * OH * OW * Cin_t
+    with _span("tc_gemm_kernel", f"convT dgrad {Cin_t}<-{Cout_t} k{R}s{stride}", 2.0 * N * OH * OW * Cin_t * R * S * Cout_t, "flop"):
+        st = _fn("gabril_convt_dgrad")(ptr(dy), ptr(w), ptr(gate), ptr(dx), c_int(N), c_int(H), c_int(W),
+                                       c_int(Cout_t), c_int(Cin_t), c_int(R), c_int(S), c_int(stride), c_int(pad),
+                                       stream())
+    _lib.check(st, "gabril_convt_dgrad")
+    return dx
+
+
+def gp_head_fwd(x, wp, bias, target_base, target_bstride, dout, loss_part, dbias, gscale, out=None):
+    """x bf16 [B,h,w,C]; wp bf16 [C,1,Kp]; target_base: fp32 tensor whose data_ptr is sample 0's plane."""
+    _chk_bf16(x, "x"); _chk_bf16(wp, "wp"); _chk(dout, torch.float32, "dout")
+    B, h, w, C = x.shape
+    Kp = wp.shape[-1]
+    _call("gabril_gp_head_fwd", ptr(x), ptr(wp), c_int(Kp), ptr(bias), ptr(target_base), c_ll(target_bstride),
+          ptr(out), ptr(dout), ptr(loss_part), ptr(dbias), c_int(B), c_int(h), c_int(w), c_int(C), c_float(gscale),
+          stream(), work=float(x.numel() * 2 + B * 4 * h * w * 12))
+
+
+def gp_dout_patches(dout, patches):
+    _chk(dout, torch.float32, "dout"); _chk_bf16(patches, "patches")
+    B, H, W = dout.shape
+    Kp = patches.shape[1]
+    assert patches.shape[0] == B * (H // 2) * (W // 2)
+    _call("gabril_gp_dout_patches", ptr(dout), ptr(patches), c_int(Kp), c_int(B), c_int(H // 2), c_int(W // 2),
+          stream(), work=float(dout.numel() * 4 + patches.numel() * 2))
+
 # ---- layout helpers (host-side plumbing, torch ops) ------------------------------------------
 def w_oihw_to_internal(w_oihw: torch.Tensor) -> torch.Tensor:
     """[Cout,Cin,R,S] -> [Cout,R*S,Cin] (same dtype)."""

@@ -172,6 +172,29 @@ int gabril_conv1_s2d_fwd(const void* patches, const void* w, const float* bias, 
                          int SH, int SW, int img_h, int img_w, int Kp, int Cout, int relu,
                          cudaStream_t stream);
 
+/* ---- gaze-predictor pre-training (train_gaze_predictor.py:83-101): AutoEncoder = Encoder + Decoder
+ * (linear_models.py:210-282, 356-367), MSE against the last aggregated heat map.
+ * nn.ConvTranspose2d with weight Wt[Cin_t][Cout_t][R][S] runs on the convolution kernels through the
+ * internal weight w[Cin_t][R*S][Cout_t]: forward = data gradient of the conv Cout_t -> Cin_t (+ bias,
+ * ReLU), backward-data = that conv's forward (+ ReLU gate), weight gradient = gabril_conv_wgrad with the
+ * roles of x and dy exchanged.  x [N,OH,OW,Cin_t] -> y [N,H,W,Cout_t]; k4/s2/p0|p1 and stride 1. */
+int gabril_convt_fwd(const void* x, const void* w, const float* bias, void* y, int N, int H, int W,
+                     int Cout_t, int Cin_t, int R, int S, int stride, int pad, int relu,
+                     cudaStream_t stream);
+int gabril_convt_dgrad(const void* dy, const void* w, const void* gate, void* dx, int N, int H, int W,
+                       int Cout_t, int Cin_t, int R, int S, int stride, int pad, cudaStream_t stream);
+/* _conv_trans_4 (C -> 1 channel, k4/s2/p1) + nn.MSELoss: x bf16 [B,h,w,C], wp bf16 [C][Kp] (tap ky*4+kx),
+ * target plane b at target + b*target_bstride ([2h][2w] fp32).  Writes out (optional) and
+ * dout = 2*(out - target)*gscale as fp32 [B,2h,2w]; ADDS the per-sample squared error into
+ * loss_part[B] and sum(dout) into dbias[1] (both zeroed by the caller). */
+int gabril_gp_head_fwd(const void* x, const void* wp, int Kp, const float* bias, const float* target,
+                       long long target_bstride, float* out, float* dout, float* loss_part,
+                       float* dbias, int B, int h, int w, int C, float gscale, cudaStream_t stream);
+/* dout fp32 [B,2h,2w] -> bf16 patch matrix [B*h*w, Kp] of the k4/s2/p1 window of every input pixel
+ * (columns 16.. zero): the backward of _conv_trans_4 then is two patch GEMMs. */
+int gabril_gp_dout_patches(const float* dout, void* patches_bf16, int Kp, int B, int h, int w,
+                           cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -65,3 +65,36 @@ def make_weights(c_in, seed=7, action_dim=7):
                 sd[k] = torch.randn(shp, generator=g) * (gain / fan_in ** 0.5)
         out[mod] = sd
     return out
+
+
+def decoder_shapes():
+    """Decoder(1, 64, 128, 2, 32).state_dict() shapes (linear_models.py:210-268); nn.ConvTranspose2d
+    weights are [in, out, k, k]."""
+    return {
+        "_conv_1.weight": (128, 64, 3, 3), "_conv_1.bias": (128,),
+        "_residual_stack._layers.0._block.1.weight": (32, 128, 3, 3),
+        "_residual_stack._layers.0._block.3.weight": (128, 32, 1, 1),
+        "_residual_stack._layers.1._block.1.weight": (32, 128, 3, 3),
+        "_residual_stack._layers.1._block.3.weight": (128, 32, 1, 1),
+        "_conv_trans_1.weight": (128, 128, 3, 3), "_conv_trans_1.bias": (128,),
+        "_conv_trans_2.weight": (128, 64, 4, 4), "_conv_trans_2.bias": (64,),
+        "_conv_trans_3.weight": (64, 32, 4, 4), "_conv_trans_3.bias": (32,),
+        "_conv_trans_4.weight": (32, 1, 4, 4), "_conv_trans_4.bias": (1,),
+    }
+
+
+def make_weights_gp(c_in, seed=9):
+    """Deterministic weights of the gaze-predictor AutoEncoder: {"encoder": sd, "decoder": sd}."""
+    enc = make_weights(c_in, seed=seed)["encoder"]
+    g = torch.Generator().manual_seed(seed + 1000)
+    dec = {}
+    for k, shp in decoder_shapes().items():
+        if k.endswith("bias"):
+            dec[k] = (torch.rand(shp, generator=g) - 0.5) * 0.1
+        else:
+            # fan-in of a transposed convolution: in_channels * k*k / stride^2 taps reach one output
+            fan_in = shp[0] * shp[2] * shp[3] if "trans" in k else shp[1] * shp[2] * shp[3]
+            if "trans" in k and shp[2] == 4:
+                fan_in //= 4
+            dec[k] = torch.randn(shp, generator=g) * ((2.0 / fan_in) ** 0.5)
+    return {"encoder": enc, "decoder": dec}
