@@ -14,7 +14,7 @@ from typing import Dict
 
 import torch
 
-from . import ops
+from . import ddp, ops
 from .engine import StepEngine
 from .gaze import GazePreprocessor
 from .model import GazePredictorSpec, ParamArena
@@ -109,6 +109,8 @@ class GazePredictorEngine(StepEngine):
         ops.colsum_bf16(dt, a.G("dec.conv1.b"))
         ops.conv_wgrad(dt, b["z"], a.G("dec.conv1.w"), 3, 3, 1, 1)
         ops.conv_dgrad(dt, a.WB("dec.conv1.w"), b["dz"], 3, 3, 1, 1)
+        if self.on_heads_grads_ready is not None:   # decoder gradients complete: first all-reduce bucket
+            self.on_heads_grads_ready()
         self._encoder_bwd()
         self._accum_count += 1
         if self.on_all_grads_ready is not None:
@@ -165,3 +167,132 @@ def save_gaze_predictor(arena: ParamArena, ckpt_dir: str, epoch: int, params: di
         torch.save(sd, os.path.join(ckpt_dir, "model.torch"))
     with open(os.path.join(ckpt_dir, "params.json"), "w") as f:
         json.dump(params, f, indent=2)
+
+
+# ------------------------------------------------------------------------------------------------
+# GazePredictorTrainer (train_gaze_predictor.py:22-121): the five BaseTrainer hooks over the engine
+# ------------------------------------------------------------------------------------------------
+def _trainer_classes():
+    from .trainer import ArenaModule, BaseTrainer, _StepLoss
+
+    class _AutoEncoderFacade:
+        """state_dict()/load_state_dict()/parameters() of the reference's AutoEncoder module."""
+
+        def __init__(self, arena):
+            self.arena = arena
+            self.encoder, self.decoder = ArenaModule(arena, "encoder"), ArenaModule(arena, "decoder")
+            self.training = True
+
+        def state_dict(self):
+            return autoencoder_state_dict(self.arena)
+
+        def load_state_dict(self, sd, strict: bool = True):
+            load_autoencoder_state_dict(self.arena, sd)
+
+        def parameters(self):
+            return self.encoder.parameters() + self.decoder.parameters()
+
+        def train(self, mode: bool = True):
+            self.training = mode
+            return self
+
+        def eval(self):
+            return self.train(False)
+
+    class GazePredictorTrainer(BaseTrainer):
+        def build_models(self):
+            c = self.cfg
+            if self.device.type != "cuda":
+                raise RuntimeError("GazePredictorTrainer needs a CUDA device (sm_100a); there is no CPU fallback")
+            S = int(c.data.frame_stack)
+            spec = GazePredictorSpec(S * (1 if c.model.grayscale else 3), int(c.data.img_height),
+                                     int(c.data.img_width), int(c.model.embedding_dim), int(c.model.num_hiddens),
+                                     int(c.model.num_residual_layers), int(c.model.num_residual_hiddens))
+            self.spec = spec
+            self.arena = ParamArena(spec, self.device)
+            self.arena.init_reference_style()
+            ddp.broadcast_arena(self.arena.p)
+            self.arena.refresh_shadow()
+            g = c.gaze
+            self.gaze_preprocessor = GazePreprocessor(
+                img_height=int(c.data.img_height), img_width=int(c.data.img_width),
+                gaze_sigma=float(g.get("sigma", g.get("mask_sigma", 30.0))),
+                gaze_coeff=float(g.get("coeff", g.get("mask_coeff", 0.8))), maxpoints=int(g.max_points),
+                device=str(self.device), temporal_mode=str(g.get("temporal_mode", "alpha_decay")),
+                temporal_sigmas=g.get("temporal_sigmas", None), temporal_coeffs=g.get("temporal_coeffs", None),
+                temporal_offset_start=int(g.get("temporal_offset_start", 0)))
+            self.engine = GazePredictorEngine(spec, self.arena, self.gaze_preprocessor,
+                                              grayscale=bool(c.model.grayscale), frame_stack=S,
+                                              grad_accum=int(c.training.gradient_accumulation_steps))
+            self.reducer = ddp.attach(self.engine, self.arena)
+            self.model = _AutoEncoderFacade(self.arena)
+
+        def get_optim_params(self):
+            return self.model.parameters()
+
+        def set_train_mode(self):
+            self.model.train()
+
+        def compute_loss(self, batch):
+            """-> (loss tensor, batch size, {"loss": float}) like train_gaze_predictor.py:83-101."""
+            gaze_key = self.cfg.data.get("gaze_key", "gaze_coords")
+            frames = batch["obs"]["image"].to(self.device, non_blocking=True)
+            gaze = batch["obs"][gaze_key].to(self.device, non_blocking=True)
+            if gaze.dim() == 4:
+                gaze = gaze.reshape(gaze.shape[0], gaze.shape[1], -1)
+            losses = self.engine.forward(frames.contiguous(), gaze.contiguous().float())
+            value = self.engine.loss_host()
+            anchor = torch.zeros((), device=self.device, requires_grad=True)
+            loss = _StepLoss.apply(anchor, self, losses[0])
+            return loss, int(frames.shape[0]), {"loss": value, "Loss/total": value}
+
+        def _run_backward(self):
+            self.engine.backward()
+
+        def zero_grad(self):
+            self.engine.zero_grad()
+
+        def optimizer_step(self):
+            self.reducer.finish()
+            self.opt_step += 1
+            s = self.schedule
+            self.engine.adam_step(self.opt_step, s.lr, weight_decay=s.weight_decay, decoupled=s.decoupled,
+                                  grad_scale=self.reducer.grad_scale)
+
+        def save_for_epoch(self, epoch: int):
+            c = self.cfg
+            g = c.gaze
+            params = gaze_predictor_params(
+                dict(grayscale=bool(c.model.grayscale), embedding_dim=int(c.model.embedding_dim),
+                     num_hiddens=int(c.model.num_hiddens), num_residual_layers=int(c.model.num_residual_layers),
+                     num_residual_hiddens=int(c.model.num_residual_hiddens)),
+                dict(frame_stack=int(c.data.frame_stack)),
+                dict(sigma=float(g.get("sigma", g.get("mask_sigma", 30.0))),
+                     coeff=float(g.get("coeff", g.get("mask_coeff", 0.8)))),
+                str(self.checkpoint_dir), int(epoch))
+            save_gaze_predictor(self.arena, str(self.checkpoint_dir), int(epoch), params,
+                                final=(int(epoch) == int(c.training.epochs)))
+            self._print_rank0(f"Saved checkpoint: {self.checkpoint_dir}/model_ep{epoch}.torch")
+
+    return GazePredictorTrainer
+
+
+def __getattr__(name):
+    if name == "GazePredictorTrainer":
+        return _trainer_classes()
+    raise AttributeError(name)
+
+
+def main(argv=None):
+    """`python -m gabril_carla_b200.train_gaze_predictor key=value ...` (train_gaze_predictor.py:124-140);
+    defaults of train_gaze.yaml that differ from train_bc_base.yaml: seed 1, step scheduler."""
+    import sys
+    from .config import load_config
+    args = ["training.seed=1", "scheduler.type=step"] + list(sys.argv[1:] if argv is None else argv)
+    cfg = load_config(args)
+    trainer = _trainer_classes()(cfg)
+    trainer.train()
+    if os.environ.get("RANK", "0") == "0":
+        print("Training completed!")
+    ddp.destroy_distributed_if_initialized()
+    return trainer

@@ -176,3 +176,27 @@ def test_training_reduces_loss_and_checkpoint_layout(tmp_path):
         pj = json.load(f)
     assert set(pj) == {"model_type", "grayscale", "stack", "embedding_dim", "num_hiddens", "num_residual_layers",
                        "num_residual_hiddens", "gaze_mask_sigma", "gaze_mask_coeff", "models_path", "epochs"}
+
+
+def test_gaze_predictor_trainer_cli_two_epochs(tmp_path):
+    """The reference-style trainer surface: five hooks, BaseTrainer.train(), model_ep{E}.torch + model.torch +
+    params.json; the saved state_dict loads into the oracle's AutoEncoder restatement."""
+    from gabril_carla_b200.gaze_predictor import main
+    tr = main(["data.hdf5_path=synthetic:64", "data.batch_size=32", "training.epochs=2", "training.save_interval=1",
+               "scheduler.type=none", "optimizer.lr=2e-4", f"logging.checkpoint_dir={tmp_path}",
+               f"logging.log_dir={tmp_path}"])
+    d = tr.checkpoint_dir
+    assert (d / "model_ep1.torch").exists() and (d / "model_ep2.torch").exists() and (d / "model.torch").exists()
+    pj = json.load(open(d / "params.json"))
+    assert pj["model_type"] == "gaze_predictor" and pj["epochs"] == 2 and pj["stack"] == 2
+    sd = torch.load(d / "model.torch", weights_only=True)
+    enc = {k[len("encoder."):]: v for k, v in sd.items() if k.startswith("encoder.")}
+    dec = {k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")}
+    batch = next(iter(tr.train_loader))
+    img, gaze = batch["obs"]["image"].cpu(), batch["obs"]["gaze_coords"].cpu()
+    tr.zero_grad()
+    loss, bs, metrics = tr.compute_loss(batch)
+    with torch.no_grad():
+        ref, _, _ = O.gaze_predictor_loss(enc, dec, img, gaze.reshape(gaze.shape[0], gaze.shape[1], -1))
+    assert bs == 32 and abs(metrics["loss"] - ref.item()) <= 5e-3 * abs(ref.item()), (metrics, ref.item())
+    assert tr.last_epoch_loss == tr.last_epoch_loss  # finite
