@@ -281,6 +281,8 @@ def main_ours(args):
     if is_dist:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, e2e_ms = t[0].item(), (t[1].item() if e2e_ms is not None else None)
+    if is_dist:
+        dist.barrier()   # every rank leaves the measured part together; only rank 0 reports
     if rank != 0:
         return
     hbm, tf_burst, tf_sust, how = load_peaks()
@@ -321,8 +323,6 @@ def main_ours(args):
         r = cpu_reference_run(args, 5, 2)
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}
     print(json.dumps(line), flush=True)
-    if is_dist:
-        dist.barrier()
 
 
 if __name__ == "__main__":
