@@ -29,6 +29,18 @@ def make_batch(B, L=2, H=180, W=320, P=5, A=7, seed=0, smooth=True, edge_cases=T
     return img.contiguous(), gaze.reshape(B, L, P * 2).contiguous(), actions.contiguous()
 
 
+def make_batch_n1(seed=17):
+    """Batch of 4 for the `gaze.ratio < 1` selection (train_bc.py:236-240): samples 0/1 are ordinary
+    frames (content hash r = 0 => always selected), samples 2/3 are black frames with one or two lit
+    pixels whose hash is r = 0.7656 (dropped at ratio 0.5) and r = 0.1699 (kept)."""
+    img, gaze, act = make_batch(4, seed=seed)
+    img[2:] = 0
+    img[2, 1, 100, 200] = torch.tensor([255, 255, 255], dtype=torch.uint8)
+    img[2, 0, 17, 5] = torch.tensor([33, 77, 120], dtype=torch.uint8)
+    img[3, 1, 60, 300] = torch.tensor([128, 0, 0], dtype=torch.uint8)
+    return img.contiguous(), gaze, act
+
+
 # reference state_dict layout (SURVEY.md §8a row 14): key -> shape, c = encoder input channels
 def reference_shapes(c_in, action_dim=7):
     enc = {"_conv_1.weight": (32, c_in, 4, 4), "_conv_1.bias": (32,),
