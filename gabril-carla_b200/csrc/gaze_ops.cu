@@ -327,8 +327,8 @@ obs_patches_tiled_kernel(const uint8_t* __restrict__ frames, bf16* __restrict__ 
 // probability itself in test mode.
 // =================================================================================================
 __global__ void __launch_bounds__(256)
-gmd_keep_kernel(const float* __restrict__ g, float* __restrict__ K, unsigned int* __restrict__ mnmx,
-                int B, int S, int H, int W, int h, int w) {
+gmd_keep_kernel(const float* __restrict__ g, const float* __restrict__ sel, float* __restrict__ K,
+                unsigned int* __restrict__ mnmx, int B, int S, int H, int W, int h, int w) {
   __shared__ float scratch[32];
   const int n = h * w;
   const long long total = (long long)B * n;
@@ -344,7 +344,9 @@ gmd_keep_kernel(const float* __restrict__ g, float* __restrict__ K, unsigned int
     bicubic_taps(oy, sy, H, iy, wy);
     bicubic_taps(ox, sx, W, ix, wx);
     float acc = 0.f;
-    for (int s = 0; s < S; ++s) {
+    // samples that do not use gaze (ivg = 0) see an all-zero heat map (train_bc.py:258)
+    const int Suse = (sel && __ldg(sel + b) <= 0.f) ? 0 : S;
+    for (int s = 0; s < Suse; ++s) {
       const float* gp = g + ((long long)b * S + s) * H * W;
       float rows[4];
 #pragma unroll
@@ -404,12 +406,60 @@ rowmask_apply_nchw_kernel(const float* __restrict__ z, const float* __restrict__
 }
 
 // =================================================================================================
+// gaze.ratio < 1 (train_bc.py:230-240): per-sample content hash r = frac(|sum(obs) * 123456.789|)
+// in fp32, sample uses gaze iff r < ratio.  sum(obs) is over the formatted frame stack (the exact
+// fp32 values of obs_format).  One CTA per sample, fixed summation order.  For any frame whose
+// normalised pixel sum exceeds 2^23 / 123456.789 = 68 the fp32 product has no fractional bits, so
+// r = 0 whatever the order of the additions; below that the reference's own
+// result depends on the reduction order of the device it runs on.
+// sel_stats[0] = number selected, sel_stats[1] = B / number selected (inf when none: the
+// reference's mean over an empty selection is NaN as well).
+// =================================================================================================
+__global__ void __launch_bounds__(256)
+ivg_key_kernel(const uint8_t* __restrict__ frames, float* __restrict__ sel, int B, int L, int S,
+               int center, int H, int W, int gray, float ratio) {
+  __shared__ float scratch[32];
+  const int b = blockIdx.x;
+  const long long HW = (long long)H * W;
+  float acc = 0.f;
+  for (int s = 0; s < S; ++s) {
+    int t = center - S + 1 + s;
+    t = t < 0 ? 0 : (t > L - 1 ? L - 1 : t);
+    const uint8_t* fp = frames + ((long long)b * L + t) * HW * 3;
+    for (long long i = threadIdx.x; i < HW; i += blockDim.x) {
+      const float r = __fdiv_rn((float)fp[3 * i + 0], 255.f), g = __fdiv_rn((float)fp[3 * i + 1], 255.f),
+                  bl = __fdiv_rn((float)fp[3 * i + 2], 255.f);
+      if (gray) acc += __fadd_rn(__fadd_rn(__fmul_rn(0.299f, r), __fmul_rn(0.587f, g)), __fmul_rn(0.114f, bl));
+      else acc += r + g + bl;
+    }
+  }
+  const float key = block_sum(acc, scratch);
+  if (threadIdx.x == 0) {
+    const float v = fabsf(__fmul_rn(key, 123456.789f));
+    const float r = v - truncf(v);
+    sel[b] = (ratio >= 1.f) ? 1.f : ((ratio <= 0.f) ? 0.f : (r < ratio ? 1.f : 0.f));
+  }
+}
+
+__global__ void __launch_bounds__(256) ivg_count_kernel(const float* __restrict__ sel,
+                                                        float* __restrict__ stats, int B) {
+  __shared__ float scratch[32];
+  float c = 0.f;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) c += sel[i] > 0.f ? 1.f : 0.f;
+  c = block_sum(c, scratch);
+  if (threadIdx.x == 0) { stats[0] = c; stats[1] = __fdiv_rn((float)B, c); }
+}
+
+// =================================================================================================
 // K5: get_gaze_mask forward / backward and the fused Reg-MSE loss + gradient.
 // One CTA = one sample; thread x owns output column x (blockDim = W rounded to a warp multiple).
 // Shared: p[n] softmax, t[h][W] row-interpolated map, sacc[h][W] y-adjoint accumulators,
 // bicubic tap tables for both axes, dp[n].
 // =================================================================================================
-enum { MODE_MSE = 0, MODE_MASK_FWD = 1, MODE_MASK_BWD = 2 };
+// MODE_KL / MODE_TV / MODE_JS: train_bc.py:152-167 - both maps divided by their (detached) sums
+// + 1e-8, then KL(g1 || g2), sum |g1 - g2| or the Jensen-Shannon form with eps = 1e-6 inside the logs;
+// loss_part[b] is the per-sample sum, the caller divides by the number of selected samples.
+enum { MODE_MSE = 0, MODE_MASK_FWD = 1, MODE_MASK_BWD = 2, MODE_KL = 3, MODE_TV = 4, MODE_JS = 5 };
 
 struct RegArgs {
   const void* z;         // bf16 [B, n, C] (NHWC) or fp32 [B, C, n] (NCHW)
@@ -421,6 +471,7 @@ struct RegArgs {
   void* dz;              // gradient w.r.t. z, same layout as z (MODE_MSE / MODE_MASK_BWD)
   float* loss_part;      // MODE_MSE: [B] per-sample sum of squared differences
   float* stats;          // optional [B][4]: min, max, argmin, argmax of the up-sampled map
+  const float* scale_dev;  // optional device scalar multiplied into grad_scale (B / n_selected)
   float beta, grad_scale;
   int B, C, h, w, H, W;
 };
@@ -432,6 +483,8 @@ struct RegArgs {
 template <bool NHWC_BF16, int MODE, int MAXT>
 __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __grid_constant__ RegArgs a) {
   extern __shared__ __align__(16) float sm[];
+  constexpr bool LOSS = MODE == MODE_MSE || MODE >= MODE_KL;  // fused loss + gradient modes
+  constexpr bool DISTN = MODE >= MODE_KL;                     // sum-normalised divergences
   const int h = a.h, w = a.w, H = a.H, W = a.W, C = a.C, n = h * w, n4 = (n + 3) & ~3;
   float* p = sm;                                        // [n4]
   float* tmap = p + n4;                                 // [h][W]
@@ -456,7 +509,7 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __
   const bf16* zb16 = reinterpret_cast<const bf16*>(a.z) + (long long)b * n * C;
   const float* zf32 = reinterpret_cast<const float*>(a.z) + (long long)b * n * C;
 
-  if (MODE == MODE_MSE && skip) {
+  if (LOSS && skip) {
     // sample not selected: zero gradient, zero loss
     if (NHWC_BF16) {
       uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(a.dz) + (long long)b * n * C);
@@ -572,7 +625,9 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __
   // ---- pass 1: extrema (first occurrence wins ties, like torch's CPU max/min) ----
   float vmin = FLT_MAX, vmax = -FLT_MAX;
   int imin = 0x7fffffff, imax = 0x7fffffff;
+  float usum = 0.f, g1sum = 0.f;  // DISTN: column sums of the raw map and of the target
   if (col_ok) {
+    const float* g1c = DISTN ? a.g1 + (long long)b * a.g1_bstride + x : nullptr;
     for (int r = 0; r < nruns; ++r) {
       const int y0 = max(ya, ystart[r]), y1 = min(yb, ystart[r + 1]);
       if (y0 >= y1) continue;
@@ -582,6 +637,7 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __
         const float u = u_of(wy4[y]);
         if (u < vmin) { vmin = u; imin = y; }
         if (u > vmax) { vmax = u; imax = y; }
+        if (DISTN) { usum += u; g1sum += __ldg(g1c + y * W); }
       }
     }
     if (imin != 0x7fffffff) imin = imin * W + x;
@@ -631,9 +687,29 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __
   // ---- pass 2: g2, loss, d(loss)/du accumulated through the y-adjoint into sacc ----
   // (training path: the two divisions by rng are multiplications by 1/rng; 0/0 still gives NaN)
   const float inv_rng = __fdiv_rn(1.f, rng);
+  const float gs = a.scale_dev ? a.grad_scale * __ldg(a.scale_dev) : a.grad_scale;
+  float iS1 = 0.f, iS2 = 0.f;
+  if (DISTN) {
+    // S1 = sum g1 + 1e-8; S2 = sum (u - mn) / rng + 1e-8 (block sums in double: the second one
+    // is a difference of two sums of 57 600 terms)
+    __shared__ double dred[2][32];
+    double du = usum, dg = g1sum;
+    for (int o = 16; o > 0; o >>= 1) {
+      du += __shfl_xor_sync(0xffffffffu, du, o);
+      dg += __shfl_xor_sync(0xffffffffu, dg, o);
+    }
+    if (lane == 0) { dred[0][wid] = du; dred[1][wid] = dg; }
+    __syncthreads();
+    du = 0.0; dg = 0.0;
+    for (int i = 0; i < nwarp; ++i) { du += dred[0][i]; dg += dred[1][i]; }
+    const double S2 = (du - (double)(H * W) * (double)mn) / (double)rng + 1e-8;
+    const double S1 = dg + 1e-8;
+    iS1 = (float)(1.0 / S1);
+    iS2 = (float)(1.0 / S2);
+  }
   float sq = 0.f, E = 0.f, F = 0.f;
   if (col_ok) {
-    const float* gsrc = (MODE == MODE_MSE) ? a.g1 + (long long)b * a.g1_bstride
+    const float* gsrc = LOSS ? a.g1 + (long long)b * a.g1_bstride
                                            : a.grad_in + (long long)b * H * W;
     gsrc += x;
     for (int r = 0; r < nruns; ++r) {
@@ -654,7 +730,23 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __
             if (MODE == MODE_MSE) {
               const float d = g2 - gv[k];
               sq = fmaf(d, d, sq);
-              e = 2.f * d * a.grad_scale;
+              e = 2.f * d * gs;
+            } else if (MODE == MODE_TV) {
+              const float d = gv[k] * iS1 - g2 * iS2;
+              sq += fabsf(d);
+              e = (d > 0.f ? -iS2 : (d < 0.f ? iS2 : 0.f)) * gs;
+            } else if (MODE == MODE_KL) {
+              const float pa = gv[k] * iS1, pb = g2 * iS2;
+              const float ib = __fdiv_rn(1.f, pb + 1e-6f);
+              sq = fmaf(pa, logf((pa + 1e-6f) * ib), sq);
+              e = -pa * ib * iS2 * gs;
+            } else if (MODE == MODE_JS) {
+              const float pa = gv[k] * iS1, pb = g2 * iS2;
+              const float im = __fdiv_rn(1.f, 0.5f * (pa + pb) + 1e-6f);
+              const float la = logf((pa + 1e-6f) * im), lb = logf((pb + 1e-6f) * im);
+              sq += 0.5f * (pa * la + pb * lb);
+              // d/dpb of 0.5 [pa log((pa+e)/(m+e)) + pb log((pb+e)/(m+e))], m = (pa + pb) / 2
+              e = 0.5f * (lb + __fdiv_rn(pb, pb + 1e-6f) - 0.5f * (pa + pb) * im) * iS2 * gs;
             } else {
               e = gv[k];
             }
@@ -672,7 +764,7 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __
   }
   const float Esum = block_sum(E, scratch);
   const float Fsum = block_sum(F, scratch);
-  if (MODE == MODE_MSE) {
+  if (LOSS) {
     const float sqsum = block_sum(sq, scratch);
     if (tid == 0) a.loss_part[b] = sqsum;
   }
@@ -863,11 +955,18 @@ int gabril_obs_patches_s2d(const uint8_t* frames, void* patches, int B, int L, i
 int gabril_gmd_mask(const float* g, const float* A, float* K_ws, unsigned int* mnmx_ws,
                     float* rowmask, float* keep_out, int B, int S, int H, int W, int h, int w,
                     float drop_p, int test_mode, cudaStream_t stream) {
+  return gabril_gmd_mask_sel(g, nullptr, A, K_ws, mnmx_ws, rowmask, keep_out, B, S, H, W, h, w, drop_p,
+                             test_mode, stream);
+}
+
+int gabril_gmd_mask_sel(const float* g, const float* sel, const float* A, float* K_ws,
+                        unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B, int S, int H,
+                        int W, int h, int w, float drop_p, int test_mode, cudaStream_t stream) {
   if (!g || !K_ws || !mnmx_ws || !rowmask || (!A && !test_mode)) return GABRIL_ERR_NULL;
   if (B <= 0 || S < 1) return GABRIL_ERR_BAD_SHAPE;
   const long long total = (long long)B * h * w;
   gmd_init_kernel<<<1, 1, 0, stream>>>(mnmx_ws);
-  gmd_keep_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(g, K_ws, mnmx_ws, B, S, H, W, h, w);
+  gmd_keep_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(g, sel, K_ws, mnmx_ws, B, S, H, W, h, w);
   gmd_mask_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(K_ws, A, mnmx_ws, rowmask, keep_out,
                                                                      total, drop_p, test_mode);
   GABRIL_CHECK_LAUNCH();
@@ -906,12 +1005,41 @@ int gabril_gaze_mask_bwd(const void* z, int z_nhwc_bf16, const float* grad_mask,
 int gabril_reg_mse(const void* z, int z_nhwc_bf16, const float* g1, long long g1_bstride,
                    const float* sel, void* dz, float* loss_part, float* stats, int B, int C, int h,
                    int w, int H, int W, float beta, float grad_scale, cudaStream_t stream) {
+  return gabril_reg_dist(z, z_nhwc_bf16, g1, g1_bstride, sel, nullptr, GABRIL_DIST_MSE, dz, loss_part,
+                         stats, B, C, h, w, H, W, beta, grad_scale, stream);
+}
+
+int gabril_reg_dist(const void* z, int z_nhwc_bf16, const float* g1, long long g1_bstride,
+                    const float* sel, const float* scale_dev, int dist, void* dz, float* loss_part,
+                    float* stats, int B, int C, int h, int w, int H, int W, float beta,
+                    float grad_scale, cudaStream_t stream) {
   if (!z || !g1 || !dz || !loss_part) return GABRIL_ERR_NULL;
   RegArgs a = {};
   a.z = z; a.g1 = g1; a.g1_bstride = g1_bstride; a.sel = sel; a.dz = dz; a.loss_part = loss_part;
-  a.stats = stats; a.beta = beta; a.grad_scale = grad_scale;
+  a.stats = stats; a.beta = beta; a.grad_scale = grad_scale; a.scale_dev = scale_dev;
   a.B = B; a.C = C; a.h = h; a.w = w; a.H = H; a.W = W;
-  return z_nhwc_bf16 ? launch_reg<true, MODE_MSE>(a, stream) : launch_reg<false, MODE_MSE>(a, stream);
+  switch (dist) {
+    case GABRIL_DIST_MSE:
+      return z_nhwc_bf16 ? launch_reg<true, MODE_MSE>(a, stream) : launch_reg<false, MODE_MSE>(a, stream);
+    case GABRIL_DIST_KL:
+      return z_nhwc_bf16 ? launch_reg<true, MODE_KL>(a, stream) : launch_reg<false, MODE_KL>(a, stream);
+    case GABRIL_DIST_TV:
+      return z_nhwc_bf16 ? launch_reg<true, MODE_TV>(a, stream) : launch_reg<false, MODE_TV>(a, stream);
+    case GABRIL_DIST_JS:
+      return z_nhwc_bf16 ? launch_reg<true, MODE_JS>(a, stream) : launch_reg<false, MODE_JS>(a, stream);
+    default:
+      return GABRIL_ERR_BAD_SHAPE;
+  }
+}
+
+int gabril_ivg_select(const uint8_t* frames, float* sel, float* sel_stats, int B, int L, int S,
+                      int center, int H, int W, int grayscale, float ratio, cudaStream_t stream) {
+  if (!frames || !sel || !sel_stats) return GABRIL_ERR_NULL;
+  if (B <= 0 || B > 65535 * 16 || S < 1 || L < 1 || H < 1 || W < 1) return GABRIL_ERR_BAD_SHAPE;
+  ivg_key_kernel<<<B, 256, 0, stream>>>(frames, sel, B, L, S, center, H, W, grayscale, ratio);
+  ivg_count_kernel<<<1, 256, 0, stream>>>(sel, sel_stats, B);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
 }
 
 }  // extern "C"

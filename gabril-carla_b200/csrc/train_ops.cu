@@ -86,8 +86,8 @@ mse_head_kernel(const float* __restrict__ raw, int ld_raw, const float* __restri
 // losses[2] = lambda * reg + actor.  One block, fixed summation order (deterministic).
 __global__ void __launch_bounds__(256)
 finalize_losses_kernel(const float* __restrict__ actor_part, const float* __restrict__ reg_part,
-                       int B, float actor_scale, float reg_scale, float lambda,
-                       float* __restrict__ losses) {
+                       int B, float actor_scale, float reg_scale, const float* __restrict__ reg_scale_dev,
+                       float lambda, float* __restrict__ losses) {
   __shared__ float sa[256], sr[256];
   float a = 0.f, r = 0.f;
   for (int i = threadIdx.x; i < B; i += 256) {
@@ -102,7 +102,8 @@ finalize_losses_kernel(const float* __restrict__ actor_part, const float* __rest
     __syncthreads();
   }
   if (threadIdx.x == 0) {
-    const float actor = sa[0] * actor_scale, reg = sr[0] * reg_scale;
+    const float actor = sa[0] * actor_scale;
+    const float reg = reg_scale_dev ? sr[0] * reg_scale * reg_scale_dev[0] : sr[0] * reg_scale;
     losses[0] = actor;
     losses[1] = reg;
     losses[2] = lambda * reg + actor;
@@ -220,9 +221,16 @@ int gabril_mse_head(const float* raw, int ld_raw, const float* bias, const float
 
 int gabril_finalize_losses(const float* actor_part, const float* reg_part, int B, float actor_scale,
                            float reg_scale, float lambda, float* losses, cudaStream_t stream) {
+  return gabril_finalize_losses_sel(actor_part, reg_part, B, actor_scale, reg_scale, nullptr, lambda,
+                                    losses, stream);
+}
+
+int gabril_finalize_losses_sel(const float* actor_part, const float* reg_part, int B,
+                               float actor_scale, float reg_scale, const float* reg_scale_dev,
+                               float lambda, float* losses, cudaStream_t stream) {
   if (!actor_part || !losses) return GABRIL_ERR_NULL;
   finalize_losses_kernel<<<1, 256, 0, stream>>>(actor_part, reg_part, B, actor_scale, reg_scale,
-                                                lambda, losses);
+                                                reg_scale_dev, lambda, losses);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
 }

@@ -23,7 +23,8 @@ class StepEngine:
     def __init__(self, spec: PolicySpec, arena: ParamArena, gaze_pre: GazePreprocessor, *,
                  gaze_method: str = "Reg", dp_method: str = "None", grayscale: bool = True,
                  frame_stack: int = 2, beta: float = 50.0, lam: float = 10.0,
-                 aggregate: bool = True, grad_accum: int = 1, seed: int = 0):
+                 aggregate: bool = True, grad_accum: int = 1, seed: int = 0,
+                 prob_dist_type: str = "MSE", gaze_ratio: float = 1.0):
         if gaze_method not in ("None", "Reg", "Teacher"):
             raise NotImplementedError(f"gaze.method={gaze_method} is outside the B200 hot path "
                                       "(supported: None, Reg, Teacher)")
@@ -43,7 +44,10 @@ class StepEngine:
         self.rng = torch.Generator(device=self.device)
         self.rng.manual_seed(seed)
         self.injected_A: Optional[torch.Tensor] = None  # parity tests inject GMD's uniform draw
-        self.gaze_ratio = 1.0
+        if prob_dist_type not in ops.DIST_KINDS:
+            raise ValueError(f"Invalid prob_dist_type: {prob_dist_type}")   # train_bc.py:171
+        self.prob_dist_type = prob_dist_type
+        self.gaze_ratio = float(gaze_ratio)
         self._accum_count = 0
         self.on_heads_grads_ready = None   # hooks for the data-parallel bucket all-reduce
         self.on_all_grads_ready = None
@@ -73,6 +77,8 @@ class StepEngine:
         b["a5"], b["z"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.E)
         b["heat"] = torch.empty(B, self.S, s.H, s.W, device=dev, dtype=f32)
         b["rowmask"] = torch.empty(B, s.n, device=dev, dtype=f32)
+        b["sel"] = torch.empty(B, device=dev, dtype=f32)
+        b["sel_stats"] = torch.empty(2, device=dev, dtype=f32)
         b["K"] = torch.empty(B, s.n, device=dev, dtype=f32)
         b["mnmx"] = torch.empty(2, device=dev, dtype=torch.int32)
         b["zf_raw"] = torch.empty(B, s.Z, device=dev, dtype=f32)
@@ -120,13 +126,18 @@ class StepEngine:
         ops.obs_patches_s2d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["patches"])
         if self.use_reg or self.use_gmd:
             self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
+        # ---- which samples use gaze (train_bc.py:230-240); all of them at gaze.ratio >= 1 ----
+        self.sel = self.sel_stats = None
+        if self.gaze_ratio < 1.0 and (self.use_reg or self.use_gmd):
+            self.sel, self.sel_stats = ops.ivg_select(frames, self.S, center, self.grayscale,
+                                                      self.gaze_ratio, b["sel"], b["sel_stats"])
         rowmask = None
         if self.use_gmd:
             # A is drawn before the interpolation, like gaze_utils.py:36
             A = self.injected_A if self.injected_A is not None else torch.rand(
                 B, s.n, device=self.device, dtype=torch.float32, generator=self.rng)
             ops.gmd_mask(b["heat"], A.reshape(B, s.n), s.h, s.w, 0.7, False, rowmask=b["rowmask"],
-                         ws=(b["K"], b["mnmx"]))
+                         ws=(b["K"], b["mnmx"]), sel=self.sel)
             rowmask = b["rowmask"]
         self._encoder_fwd(rowmask)
         self._heads_fwd(actions, center)
@@ -177,13 +188,18 @@ class StepEngine:
         # ---- regulariser (train_bc.py:145-150,168-169) on the (post-dropout) z ----
         reg_scale = 0.0
         if self.use_reg:
-            n_sel = B  # gaze.ratio = 1
-            reg_scale = 1.0 / (n_sel * s.H * s.W)
+            # mean over the selected samples (and, for MSE, their pixels); with gaze.ratio < 1 the
+            # number selected is a device scalar: sel_stats[1] = B / n_selected rescales both uses
+            reg_scale = 1.0 / (B * s.H * s.W) if self.prob_dist_type == "MSE" else 1.0 / B
             g1 = b["heat"][:, self.S - 1]
-            ops.reg_mse(b["z"], g1, b["heat"].stride(0), s.H, s.W, self.beta,
-                        self.lam * scale * reg_scale, b["dz_reg"], b["reg_part"], stats=b["stats"])
+            sdev = self.sel_stats[1:] if self.sel_stats is not None else None
+            ops.reg_dist(b["z"], g1, b["heat"].stride(0), s.H, s.W, self.beta,
+                         self.lam * scale * reg_scale, b["dz_reg"], b["reg_part"],
+                         kind=self.prob_dist_type, sel=self.sel, scale_dev=sdev, stats=b["stats"])
         ops.finalize_losses(b["actor_part"], b["reg_part"] if self.use_reg else None, B,
-                            1.0 / (B * s.A), reg_scale, self.lam, b["losses"])
+                            1.0 / (B * s.A), reg_scale, self.lam, b["losses"],
+                            reg_scale_dev=(self.sel_stats[1:] if self.use_reg and self.sel_stats is not None
+                                           else None))
         return b["losses"]
 
     # ------------------------------------------------------------------------------------------

@@ -338,8 +338,9 @@ def gaze_splat(gaze, out, ktab, Lk_host, agg_coeff, step_coeff, normalize_base, 
     return out
 
 
-def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=None, ws=None):
-    """g fp32 [B,S,H,W], A fp32 [B,h*w] -> rowmask fp32 [B,h*w] (gaze_utils.py:33-52)."""
+def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=None, ws=None, sel=None):
+    """g fp32 [B,S,H,W], A fp32 [B,h*w] -> rowmask fp32 [B,h*w] (gaze_utils.py:33-52); sel fp32 [B]
+    (optional): samples with sel <= 0 see a zero heat map (train_bc.py:258)."""
     _chk(g, torch.float32, "g"); _chk(A, torch.float32, "A")
     B, S, H, W = g.shape
     if rowmask is None:
@@ -347,7 +348,7 @@ def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=Non
     if ws is None:
         ws = (torch.empty(B, h * w, device=g.device, dtype=torch.float32),
               torch.empty(2, device=g.device, dtype=torch.int32))
-    _call("gabril_gmd_mask", ptr(g), ptr(A), ptr(ws[0]), ptr(ws[1]), ptr(rowmask), ptr(keep_out),
+    _call("gabril_gmd_mask_sel", ptr(g), ptr(sel), ptr(A), ptr(ws[0]), ptr(ws[1]), ptr(rowmask), ptr(keep_out),
           c_int(B), c_int(S), c_int(H), c_int(W), c_int(h), c_int(w), c_float(drop_p),
           c_int(int(test_mode)), stream(), work=float(B * h * w * (16 * S * 4 + 16)))
     return rowmask
@@ -411,6 +412,38 @@ def reg_mse(z, g1_base, g1_bstride, H, W, beta, grad_scale, dz, loss_part, sel=N
           work=float(B * (2 * z.element_size() * C * h * w + 4 * H * W)))
 
 
+DIST_KINDS = {"MSE": 0, "KL": 1, "TV": 2, "JS": 3}
+
+
+def reg_dist(z, g1_base, g1_bstride, H, W, beta, grad_scale, dz, loss_part, kind="MSE", sel=None,
+             scale_dev=None, stats=None):
+    """Fused regulariser forward+backward for gaze.prob_dist_type in {MSE, KL, TV, JS}
+    (train_bc.py:152-169); scale_dev: optional device scalar multiplied into grad_scale."""
+    assert z.is_cuda and z.is_contiguous()
+    if kind not in DIST_KINDS:
+        raise ValueError(f"Invalid prob_dist_type: {kind}")
+    B, C, h, w = _z_dims(z)
+    _call("gabril_reg_dist", ptr(z), c_int(_z_layout(z)), ptr(g1_base), c_ll(g1_bstride), ptr(sel),
+          ptr(scale_dev), c_int(DIST_KINDS[kind]), ptr(dz), ptr(loss_part), ptr(stats), c_int(B),
+          c_int(C), c_int(h), c_int(w), c_int(H), c_int(W), c_float(beta), c_float(grad_scale), stream(),
+          work=float(B * (2 * z.element_size() * C * h * w + 4 * H * W)))
+
+
+def ivg_select(frames, S, center, grayscale, ratio, sel=None, sel_stats=None):
+    """gaze.ratio < 1 sample selection (train_bc.py:230-240) from the uint8 frames [B,L,H,W,3].
+    Returns (sel fp32 [B], sel_stats fp32 [2] = (n_selected, B / n_selected))."""
+    _chk(frames, torch.uint8, "frames")
+    B, L, H, W, _ = frames.shape
+    if sel is None:
+        sel = torch.empty(B, device=frames.device, dtype=torch.float32)
+    if sel_stats is None:
+        sel_stats = torch.empty(2, device=frames.device, dtype=torch.float32)
+    _call("gabril_ivg_select", ptr(frames), ptr(sel), ptr(sel_stats), c_int(B), c_int(L), c_int(S),
+          c_int(center), c_int(H), c_int(W), c_int(int(grayscale)), c_float(ratio), stream(),
+          work=float(B * S * H * W * 3))
+    return sel, sel_stats
+
+
 def colsum_bf16(dy, db):
     _chk(dy, torch.bfloat16, "dy"); _chk(db, torch.float32, "db")
     C = db.numel()
@@ -434,9 +467,9 @@ def mse_head(raw, bias, actions_view, A, part, gscale, dlogits=None, dbias=None,
           ptr(dbias), ptr(part), c_int(B), c_float(gscale), stream())
 
 
-def finalize_losses(actor_part, reg_part, B, actor_scale, reg_scale, lam, losses):
-    _call("gabril_finalize_losses", ptr(actor_part), ptr(reg_part), c_int(B), c_float(actor_scale),
-          c_float(reg_scale), c_float(lam), ptr(losses), stream())
+def finalize_losses(actor_part, reg_part, B, actor_scale, reg_scale, lam, losses, reg_scale_dev=None):
+    _call("gabril_finalize_losses_sel", ptr(actor_part), ptr(reg_part), c_int(B), c_float(actor_scale),
+          c_float(reg_scale), ptr(reg_scale_dev), c_float(lam), ptr(losses), stream())
 
 
 def adam(p, g, m, v, shadow, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0,

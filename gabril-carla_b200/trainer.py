@@ -307,8 +307,6 @@ class BCTrainer(BaseTrainer):
             raise NotImplementedError(
                 f"gaze.method={c.gaze.method} / dropout.method={c.dropout.method}: the B200 hot path covers "
                 "gaze.method in {None, Reg, Teacher} x dropout.method in {None, GMD} (SURVEY.md §8b)")
-        if float(c.gaze.ratio) < 1.0 or c.gaze.prob_dist_type != "MSE":
-            raise NotImplementedError("gaze.ratio < 1 and prob_dist_type != MSE are 'next' rows (SURVEY.md §8f N1)")
         S = int(c.model.frame_stack)
         cin = S * (1 if c.model.grayscale else 3)
         spec = PolicySpec(cin, int(c.data.img_height), int(c.data.img_width), int(c.model.embedding_dim),
@@ -331,7 +329,9 @@ class BCTrainer(BaseTrainer):
                                  frame_stack=S, beta=float(c.gaze.beta), lam=float(c.gaze.lambda_weight),
                                  aggregate=bool(c.gaze.get("temporal_flag", True)),
                                  grad_accum=int(c.training.gradient_accumulation_steps),
-                                 seed=int(c.training.seed) + 7919 * self.rank)
+                                 seed=int(c.training.seed) + 7919 * self.rank,
+                                 prob_dist_type=str(c.gaze.prob_dist_type),
+                                 gaze_ratio=float(c.gaze.ratio))
         self.reducer = ddp.attach(self.engine, self.arena)
         self.encoder = ArenaModule(self.arena, "encoder")
         self.pre_actor = ArenaModule(self.arena, "pre_actor")

@@ -114,6 +114,11 @@ int gabril_gaze_splat(const float* gaze, float* out, float* ext_ws /* [B][32] fp
 int gabril_gmd_mask(const float* g, const float* A, float* K_ws, unsigned int* mnmx_ws,
                     float* rowmask, float* keep_out, int B, int S, int H, int W, int h, int w,
                     float drop_p, int test_mode, cudaStream_t stream);
+/* The same with the per-sample gaze selection of train_bc.py:258 (gg_for_cat = ivg * gg): samples
+ * with sel[b] <= 0 contribute an all-zero heat map (sel may be NULL = all selected). */
+int gabril_gmd_mask_sel(const float* g, const float* sel, const float* A, float* K_ws,
+                        unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B, int S, int H,
+                        int W, int h, int w, float drop_p, int test_mode, cudaStream_t stream);
 /* out[b, c, j] = z[b, c, j] * rowmask[b, j] on the reference's fp32 NCHW layout. */
 int gabril_rowmask_apply_nchw(const float* z, const float* rowmask, float* out, int B, int C, int n,
                               cudaStream_t stream);
@@ -133,6 +138,24 @@ int gabril_reg_mse(const void* z, int z_nhwc_bf16, const float* g1, long long g1
                    const float* sel, void* dz, float* loss_part, float* stats, int B, int C, int h,
                    int w, int H, int W, float beta, float grad_scale, cudaStream_t stream);
 
+/* The regulariser with the configured distance (gaze.prob_dist_type, train_bc.py:152-169):
+ * GABRIL_DIST_MSE as above; KL / TV / JS first divide g1 and the mask by their detached sums + 1e-8,
+ * loss_part[b] is then the per-sample sum of the divergence (the caller's mean over the selected
+ * samples = sum_b loss_part / n_selected).  scale_dev (optional): device scalar multiplied into
+ * grad_scale, e.g. sel_stats + 1 of gabril_ivg_select when the number of selected samples is only
+ * known on the device. */
+enum { GABRIL_DIST_MSE = 0, GABRIL_DIST_KL = 1, GABRIL_DIST_TV = 2, GABRIL_DIST_JS = 3 };
+int gabril_reg_dist(const void* z, int z_nhwc_bf16, const float* g1, long long g1_bstride,
+                    const float* sel, const float* scale_dev, int dist, void* dz, float* loss_part,
+                    float* stats, int B, int C, int h, int w, int H, int W, float beta,
+                    float grad_scale, cudaStream_t stream);
+/* gaze.ratio < 1 (train_bc.py:230-240): sel[b] = 1 iff frac(|sum(obs_b) * 123456.789|) < ratio, with
+ * obs the formatted frame stack of gabril_obs_format (uint8 frames [B, L, H, W, 3], window of S
+ * frames ending at `center`); ratio >= 1 selects all, <= 0 none.  sel_stats[0] = number selected,
+ * sel_stats[1] = B / number selected. */
+int gabril_ivg_select(const uint8_t* frames, float* sel, float* sel_stats, int B, int L, int S,
+                      int center, int H, int W, int grayscale, float ratio, cudaStream_t stream);
+
 /* ---- heads, losses, optimiser ------------------------------------------------------------- */
 /* db[c] += sum_rows dy[row][c]  (bias gradient of nn.Conv2d / nn.Linear); dy bf16 [M, C]. */
 int gabril_colsum_bf16(const void* dy, float* db, long long M, int C, cudaStream_t stream);
@@ -148,6 +171,10 @@ int gabril_mse_head(const float* raw, int ld_raw, const float* bias, const float
 /* losses[0] = actor, [1] = reg, [2] = lambda * reg + actor (train_bc.py:297); deterministic. */
 int gabril_finalize_losses(const float* actor_part, const float* reg_part, int B, float actor_scale,
                            float reg_scale, float lambda, float* losses, cudaStream_t stream);
+/* reg additionally multiplied by the device scalar reg_scale_dev[0] (NULL = 1). */
+int gabril_finalize_losses_sel(const float* actor_part, const float* reg_part, int B,
+                               float actor_scale, float reg_scale, const float* reg_scale_dev,
+                               float lambda, float* losses, cudaStream_t stream);
 /* torch.optim.Adam (decoupled = 0) / AdamW (1) step `step` (1-based) over a flat fp32 arena
  * (optim.py:11-28); grads are multiplied by grad_scale first; the bf16 shadow is refreshed. */
 int gabril_adam(float* p, const float* g, float* m, float* v, void* shadow_bf16, long long n,

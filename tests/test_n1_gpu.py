@@ -1,0 +1,161 @@
+"""-m gpu parity for SURVEY.md §8f row N1: KL / TV / JS regulariser variants (train_bc.py:152-167)
+and the gaze.ratio < 1 sample selection (train_bc.py:230-240), CUDA path vs the oracle (itself pinned
+on the reference's numbers by tests/test_n1_cpu.py) and vs the committed golden losses."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gabril_oracle as O
+from tests.synth import make_batch, make_batch_n1, make_weights
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "reference_vectors_n1.npz")
+
+
+@pytest.fixture(scope="module")
+def G():
+    import gabril_carla_b200  # noqa: F401
+    from gabril_carla_b200 import _lib, gaze, ops
+    _lib.init()
+
+    class NS:
+        pass
+    ns = NS()
+    ns.ops, ns.gaze, ns.lib = ops, gaze, _lib
+    return ns
+
+
+def rel(a, b):
+    return ((a - b).norm() / (b.norm() + 1e-30)).item()
+
+
+@pytest.mark.parametrize("kind", ["KL", "TV", "JS", "MSE"])
+@pytest.mark.parametrize("nhwc", [True, False])
+def test_reg_dist_fused(G, kind, nhwc):
+    """One kernel = get_gaze_mask + sum-normalisation + divergence + the whole adjoint chain."""
+    g = torch.Generator().manual_seed(9)
+    B = 5
+    z = (torch.randn(B, 64, 20, 38, generator=g) * 2.0).to(torch.bfloat16).float()
+    _, gaze, _ = make_batch(B, seed=10)
+    heat = O.stack_heatmaps(gaze, 2, 1, 180, 320, 30.0)
+    sel = torch.tensor([1.0, 0.0, 1.0, 1.0, 0.0])
+    for ivg in (torch.ones(B), sel):
+        zr = z.clone().requires_grad_(True)
+        loss = O.reg_loss(zr, heat, ivg, 50.0, (180, 320), kind)
+        (10.0 * loss).backward()
+        zin = (z.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16) if nhwc else z.clone()).to(DEV)
+        heat_d = heat.to(DEV)
+        dz = torch.full_like(zin, float("nan"))
+        part = torch.empty(B, device=DEV)
+        n_sel = int(ivg.sum().item())
+        scale = 1.0 / (B * 180 * 320) if kind == "MSE" else 1.0 / B
+        sdev = torch.tensor([B / n_sel], device=DEV)
+        G.ops.reg_dist(zin, heat_d[:, 1], heat_d.stride(0), 180, 320, 50.0, 10.0 * scale, dz, part,
+                       kind=kind, sel=ivg.to(DEV), scale_dev=sdev)
+        got_loss = part.sum().item() * scale * B / n_sel
+        assert abs(got_loss - loss.item()) <= 1e-4 * abs(loss.item()), (kind, got_loss, loss.item())
+        dref = zr.grad.permute(0, 2, 3, 1) if nhwc else zr.grad
+        derr = rel(dz.float().cpu(), dref)
+        # NHWC: bf16 output rounding (2^-9 per element); NCHW fp32: summation order only.
+        # TV's gradient is a sign function of (g1 - g2): pixels within rounding of a tie may flip.
+        tol = (5e-3 if nhwc else 2e-4) * (4.0 if kind == "TV" else 1.0)
+        assert derr <= tol, (kind, nhwc, derr)
+        unsel = ivg == 0
+        assert torch.count_nonzero(dz.float().cpu()[unsel]) == 0
+        assert torch.count_nonzero(part.cpu()[unsel]) == 0
+
+
+def test_ivg_select(G):
+    gold = np.load(GOLD)
+    img, gaze, _ = make_batch_n1()
+    sel, stats = G.ops.ivg_select(img.to(DEV), 2, 1, True, 0.5)
+    assert sel.cpu().tolist() == gold["ivg/sel_0.5"].tolist() == [1.0, 1.0, 0.0, 1.0]
+    assert stats.cpu().tolist() == [3.0, 4.0 / 3.0] or abs(stats[1].item() - 4 / 3) < 1e-6
+    # thresholds either side of the two non-trivial hashes r = 0.765625 and r = 0.169921875 (exact)
+    assert G.ops.ivg_select(img.to(DEV), 2, 1, True, 0.77)[0].cpu().tolist() == [1.0, 1.0, 1.0, 1.0]
+    assert G.ops.ivg_select(img.to(DEV), 2, 1, True, 0.765625)[0].cpu().tolist() == [1.0, 1.0, 0.0, 1.0]
+    assert G.ops.ivg_select(img.to(DEV), 2, 1, True, 0.1699)[0].cpu().tolist() == [1.0, 1.0, 0.0, 0.0]
+    assert G.ops.ivg_select(img.to(DEV), 2, 1, True, 1.0)[0].cpu().tolist() == [1.0] * 4
+    s0, st0 = G.ops.ivg_select(img.to(DEV), 2, 1, True, 0.0)
+    assert s0.cpu().tolist() == [0.0] * 4 and st0[0].item() == 0.0 and torch.isinf(st0[1])
+    # RGB stack: ordinary frames hash to r = 0 as well (sum >> 68)
+    assert G.ops.ivg_select(img.to(DEV), 2, 1, False, 0.01)[0].cpu().tolist()[:2] == [1.0, 1.0]
+    # against the oracle on a larger ordinary batch
+    img2, gaze2, _ = make_batch(8, seed=5)
+    obs, _, _ = O.prepare_for_bc(img2, gaze2, 2, True, 180, 320, 30.0, 0.7, 5, True)
+    assert G.ops.ivg_select(img2.to(DEV), 2, 1, True, 0.3)[0].cpu().tolist() == O.uses_gaze(obs, 0.3).tolist()
+
+
+def test_gmd_mask_with_selection(G):
+    _, gaze, _ = make_batch(8, seed=7)
+    heat = O.stack_heatmaps(gaze, 2, 1, 180, 320, 30.0)
+    ivg = torch.tensor([1, 0, 1, 1, 0, 1, 0, 1], dtype=torch.float32)
+    A = torch.rand(8, 760, generator=torch.Generator().manual_seed(0))
+    keep = torch.empty(8, 760, device=DEV)
+    mask = G.ops.gmd_mask(heat.to(DEV), A.to(DEV), 20, 38, 0.7, False, keep_out=keep, sel=ivg.to(DEV)).cpu()
+    K = O.gmd_keep_prob(ivg.view(-1, 1, 1, 1) * heat, (20, 38)).reshape(8, 760)
+    assert (keep.cpu() - K).abs().max().item() <= 2e-6
+    decided = (A - K).abs() > 1e-5
+    assert torch.equal(mask[decided], (A < K).float()[decided])
+
+
+def build_engine(kind, ratio, dp):
+    import gabril_carla_b200  # noqa: F401
+    from gabril_carla_b200.engine import StepEngine
+    from gabril_carla_b200.gaze import GazePreprocessor
+    from gabril_carla_b200.model import ParamArena, PolicySpec
+    spec = PolicySpec(2)
+    arena = ParamArena(spec, DEV)
+    arena.load_reference(make_weights(2, seed=7))
+    eng = StepEngine(spec, arena, GazePreprocessor(device=DEV), gaze_method="Reg", dp_method=dp,
+                     grayscale=True, prob_dist_type=kind, gaze_ratio=ratio)
+    return spec, arena, eng
+
+
+@pytest.mark.parametrize("kind,ratio,dp", [("KL", 1.0, "None"), ("TV", 1.0, "None"), ("JS", 1.0, "None"),
+                                           ("MSE", 0.5, "None"), ("MSE", 0.5, "GMD"), ("KL", 0.5, "GMD")])
+def test_step_variants_match_reference_and_oracle(kind, ratio, dp):
+    """Whole step on the golden batch with the golden weights: losses against the reference's own
+    numbers (fp32; 5e-3 as in test_step_gpu) and, with our activations injected, losses 1e-3 and
+    gradients 1e-2 / 2e-2 (TV) against the bf16-emulating oracle."""
+    gold = np.load(GOLD)
+    spec, arena, eng = build_engine(kind, ratio, dp)
+    batch = make_batch_n1()
+    A = torch.from_numpy(gold["gmd/A"])
+    if dp == "GMD":
+        eng.injected_A = A.reshape(4, 760).to(DEV)
+    eng.zero_grad()
+    eng.forward(*(t.to(DEV) for t in batch))
+    eng.backward()
+    actor, reg, total = eng.losses_host()
+    from gabril_carla_b200 import _lib
+    _lib.poll_error()
+    tag = f"step/{kind}_r{ratio}_{dp}"
+    for name, got in (("actor", actor), ("reg", reg), ("total", total)):
+        ref = float(gold[f"{tag}/{name}"])
+        assert abs(got - ref) <= 5e-3 * abs(ref), (name, got, ref)
+    if ratio < 1.0:
+        assert eng.sel.cpu().tolist() == [1.0, 1.0, 0.0, 1.0]
+    from tests.test_step_gpu import our_activations
+    ours = our_activations(eng)
+    sds = {m: {k: v.cpu().clone().requires_grad_(True) for k, v in sd.items()}
+           for m, sd in arena.state_dicts().items()}
+    o_total, o_actor, o_reg, _ = O.bc_losses(sds["encoder"], sds["pre_actor"], sds["actor"], *batch,
+                                             gaze_method="Reg", dp_method=dp, ratio=ratio,
+                                             prob_dist_type=kind, gmd_A=A, emulate_bf16=True, inject=ours)
+    o_total.backward()
+    for name, got, ref in (("actor", actor, o_actor.item()), ("reg", reg, o_reg.item()),
+                           ("total", total, o_total.item())):
+        assert abs(got - ref) <= 1e-3 * abs(ref), (name, got, ref)
+    grads = arena.grad_dicts()
+    worst, worst_k = 0.0, None
+    for mod in grads:
+        for k, gv in grads[mod].items():
+            r = rel(gv.cpu().flatten(), sds[mod][k].grad.flatten()) * (0.5 if k.endswith("bias") else 1.0)
+            if r > worst:
+                worst, worst_k = r, (mod, k)
+    print(f"[{tag}] losses actor {actor:.6f} reg {reg:.6f}; worst grad rel {worst:.2e} at {worst_k}")
+    assert worst <= (2e-2 if kind == "TV" else 1e-2), (worst, worst_k)
