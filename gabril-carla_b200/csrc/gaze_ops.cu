@@ -379,7 +379,8 @@ __global__ void gmd_init_kernel(unsigned int* mnmx) {
 __global__ void __launch_bounds__(256)
 gmd_mask_kernel(const float* __restrict__ K, const float* __restrict__ A,
                 const unsigned int* __restrict__ mnmx, float* __restrict__ rowmask,
-                float* __restrict__ keep_out, long long total, float drop_p, int test_mode) {
+                float* __restrict__ keep_out, long long total, float drop_p, int test_mode,
+                int layout, int h, int w, int SH, int SW) {
   const float mn = ordered_to_f32(mnmx[0]), mx = ordered_to_f32(mnmx[1]);
   const float den = __fadd_rn(__fsub_rn(mx, mn), 1e-8f);
   const float one_minus = (float)(1.0 - (double)drop_p);
@@ -388,7 +389,18 @@ gmd_mask_kernel(const float* __restrict__ K, const float* __restrict__ A,
     const float kh = __fdiv_rn(__fsub_rn(K[idx], mn), den);
     const float kt = __fadd_rn(__fmul_rn(drop_p, kh), one_minus);
     if (keep_out) keep_out[idx] = kt;
-    rowmask[idx] = test_mode ? kt : ((A[idx] < kt) ? 1.f : 0.f);
+    long long o = idx;
+    if (layout != GABRIL_MASK_PLAIN) {
+      // the storage order of the activation the mask multiplies (pixel (oy, ox) sits at (oy+1, ox+1)
+      // of a zero-bordered grid; conv_1's output additionally space-to-depth by 2)
+      const int n = h * w;
+      const long long b = idx / n;
+      const int j = (int)(idx - b * n), oy = j / w + 1, ox = j % w + 1;
+      o = (layout == GABRIL_MASK_S2D)
+              ? ((b * SH + (oy >> 1)) * SW + (ox >> 1)) * 4 + ((oy & 1) * 2 + (ox & 1))
+              : (b * SH + oy) * SW + ox;
+    }
+    rowmask[o] = test_mode ? kt : ((A[idx] < kt) ? 1.f : 0.f);
   }
 }
 
@@ -962,13 +974,25 @@ int gabril_gmd_mask(const float* g, const float* A, float* K_ws, unsigned int* m
 int gabril_gmd_mask_sel(const float* g, const float* sel, const float* A, float* K_ws,
                         unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B, int S, int H,
                         int W, int h, int w, float drop_p, int test_mode, cudaStream_t stream) {
+  return gabril_gmd_mask_layout(g, sel, A, K_ws, mnmx_ws, rowmask, keep_out, B, S, H, W, h, w, drop_p,
+                                test_mode, GABRIL_MASK_PLAIN, 0, 0, stream);
+}
+
+int gabril_gmd_mask_layout(const float* g, const float* sel, const float* A, float* K_ws,
+                           unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B, int S,
+                           int H, int W, int h, int w, float drop_p, int test_mode, int layout,
+                           int SH, int SW, cudaStream_t stream) {
+  if (layout == GABRIL_MASK_S2D && (2 * SH < h + 2 || 2 * SW < w + 2)) return GABRIL_ERR_BAD_SHAPE;
+  if (layout == GABRIL_MASK_BORDERED && (SH < h + 2 || SW < w + 2)) return GABRIL_ERR_BAD_SHAPE;
+  if (layout < GABRIL_MASK_PLAIN || layout > GABRIL_MASK_BORDERED) return GABRIL_ERR_BAD_SHAPE;
   if (!g || !K_ws || !mnmx_ws || !rowmask || (!A && !test_mode)) return GABRIL_ERR_NULL;
   if (B <= 0 || S < 1) return GABRIL_ERR_BAD_SHAPE;
   const long long total = (long long)B * h * w;
   gmd_init_kernel<<<1, 1, 0, stream>>>(mnmx_ws);
   gmd_keep_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(g, sel, K_ws, mnmx_ws, B, S, H, W, h, w);
   gmd_mask_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(K_ws, A, mnmx_ws, rowmask, keep_out,
-                                                                     total, drop_p, test_mode);
+                                                                     total, drop_p, test_mode, layout,
+                                                                     h, w, SH, SW);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
 }

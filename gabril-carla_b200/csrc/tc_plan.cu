@@ -551,6 +551,17 @@ int gabril_conv_flat(const void* x, const void* w, const float* bias, const void
                      const void* gate, void* y, int N, int Hg, int Wg, int Cx, int Cy, int R, int S,
                      int valid_h, int valid_w, int o_rows, int o_pitch, int o_off_h, int o_off_w,
                      int relu, int transpose_w, cudaStream_t stream) {
+  return gabril_conv_flat_masked(x, w, bias, resid, gate, nullptr, y, N, Hg, Wg, Cx, Cy, R, S, valid_h,
+                                 valid_w, o_rows, o_pitch, o_off_h, o_off_w, relu, transpose_w, stream);
+}
+
+// rowmask: per OUTPUT-STORAGE pixel multiplier (index = pixel index of y after the remap), applied
+// after bias / ReLU - the in-encoder gaze dropout of linear_models.py:194-199.
+int gabril_conv_flat_masked(const void* x, const void* w, const float* bias, const void* resid,
+                            const void* gate, const float* rowmask, void* y, int N, int Hg, int Wg,
+                            int Cx, int Cy, int R, int S, int valid_h, int valid_w, int o_rows,
+                            int o_pitch, int o_off_h, int o_off_w, int relu, int transpose_w,
+                            cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
   if (Cx % 64 || N <= 0 || R < 1 || S < 1 || S > 8) return GABRIL_ERR_BAD_SHAPE;
@@ -607,7 +618,7 @@ int gabril_conv_flat(const void* x, const void* w, const float* bias, const void
   // epilogue
   p.out_mode = tc::OUT_BF16;
   p.out = y; p.ldo = Cy;
-  p.bias = bias; p.resid = (const bf16*)resid; p.gate = (const bf16*)gate; p.rowmask = nullptr;
+  p.bias = bias; p.resid = (const bf16*)resid; p.gate = (const bf16*)gate; p.rowmask = rowmask;
   p.relu = relu;
   if (valid_h > 0) {
     p.remap = 1; p.remap_sh = 1; p.remap_sw = 1;
@@ -712,6 +723,14 @@ int gabril_conv_wgrad_flat(const void* dy, const void* x, float* dw, int N, int 
 int gabril_conv1_s2d_fwd(const void* patches, const void* w, const float* bias, void* y, int N,
                          int SH, int SW, int img_h, int img_w, int Kp, int Cout, int relu,
                          cudaStream_t stream) {
+  return gabril_conv1_s2d_fwd_masked(patches, w, bias, nullptr, y, N, SH, SW, img_h, img_w, Kp, Cout,
+                                     relu, stream);
+}
+
+// rowmask: one multiplier per patch row (space-to-depth order [N, SH, SW, 4]), after bias / ReLU.
+int gabril_conv1_s2d_fwd_masked(const void* patches, const void* w, const float* bias,
+                                const float* rowmask, void* y, int N, int SH, int SW, int img_h,
+                                int img_w, int Kp, int Cout, int relu, cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
   if (Kp % 32 || !fwd_cout_ok(Cout) || N <= 0) return GABRIL_ERR_BAD_SHAPE;
@@ -741,7 +760,7 @@ int gabril_conv1_s2d_fwd(const void* patches, const void* w, const float* bias, 
   if (rc) return rc;
   p.out_mode = tc::OUT_BF16;
   p.out = y; p.ldo = Cout;
-  p.bias = bias; p.relu = relu;
+  p.bias = bias; p.relu = relu; p.rowmask = rowmask;
   p.border_h = SH; p.border_w = SW; p.s2d_H = img_h; p.s2d_W = img_w;
   p.err_flag = g_err_flag;
   size_t smem;

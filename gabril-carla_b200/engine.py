@@ -28,13 +28,14 @@ class StepEngine:
         if gaze_method not in ("None", "Reg", "Teacher"):
             raise NotImplementedError(f"gaze.method={gaze_method} is outside the B200 hot path "
                                       "(supported: None, Reg, Teacher)")
-        if dp_method not in ("None", "GMD"):
+        if dp_method not in ("None", "GMD", "IGMD"):
             raise NotImplementedError(f"dropout.method={dp_method} is outside the B200 hot path "
-                                      "(supported: None, GMD)")
+                                      "(supported: None, GMD, IGMD)")
         _lib.init()
         self.spec, self.arena, self.gaze_pre = spec, arena, gaze_pre
         self.use_reg = gaze_method in ("Reg", "Teacher")
         self.use_gmd = dp_method == "GMD"
+        self.use_igmd = dp_method == "IGMD"   # in-encoder dropout, linear_models.py:194-199
         self.grayscale, self.S = grayscale, frame_stack
         self.beta, self.lam, self.aggregate = float(beta), float(lam), aggregate
         self.grad_accum = max(1, int(grad_accum))
@@ -44,6 +45,7 @@ class StepEngine:
         self.rng = torch.Generator(device=self.device)
         self.rng.manual_seed(seed)
         self.injected_A: Optional[torch.Tensor] = None  # parity tests inject GMD's uniform draw
+        self.injected_A_igmd = None                     # ... and IGMD's pair ([B,H1*W1], [B,H2*W2])
         if prob_dist_type not in ops.DIST_KINDS:
             raise ValueError(f"Invalid prob_dist_type: {prob_dist_type}")   # train_bc.py:171
         self.prob_dist_type = prob_dist_type
@@ -80,6 +82,13 @@ class StepEngine:
         b["sel"] = torch.empty(B, device=dev, dtype=f32)
         b["sel_stats"] = torch.empty(2, device=dev, dtype=f32)
         b["K"] = torch.empty(B, s.n, device=dev, dtype=f32)
+        if self.use_igmd:
+            # masks in the storage order of the activations they multiply (cells of border pixels
+            # are never read for a stored value: those rows are zeroed by the conv epilogues)
+            b["rm1"] = torch.zeros(B * self.SH * self.SW * 4, device=dev, dtype=f32)
+            b["rm2"] = torch.zeros(B * self.SH * self.SW, device=dev, dtype=f32)
+            b["K1"] = torch.empty(B, s.H1 * s.W1, device=dev, dtype=f32)
+            b["K2"] = torch.empty(B, s.H2 * s.W2, device=dev, dtype=f32)
         b["mnmx"] = torch.empty(2, device=dev, dtype=torch.int32)
         b["zf_raw"] = torch.empty(B, s.Z, device=dev, dtype=f32)
         b["zf"] = torch.empty(B, s.Z, device=dev, dtype=bf)
@@ -124,11 +133,11 @@ class StepEngine:
         center = L - 1
         # ---- preprocessing (prepare_for_bc, data_loader_robomimic.py:318-360) ----
         ops.obs_patches_s2d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["patches"])
-        if self.use_reg or self.use_gmd:
+        if self.use_reg or self.use_gmd or self.use_igmd:
             self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
         # ---- which samples use gaze (train_bc.py:230-240); all of them at gaze.ratio >= 1 ----
         self.sel = self.sel_stats = None
-        if self.gaze_ratio < 1.0 and (self.use_reg or self.use_gmd):
+        if self.gaze_ratio < 1.0 and (self.use_reg or self.use_gmd or self.use_igmd):
             self.sel, self.sel_stats = ops.ivg_select(frames, self.S, center, self.grayscale,
                                                       self.gaze_ratio, b["sel"], b["sel_stats"])
         rowmask = None
@@ -139,17 +148,34 @@ class StepEngine:
             ops.gmd_mask(b["heat"], A.reshape(B, s.n), s.h, s.w, 0.7, False, rowmask=b["rowmask"],
                          ws=(b["K"], b["mnmx"]), sel=self.sel)
             rowmask = b["rowmask"]
-        self._encoder_fwd(rowmask)
+        igmd = None
+        if self.use_igmd:
+            # apply_gmd_dropout after conv_1 + ReLU (90x160) and conv_2 + ReLU (45x80): the same keep
+            # map as GMD, interpolated to each size, its own uniform draw per layer
+            if self.injected_A_igmd is not None:
+                A1, A2 = self.injected_A_igmd
+            else:
+                A1 = torch.rand(B, s.H1 * s.W1, device=self.device, dtype=torch.float32, generator=self.rng)
+                A2 = torch.rand(B, s.H2 * s.W2, device=self.device, dtype=torch.float32, generator=self.rng)
+            ops.gmd_mask(b["heat"], A1.reshape(B, -1), s.H1, s.W1, 0.7, False, rowmask=b["rm1"],
+                         ws=(b["K1"], b["mnmx"]), sel=self.sel, layout="s2d", grid=(self.SH, self.SW))
+            ops.gmd_mask(b["heat"], A2.reshape(B, -1), s.H2, s.W2, 0.7, False, rowmask=b["rm2"],
+                         ws=(b["K2"], b["mnmx"]), sel=self.sel, layout="bordered", grid=(self.SH, self.SW))
+            igmd = (b["rm1"], b["rm2"])
+        self._encoder_fwd(rowmask, igmd)
         self._heads_fwd(actions, center)
         return b["losses"]
 
-    def _encoder_fwd(self, rowmask=None):
-        """Encoder.forward (linear_models.py:191-207) from the patch matrix to z."""
+    def _encoder_fwd(self, rowmask=None, igmd=None):
+        """Encoder.forward (linear_models.py:191-207) from the patch matrix to z.  rowmask: GMD mask
+        fused into conv_6's epilogue; igmd = (mask after conv_1, mask after conv_2): the stored a1 / a2
+        are the dropped-out activations, so their `> 0` gates carry the mask through the backward."""
         s, a, b, B = self.spec, self.arena, self.buf, self.B
         ops.conv1_s2d_fwd(b["patches"], a.WB("enc.conv1.w"), a.P("enc.conv1.b"), b["a1s"], B, self.SH,
-                          self.SW, s.H1, s.W1, relu=True)
+                          self.SW, s.H1, s.W1, relu=True, rowmask=igmd[0] if igmd else None)
         ops.conv_flat(b["a1s"], a.WB("enc.conv2.w"), b["a2p"], 2, 2, bias=a.P("enc.conv2.b"),
-                      valid=(s.H2, s.W2), out_geom=(self.SH, self.SW, 1, 1), relu=True)
+                      valid=(s.H2, s.W2), out_geom=(self.SH, self.SW, 1, 1), relu=True,
+                      rowmask=igmd[1] if igmd else None)
         ops.conv_fwd(b["a2p"], a.WB("enc.conv3.w"), a.P("enc.conv3.b"), b["a3"], 4, 4, 2, 0, relu=True)
         # conv_4 has no activation of its own; the first Residual's in-place ReLU rectifies it (F7)
         ops.conv_fwd(b["a3"], a.WB("enc.conv4.w"), a.P("enc.conv4.b"), b["r-1"], 3, 3, 1, 0, relu=True)

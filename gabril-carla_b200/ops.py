@@ -125,7 +125,7 @@ def conv_wgrad(dy, x, dw, R, S, stride, pad, direct_store=False):
 
 # ---- flat-slab convolutions over zero-bordered tensors (csrc/tc_plan.cu) ----------------------
 def conv_flat(x, w, y, R, S, *, bias=None, resid=None, gate=None, valid=None, out_geom=None, relu=False,
-              transpose_w=False, flop_pixels=None):
+              transpose_w=False, flop_pixels=None, rowmask=None):
     """x [N,Hg,Wg,Cx] bf16 zero-bordered; out(q) = sum_{r,s} x_flat[q + r*Wg + s] . W(r,s) for every
     flat pixel q.  valid=(vh, vw), out_geom=(o_rows, o_pitch, off_h, off_w): pixel (n,i,j) with
     i<vh, j<vw is stored at y row (n*o_rows + i+off_h)*o_pitch + j+off_w; valid=None stores every
@@ -144,8 +144,8 @@ def conv_flat(x, w, y, R, S, *, bias=None, resid=None, gate=None, valid=None, ou
     with _span("tc_gemm_kernel", f"{'dgrad' if transpose_w else 'fwd'}-flat {Cx}->{Cy} k{R}x{S}",
                2.0 * (flop_pixels if flop_pixels is not None else N * (vh or Hg) * (vw or Wg)) * Cy * R * S * Cx,
                "flop"):
-        st = _fn("gabril_conv_flat")(ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(gate), ptr(y), c_int(N),
-                                     c_int(Hg), c_int(Wg), c_int(Cx), c_int(Cy), c_int(R), c_int(S),
+        st = _fn("gabril_conv_flat_masked")(ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(gate), ptr(rowmask),
+                                     ptr(y), c_int(N), c_int(Hg), c_int(Wg), c_int(Cx), c_int(Cy), c_int(R), c_int(S),
                                      c_int(vh), c_int(vw), c_int(o_rows), c_int(o_pitch), c_int(off_h),
                                      c_int(off_w), c_int(int(relu)), c_int(int(transpose_w)), stream())
     _lib.check(st, "gabril_conv_flat")
@@ -167,7 +167,7 @@ def conv_wgrad_flat(dy, x, dw, R, S, dy_row_off, flop_pixels=None):
     return dw
 
 
-def conv1_s2d_fwd(patches, w, bias, y, N, SH, SW, img_h, img_w, relu=True):
+def conv1_s2d_fwd(patches, w, bias, y, N, SH, SW, img_h, img_w, relu=True, rowmask=None):
     """patches bf16 [N*SH*SW*4, Kp] (space-to-depth row order), w [Cout,1,Kp] -> y [N,SH,SW,4*Cout];
     rows of padding pixels are stored as exact zeros."""
     _chk_bf16(patches, "patches"); _chk_bf16(w, "w"); _chk_bf16(y, "y")
@@ -175,7 +175,8 @@ def conv1_s2d_fwd(patches, w, bias, y, N, SH, SW, img_h, img_w, relu=True):
     Cout = w.shape[0]
     assert patches.shape[0] == N * SH * SW * 4 and y.numel() == N * SH * SW * 4 * Cout
     with _span("tc_gemm_kernel", f"fwd {Kp}->{Cout} k1s1", 2.0 * N * img_h * img_w * Cout * Kp, "flop"):
-        st = _fn("gabril_conv1_s2d_fwd")(ptr(patches), ptr(w), ptr(bias), ptr(y), c_int(N), c_int(SH), c_int(SW),
+        st = _fn("gabril_conv1_s2d_fwd_masked")(ptr(patches), ptr(w), ptr(bias), ptr(rowmask), ptr(y), c_int(N),
+                                         c_int(SH), c_int(SW),
                                          c_int(img_h), c_int(img_w), c_int(Kp), c_int(Cout), c_int(int(relu)),
                                          stream())
     _lib.check(st, "gabril_conv1_s2d_fwd")
@@ -338,9 +339,15 @@ def gaze_splat(gaze, out, ktab, Lk_host, agg_coeff, step_coeff, normalize_base, 
     return out
 
 
-def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=None, ws=None, sel=None):
+MASK_LAYOUTS = {"plain": 0, "s2d": 1, "bordered": 2}
+
+
+def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=None, ws=None, sel=None,
+             layout="plain", grid=(0, 0)):
     """g fp32 [B,S,H,W], A fp32 [B,h*w] -> rowmask fp32 [B,h*w] (gaze_utils.py:33-52); sel fp32 [B]
-    (optional): samples with sel <= 0 see a zero heat map (train_bc.py:258)."""
+    (optional): samples with sel <= 0 see a zero heat map (train_bc.py:258).  layout / grid=(SH, SW):
+    storage order of the mask (include/gabril_b200.h, gabril_gmd_mask_layout); rowmask must then be
+    given, sized for that storage."""
     _chk(g, torch.float32, "g"); _chk(A, torch.float32, "A")
     B, S, H, W = g.shape
     if rowmask is None:
@@ -348,9 +355,10 @@ def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=Non
     if ws is None:
         ws = (torch.empty(B, h * w, device=g.device, dtype=torch.float32),
               torch.empty(2, device=g.device, dtype=torch.int32))
-    _call("gabril_gmd_mask_sel", ptr(g), ptr(sel), ptr(A), ptr(ws[0]), ptr(ws[1]), ptr(rowmask), ptr(keep_out),
+    assert layout == "plain" or rowmask is not None
+    _call("gabril_gmd_mask_layout", ptr(g), ptr(sel), ptr(A), ptr(ws[0]), ptr(ws[1]), ptr(rowmask), ptr(keep_out),
           c_int(B), c_int(S), c_int(H), c_int(W), c_int(h), c_int(w), c_float(drop_p),
-          c_int(int(test_mode)), stream(), work=float(B * h * w * (16 * S * 4 + 16)))
+          c_int(int(test_mode)), c_int(MASK_LAYOUTS[layout]), c_int(grid[0]), c_int(grid[1]), stream(), work=float(B * h * w * (16 * S * 4 + 16)))
     return rowmask
 
 

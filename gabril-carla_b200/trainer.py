@@ -303,10 +303,10 @@ class BCTrainer(BaseTrainer):
         c = self.cfg
         if self.device.type != "cuda":
             raise RuntimeError("BCTrainer needs a CUDA device (sm_100a); there is no CPU fallback")
-        if c.gaze.method not in ("None", "Reg", "Teacher") or c.dropout.method not in ("None", "GMD"):
+        if c.gaze.method not in ("None", "Reg", "Teacher") or c.dropout.method not in ("None", "GMD", "IGMD"):
             raise NotImplementedError(
                 f"gaze.method={c.gaze.method} / dropout.method={c.dropout.method}: the B200 hot path covers "
-                "gaze.method in {None, Reg, Teacher} x dropout.method in {None, GMD} (SURVEY.md §8b)")
+                "gaze.method in {None, Reg, Teacher} x dropout.method in {None, GMD, IGMD} (SURVEY.md §8b, §8f N1)")
         S = int(c.model.frame_stack)
         cin = S * (1 if c.model.grayscale else 3)
         spec = PolicySpec(cin, int(c.data.img_height), int(c.data.img_width), int(c.model.embedding_dim),

@@ -119,6 +119,16 @@ int gabril_gmd_mask(const float* g, const float* A, float* K_ws, unsigned int* m
 int gabril_gmd_mask_sel(const float* g, const float* sel, const float* A, float* K_ws,
                         unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B, int S, int H,
                         int W, int h, int w, float drop_p, int test_mode, cudaStream_t stream);
+/* The same, writing the mask in the storage order of the activation it multiplies - the in-encoder
+ * dropout IGMD of linear_models.py:194-199 (after conv_1 + ReLU at 90x160, after conv_2 + ReLU at
+ * 45x80): PLAIN [B, h*w]; S2D [B, SH, SW, 4] (pixel (y, x) at ((y+1)>>1, (x+1)>>1, ((y+1)&1)*2 +
+ * ((x+1)&1)), the patch-row order of gabril_obs_patches_s2d / gabril_conv1_s2d_fwd); BORDERED
+ * [B, SH, SW] (pixel (y, x) at (y+1, x+1)).  Cells that hold no pixel are not written. */
+enum { GABRIL_MASK_PLAIN = 0, GABRIL_MASK_S2D = 1, GABRIL_MASK_BORDERED = 2 };
+int gabril_gmd_mask_layout(const float* g, const float* sel, const float* A, float* K_ws,
+                           unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B, int S,
+                           int H, int W, int h, int w, float drop_p, int test_mode, int layout,
+                           int SH, int SW, cudaStream_t stream);
 /* out[b, c, j] = z[b, c, j] * rowmask[b, j] on the reference's fp32 NCHW layout. */
 int gabril_rowmask_apply_nchw(const float* z, const float* rowmask, float* out, int B, int C, int n,
                               cudaStream_t stream);
@@ -198,6 +208,18 @@ int gabril_conv_wgrad_flat(const void* dy, const void* x, float* dw, int N, int 
 int gabril_conv1_s2d_fwd(const void* patches, const void* w, const float* bias, void* y, int N,
                          int SH, int SW, int img_h, int img_w, int Kp, int Cout, int relu,
                          cudaStream_t stream);
+/* The two forward layers with a per-pixel multiplier applied after bias / ReLU (IGMD,
+ * linear_models.py:194-199).  rowmask is indexed by the pixel index of the OUTPUT storage: patch-row
+ * order for conv_1 (GABRIL_MASK_S2D), bordered [N, o_rows, o_pitch] for the flat convolution
+ * (GABRIL_MASK_BORDERED); NULL = no mask. */
+int gabril_conv_flat_masked(const void* x, const void* w, const float* bias, const void* resid,
+                            const void* gate, const float* rowmask, void* y, int N, int Hg, int Wg,
+                            int Cx, int Cy, int R, int S, int valid_h, int valid_w, int o_rows,
+                            int o_pitch, int o_off_h, int o_off_w, int relu, int transpose_w,
+                            cudaStream_t stream);
+int gabril_conv1_s2d_fwd_masked(const void* patches, const void* w, const float* bias,
+                                const float* rowmask, void* y, int N, int SH, int SW, int img_h,
+                                int img_w, int Kp, int Cout, int relu, cudaStream_t stream);
 
 /* ---- gaze-predictor pre-training (train_gaze_predictor.py:83-101): AutoEncoder = Encoder + Decoder
  * (linear_models.py:210-282, 356-367), MSE against the last aggregated heat map.

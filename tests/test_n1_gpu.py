@@ -102,6 +102,32 @@ def test_gmd_mask_with_selection(G):
     assert torch.equal(mask[decided], (A < K).float()[decided])
 
 
+def test_gmd_mask_storage_layouts(G):
+    """IGMD masks are written in the storage order of conv_1's (space-to-depth) and conv_2's
+    (bordered) outputs: same values as the plain mask, permuted."""
+    B, SH, SW = 3, 47, 82
+    _, gaze, _ = make_batch(B, seed=7)
+    heat = O.stack_heatmaps(gaze, 2, 1, 180, 320, 30.0).to(DEV)
+    for (h, w, layout) in ((90, 160, "s2d"), (45, 80, "bordered")):
+        A = torch.rand(B, h * w, generator=torch.Generator().manual_seed(1)).to(DEV)
+        plain = G.ops.gmd_mask(heat, A, h, w, 0.7, False).view(B, h, w)
+        K = O.gmd_keep_prob(heat.cpu(), (h, w)).reshape(B, h * w)
+        decided = (A.cpu() - K).abs() > 1e-5
+        assert torch.equal(plain.cpu().view(B, -1)[decided], (A.cpu() < K).float()[decided])
+        n_cells = B * SH * SW * (4 if layout == "s2d" else 1)
+        out = torch.full((n_cells,), -1.0, device=DEV)
+        G.ops.gmd_mask(heat, A, h, w, 0.7, False, rowmask=out, layout=layout, grid=(SH, SW))
+        if layout == "s2d":
+            # cell (b, sh, sw, qh, qw) holds pixel (2 sh + qh - 1, 2 sw + qw - 1)
+            g = out.view(B, SH, SW, 2, 2).permute(0, 1, 3, 2, 4).reshape(B, 2 * SH, 2 * SW)
+        else:
+            g = out.view(B, SH, SW)
+        assert torch.equal(g[:, 1:h + 1, 1:w + 1], plain)
+        g = g.clone()
+        g[:, 1:h + 1, 1:w + 1] = -1.0
+        assert (g == -1.0).all()   # nothing else written
+
+
 def build_engine(kind, ratio, dp):
     import gabril_carla_b200  # noqa: F401
     from gabril_carla_b200.engine import StepEngine
@@ -116,7 +142,8 @@ def build_engine(kind, ratio, dp):
 
 
 @pytest.mark.parametrize("kind,ratio,dp", [("KL", 1.0, "None"), ("TV", 1.0, "None"), ("JS", 1.0, "None"),
-                                           ("MSE", 0.5, "None"), ("MSE", 0.5, "GMD"), ("KL", 0.5, "GMD")])
+                                           ("MSE", 0.5, "None"), ("MSE", 0.5, "GMD"), ("KL", 0.5, "GMD"),
+                                           ("MSE", 1.0, "IGMD")])
 def test_step_variants_match_reference_and_oracle(kind, ratio, dp):
     """Whole step on the golden batch with the golden weights: losses against the reference's own
     numbers (fp32; 5e-3 as in test_step_gpu) and, with our activations injected, losses 1e-3 and
@@ -124,9 +151,15 @@ def test_step_variants_match_reference_and_oracle(kind, ratio, dp):
     gold = np.load(GOLD)
     spec, arena, eng = build_engine(kind, ratio, dp)
     batch = make_batch_n1()
-    A = torch.from_numpy(gold["gmd/A"])
+    gen = torch.Generator().manual_seed(21)      # the draws of tests/golden/make_golden_n1.py
+    A = torch.rand(4, 1, 20, 38, generator=gen)
+    A1, A2 = torch.rand(4, 1, 90, 160, generator=gen), torch.rand(4, 1, 45, 80, generator=gen)
+    assert np.array_equal(A.numpy(), gold["gmd/A"])
     if dp == "GMD":
         eng.injected_A = A.reshape(4, 760).to(DEV)
+    if dp == "IGMD":
+        eng.injected_A_igmd = (A1.reshape(4, -1).to(DEV), A2.reshape(4, -1).to(DEV))
+        A = (A1, A2)
     eng.zero_grad()
     eng.forward(*(t.to(DEV) for t in batch))
     eng.backward()
