@@ -220,6 +220,42 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
                                  wtap, chunk_c * p.kc);
             }
           }
+        } else if (p.swap_ab) {
+          // WGRAD, operands exchanged: A = one im2col activation tile per tap, B = the dY rows
+          const uint32_t tx = tl.ntaps * p.a_boxes * p.a_box_bytes + p.b_boxes * p.b_box_bytes;
+          for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+            const int s = st;
+            const uint32_t ph = st_ph;
+            if (++st == p.stages) { st = 0; st_ph ^= 1; }
+            if (s % kProducers != me) continue;
+            if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { report_timeout(p, 109); ok = false; break; }
+            const uint32_t a_dst = smem_base + s * stage_bytes;
+            const uint32_t b_dst = a_dst + p.a_stage_bytes;
+            const uint32_t full = full0 + 8 * s;
+            ptx::mbar_arrive_expect_tx(full, tx);
+            const int p0 = kb * p.kc;
+            for (int i = 0; i < p.b_boxes; ++i)
+              ptx::tma_load_2d(b_dst + i * p.b_box_bytes, &p.mapB, full, n0 + i * p.b_box_w, p0);
+            if (p.a_im2col) {
+              const int n_img = p0 / ohw;
+              const int rem = p0 - n_img * ohw;
+              const int oh = rem / oww;
+              const int ow = rem - oh * oww;
+              const int w_base = ow * p.trav_stride_w + p.lower_w[0];
+              const int h_base = oh * p.trav_stride_h + p.lower_h[0];
+              for (int tt = 0; tt < tl.ntaps; ++tt) {
+                const int tap = tl.tap0 + tt;
+                const int rp = tap / p.S, sp = tap - rp * p.S;
+                for (int i = 0; i < p.a_boxes; ++i)
+                  ptx::tma_load_im2col_4d(a_dst + (tt * p.a_boxes + i) * p.a_box_bytes, &p.mapA[0],
+                                          full, m0 + i * p.a_box_w, w_base, h_base, n_img,
+                                          (uint16_t)sp, (uint16_t)rp);
+              }
+            } else {
+              for (int i = 0; i < p.a_boxes; ++i)
+                ptx::tma_load_2d(a_dst + i * p.a_box_bytes, &p.mapA[0], full, m0 + i * p.a_box_w, p0);
+            }
+          }
         } else {
           const uint32_t tx = p.a_boxes * p.a_box_bytes + tl.ntaps * p.b_boxes * p.b_box_bytes;
           for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
@@ -265,6 +301,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       bool ok = true;
       const int mma_k = p.mma_k, mma_groups = p.mma_groups, g_taps = p.g_taps;
       const uint32_t a_kstep = p.a_kstep, b_kstep = p.b_kstep, b_gstep = p.b_gstep, d_gstep = p.d_gstep;
+      const uint32_t a_gstep = p.swap_ab ? p.a_gstep : 0u;
       const uint32_t a_hi32 = (uint32_t)(p.desc_a_hi >> 32), b_hi32 = (uint32_t)(p.desc_b_hi >> 32);
       const uint32_t stage16 = stage_bytes >> 4;
       const uint32_t a_lo_const = (uint32_t)p.desc_a_hi + (smem_base >> 4);
@@ -352,11 +389,11 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
           const uint32_t b_lo = b_lo_const + (uint32_t)s * stage16;
           for (int g = 0; g < mma_groups; ++g) {
             if (g * g_taps >= tl.ntaps) break;
-            const uint32_t bg = b_lo + g * b_gstep, dg = d_base + g * d_gstep;
+            const uint32_t bg = b_lo + g * b_gstep, dg = d_base + g * d_gstep, ag = a_lo + g * a_gstep;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               if (j < mma_k) {
-                const uint64_t a_desc = ((uint64_t)a_hi32 << 32) | (uint64_t)(a_lo + j * a_kstep);
+                const uint64_t a_desc = ((uint64_t)a_hi32 << 32) | (uint64_t)(ag + j * a_kstep);
                 const uint64_t b_desc = ((uint64_t)b_hi32 << 32) | (uint64_t)(bg + j * b_kstep);
                 const uint32_t accumulate = (kb > tl.kb_begin || j > 0) ? 1u : 0u;
                 if (!dbg_skip) ptx::umma_bf16(dg, a_desc, b_desc, idesc, accumulate);
@@ -515,6 +552,17 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
                   o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]);
                   o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
                   o4[i] = o;
+                }
+              } else if (p.swap_ab) {
+                // lane = cin (row), column = cout: 32 lanes write 32 consecutive cin of one cout
+                float* o = reinterpret_cast<float*>(p.out) + (long long)col0 * p.ldo +
+                           (long long)(tl.tap0 + a) * p.tap_stride + orow;
+                if (p.out_mode == OUT_F32_STORE) {
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) o[(long long)i * p.ldo] = f[i];
+                } else {
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) atomicAdd(o + (long long)i * p.ldo, f[i]);
                 }
               } else {
                 float* o = reinterpret_cast<float*>(p.out) + orow * p.ldo +

@@ -59,6 +59,11 @@ struct Params {
   //   (16-byte units);  accumulator column = g*d_gstep;  group g covers taps [g*g_taps, ...)
   int mma_k, mma_groups, g_taps;
   uint32_t a_kstep, b_kstep, b_gstep, d_gstep;
+  // WGRAD with exchanged operands (narrow Cout): A = activation (im2col, one tile per tap, M = Cin),
+  // B = dY (one tile for all taps, N = Cout).  Group g = tap g: A start += g*a_gstep (b_gstep = 0);
+  // TMEM lane = cin, column = cout, so the epilogue writes element (cout, tap, cin) transposed.
+  int swap_ab;
+  uint32_t a_gstep;
   uint64_t desc_a_hi, desc_b_hi;  // smem descriptors with the start-address field zero
   uint32_t idesc;
   uint32_t tmem_cols;

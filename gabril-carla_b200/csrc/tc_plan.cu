@@ -433,6 +433,109 @@ int gabril_convt_dgrad(const void* dy, const void* w, const void* gate, void* dx
                        0, 1, stream);
 }
 
+// Narrow layers (Cout <= 64): with A = dY^T the UMMA M dimension would be 25-50 % filled, so the
+// operands are exchanged: A = im2col(x) of one tap (M = 128 input channels), B = dY (N = Cout), one
+// accumulator of Cout columns per tap (up to 512 / Cout taps per CTA share one dY tile).
+static bool wgrad_swap_disabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("GABRIL_WGRAD_NO_SWAP"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
+
+static int conv_wgrad_swapped(const void* dy, const void* x, float* dw, int N, int H, int W, int Cin,
+                              int Cout, int R, int S, int stride, int pad, int direct_store,
+                              cudaStream_t stream) {
+  const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+  const long long P = (long long)N * OH * OW;
+  const int T = R * S, KP = 64;
+  tc::Params p;
+  zero_params(p);
+  p.kind = tc::KIND_WGRAD;
+  p.n_classes = 1;
+  p.swap_ab = 1;
+  const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
+  p.a_im2col = plain ? 0 : 1;
+  p.kc = KP;
+  // A = x^T of one tap: M = 128 input channels = two 64-channel boxes of KP pixels
+  const int aw = 64, a_sw = aw * 2;
+  p.a_box_w = aw;
+  p.a_boxes = 2;
+  p.a_box_bytes = KP * a_sw;
+  const uint32_t a_tap_bytes = p.a_boxes * p.a_box_bytes;
+  p.desc_a_hi = desc_hi(p.a_box_bytes, 8 * a_sw, layout_type_for_bytes(a_sw));
+  // B = dY: N = Cout columns in one box
+  const int block_n = Cout, bw = Cout, b_sw = bw * 2;
+  p.block_n = block_n;
+  p.b_box_w = bw;
+  p.b_boxes = 1;
+  p.b_box_bytes = KP * b_sw;
+  p.b_stage_bytes = round_up(p.b_box_bytes, 1024);
+  p.desc_b_hi = desc_hi(p.b_box_bytes, 8 * b_sw, layout_type_for_bytes(b_sw));
+  // taps per CTA: TMEM (512 columns) and two smem stages in 200 KB; balanced tap groups
+  int n_acc = std::min(T, 512 / block_n);
+  while (n_acc > 1 && 2 * (n_acc * a_tap_bytes + p.b_stage_bytes) > 200 * 1024) --n_acc;
+  const int groups = (T + n_acc - 1) / n_acc;
+  n_acc = (T + groups - 1) / groups;
+  p.n_acc = n_acc;
+  p.taps = T;
+  p.tap_groups = groups;
+  p.S = S;
+  p.a_stage_bytes = round_up(n_acc * a_tap_bytes, 1024);
+  p.mma_k = KP / 16;
+  p.mma_groups = n_acc;
+  p.g_taps = 1;
+  p.a_kstep = (uint32_t)((16 * a_sw) >> 4);
+  p.b_kstep = (uint32_t)((16 * b_sw) >> 4);
+  p.a_gstep = a_tap_bytes >> 4;
+  p.b_gstep = 0;
+  p.d_gstep = (uint32_t)block_n;
+  p.idesc = make_idesc(1, 1, 128, block_n);
+  p.M_total[0] = Cin;
+  p.N_total = Cout;
+  p.kb_total = (int)((P + KP - 1) / KP);
+  p.OW[0] = OW; p.OHW[0] = OH * OW; p.lower_w[0] = -pad; p.lower_h[0] = -pad;
+  p.trav_stride_w = stride; p.trav_stride_h = stride;
+  int rc;
+  {
+    uint64_t dims[2] = {(uint64_t)Cout, (uint64_t)P};
+    uint64_t strides[1] = {(uint64_t)Cout * 2};
+    uint32_t box[2] = {(uint32_t)bw, (uint32_t)KP};
+    rc = tiled_map(&p.mapB, dy, 2, dims, strides, box, b_sw);
+    if (rc) return rc;
+  }
+  if (plain) {
+    uint64_t dims[2] = {(uint64_t)Cin, (uint64_t)P};
+    uint64_t strides[1] = {(uint64_t)Cin * 2};
+    uint32_t box[2] = {(uint32_t)aw, (uint32_t)KP};
+    rc = tiled_map(&p.mapA[0], x, 2, dims, strides, box, a_sw);
+  } else {
+    rc = im2col_map(&p.mapA[0], x, N, H, W, Cin, -pad, -pad, pad - (S - 1), pad - (R - 1), aw, KP,
+                    stride);
+  }
+  if (rc) return rc;
+  const int m_tiles = Cin / 128, n_tiles = 1;
+  const int occ = (n_acc * block_n <= 256 && 2 * (p.a_stage_bytes + p.b_stage_bytes) <= 100 * 1024) ? 2 : 1;
+  int splits = 1;
+  if (!direct_store) {
+    const int base = m_tiles * n_tiles * p.tap_groups;
+    splits = std::max(1, std::min(p.kb_total, (occ * g_num_sms) / base));
+  }
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.out_mode = direct_store ? tc::OUT_F32_STORE : tc::OUT_F32_ATOMIC;
+  p.out = dw;
+  p.ldo = (long long)T * Cin;
+  p.tap_stride = Cin;
+  p.err_flag = g_err_flag;
+  size_t smem;
+  pick_stages(p, &smem, occ);
+  const int mt[1] = {m_tiles};
+  finalize_schedule(p, mt, n_tiles * p.tap_groups, splits, n_acc * block_n, occ);
+  p.acc_bufs = 1;
+  p.tmem_cols = (uint32_t)p.acc_stride;
+  return tc::launch(p, 1 << 30, smem, stream);
+}
+
 // dw[Cout][R*S][Cin] (fp32) += sum_pixels dy[p, Cout]^T * im2col(x)[p, (tap, Cin)].
 // The caller zeroes dw (it lives in the flat gradient arena).  Also serves linear layers
 // (R = S = 1, H = W = 1, N = rows): dw[Cout][Cin] += dy[rows,Cout]^T x[rows,Cin].
@@ -446,6 +549,8 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
   const long long P = (long long)N * OH * OW;  // contraction length (output pixels)
   const int T = R * S;
   const int KP = 64;
+  if (Cout <= 64 && Cin % 128 == 0 && !wgrad_swap_disabled())
+    return conv_wgrad_swapped(dy, x, dw, N, H, W, Cin, Cout, R, S, stride, pad, direct_store, stream);
   tc::Params p;
   zero_params(p);
   p.kind = tc::KIND_WGRAD;
