@@ -13,6 +13,7 @@
   } while (0)
 
 int gabril_set_cuda_error(cudaError_t e);
+void gabril_set_error(const char* msg);
 
 typedef __nv_bfloat16 bf16;
 

@@ -13,6 +13,8 @@ int gabril_set_cuda_error(cudaError_t e) {
   return GABRIL_ERR_CUDA;
 }
 
+void gabril_set_error(const char* msg) { snprintf(g_last_error, sizeof(g_last_error), "%s", msg); }
+
 extern "C" {
 
 int gabril_version(void) { return 100; }

@@ -453,7 +453,15 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       // gate / residual operands of the first 32 columns are fetched BEFORE waiting for the MMAs:
       // their global-memory latency hides behind the main loop of this tile
       uint4 gpre[4], rpre[4];
+      uint32_t gw[4] = {0u, 0u, 0u, 0u};
       if (p.out_mode == OUT_BF16 && row_ok) {
+        if (p.gate_bits) {
+          // the sign words of every 32-column chunk of this row: 4 bytes per chunk instead of 64
+          const uint32_t* gb = p.gate_bits + (off0 >> 5);
+#pragma unroll
+          for (int ci = 0; ci < 4; ++ci)
+            if (ci * 32 < p.block_n && n0 + ci * 32 < p.N_total) gw[ci] = __ldg(gb + ci);
+        }
         if (p.gate) {
           const uint4* g4 = reinterpret_cast<const uint4*>(p.gate + off0);
 #pragma unroll
@@ -471,11 +479,16 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       if (!ok) break;
       ptx::tc_fence_after();
       const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + buf * p.acc_stride;
+      // The chunk loop is deliberately NOT unrolled: one epilogue warp runs alone on its SM
+      // sub-partition, so straight-line code is instruction-fetch bound (ncu: half of the epilogue's
+      // stall samples were stall_no_inst with the loop unrolled four times); a rolled body of a few
+      // hundred instructions stays in the instruction cache across chunks and tiles.
+      const int n_chunks = (p.block_n + 31) >> 5;
       for (int a = 0; a < tl.ntaps; ++a) {
-#pragma unroll
-        for (int ci = 0; ci < 4; ++ci) {
+#pragma unroll 1
+        for (int ci = 0; ci < n_chunks; ++ci) {
           const int c = ci * 32;
-          if (c < p.block_n) {
+          {
             uint32_t v[32];
             if (p.out_mode == OUT_BF16 && row_ok && (ci > 0 || a > 0)) {  // chunk 0 was fetched before the wait
               if (p.gate) {
@@ -535,6 +548,11 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
                     f[8 * i + 7] = bf16hi(g.w) > 0.f ? f[8 * i + 7] : 0.f;
                   }
                 }
+                if (p.gate_bits) {
+                  const uint32_t g = ci == 0 ? gw[0] : ci == 1 ? gw[1] : ci == 2 ? gw[2] : gw[3];
+#pragma unroll
+                  for (int i = 0; i < 32; ++i) f[i] = ((g >> i) & 1u) ? f[i] : 0.f;
+                }
                 if (p.rowmask) {
 #pragma unroll
                   for (int i = 0; i < 32; ++i) f[i] *= rmask;
@@ -544,6 +562,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
                   for (int i = 0; i < 32; ++i) f[i] = 0.f;
                 }
                 uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + off);
+                uint32_t sign_word = 0u;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                   uint4 o;
@@ -552,7 +571,17 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
                   o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]);
                   o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
                   o4[i] = o;
+                  if (p.bits_out) {
+                    // the predicate of the `gate` path on the value as stored: bf16 > 0
+                    const uint32_t w4[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                      sign_word |= ((int)(w4[k] << 16) > 0 ? 1u : 0u) << (8 * i + 2 * k);
+                      sign_word |= ((int)(w4[k] & 0xffff0000u) > 0 ? 1u : 0u) << (8 * i + 2 * k + 1);
+                    }
+                  }
                 }
+                if (p.bits_out) p.bits_out[off >> 5] = sign_word;
               } else if (p.swap_ab) {
                 // lane = cin (row), column = cout: 32 lanes write 32 consecutive cin of one cout
                 float* o = reinterpret_cast<float*>(p.out) + (long long)col0 * p.ldo +
@@ -599,7 +628,29 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
 // ---------------------------------------------------------------------------------------------
 static std::once_flag g_attr_once;
 
-int launch(const Params& p, int num_sms, size_t smem_bytes, cudaStream_t stream) {
+static thread_local const void* t_next_gate_bits = nullptr;
+static thread_local void* t_next_bits_out = nullptr;
+
+void set_next_bits(const void* gate_bits, void* bits_out) {
+  t_next_gate_bits = gate_bits;
+  t_next_bits_out = bits_out;
+}
+
+int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stream) {
+  Params p = p_in;
+  if (t_next_gate_bits || t_next_bits_out) {
+    const void* gb = t_next_gate_bits;
+    void* bo = t_next_bits_out;
+    t_next_gate_bits = nullptr;
+    t_next_bits_out = nullptr;
+    // sign words cover 32 consecutive channels of one row of a bf16 output
+    if (p.out_mode != OUT_BF16 || (p.ldo & 31) || (p.block_n & 31)) {
+      gabril_set_error("gabril_conv_epilogue_bits: the next launch has no bf16 output with 32-aligned rows");
+      return GABRIL_ERR_BAD_SHAPE;
+    }
+    if (gb) { p.gate_bits = (const uint32_t*)gb; p.gate = nullptr; }
+    p.bits_out = (uint32_t*)bo;
+  }
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(g_attr_once, [] {
     attr_err = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

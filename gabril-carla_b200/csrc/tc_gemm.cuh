@@ -75,6 +75,11 @@ struct Params {
   const __nv_bfloat16* resid;   // added before ReLU / gate (same indexing as out), or null
   const __nv_bfloat16* gate;    // out = gate > 0 ? out : 0 (ReLU backward), or null
   const float* rowmask;         // per output row multiplier (GMD mask), or null
+  // packed sign bits (1 bit per element, word (off >> 5) covers elements off .. off + 31 of the
+  // tensor indexed like out): gate_bits replaces the `gate` tensor read (64 B -> 4 B per 32-column
+  // chunk); bits_out receives (stored bf16 value > 0) for every chunk this launch stores
+  const uint32_t* gate_bits;
+  uint32_t* bits_out;
   int relu;
   // remap: tile row (n, jh, jw) over the Hs x Ws grid of its class -> row
   //        (n*OHf + jh*remap_sh + ah)*OWf + jw*remap_sw + aw of the output tensor
@@ -109,5 +114,9 @@ struct Params {
 
 // Fills the launch geometry and launches; returns a negative gabril status on failure.
 int launch(const Params& p, int num_sms, size_t smem_bytes, cudaStream_t stream);
+
+// Launch attribute of the NEXT launch() on the calling host thread (consumed by it): see
+// gabril_conv_epilogue_bits in include/gabril_b200.h.
+void set_next_bits(const void* gate_bits, void* bits_out);
 
 }  // namespace tc

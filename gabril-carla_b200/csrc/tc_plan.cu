@@ -242,6 +242,11 @@ extern "C" {
 
 int gabril_tc_init(void) { return resolve_driver(); }
 
+int gabril_conv_epilogue_bits(const void* gate_bits, void* sign_bits_out) {
+  tc::set_next_bits(gate_bits, sign_bits_out);
+  return GABRIL_OK;
+}
+
 int gabril_poll_error(void) {
   if (!g_err_flag) return 0;
   int v = 0;

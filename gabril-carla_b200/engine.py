@@ -77,6 +77,11 @@ class StepEngine:
             b[f"h{i}"] = act(s.h, s.w, s.RH)
             b[f"r{i}"] = act(s.h, s.w, s.NH)
         b["a5"], b["z"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.E)
+        # packed ReLU sign words of every rectified activation (1 bit per element, written by the
+        # forward epilogues, read by the dgrad epilogues in place of the activation itself); zeroed:
+        # words of never-stored border pixels must read as "not positive"
+        for name in ["a1s", "a2p", "a3", "a5"] + [f"r{i}" for i in range(-1, s.NR)] + [f"h{i}" for i in range(s.NR)]:
+            b["sb_" + name] = ops.sign_bits_like(b[name])
         b["heat"] = torch.empty(B, self.S, s.H, s.W, device=dev, dtype=f32)
         b["rowmask"] = torch.empty(B, s.n, device=dev, dtype=f32)
         b["sel"] = torch.empty(B, device=dev, dtype=f32)
@@ -172,22 +177,27 @@ class StepEngine:
         are the dropped-out activations, so their `> 0` gates carry the mask through the backward."""
         s, a, b, B = self.spec, self.arena, self.buf, self.B
         ops.conv1_s2d_fwd(b["patches"], a.WB("enc.conv1.w"), a.P("enc.conv1.b"), b["a1s"], B, self.SH,
-                          self.SW, s.H1, s.W1, relu=True, rowmask=igmd[0] if igmd else None)
+                          self.SW, s.H1, s.W1, relu=True, rowmask=igmd[0] if igmd else None,
+                          bits_out=b["sb_a1s"])
         ops.conv_flat(b["a1s"], a.WB("enc.conv2.w"), b["a2p"], 2, 2, bias=a.P("enc.conv2.b"),
                       valid=(s.H2, s.W2), out_geom=(self.SH, self.SW, 1, 1), relu=True,
-                      rowmask=igmd[1] if igmd else None)
-        ops.conv_fwd(b["a2p"], a.WB("enc.conv3.w"), a.P("enc.conv3.b"), b["a3"], 4, 4, 2, 0, relu=True)
+                      rowmask=igmd[1] if igmd else None, bits_out=b["sb_a2p"])
+        ops.conv_fwd(b["a2p"], a.WB("enc.conv3.w"), a.P("enc.conv3.b"), b["a3"], 4, 4, 2, 0, relu=True,
+                     bits_out=b["sb_a3"])
         # conv_4 has no activation of its own; the first Residual's in-place ReLU rectifies it (F7)
-        ops.conv_fwd(b["a3"], a.WB("enc.conv4.w"), a.P("enc.conv4.b"), b["r-1"], 3, 3, 1, 0, relu=True)
+        ops.conv_fwd(b["a3"], a.WB("enc.conv4.w"), a.P("enc.conv4.b"), b["r-1"], 3, 3, 1, 0, relu=True,
+                     bits_out=b["sb_r-1"])
         for i in range(s.NR):
             prev = b[f"r{i - 1}"]
-            ops.conv_fwd(prev, a.WB(f"enc.res{i}.c3.w"), None, b[f"h{i}"], 3, 3, 1, 1, relu=True)
+            ops.conv_fwd(prev, a.WB(f"enc.res{i}.c3.w"), None, b[f"h{i}"], 3, 3, 1, 1, relu=True,
+                         bits_out=b[f"sb_h{i}"])
             # relu(x) + block(x); the next consumer (next Residual / the stack's final ReLU)
             # rectifies it again, so the rectified value is what gets stored
             ops.conv_fwd(b[f"h{i}"], a.WB(f"enc.res{i}.c1.w"), None, b[f"r{i}"], 1, 1, 1, 0, relu=True,
-                         resid=prev)
+                         resid=prev, bits_out=b[f"sb_r{i}"])
         last = b[f"r{s.NR - 1}"]
-        ops.conv_fwd(last, a.WB("enc.conv5.w"), a.P("enc.conv5.b"), b["a5"], 5, 5, 1, 2, relu=True)
+        ops.conv_fwd(last, a.WB("enc.conv5.w"), a.P("enc.conv5.b"), b["a5"], 5, 5, 1, 2, relu=True,
+                     bits_out=b["sb_a5"])
         ops.conv_fwd(b["a5"], a.WB("enc.conv6.w"), a.P("enc.conv6.b"), b["z"], 5, 5, 1, 2, relu=False,
                      rowmask=rowmask.view(-1) if rowmask is not None else None)
 
@@ -263,35 +273,36 @@ class StepEngine:
         """Backward of the encoder from b["dz"] (gradient w.r.t. z) to every encoder weight gradient."""
         s, a, b, B = self.spec, self.arena, self.buf, self.B
         # conv_6 / conv_5
-        last = b[f"r{s.NR - 1}"]
+        last, sb_last = b[f"r{s.NR - 1}"], b[f"sb_r{s.NR - 1}"]
         ops.colsum_bf16(b["dz"], a.G("enc.conv6.b"))
         ops.conv_wgrad(b["dz"], b["a5"], a.G("enc.conv6.w"), 5, 5, 1, 2)
-        ops.conv_dgrad(b["dz"], a.WB("enc.conv6.w"), b["da5"], 5, 5, 1, 2, gate=b["a5"])
+        ops.conv_dgrad(b["dz"], a.WB("enc.conv6.w"), b["da5"], 5, 5, 1, 2, gate_bits=b["sb_a5"])
         ops.colsum_bf16(b["da5"], a.G("enc.conv5.b"))
         ops.conv_wgrad(b["da5"], last, a.G("enc.conv5.w"), 5, 5, 1, 2)
         dt, other = b["dt_a"], b["dt_b"]
-        ops.conv_dgrad(b["da5"], a.WB("enc.conv5.w"), dt, 5, 5, 1, 2, gate=last)
+        ops.conv_dgrad(b["da5"], a.WB("enc.conv5.w"), dt, 5, 5, 1, 2, gate_bits=sb_last)
         # residual stack, last block first
         for i in reversed(range(s.NR)):
             prev = b[f"r{i - 1}"]
             ops.conv_wgrad(dt, b[f"h{i}"], a.G(f"enc.res{i}.c1.w"), 1, 1, 1, 0)
-            ops.conv_dgrad(dt, a.WB(f"enc.res{i}.c1.w"), b["dh"], 1, 1, 1, 0, gate=b[f"h{i}"])
+            ops.conv_dgrad(dt, a.WB(f"enc.res{i}.c1.w"), b["dh"], 1, 1, 1, 0, gate_bits=b[f"sb_h{i}"])
             ops.conv_wgrad(b["dh"], prev, a.G(f"enc.res{i}.c3.w"), 3, 3, 1, 1)
-            ops.conv_dgrad(b["dh"], a.WB(f"enc.res{i}.c3.w"), other, 3, 3, 1, 1, addend=dt, gate=prev)
+            ops.conv_dgrad(b["dh"], a.WB(f"enc.res{i}.c3.w"), other, 3, 3, 1, 1, addend=dt,
+                           gate_bits=b[f"sb_r{i - 1}"])
             dt, other = other, dt
         # conv_4 .. conv_1
         ops.colsum_bf16(dt, a.G("enc.conv4.b"))
         ops.conv_wgrad(dt, b["a3"], a.G("enc.conv4.w"), 3, 3, 1, 0)
-        ops.conv_dgrad(dt, a.WB("enc.conv4.w"), b["da3"], 3, 3, 1, 0, gate=b["a3"])
+        ops.conv_dgrad(dt, a.WB("enc.conv4.w"), b["da3"], 3, 3, 1, 0, gate_bits=b["sb_a3"])
         ops.colsum_bf16(b["da3"], a.G("enc.conv3.b"))
         # conv_3 over the zero-bordered a2p (pad 0): the border gradients are gated to zero by a2p itself
         ops.conv_wgrad(b["da3"], b["a2p"], a.G("enc.conv3.w"), 4, 4, 2, 0)
-        ops.conv_dgrad(b["da3"], a.WB("enc.conv3.w"), b["da2p"], 4, 4, 2, 0, gate=b["a2p"])
+        ops.conv_dgrad(b["da3"], a.WB("enc.conv3.w"), b["da2p"], 4, 4, 2, 0, gate_bits=b["sb_a2p"])
         ops.colsum_bf16(b["da2p"], a.G("enc.conv2.b"))
         # conv_2 on the space-to-depth grid: dY pixel (i, j) sits at flat row q + SW + 1
         ops.conv_wgrad_flat(b["da2p"], b["a1s"], a.G("enc.conv2.w"), 2, 2, self.SW + 1,
                             flop_pixels=B * s.H2 * s.W2)
-        ops.conv_flat(b["da2p"], a.WB("enc.conv2.w"), b["da1s"], 2, 2, gate=b["a1s"], transpose_w=True,
+        ops.conv_flat(b["da2p"], a.WB("enc.conv2.w"), b["da1s"], 2, 2, gate_bits=b["sb_a1s"], transpose_w=True,
                       flop_pixels=B * s.H2 * s.W2)  # algorithmic FLOPs of the k4/s2 dgrad
         M1 = B * self.SH * self.SW * 4
         ops.colsum_bf16(b["da1s"].view(M1, s.C1), a.G("enc.conv1.b"))

@@ -67,12 +67,33 @@ def _chk_bf16(t, name):
         raise ValueError(f"{name}: expected contiguous CUDA bf16 tensor, got {t.dtype} {t.device}")
 
 
+def _epilogue_bits(gate_bits, bits_out, out):
+    """Attach packed ReLU sign words (int32 [out.numel() / 32]) to the next conv launch:
+    gate_bits is read instead of a `gate` tensor, bits_out receives (stored value > 0)."""
+    if gate_bits is None and bits_out is None:
+        return
+    for t, name in ((gate_bits, "gate_bits"), (bits_out, "bits_out")):
+        if t is None:
+            continue
+        if t.dtype != torch.int32 or not t.is_cuda or not t.is_contiguous() or t.numel() * 32 != out.numel():
+            raise ValueError(f"{name}: expected contiguous CUDA int32 tensor of {out.numel() // 32} words")
+    if _NAIVE:
+        raise RuntimeError("sign-bit gates exist only on the tcgen05 path")
+    _lib.check(_lib.init().gabril_conv_epilogue_bits(ptr(gate_bits), ptr(bits_out)), "gabril_conv_epilogue_bits")
+
+
+def sign_bits_like(t):
+    """Zeroed sign-word buffer for a bf16 activation tensor (1 bit per element)."""
+    assert t.numel() % 32 == 0
+    return torch.zeros(t.numel() // 32, device=t.device, dtype=torch.int32)
+
+
 def conv_out_hw(H, W, R, S, stride, pad):
     return (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
 
 
 def conv_fwd(x, w, bias, y, R, S, stride, pad, relu=False, resid=None, rowmask=None,
-             out_f32_atomic=False, splits=1):
+             out_f32_atomic=False, splits=1, bits_out=None):
     """x [N,H,W,Cin] bf16, w [Cout,R*S,Cin] bf16, bias fp32[Cout] or None -> y [N,OH,OW,Cout]."""
     _chk_bf16(x, "x"); _chk_bf16(w, "w"); _chk_bf16(resid, "resid")
     N, H, W, Cin = x.shape
@@ -82,6 +103,7 @@ def conv_fwd(x, w, bias, y, R, S, stride, pad, relu=False, resid=None, rowmask=N
     assert y.numel() == N * OH * OW * Cout, (y.shape, N, OH, OW, Cout)
     assert y.dtype == (torch.float32 if out_f32_atomic else torch.bfloat16)
     with _span("tc_gemm_kernel", f"fwd {Cin}->{Cout} k{R}s{stride}", 2.0 * N * OH * OW * Cout * R * S * Cin, "flop"):
+        _epilogue_bits(None, bits_out, y)
         st = _fn("gabril_conv_fwd")(ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(rowmask), ptr(y),
                                     c_int(N), c_int(H), c_int(W), c_int(Cin), c_int(Cout), c_int(R),
                                     c_int(S), c_int(stride), c_int(pad), c_int(int(relu)),
@@ -90,7 +112,7 @@ def conv_fwd(x, w, bias, y, R, S, stride, pad, relu=False, resid=None, rowmask=N
     return y
 
 
-def conv_dgrad(dy, w, dx, R, S, stride, pad, addend=None, gate=None, rowmask=None):
+def conv_dgrad(dy, w, dx, R, S, stride, pad, addend=None, gate=None, rowmask=None, gate_bits=None):
     """dy [N,OH,OW,Cout] bf16 -> dx [N,H,W,Cin] bf16 (shape taken from dx)."""
     _chk_bf16(dy, "dy"); _chk_bf16(w, "w"); _chk_bf16(dx, "dx")
     _chk_bf16(addend, "addend"); _chk_bf16(gate, "gate")
@@ -99,6 +121,7 @@ def conv_dgrad(dy, w, dx, R, S, stride, pad, addend=None, gate=None, rowmask=Non
     OH, OW = conv_out_hw(H, W, R, S, stride, pad)
     assert dy.numel() == N * OH * OW * Cout, (dy.shape, N, OH, OW, Cout)
     with _span("tc_gemm_kernel", f"dgrad {Cin}<-{Cout} k{R}s{stride}", 2.0 * N * OH * OW * Cout * R * S * Cin, "flop"):
+        _epilogue_bits(gate_bits, None, dx)
         st = _fn("gabril_conv_dgrad")(ptr(dy), ptr(w), ptr(addend), ptr(gate), ptr(rowmask), ptr(dx),
                                       c_int(N), c_int(H), c_int(W), c_int(Cin), c_int(Cout), c_int(R),
                                       c_int(S), c_int(stride), c_int(pad), stream())
@@ -125,7 +148,7 @@ def conv_wgrad(dy, x, dw, R, S, stride, pad, direct_store=False):
 
 # ---- flat-slab convolutions over zero-bordered tensors (csrc/tc_plan.cu) ----------------------
 def conv_flat(x, w, y, R, S, *, bias=None, resid=None, gate=None, valid=None, out_geom=None, relu=False,
-              transpose_w=False, flop_pixels=None, rowmask=None):
+              transpose_w=False, flop_pixels=None, rowmask=None, gate_bits=None, bits_out=None):
     """x [N,Hg,Wg,Cx] bf16 zero-bordered; out(q) = sum_{r,s} x_flat[q + r*Wg + s] . W(r,s) for every
     flat pixel q.  valid=(vh, vw), out_geom=(o_rows, o_pitch, off_h, off_w): pixel (n,i,j) with
     i<vh, j<vw is stored at y row (n*o_rows + i+off_h)*o_pitch + j+off_w; valid=None stores every
@@ -144,6 +167,7 @@ def conv_flat(x, w, y, R, S, *, bias=None, resid=None, gate=None, valid=None, ou
     with _span("tc_gemm_kernel", f"{'dgrad' if transpose_w else 'fwd'}-flat {Cx}->{Cy} k{R}x{S}",
                2.0 * (flop_pixels if flop_pixels is not None else N * (vh or Hg) * (vw or Wg)) * Cy * R * S * Cx,
                "flop"):
+        _epilogue_bits(gate_bits, bits_out, y)
         st = _fn("gabril_conv_flat_masked")(ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(gate), ptr(rowmask),
                                      ptr(y), c_int(N), c_int(Hg), c_int(Wg), c_int(Cx), c_int(Cy), c_int(R), c_int(S),
                                      c_int(vh), c_int(vw), c_int(o_rows), c_int(o_pitch), c_int(off_h),
@@ -167,7 +191,7 @@ def conv_wgrad_flat(dy, x, dw, R, S, dy_row_off, flop_pixels=None):
     return dw
 
 
-def conv1_s2d_fwd(patches, w, bias, y, N, SH, SW, img_h, img_w, relu=True, rowmask=None):
+def conv1_s2d_fwd(patches, w, bias, y, N, SH, SW, img_h, img_w, relu=True, rowmask=None, bits_out=None):
     """patches bf16 [N*SH*SW*4, Kp] (space-to-depth row order), w [Cout,1,Kp] -> y [N,SH,SW,4*Cout];
     rows of padding pixels are stored as exact zeros."""
     _chk_bf16(patches, "patches"); _chk_bf16(w, "w"); _chk_bf16(y, "y")
@@ -175,6 +199,7 @@ def conv1_s2d_fwd(patches, w, bias, y, N, SH, SW, img_h, img_w, relu=True, rowma
     Cout = w.shape[0]
     assert patches.shape[0] == N * SH * SW * 4 and y.numel() == N * SH * SW * 4 * Cout
     with _span("tc_gemm_kernel", f"fwd {Kp}->{Cout} k1s1", 2.0 * N * img_h * img_w * Cout * Kp, "flop"):
+        _epilogue_bits(None, bits_out, y)
         st = _fn("gabril_conv1_s2d_fwd_masked")(ptr(patches), ptr(w), ptr(bias), ptr(rowmask), ptr(y), c_int(N),
                                          c_int(SH), c_int(SW),
                                          c_int(img_h), c_int(img_w), c_int(Kp), c_int(Cout), c_int(int(relu)),

@@ -48,6 +48,17 @@ int gabril_tc_init(void);
 int gabril_poll_error(void);
 
 /* ---- dense contractions: tcgen05 / TMEM / TMA implicit GEMM ------------------------------ */
+/* Launch attribute of the NEXT conv / linear call below made by the calling host thread (consumed
+ * by it; the call must produce a bf16 output whose channel count is a multiple of 32).
+ * Packed ReLU sign bits: one uint32 word per 32 consecutive channels of one pixel, word index =
+ * (element offset into the output tensor) / 32, bit i = (element i of the chunk, as stored in
+ * bf16, > 0) — the predicate of nn.ReLU's backward (linear_models.py:78-102,191-207 ReLU calls).
+ *   sign_bits_out: the call also writes the sign words of everything it stores (forward);
+ *   gate_bits:     the call reads these words instead of its `gate` tensor (backward): 4 bytes of
+ *                  HBM traffic per 32 channels instead of 64.
+ * Either may be NULL.  The buffers must be zero wherever the output tensor is never stored
+ * (zero borders). */
+int gabril_conv_epilogue_bits(const void* gate_bits, void* sign_bits_out);
 /* nn.Conv2d / nn.Linear forward — linear_models.py:141-207, train_bc.py:79-82.
  * y = relu?( conv(x, w) + bias + resid ) * rowmask ; out_f32_atomic: y is fp32 and the raw
  * products are atomically added (split-K linear), epilogue terms are then ignored. */

@@ -35,6 +35,13 @@ def rel(a, b):
     return ((a.double() - b).norm() / (b.norm() + 1e-30)).item()
 
 
+def pack_signs(t):
+    """Host restatement of the sign words: word k covers elements 32k .. 32k+31, bit i = (element > 0)."""
+    pos = (t.float().reshape(-1, 32) > 0).to(torch.int64)
+    words = (pos << torch.arange(32, dtype=torch.int64)).sum(1)
+    return torch.where(words >= 2 ** 31, words - 2 ** 32, words).to(torch.int32)
+
+
 @pytest.mark.parametrize("N", [3, 40])
 @pytest.mark.parametrize("layer", LAYERS, ids=[l[0] for l in LAYERS])
 def test_conv_fwd_dgrad_wgrad(ops, layer, N):
@@ -61,12 +68,22 @@ def test_conv_fwd_dgrad_wgrad(ops, layer, N):
     ref = F.relu(F.conv2d(x64, w64, bias.double(), stride=stride, padding=pad).permute(0, 2, 3, 1)
                  + resid.double()) * rowmask.double().view(N, OH, OW, 1)
     assert rel(y.cpu(), ref) <= 4e-3  # bf16 output rounding (2^-9)
+    # the same launch with packed ReLU sign words: identical output, words = (stored value > 0)
+    y2 = torch.full_like(y, float("nan"))
+    sb = torch.full((y.numel() // 32,), -1, device=DEV, dtype=torch.int32)
+    ops.conv_fwd(xd, wd, bias.to(DEV), y2, R, S, stride, pad, relu=True, resid=resid.to(DEV),
+                 rowmask=rowmask.to(DEV), bits_out=sb)
+    assert torch.equal(y2, y) and torch.equal(sb.cpu(), pack_signs(y.cpu()))
     # dgrad: + addend, gated
     dx = torch.full((N, H, W, Cin), float("nan"), device=DEV, dtype=torch.bfloat16)
     ops.conv_dgrad(dy.to(DEV), wd, dx, R, S, stride, pad, addend=addend.to(DEV), gate=gate.to(DEV))
     dref = torch.nn.grad.conv2d_input((N, Cin, H, W), w64, dy64, stride=stride, padding=pad).permute(0, 2, 3, 1)
     dref = (dref + addend.double()) * (gate.double() > 0)
     assert rel(dx.cpu(), dref) <= 4e-3
+    # gate read as packed sign words instead of the tensor: bit-identical result
+    dx2 = torch.full_like(dx, float("nan"))
+    ops.conv_dgrad(dy.to(DEV), wd, dx2, R, S, stride, pad, addend=addend.to(DEV), gate_bits=pack_signs(gate).to(DEV))
+    assert torch.equal(dx2, dx)
     # wgrad: fp32 accumulate (split over CTAs with fp32 atomics), and direct store for linears
     dw = torch.zeros(Cout, R * S, Cin, device=DEV, dtype=torch.float32)
     ops.conv_wgrad(dy.to(DEV), xd, dw, R, S, stride, pad)
@@ -136,6 +153,12 @@ def test_conv_flat_fwd_dgrad_wgrad(ops, layer, N):
     yc = y.cpu()
     assert rel(yc[:, 1:-1, 1:-1], ref) <= 4e-3
     assert (yc[:, 0] == 7).all() and (yc[:, -1] == 7).all() and (yc[:, :, 0] == 7).all() and (yc[:, :, -1] == 7).all()
+    # sign words of the stored pixels only: the words of the (never stored) border stay zero
+    y2 = torch.zeros_like(y)
+    sb = torch.zeros(y.numel() // 32, device=DEV, dtype=torch.int32)
+    ops.conv_flat(xd, wd, y2, R, R, bias=bias.to(DEV), valid=(OH, OW), out_geom=(OH + 2, OW + 2, 1, 1), relu=True,
+                  bits_out=sb)
+    assert torch.equal(y2[:, 1:-1, 1:-1], y[:, 1:-1, 1:-1]) and torch.equal(sb.cpu(), pack_signs(y2.cpu()))
     # dgrad: dy zero-bordered by R-1 on the x grid; every pixel of the x grid is produced, gated
     dyp = torch.zeros(N, Hg + R - 1, Wg + R - 1, Cout, dtype=torch.bfloat16)
     dyp[:, R - 1:R - 1 + OH, R - 1:R - 1 + OW] = dy
@@ -146,6 +169,10 @@ def test_conv_flat_fwd_dgrad_wgrad(ops, layer, N):
                       transpose_w=True)
         dref = torch.nn.grad.conv2d_input((N, Cin, Hg, Wg), w64, dy64).permute(0, 2, 3, 1) * (gate.double() > 0)
         assert rel(dx.cpu(), dref) <= 4e-3
+        dx2 = torch.full_like(dx, float("nan"))
+        ops.conv_flat(dyp.to(DEV), wd, dx2, R, R, gate_bits=pack_signs(gate).to(DEV), valid=(Hg, Wg),
+                      out_geom=(Hg, Wg, 0, 0), transpose_w=True)
+        assert torch.equal(dx2, dx)
     # wgrad on the x grid: dy stored at the top-left of a zero tensor with x's geometry
     dyg = torch.zeros(N, Hg, Wg, Cout, dtype=torch.bfloat16)
     dyg[:, :OH, :OW] = dy
