@@ -27,20 +27,24 @@ struct Tile {
   int cls, m0, n0, tap0, ntaps, kb_begin, kb_end;
 };
 
+__device__ __forceinline__ int fdiv(int n, const FastDiv& d) {
+  return (int)((__umulhi((uint32_t)n, d.mul) + (uint32_t)n) >> d.shr);
+}
+
 // tile id -> (m tile over the concatenated classes, n tile [x tap group], split)
 __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
   Tile r;
-  int mi = t % p.tiles_m_total;
-  const int rest = t / p.tiles_m_total;
-  const int y = rest % p.n_tiles;
-  const int split = rest / p.n_tiles;
+  const int rest = fdiv(t, p.fd_tiles_m);
+  int mi = t - rest * p.tiles_m_total;
+  const int split = fdiv(rest, p.fd_n_tiles);
+  const int y = rest - split * p.n_tiles;
   int cls = 0;
   while (cls + 1 < p.n_classes && mi >= p.tiles_m[cls]) { mi -= p.tiles_m[cls]; ++cls; }
   r.cls = cls;
   r.m0 = mi * 128;
   int n_tile = y, tg = 0;
   if (p.kind == KIND_WGRAD) {
-    n_tile = y / p.tap_groups;
+    n_tile = fdiv(y, p.fd_tap_groups);
     tg = y - n_tile * p.tap_groups;
   }
   r.n0 = n_tile * p.block_n;
@@ -181,9 +185,9 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
         } else if (p.kind == KIND_FWD) {
           int w_base = 0, h_base = 0, n_img = 0;
           if (p.a_im2col) {
-            n_img = m0 / ohw;
+            n_img = fdiv(m0, p.fd_ohw[cls]);
             const int rem = m0 - n_img * ohw;
-            const int oh = rem / oww;
+            const int oh = fdiv(rem, p.fd_ow[cls]);
             const int ow = rem - oh * oww;
             w_base = ow * p.trav_stride_w + p.lower_w[cls];
             h_base = oh * p.trav_stride_h + p.lower_h[cls];
@@ -237,9 +241,9 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
             for (int i = 0; i < p.b_boxes; ++i)
               ptx::tma_load_2d(b_dst + i * p.b_box_bytes, &p.mapB, full, n0 + i * p.b_box_w, p0);
             if (p.a_im2col) {
-              const int n_img = p0 / ohw;
+              const int n_img = fdiv(p0, p.fd_ohw[0]);
               const int rem = p0 - n_img * ohw;
-              const int oh = rem / oww;
+              const int oh = fdiv(rem, p.fd_ow[0]);
               const int ow = rem - oh * oww;
               const int w_base = ow * p.trav_stride_w + p.lower_w[0];
               const int h_base = oh * p.trav_stride_h + p.lower_h[0];
@@ -272,9 +276,9 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
             for (int i = 0; i < p.a_boxes; ++i)
               ptx::tma_load_2d(a_dst + i * p.a_box_bytes, &p.mapA[0], full, m0 + i * p.a_box_w, p0);
             if (p.a_im2col) {
-              const int n_img = p0 / ohw;
+              const int n_img = fdiv(p0, p.fd_ohw[0]);
               const int rem = p0 - n_img * ohw;
-              const int oh = rem / oww;
+              const int oh = fdiv(rem, p.fd_ow[0]);
               const int ow = rem - oh * oww;
               const int w_base = ow * p.trav_stride_w + p.lower_w[0];
               const int h_base = oh * p.trav_stride_h + p.lower_h[0];
@@ -427,9 +431,9 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       long long orow = row;
       if (p.remap && row_ok) {
         const int hw = p.Hs[cls] * p.Ws[cls];
-        const int n = row / hw;
+        const int n = fdiv(row, p.fd_hw[cls]);
         const int rem = row - n * hw;
-        const int jh = rem / p.Ws[cls];
+        const int jh = fdiv(rem, p.fd_ws[cls]);
         const int jw = rem - jh * p.Ws[cls];
         orow = ((long long)n * p.OHf + (jh * p.remap_sh + p.ah[cls])) * p.OWf +
                (jw * p.remap_sw + p.aw[cls]);
@@ -438,13 +442,14 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       bool zero_row = false;
       if (p.s2d_H > 0 && row_ok) {
         const int qd = row & 3, sp = row >> 2;
-        const int sw = sp % p.border_w, sh = (sp / p.border_w) % p.border_h;
+        const int spr = fdiv(sp, p.fd_border_w);
+        const int sw = sp - spr * p.border_w, sh = spr - fdiv(spr, p.fd_border_h) * p.border_h;
         const int ih = 2 * sh + (qd >> 1) - 1, iw = 2 * sw + (qd & 1) - 1;
         zero_row = ih < 0 || ih >= p.s2d_H || iw < 0 || iw >= p.s2d_W;
       } else if (p.border_h > 0 && row_ok) {
         const int hw = p.border_h * p.border_w;
-        const int rem = row % hw;
-        const int y = rem / p.border_w;
+        const int rem = row - fdiv(row, p.fd_border_hw) * hw;
+        const int y = fdiv(rem, p.fd_border_w);
         const int x = rem - y * p.border_w;
         zero_row = (y == 0) || (y == p.border_h - 1) || (x == 0) || (x == p.border_w - 1);
       }
@@ -571,15 +576,12 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
                   o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]);
                   o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
                   o4[i] = o;
-                  if (p.bits_out) {
-                    // the predicate of the `gate` path on the value as stored: bf16 > 0
-                    const uint32_t w4[4] = {o.x, o.y, o.z, o.w};
+                }
+                if (p.bits_out) {
+                  // ReLU's backward predicate on the fp32 value (the stored bf16 is > 0 exactly when
+                  // it is, except below bf16's smallest subnormal, where this follows the fp32 reference)
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                      sign_word |= ((int)(w4[k] << 16) > 0 ? 1u : 0u) << (8 * i + 2 * k);
-                      sign_word |= ((int)(w4[k] & 0xffff0000u) > 0 ? 1u : 0u) << (8 * i + 2 * k + 1);
-                    }
-                  }
+                  for (int i = 0; i < 32; ++i) sign_word |= (f[i] > 0.f) ? (1u << i) : 0u;
                 }
                 if (p.bits_out) p.bits_out[off >> 5] = sign_word;
               } else if (p.swap_ab) {
@@ -650,6 +652,28 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     }
     if (gb) { p.gate_bits = (const uint32_t*)gb; p.gate = nullptr; }
     p.bits_out = (uint32_t*)bo;
+  }
+  auto magic = [](int d) {
+    FastDiv f{0u, 0u};
+    if (d > 1) {
+      uint32_t l = 0;
+      while ((1ull << l) < (unsigned long long)d) ++l;
+      f.mul = (uint32_t)((((1ull << l) - (unsigned long long)d) << 32) / (unsigned long long)d + 1ull);
+      f.shr = l;
+    }
+    return f;
+  };
+  p.fd_tiles_m = magic(p.tiles_m_total);
+  p.fd_n_tiles = magic(p.n_tiles);
+  p.fd_tap_groups = magic(p.tap_groups);
+  p.fd_border_w = magic(p.border_w);
+  p.fd_border_h = magic(p.border_h);
+  p.fd_border_hw = magic(p.border_h * p.border_w);
+  for (int c = 0; c < 4; ++c) {
+    p.fd_hw[c] = magic(p.Hs[c] * p.Ws[c]);
+    p.fd_ws[c] = magic(p.Ws[c]);
+    p.fd_ohw[c] = magic(p.OHW[c]);
+    p.fd_ow[c] = magic(p.OW[c]);
   }
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(g_attr_once, [] {

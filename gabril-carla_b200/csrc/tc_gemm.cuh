@@ -27,6 +27,13 @@ constexpr int kThreads = 32 * (kFirstProducerWarp + kProducers);
 enum Kind { KIND_FWD = 0, KIND_WGRAD = 1 };
 enum OutMode { OUT_BF16 = 0, OUT_F32_STORE = 1, OUT_F32_ATOMIC = 2 };
 
+// n / d for 0 <= n < 2^31 as (umulhi(n, mul) + n) >> shr (round-up multiplier, Granlund-Montgomery):
+// the epilogue warps decode a tile and a pixel per tile, and a runtime 32-bit division is a serial
+// chain of ~30 instructions on a warp that runs alone on its scheduler.
+struct FastDiv {
+  uint32_t mul, shr;
+};
+
 struct Params {
   CUtensorMap mapA[4];  // FWD: activation (one per strided-dgrad parity class); WGRAD: dY (tiled)
   CUtensorMap mapB;     // FWD: weights [Cout][tap][Cin];  WGRAD: activation (im2col or tiled)
@@ -108,6 +115,10 @@ struct Params {
   int tiles_m[4], tiles_m_total, n_tiles, n_splits, total_tiles;
   int acc_bufs, acc_stride;  // TMEM accumulator ring (1 or 2 buffers of acc_stride columns)
   long long tap_stride;  // WGRAD: element (m, tap, n) at out + m*ldo + tap*tap_stride + n
+  // magic numbers of the divisions above, filled by launch() from the fields they belong to
+  FastDiv fd_tiles_m, fd_n_tiles, fd_tap_groups, fd_border_w, fd_border_h, fd_border_hw;
+  FastDiv fd_hw[4], fd_ws[4];    // remap: Hs*Ws, Ws per class
+  FastDiv fd_ohw[4], fd_ow[4];   // im2col traversal: OHW, OW per class
   int* err_flag;
   int debug;  // perf experiments only: bit0 = producer skips the TMA copies, bit1 = issuer skips the MMAs
 };
