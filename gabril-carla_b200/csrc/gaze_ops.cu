@@ -216,8 +216,9 @@ constexpr int kPatchRows = 6;
 
 template <int S_, bool GRAY>
 __global__ void __launch_bounds__(256)
-obs_patches_tiled_kernel(const uint8_t* __restrict__ frames, bf16* __restrict__ out, int L,
-                         int center, int H, int W, int OH, int OW, int Kp, int SH, int SW) {
+obs_patches_tiled_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__ widx,
+                         bf16* __restrict__ out, int L, int center, int H, int W, int OH, int OW,
+                         int Kp, int SH, int SW) {
   constexpr int CP = GRAY ? 1 : 3;
   constexpr int C0 = S_ * CP;
   constexpr int NR = 2 * kPatchRows + 2;
@@ -240,9 +241,12 @@ obs_patches_tiled_kernel(const uint8_t* __restrict__ frames, bf16* __restrict__ 
     const int fs = rs % S_, r = rs / S_;
     const int ih = ih0 + r;
     if (ih >= 0 && ih < H) {
-      const int f = frame_index(fs, S_, center, L);
+      // batch layout [B, L, H, W, 3], or (widx != NULL) a frame store [N, H, W, 3] addressed through
+      // the window table widx[b][fs] of gabril_store_windows: no batch tensor is materialised
+      const long long fr = widx ? __ldg(widx + (long long)b * S_ + fs)
+                                : (long long)b * L + frame_index(fs, S_, center, L);
       const uint4* src = reinterpret_cast<const uint4*>(
-          frames + (((long long)b * L + f) * H + ih) * (long long)row_bytes);
+          frames + (fr * H + ih) * (long long)row_bytes);
       reinterpret_cast<uint4*>(raw + (size_t)rs * row_bytes)[v] = __ldg(src + v);
     }
   }
@@ -418,6 +422,40 @@ rowmask_apply_nchw_kernel(const float* __restrict__ z, const float* __restrict__
 }
 
 // =================================================================================================
+// Device-resident demonstration store.  robomimic's SequenceDataset with
+// frame_stack = S, seq_length = 1 returns, for the sampled step i of a demo that starts at step d,
+// the steps max(i - S + 1 + s, d), s = 0..S-1 (the demo's first frame repeated as front padding:
+// vlm_gaze/robomimic/utils/dataset.py:609-628, pad_sequence(pad_same=True)).  The store keeps all
+// steps of all demos back to back in HBM, demo_first[i] = d; a batch is a table of frame indices
+// and every consumer (patch kernel, content hash, gaze / action row gather) reads through it.
+// Integer work: bit-exact.
+// =================================================================================================
+__global__ void __launch_bounds__(256)
+store_windows_kernel(const long long* __restrict__ step_idx, const long long* __restrict__ demo_first,
+                     long long* __restrict__ widx, int B, int S, long long n_steps) {
+  const long long total = (long long)B * S;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int s = (int)(i % S);
+    long long c = step_idx[i / S];
+    c = c < 0 ? 0 : (c > n_steps - 1 ? n_steps - 1 : c);
+    const long long t = c - (S - 1) + s, d = demo_first[c];
+    widx[i] = t > d ? t : d;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+store_gather_rows_kernel(const float* __restrict__ src, const long long* __restrict__ widx,
+                         float* __restrict__ dst, long long rows, int row_len) {
+  const long long total = rows * row_len;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / row_len;
+    dst[i] = __ldg(src + widx[r] * row_len + (i - r * row_len));
+  }
+}
+
+// =================================================================================================
 // gaze.ratio < 1 (train_bc.py:230-240): per-sample content hash r = frac(|sum(obs) * 123456.789|)
 // in fp32, sample uses gaze iff r < ratio.  sum(obs) is over the formatted frame stack (the exact
 // fp32 values of obs_format).  One CTA per sample, fixed summation order.  For any frame whose
@@ -428,8 +466,9 @@ rowmask_apply_nchw_kernel(const float* __restrict__ z, const float* __restrict__
 // reference's mean over an empty selection is NaN as well).
 // =================================================================================================
 __global__ void __launch_bounds__(256)
-ivg_key_kernel(const uint8_t* __restrict__ frames, float* __restrict__ sel, int B, int L, int S,
-               int center, int H, int W, int gray, float ratio) {
+ivg_key_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__ widx,
+               float* __restrict__ sel, int B, int L, int S, int center, int H, int W, int gray,
+               float ratio) {
   __shared__ float scratch[32];
   const int b = blockIdx.x;
   const long long HW = (long long)H * W;
@@ -437,7 +476,7 @@ ivg_key_kernel(const uint8_t* __restrict__ frames, float* __restrict__ sel, int 
   for (int s = 0; s < S; ++s) {
     int t = center - S + 1 + s;
     t = t < 0 ? 0 : (t > L - 1 ? L - 1 : t);
-    const uint8_t* fp = frames + ((long long)b * L + t) * HW * 3;
+    const uint8_t* fp = frames + (widx ? widx[(long long)b * S + s] : (long long)b * L + t) * HW * 3;
     for (long long i = threadIdx.x; i < HW; i += blockDim.x) {
       const float r = __fdiv_rn((float)fp[3 * i + 0], 255.f), g = __fdiv_rn((float)fp[3 * i + 1], 255.f),
                   bl = __fdiv_rn((float)fp[3 * i + 2], 255.f);
@@ -896,7 +935,8 @@ int gabril_obs_format(const uint8_t* frames, float* out, int B, int L, int S, in
 }
 
 static int obs_patches_impl(const uint8_t* frames, void* patches, int B, int L, int S, int center,
-                            int H, int W, int grayscale, int Kp, int SH, int SW, cudaStream_t stream) {
+                            int H, int W, int grayscale, int Kp, int SH, int SW, cudaStream_t stream,
+                            const long long* widx = nullptr) {
   if (!frames || !patches) return GABRIL_ERR_NULL;
   const int C0 = S * (grayscale ? 1 : 3);
   if (B <= 0 || S < 1 || S > 4 || Kp < 16 * C0 || Kp % 4) return GABRIL_ERR_BAD_SHAPE;
@@ -917,8 +957,8 @@ static int obs_patches_impl(const uint8_t* frames, void* patches, int B, int L, 
                            cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);               \
       attr_done = true;                                                                            \
     }                                                                                              \
-    obs_patches_tiled_kernel<SS, GG><<<tgrid, 256, smem, stream>>>(frames, out, L, center, H, W,   \
-                                                                   OH, OW, Kp, SH, SW);            \
+    obs_patches_tiled_kernel<SS, GG><<<tgrid, 256, smem, stream>>>(frames, widx, out, L, center,   \
+                                                                   H, W, OH, OW, Kp, SH, SW);      \
   } while (0)
       if (grayscale && S == 2) GABRIL_TILED_CASE(2, true);
       else if (grayscale && S == 4) GABRIL_TILED_CASE(4, true);
@@ -929,7 +969,7 @@ static int obs_patches_impl(const uint8_t* frames, void* patches, int B, int L, 
       return GABRIL_OK;
     }
   }
-  if (SH > 0) return GABRIL_ERR_BAD_SHAPE;  // the space-to-depth row order needs the tiled kernel
+  if (SH > 0 || widx) return GABRIL_ERR_BAD_SHAPE;  // s2d row order / store addressing: tiled kernel only
 #define GABRIL_PATCH_CASE(SS, GG)                                                              \
   obs_patches_kernel<SS, GG><<<grid, 256, 0, stream>>>(frames, out, B, L, center, H, W, OH, OW, Kp)
   if (grayscale) {
@@ -1060,7 +1100,50 @@ int gabril_ivg_select(const uint8_t* frames, float* sel, float* sel_stats, int B
                       int center, int H, int W, int grayscale, float ratio, cudaStream_t stream) {
   if (!frames || !sel || !sel_stats) return GABRIL_ERR_NULL;
   if (B <= 0 || B > 65535 * 16 || S < 1 || L < 1 || H < 1 || W < 1) return GABRIL_ERR_BAD_SHAPE;
-  ivg_key_kernel<<<B, 256, 0, stream>>>(frames, sel, B, L, S, center, H, W, grayscale, ratio);
+  ivg_key_kernel<<<B, 256, 0, stream>>>(frames, nullptr, sel, B, L, S, center, H, W, grayscale, ratio);
+  ivg_count_kernel<<<1, 256, 0, stream>>>(sel, sel_stats, B);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+// ---- device-resident demonstration store -----------------------------------------
+int gabril_store_windows(const long long* step_idx, const long long* demo_first, long long* widx,
+                         int B, int S, long long n_steps, cudaStream_t stream) {
+  if (!step_idx || !demo_first || !widx) return GABRIL_ERR_NULL;
+  if (B <= 0 || S < 1 || S > kMaxS || n_steps < 1) return GABRIL_ERR_BAD_SHAPE;
+  const long long total = (long long)B * S;
+  store_windows_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(step_idx, demo_first, widx,
+                                                                         B, S, n_steps);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_store_gather_rows(const float* src, const long long* widx, float* dst, long long rows,
+                             int row_len, cudaStream_t stream) {
+  if (!src || !widx || !dst) return GABRIL_ERR_NULL;
+  if (rows <= 0 || row_len < 1) return GABRIL_ERR_BAD_SHAPE;
+  const long long total = rows * row_len;
+  store_gather_rows_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(src, widx, dst, rows,
+                                                                             row_len);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_obs_patches_s2d_store(const uint8_t* store, const long long* widx, void* patches, int B,
+                                 int S, int H, int W, int grayscale, int Kp, int SH, int SW,
+                                 cudaStream_t stream) {
+  if (!widx) return GABRIL_ERR_NULL;
+  const int OH = (H + 2 - 4) / 2 + 1, OW = (W + 2 - 4) / 2 + 1;
+  if (SH < (OH + 2) / 2 || SW < (OW + 2) / 2) return GABRIL_ERR_BAD_SHAPE;
+  return obs_patches_impl(store, patches, B, S, S, S - 1, H, W, grayscale, Kp, SH, SW, stream, widx);
+}
+
+int gabril_ivg_select_store(const uint8_t* store, const long long* widx, float* sel, float* sel_stats,
+                            int B, int S, int H, int W, int grayscale, float ratio,
+                            cudaStream_t stream) {
+  if (!store || !widx || !sel || !sel_stats) return GABRIL_ERR_NULL;
+  if (B <= 0 || B > 65535 * 16 || S < 1 || H < 1 || W < 1) return GABRIL_ERR_BAD_SHAPE;
+  ivg_key_kernel<<<B, 256, 0, stream>>>(store, widx, sel, B, S, S, S - 1, H, W, grayscale, ratio);
   ivg_count_kernel<<<1, 256, 0, stream>>>(sel, sel_stats, B);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;

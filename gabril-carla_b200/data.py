@@ -116,7 +116,8 @@ class ShardedBatches:
     wrapping to a multiple of the world size, rank r takes indices r::world."""
 
     def __init__(self, store: DemoStore, batch_size: int, rank: int = 0, world: int = 1, seed: int = 0,
-                 shuffle: bool = True):
+                 shuffle: bool = True, fused: bool = False):
+        self.fused = bool(fused)
         self.store, self.bs, self.rank, self.world, self.seed, self.shuffle = store, int(batch_size), rank, world, seed, shuffle
         self.epoch = 0
         self.per_rank = math.ceil(len(store) / world)
@@ -143,4 +144,9 @@ class ShardedBatches:
     def __iter__(self) -> Iterator[Dict]:
         idx = self.indices().to(self.store.device)
         for lo in range(0, idx.numel(), self.bs):
-            yield self.store.batch(idx[lo:lo + self.bs])
+            if self.fused and self.store.device.type == "cuda":
+                # device-resident feed: the trainer hands (store, step indices) to
+                # StepEngine.forward_store, no batch tensors are built
+                yield {"store": self.store, "step_idx": idx[lo:lo + self.bs].contiguous()}
+            else:
+                yield self.store.batch(idx[lo:lo + self.bs])

@@ -130,7 +130,6 @@ class StepEngine:
         """frames u8 [B,L,H,W,3], gaze f32 [B,L,P*2], actions f32 [B,L,A] or [B,A] (all on device).
         Runs the forward pass, the losses and the loss-side gradient seeds.  Returns the device
         tensor losses = [actor, reg, total]."""
-        s, a = self.spec, self.arena
         B, L = frames.shape[0], frames.shape[1]
         if B != self.B:
             self._alloc(B)
@@ -138,13 +137,45 @@ class StepEngine:
         center = L - 1
         # ---- preprocessing (prepare_for_bc, data_loader_robomimic.py:318-360) ----
         ops.obs_patches_s2d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["patches"])
-        if self.use_reg or self.use_gmd or self.use_igmd:
-            self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
         # ---- which samples use gaze (train_bc.py:230-240); all of them at gaze.ratio >= 1 ----
         self.sel = self.sel_stats = None
         if self.gaze_ratio < 1.0 and (self.use_reg or self.use_gmd or self.use_igmd):
             self.sel, self.sel_stats = ops.ivg_select(frames, self.S, center, self.grayscale,
                                                       self.gaze_ratio, b["sel"], b["sel_stats"])
+        return self._forward_rest(gaze, actions, center)
+
+    def forward_store(self, store, step_idx: torch.Tensor):
+        """Device-resident feed: `store` is a DemoStore living in HBM, step_idx int64
+        [B] the sampled steps.  Replaces SequenceDataset.get_item + DataLoader + H2D
+        (robomimic/utils/dataset.py:503-633, train_bc.py:204-207): the frame window table is built on
+        the device and conv_1's patch kernel, the content hash and the gaze / action gathers read the
+        store through it, so the uint8 batch [B,S,H,W,3] never exists.  Same results, bit for bit, as
+        forward(*store.batch(step_idx))."""
+        if store.images.device != self.device or store.S != self.S:
+            raise RuntimeError("forward_store needs a DemoStore on the engine's device with the same "
+                               f"frame_stack (store on {store.images.device}, S={store.S})")
+        B = step_idx.numel()
+        if B != self.B:
+            self._alloc(B)
+        b = self.buf
+        if "widx" not in b:
+            b["widx"] = torch.empty(B, self.S, device=self.device, dtype=torch.int64)
+        center = self.S - 1
+        widx = ops.store_windows(step_idx.to(self.device, torch.int64).contiguous(), store.first, self.S,
+                                 out=b["widx"])
+        ops.obs_patches_s2d_store(store.images, widx, self.grayscale, self.SH, self.SW, b["patches"])
+        self.sel = self.sel_stats = None
+        if self.gaze_ratio < 1.0 and (self.use_reg or self.use_gmd or self.use_igmd):
+            self.sel, self.sel_stats = ops.ivg_select_store(store.images, widx, self.grayscale,
+                                                            self.gaze_ratio, b["sel"], b["sel_stats"])
+        gaze = ops.store_gather_rows(store.gaze, widx)
+        actions = ops.store_gather_rows(store.actions, widx)
+        return self._forward_rest(gaze, actions, center)
+
+    def _forward_rest(self, gaze, actions, center):
+        s, a, b, B = self.spec, self.arena, self.buf, self.B
+        if self.use_reg or self.use_gmd or self.use_igmd:
+            self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
         rowmask = None
         if self.use_gmd:
             # A is drawn before the interpolation, like gaze_utils.py:36

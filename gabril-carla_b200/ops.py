@@ -477,6 +477,57 @@ def ivg_select(frames, S, center, grayscale, ratio, sel=None, sel_stats=None):
     return sel, sel_stats
 
 
+# ---- device-resident demonstration store (SURVEY 8f N2) ----------------------------------------
+def store_windows(step_idx, demo_first, S, out=None):
+    """[B] sampled step indices -> int64 [B,S] frame indices (robomimic frame_stack=S, seq_length=1:
+    steps idx-S+1..idx, clamped to the first step of the demo; dataset.py:609-628)."""
+    _chk(step_idx, torch.int64, "step_idx"); _chk(demo_first, torch.int64, "demo_first")
+    B = step_idx.numel()
+    if out is None:
+        out = torch.empty(B, S, device=step_idx.device, dtype=torch.int64)
+    _call("gabril_store_windows", ptr(step_idx), ptr(demo_first), ptr(out), c_int(B), c_int(S),
+          c_ll(demo_first.numel()), stream(), work=float(B * S * 24))
+    return out
+
+
+def store_gather_rows(src, widx, out=None):
+    """src fp32 [N,R], widx int64 [B,S] -> fp32 [B,S,R]."""
+    _chk(src, torch.float32, "src"); _chk(widx, torch.int64, "widx")
+    R = src.shape[1]
+    if out is None:
+        out = torch.empty(*widx.shape, R, device=src.device, dtype=torch.float32)
+    _call("gabril_store_gather_rows", ptr(src), ptr(widx), ptr(out), c_ll(widx.numel()), c_int(R),
+          stream(), work=float(widx.numel() * (8 + 8 * R)))
+    return out
+
+
+def obs_patches_s2d_store(store_frames, widx, grayscale, SH, SW, out):
+    """obs_patches_s2d reading frame widx[b,s] of the uint8 store [N,H,W,3] (no batch tensor)."""
+    _chk(store_frames, torch.uint8, "store_frames"); _chk(widx, torch.int64, "widx")
+    N, H, W, C = store_frames.shape
+    B, S = widx.shape
+    Kp = conv1_kp(S, grayscale)
+    assert out.shape == (B * SH * SW * 4, Kp) and out.dtype == torch.bfloat16
+    _call("gabril_obs_patches_s2d_store", ptr(store_frames), ptr(widx), ptr(out), c_int(B), c_int(S),
+          c_int(H), c_int(W), c_int(int(grayscale)), c_int(Kp), c_int(SH), c_int(SW), stream(),
+          work=float(B * S * H * W * 3 + B * (H // 2) * (W // 2) * Kp * 2))
+    return out
+
+
+def ivg_select_store(store_frames, widx, grayscale, ratio, sel=None, sel_stats=None):
+    _chk(store_frames, torch.uint8, "store_frames"); _chk(widx, torch.int64, "widx")
+    N, H, W, _ = store_frames.shape
+    B, S = widx.shape
+    if sel is None:
+        sel = torch.empty(B, device=widx.device, dtype=torch.float32)
+    if sel_stats is None:
+        sel_stats = torch.empty(2, device=widx.device, dtype=torch.float32)
+    _call("gabril_ivg_select_store", ptr(store_frames), ptr(widx), ptr(sel), ptr(sel_stats), c_int(B),
+          c_int(S), c_int(H), c_int(W), c_int(int(grayscale)), c_float(ratio), stream(),
+          work=float(B * S * H * W * 3))
+    return sel, sel_stats
+
+
 def colsum_bf16(dy, db):
     _chk(dy, torch.bfloat16, "dy"); _chk(db, torch.float32, "db")
     C = db.numel()

@@ -235,7 +235,8 @@ class BaseTrainer:
             store = store.to(self.device) if nbytes < 0.5 * free else store.pin()
         self.train_dataset = store
         self.train_loader = ShardedBatches(store, int(c.data.batch_size), self.rank, self.world_size,
-                                           seed=int(c.training.seed), shuffle=True)
+                                           seed=int(c.training.seed), shuffle=True,
+                                           fused=getattr(self, "fused_feed", False))
         self.train_sampler = self.train_loader
 
     def _setup_model(self):
@@ -290,6 +291,9 @@ class BaseTrainer:
 
 class BCTrainer(BaseTrainer):
     """GABRIL / GABRIL+GMD behaviour-cloning trainer (train_bc.py:20-335) over the fused step."""
+    # HBM-resident stores feed StepEngine.forward_store directly (SURVEY 8f N2); a host-resident
+    # store (too large for HBM) still goes through batch dicts + H2D like the reference
+    fused_feed = True
 
     def __init__(self, cfg):
         super().__init__(cfg)
@@ -351,6 +355,13 @@ class BCTrainer(BaseTrainer):
         train_bc.py:203-299.  The returned tensor's .backward() runs the kernel backward."""
         gaze_key = self.cfg.data.get("gaze_key", "gaze_coords")
         dev = self.device
+        if "store" in batch:   # device-resident feed (data.ShardedBatches(fused=True))
+            losses = self.engine.forward_store(batch["store"], batch["step_idx"])
+            actor, reg, total = self.engine.losses_host()
+            anchor = torch.zeros((), device=dev, requires_grad=True)
+            loss = _StepLoss.apply(anchor, self, losses[2])
+            return loss, int(batch["step_idx"].numel()), {"Loss/actor": actor, "Loss/reg": reg,
+                                                          "Loss/total": total}
         frames = batch["obs"]["image"].to(dev, non_blocking=True)
         gaze = batch["obs"][gaze_key].to(dev, non_blocking=True)
         actions = batch["actions"].to(dev, non_blocking=True)

@@ -177,6 +177,28 @@ int gabril_reg_dist(const void* z, int z_nhwc_bf16, const float* g1, long long g
 int gabril_ivg_select(const uint8_t* frames, float* sel, float* sel_stats, int B, int L, int S,
                       int center, int H, int W, int grayscale, float ratio, cudaStream_t stream);
 
+/* ---- device-resident demonstration store: replaces SequenceDataset.get_item
+ * (vlm_gaze/robomimic/utils/dataset.py:503-633, frame_stack = S, seq_length = 1, pad_frame_stack)
+ * and the DataLoader's host->device copy of the batch dict (train_bc.py:204-207).  The store holds
+ * every step of every demo back to back: frames uint8 [N, H, W, 3], gaze fp32 [N, P*2], actions
+ * fp32 [N, A], demo_first int64 [N] = first step of the demo step i belongs to. ------------------ */
+/* widx[b][s] = max(step_idx[b] - S + 1 + s, demo_first[step_idx[b]])  (dataset.py:609-628: the
+ * first frame of a demo repeated as front padding); step_idx clamped into [0, n_steps-1]. */
+int gabril_store_windows(const long long* step_idx, const long long* demo_first, long long* widx,
+                         int B, int S, long long n_steps, cudaStream_t stream);
+/* dst[r][:] = src[widx[r]][:] for r < rows (gaze and action rows of the batch dict). */
+int gabril_store_gather_rows(const float* src, const long long* widx, float* dst, long long rows,
+                             int row_len, cudaStream_t stream);
+/* gabril_obs_patches_s2d reading frame widx[b][s] of the store instead of frame s of batch row b:
+ * the uint8 batch tensor [B, S, H, W, 3] is never materialised. */
+int gabril_obs_patches_s2d_store(const uint8_t* store, const long long* widx, void* patches_bf16,
+                                 int B, int S, int H, int W, int grayscale, int Kp, int SH, int SW,
+                                 cudaStream_t stream);
+/* gabril_ivg_select over the same window table. */
+int gabril_ivg_select_store(const uint8_t* store, const long long* widx, float* sel, float* sel_stats,
+                            int B, int S, int H, int W, int grayscale, float ratio,
+                            cudaStream_t stream);
+
 /* ---- heads, losses, optimiser ------------------------------------------------------------- */
 /* db[c] += sum_rows dy[row][c]  (bias gradient of nn.Conv2d / nn.Linear); dy bf16 [M, C]. */
 int gabril_colsum_bf16(const void* dy, float* db, long long M, int C, cudaStream_t stream);
