@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--cpu-batch", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-store-feed", action="store_true")
+    ap.add_argument("--store-steps", type=int, default=8192, help="steps held by the HBM-resident store leg")
     ap.add_argument("--trace-out", default="")
     return ap.parse_args()
 
@@ -273,14 +275,47 @@ def main_ours(args):
         e1.record()
         barrier()
         e2e_ms = e0.elapsed_time(e1) / args.steps
+    # ---- timed region 3: HBM-resident demonstration store, a fresh random batch of
+    #      step indices every step, frames read through the window table (no batch tensor, no H2D) ----
+    store_ms = None
+    if not args.no_store_feed:
+        from gabril_carla_b200.data import DemoStore
+        n_store = args.store_steps
+        g = torch.Generator(device=device).manual_seed(7 + rank)
+        imgs = torch.randint(0, 256, (n_store, spec.H, spec.W, 3), device=device, dtype=torch.uint8, generator=g)
+        gz = torch.rand(n_store, 10, device=device, generator=g)
+        gz[torch.rand(n_store, 10, device=device, generator=g) < 0.2] = -1.0
+        store = DemoStore(imgs, gz, torch.rand(n_store, spec.A, device=device, generator=g),
+                          torch.arange(0, n_store, 250), eng.S).to(device)
+        idxs = [torch.randint(0, n_store, (B,), device=device, generator=g) for _ in range(args.steps)]
+
+        def store_step(idx):
+            step_no[0] += 1
+            eng.zero_grad()
+            eng.forward_store(store, idx)
+            eng.backward()
+            red.finish()
+            eng.adam_step(step_no[0], lr, grad_scale=red.grad_scale)
+
+        for i in range(3):
+            store_step(idxs[i % len(idxs)])
+        barrier()
+        e0.record()
+        for i in range(args.steps):
+            store_step(idxs[i])
+        e1.record()
+        barrier()
+        store_ms = e0.elapsed_time(e1) / args.steps
+        del store, imgs
     sampler.stop_flag = True
     sampler.join(timeout=2)
     _lib.poll_error()
 
-    t = torch.tensor([ms, e2e_ms or 0.0], device=device, dtype=torch.float64)
+    t = torch.tensor([ms, e2e_ms or 0.0, store_ms or 0.0], device=device, dtype=torch.float64)
     if is_dist:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, e2e_ms = t[0].item(), (t[1].item() if e2e_ms is not None else None)
+    store_ms = t[2].item() if store_ms is not None else None
     if is_dist:
         dist.barrier()   # every rank leaves the measured part together; only rank 0 reports
     if rank != 0:
@@ -309,6 +344,11 @@ def main_ours(args):
                      "step_flop_frac_of_peak": FLOP_PER_SAMPLE[gray] * B / (ms * 1e-3) / 1e12 / tf_sust},
         "losses_last_step": {"actor": losses[0], "reg": losses[1], "total": losses[2]},
     }
+    if store_ms:
+        line["store_feed"] = {"value": total / (store_ms * 1e-3), "unit": "samples/s", "ms_per_step": store_ms,
+                              "store_steps": args.store_steps, "h2d_bytes_per_step": 0,
+                              "note": "HBM-resident uint8 frame store, random step indices per step, "
+                                      "StepEngine.forward_store (window table + patch kernel reading the store)"}
     if args.trace_out:
         agg = {}
         for k, lab, work, unit, t_ms in rows:

@@ -110,6 +110,20 @@ def load_store(path: str, frame_stack: int, cfg_data=None, seed: int = 0) -> Dem
                      t.get("demo_start", torch.zeros(1, dtype=torch.long)), frame_stack, gaze_key)
 
 
+class StoreBatch(dict):
+    """Batch of an HBM-resident store: {"store", "step_idx"}.  The reference's batch-dict keys
+    ("obs", "actions") are materialised on first access, for callers that look inside a batch."""
+
+    def __init__(self, store: DemoStore, step_idx: torch.Tensor):
+        super().__init__(store=store, step_idx=step_idx)
+
+    def __missing__(self, key):
+        if key in ("obs", "actions"):
+            self.update(self["store"].batch(self["step_idx"]))
+            return dict.__getitem__(self, key)
+        raise KeyError(key)
+
+
 class ShardedBatches:
     """DistributedSampler(shuffle=True, drop_last=False) + DataLoader(batch_size=per-rank batch)
     semantics (base_trainer.py:88-92, data.py:62-71): a seeded permutation per epoch, padded by
@@ -147,6 +161,6 @@ class ShardedBatches:
             if self.fused and self.store.device.type == "cuda":
                 # device-resident feed: the trainer hands (store, step indices) to
                 # StepEngine.forward_store, no batch tensors are built
-                yield {"store": self.store, "step_idx": idx[lo:lo + self.bs].contiguous()}
+                yield StoreBatch(self.store, idx[lo:lo + self.bs].contiguous())
             else:
                 yield self.store.batch(idx[lo:lo + self.bs])

@@ -172,6 +172,42 @@ class StepEngine:
         actions = ops.store_gather_rows(store.actions, widx)
         return self._forward_rest(gaze, actions, center)
 
+    def predict(self, frames: torch.Tensor, g: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Inference: BCAgent._process_observation's formatting + _predict_control
+        (eval/my_agents/bc_agent.py:228-305).  frames u8 [B,S,H,W,3]; g fp32 [B,C,H,W] = the gaze
+        predictor's map (only its last channel is used, clipped into [0,1] like :278-279), needed for
+        dropout.method GMD / IGMD, which run in test mode: z * K instead of z * (A < K)
+        (gaze_utils.py:49-51, linear_models.py:194-199 with the encoder in eval()).  Forward kernels
+        only; gradients, losses and Adam state are not touched.  Returns the action vector
+        fp32 [B, action_dim] (a view of an engine buffer, overwritten by the next call)."""
+        s, a = self.spec, self.arena
+        B, L = frames.shape[0], frames.shape[1]
+        if B != self.B:
+            self._alloc(B)
+        b = self.buf
+        ops.obs_patches_s2d(frames, self.S, L - 1, self.grayscale, self.SH, self.SW, b["patches"])
+        rowmask = igmd = None
+        if self.use_gmd or self.use_igmd:
+            if g is None:
+                raise RuntimeError(f"dropout.method={'GMD' if self.use_gmd else 'IGMD'} needs the "
+                                   "predicted gaze map g at inference (bc_agent.py:276-279)")
+            gl = g[:, -1:].float().clamp(0.0, 1.0).contiguous()
+            dummy = b["K"]   # A is not read in test mode
+            if self.use_gmd:
+                rowmask = ops.gmd_mask(gl, dummy, s.h, s.w, 0.7, True, rowmask=b["rowmask"],
+                                       ws=(b["K"], b["mnmx"]))
+            else:
+                ops.gmd_mask(gl, b["K1"], s.H1, s.W1, 0.7, True, rowmask=b["rm1"], ws=(b["K1"], b["mnmx"]),
+                             layout="s2d", grid=(self.SH, self.SW))
+                ops.gmd_mask(gl, b["K2"], s.H2, s.W2, 0.7, True, rowmask=b["rm2"], ws=(b["K2"], b["mnmx"]),
+                             layout="bordered", grid=(self.SH, self.SW))
+                igmd = (b["rm1"], b["rm2"])
+        self._encoder_fwd(rowmask, igmd)
+        self._heads_logits()
+        ops.mse_head(b["lg_raw"], a.P("act.2.b"), b["logits"], s.A, b["actor_part"], 0.0,
+                     logits_out=b["logits"])
+        return b["logits"]
+
     def _forward_rest(self, gaze, actions, center):
         s, a, b, B = self.spec, self.arena, self.buf, self.B
         if self.use_reg or self.use_gmd or self.use_igmd:
@@ -234,7 +270,20 @@ class StepEngine:
 
     def _heads_fwd(self, actions, center):
         s, a, b, B = self.spec, self.arena, self.buf, self.B
-        # ---- heads (train_bc.py:290-292) ----
+        self._heads_logits()
+        if actions.dim() == 3:
+            act_view = actions[:, center if center < actions.shape[1] else -1, :]
+        else:
+            act_view = actions
+        assert act_view.stride(-1) == 1 and act_view.dtype == torch.float32
+        scale = 1.0 / self.grad_accum
+        ops.mse_head(b["lg_raw"], a.P("act.2.b"), act_view, s.A, b["actor_part"],
+                     scale / (B * s.A), dlogits=b["dlog"], dbias=a.G("act.2.b"), logits_out=b["logits"])
+        return self._reg_and_losses(scale)
+
+    def _heads_logits(self):
+        """pre_actor + actor up to the raw (bias-free) logits (train_bc.py:79-82,290-291)."""
+        s, a, b, B = self.spec, self.arena, self.buf, self.B
         b["zf_raw"].zero_()
         ops.conv_fwd(b["z"].view(B, 1, 1, s.flat), a.WB("pre.w"), None, b["zf_raw"], 1, 1, 1, 0,
                      out_f32_atomic=True, splits=self.pre_splits)
@@ -244,14 +293,9 @@ class StepEngine:
         b["lg_raw"].zero_()
         ops.conv_fwd(b["act1"].view(B, 1, 1, s.Z), a.WB("act.2.w"), None, b["lg_raw"], 1, 1, 1, 0,
                      out_f32_atomic=True, splits=1)
-        if actions.dim() == 3:
-            act_view = actions[:, center if center < actions.shape[1] else -1, :]
-        else:
-            act_view = actions
-        assert act_view.stride(-1) == 1 and act_view.dtype == torch.float32
-        scale = 1.0 / self.grad_accum
-        ops.mse_head(b["lg_raw"], a.P("act.2.b"), act_view, s.A, b["actor_part"],
-                     scale / (B * s.A), dlogits=b["dlog"], dbias=a.G("act.2.b"), logits_out=b["logits"])
+
+    def _reg_and_losses(self, scale):
+        s, a, b, B = self.spec, self.arena, self.buf, self.B
         # ---- regulariser (train_bc.py:145-150,168-169) on the (post-dropout) z ----
         reg_scale = 0.0
         if self.use_reg:
