@@ -10,6 +10,7 @@ themselves (ReLU backward is a `gate > 0` predicate in the dgrad epilogue).  Qui
 (SURVEY F6-F8): Residual's in-place ReLU (skip branch sees relu(x)), conv_4 activated by the first
 Residual, the regulariser reading the post-dropout z under GMD.
 """
+import os
 from typing import Dict, Optional
 
 import torch
@@ -51,6 +52,18 @@ class StepEngine:
         self.prob_dist_type = prob_dist_type
         self.gaze_ratio = float(gaze_ratio)
         self._accum_count = 0
+        # The gaze branch (heat-map splat -> regulariser -> loss scalars) only meets the main chain at
+        # GMD's mask and at conv_6's gradient, so it runs on a side stream: the issue-bound splat
+        # overlaps the HBM-bound patch kernel / conv_1, the regulariser overlaps the small-grid heads
+        # GEMMs (forward and backward), which leave most of the SMs idle.
+        self.overlap = os.environ.get("GABRIL_NO_OVERLAP", "0") != "1"
+        self._side = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
+        self._ev = {k: torch.cuda.Event() for k in ("in", "heat", "z", "head", "reg")} if self._side else {}
+        self._reg_pending = False
+        self._colsum_pending, self._cs_i = False, 0
+        self._cs_ev = [torch.cuda.Event() for _ in range(8)] if self._side else []
+        if self._side:
+            self._ev["colsum"] = torch.cuda.Event()
         self.on_heads_grads_ready = None   # hooks for the data-parallel bucket all-reduce
         self.on_all_grads_ready = None
 
@@ -211,7 +224,18 @@ class StepEngine:
     def _forward_rest(self, gaze, actions, center):
         s, a, b, B = self.spec, self.arena, self.buf, self.B
         if self.use_reg or self.use_gmd or self.use_igmd:
-            self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
+            if self.overlap:
+                main = torch.cuda.current_stream(self.device)
+                self._ev["in"].record(main)
+                gaze.record_stream(self._side)
+                with torch.cuda.stream(self._side):
+                    self._side.wait_event(self._ev["in"])
+                    self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
+                    self._ev["heat"].record(self._side)
+                if self.use_gmd or self.use_igmd:
+                    main.wait_event(self._ev["heat"])      # the keep maps read the heat maps
+            else:
+                self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
         rowmask = None
         if self.use_gmd:
             # A is drawn before the interpolation, like gaze_utils.py:36
@@ -270,16 +294,36 @@ class StepEngine:
 
     def _heads_fwd(self, actions, center):
         s, a, b, B = self.spec, self.arena, self.buf, self.B
+        side_reg = self.overlap and self.use_reg
+        scale = 1.0 / self.grad_accum
+        if side_reg:
+            main = torch.cuda.current_stream(self.device)
+            self._ev["z"].record(main)                      # z (and sel) are complete on the main stream
+            with torch.cuda.stream(self._side):
+                self._side.wait_event(self._ev["z"])
+                reg_scale = self._reg(scale)
         self._heads_logits()
         if actions.dim() == 3:
             act_view = actions[:, center if center < actions.shape[1] else -1, :]
         else:
             act_view = actions
         assert act_view.stride(-1) == 1 and act_view.dtype == torch.float32
-        scale = 1.0 / self.grad_accum
         ops.mse_head(b["lg_raw"], a.P("act.2.b"), act_view, s.A, b["actor_part"],
                      scale / (B * s.A), dlogits=b["dlog"], dbias=a.G("act.2.b"), logits_out=b["logits"])
-        return self._reg_and_losses(scale)
+        if side_reg:
+            self._ev["head"].record(main)
+            with torch.cuda.stream(self._side):
+                self._side.wait_event(self._ev["head"])     # actor_part
+                self._finalize(reg_scale)
+                self._ev["reg"].record(self._side)
+            self._reg_pending = True                        # joined in backward() / losses_host()
+            return b["losses"]
+        return self._finalize(self._reg(scale))
+
+    def _join_reg(self):
+        if self._reg_pending:
+            torch.cuda.current_stream(self.device).wait_event(self._ev["reg"])
+            self._reg_pending = False
 
     def _heads_logits(self):
         """pre_actor + actor up to the raw (bias-free) logits (train_bc.py:79-82,290-291)."""
@@ -294,7 +338,7 @@ class StepEngine:
         ops.conv_fwd(b["act1"].view(B, 1, 1, s.Z), a.WB("act.2.w"), None, b["lg_raw"], 1, 1, 1, 0,
                      out_f32_atomic=True, splits=1)
 
-    def _reg_and_losses(self, scale):
+    def _reg(self, scale):
         s, a, b, B = self.spec, self.arena, self.buf, self.B
         # ---- regulariser (train_bc.py:145-150,168-169) on the (post-dropout) z ----
         reg_scale = 0.0
@@ -307,6 +351,10 @@ class StepEngine:
             ops.reg_dist(b["z"], g1, b["heat"].stride(0), s.H, s.W, self.beta,
                          self.lam * scale * reg_scale, b["dz_reg"], b["reg_part"],
                          kind=self.prob_dist_type, sel=self.sel, scale_dev=sdev, stats=b["stats"])
+        return reg_scale
+
+    def _finalize(self, reg_scale):
+        s, b, B = self.spec, self.buf, self.B
         ops.finalize_losses(b["actor_part"], b["reg_part"] if self.use_reg else None, B,
                             1.0 / (B * s.A), reg_scale, self.lam, b["losses"],
                             reg_scale_dev=(self.sel_stats[1:] if self.use_reg and self.sel_stats is not None
@@ -329,6 +377,7 @@ class StepEngine:
         ops.conv_wgrad(b["dact1"].view(B, 1, 1, s.Z), b["zf"].view(B, 1, 1, s.Z), a.G("act.0.w"), 1, 1, 1, 0)
         ops.conv_dgrad(b["dact1"].view(B, 1, 1, s.Z), a.WB("act.0.w"), b["dzf"].view(B, 1, 1, s.Z), 1, 1, 1, 0)
         # pre_actor
+        self._join_reg()                                    # dz_reg, losses (side stream)
         ops.colsum_bf16(b["dzf"], a.G("pre.b"))
         ops.conv_wgrad(b["dzf"].view(B, 1, 1, s.Z), b["z"].view(B, 1, 1, s.flat), a.G("pre.w"), 1, 1, 1, 0,
                        direct_store=direct)
@@ -349,10 +398,10 @@ class StepEngine:
         s, a, b, B = self.spec, self.arena, self.buf, self.B
         # conv_6 / conv_5
         last, sb_last = b[f"r{s.NR - 1}"], b[f"sb_r{s.NR - 1}"]
-        ops.colsum_bf16(b["dz"], a.G("enc.conv6.b"))
+        self._colsum(b["dz"], a.G("enc.conv6.b"))
         ops.conv_wgrad(b["dz"], b["a5"], a.G("enc.conv6.w"), 5, 5, 1, 2)
         ops.conv_dgrad(b["dz"], a.WB("enc.conv6.w"), b["da5"], 5, 5, 1, 2, gate_bits=b["sb_a5"])
-        ops.colsum_bf16(b["da5"], a.G("enc.conv5.b"))
+        self._colsum(b["da5"], a.G("enc.conv5.b"))
         ops.conv_wgrad(b["da5"], last, a.G("enc.conv5.w"), 5, 5, 1, 2)
         dt, other = b["dt_a"], b["dt_b"]
         ops.conv_dgrad(b["da5"], a.WB("enc.conv5.w"), dt, 5, 5, 1, 2, gate_bits=sb_last)
@@ -366,23 +415,42 @@ class StepEngine:
                            gate_bits=b[f"sb_r{i - 1}"])
             dt, other = other, dt
         # conv_4 .. conv_1
-        ops.colsum_bf16(dt, a.G("enc.conv4.b"))
+        self._colsum(dt, a.G("enc.conv4.b"))
         ops.conv_wgrad(dt, b["a3"], a.G("enc.conv4.w"), 3, 3, 1, 0)
         ops.conv_dgrad(dt, a.WB("enc.conv4.w"), b["da3"], 3, 3, 1, 0, gate_bits=b["sb_a3"])
-        ops.colsum_bf16(b["da3"], a.G("enc.conv3.b"))
+        self._colsum(b["da3"], a.G("enc.conv3.b"))
         # conv_3 over the zero-bordered a2p (pad 0): the border gradients are gated to zero by a2p itself
         ops.conv_wgrad(b["da3"], b["a2p"], a.G("enc.conv3.w"), 4, 4, 2, 0)
         ops.conv_dgrad(b["da3"], a.WB("enc.conv3.w"), b["da2p"], 4, 4, 2, 0, gate_bits=b["sb_a2p"])
-        ops.colsum_bf16(b["da2p"], a.G("enc.conv2.b"))
+        self._colsum(b["da2p"], a.G("enc.conv2.b"))
         # conv_2 on the space-to-depth grid: dY pixel (i, j) sits at flat row q + SW + 1
         ops.conv_wgrad_flat(b["da2p"], b["a1s"], a.G("enc.conv2.w"), 2, 2, self.SW + 1,
                             flop_pixels=B * s.H2 * s.W2)
         ops.conv_flat(b["da2p"], a.WB("enc.conv2.w"), b["da1s"], 2, 2, gate_bits=b["sb_a1s"], transpose_w=True,
                       flop_pixels=B * s.H2 * s.W2)  # algorithmic FLOPs of the k4/s2 dgrad
         M1 = B * self.SH * self.SW * 4
-        ops.colsum_bf16(b["da1s"].view(M1, s.C1), a.G("enc.conv1.b"))
+        self._colsum(b["da1s"].view(M1, s.C1), a.G("enc.conv1.b"))
         ops.conv_wgrad(b["da1s"].view(M1, 1, 1, s.C1), b["patches"].view(M1, 1, 1, s.K1p),
                        a.G("enc.conv1.w"), 1, 1, 1, 0)
+        if self._colsum_pending:
+            main = torch.cuda.current_stream(self.device)
+            self._ev["colsum"].record(self._side)
+            main.wait_event(self._ev["colsum"])             # bias gradients complete before Adam / all-reduce
+            self._colsum_pending = False
+
+    def _colsum(self, dy, db):
+        """Bias gradient db += column sums of dy.  An HBM-bound reader with no consumer before the
+        optimiser: issued on the side stream so that it runs beside the tensor-bound wgrad / dgrad
+        GEMMs of the same layer instead of between them."""
+        if not self.overlap:
+            return ops.colsum_bf16(dy, db)
+        ev = self._cs_ev[self._cs_i % len(self._cs_ev)]
+        self._cs_i += 1
+        ev.record(torch.cuda.current_stream(self.device))   # dy is complete on the main stream
+        with torch.cuda.stream(self._side):
+            self._side.wait_event(ev)
+            ops.colsum_bf16(dy, db)
+        self._colsum_pending = True
 
     def activation(self, name: str) -> torch.Tensor:
         """Stored activation `name` as a plain NHWC tensor (tests / debugging): undoes the
@@ -408,6 +476,7 @@ class StepEngine:
 
     def losses_host(self):
         """One device->host read: (actor, reg, total)."""
+        self._join_reg()
         v = self.buf["losses"].tolist()
         return v[0], v[1], v[2]
 
