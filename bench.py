@@ -48,6 +48,8 @@ def parse():
     ap.add_argument("--cpu-batch", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="CUDA-graph replays of the step (StepEngine.train_step)")
+    ap.add_argument("--no-graph", action="store_true", help="eager launches")
     ap.add_argument("--no-store-feed", action="store_true")
     ap.add_argument("--store-steps", type=int, default=8192, help="steps held by the HBM-resident store leg")
     ap.add_argument("--trace-out", default="")
@@ -205,6 +207,10 @@ def main_ours(args):
     eng = StepEngine(spec, arena, pre, gaze_method=args.gaze_method, dp_method=args.dp_method,
                      grayscale=gray, seed=1234 + rank)
     red = ddp.attach(eng, arena)
+    if args.graph:
+        eng.use_graph = True
+    if args.no_graph:
+        eng.use_graph = False
 
     # synthetic batch of this rank's shard: 64 distinct samples tiled to B, pinned on the host
     base = make_batch(min(B, 64), seed=100 + rank)
@@ -217,9 +223,7 @@ def main_ours(args):
 
     def step(batch):
         step_no[0] += 1
-        eng.zero_grad()
-        eng.forward(*batch)
-        eng.backward()
+        eng.train_step(*batch)      # zero_grad + forward + backward (CUDA-graph replays when enabled)
         red.finish()
         eng.adam_step(step_no[0], lr, grad_scale=red.grad_scale)
 
@@ -247,8 +251,10 @@ def main_ours(args):
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    t_host = time.perf_counter()
     for _ in range(args.steps):
         step(dev_batch)
+    host_enqueue_ms = (time.perf_counter() - t_host) * 1e3 / args.steps   # no sync inside: pure enqueue
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1) / args.steps
@@ -332,6 +338,8 @@ def main_ours(args):
         "config": workload_config(args, B, world),
         "clocks": sampler.summary(),
         "gpu_launches": launches_per_step * args.steps,
+        "cuda_graph": bool(eng.use_graph),
+        "host_enqueue_ms_per_step": host_enqueue_ms,   # rank 0; close to ms_per_step = launch-bound
         "e2e": {"value": (total / (e2e_ms * 1e-3)) if e2e_ms else None, "unit": "samples/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "note": "pinned host batch -> double-buffered H2D on a copy stream -> step -> losses D2H, per rank"},

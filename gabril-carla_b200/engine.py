@@ -60,6 +60,8 @@ class StepEngine:
         self._side = torch.cuda.Stream(device=self.device) if self.device.type == "cuda" else None
         self._ev = {k: torch.cuda.Event() for k in ("in", "heat", "z", "head", "reg")} if self._side else {}
         self._reg_pending = False
+        self.use_graph = os.environ.get("GABRIL_GRAPH", "0") == "1"      # train_step() only
+        self._graphs, self._warm_B = {}, 0
         self._colsum_pending, self._cs_i = False, 0
         self._cs_ev = [torch.cuda.Event() for _ in range(8)] if self._side else []
         if self._side:
@@ -227,7 +229,8 @@ class StepEngine:
             if self.overlap:
                 main = torch.cuda.current_stream(self.device)
                 self._ev["in"].record(main)
-                gaze.record_stream(self._side)
+                if not torch.cuda.is_current_stream_capturing():
+                    gaze.record_stream(self._side)
                 with torch.cuda.stream(self._side):
                     self._side.wait_event(self._ev["in"])
                     self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
@@ -364,6 +367,16 @@ class StepEngine:
     # ------------------------------------------------------------------------------------------
     def backward(self):
         """The rest of loss.backward(): every weight / bias gradient accumulated into arena.g."""
+        self._backward_heads()
+        if self.on_heads_grads_ready is not None:
+            self.on_heads_grads_ready()
+        self._encoder_bwd()
+        self._accum_count += 1
+        if self.on_all_grads_ready is not None:
+            self.on_all_grads_ready()
+
+    def _backward_heads(self):
+        """actor / pre_actor backward down to dz (+ the regulariser's share and GMD's mask)."""
         s, a, b = self.spec, self.arena, self.buf
         B = self.B
         direct = self.grad_accum == 1  # pre_actor dW: plain stores when nothing accumulates
@@ -386,12 +399,50 @@ class StepEngine:
         if rowmask is not None:
             # z' = z * M  =>  dz = dz' * M (the regulariser part is already zero where z' == 0)
             self._mask_rows(b["dz"], rowmask)
+
+    # ------------------------------------------------------------------------------------------
+    def train_step(self, frames: torch.Tensor, gaze: torch.Tensor, actions: torch.Tensor):
+        """zero_grad + forward + backward.  With use_graph (and nothing that draws random numbers or
+        accumulates over micro-batches) the step is two CUDA-graph replays, split at the point where
+        the heads' gradients are complete so that the data-parallel bucket hooks still fire between
+        them: ~60 kernel launches become 2, which is what a 128-sample shard (1.6 ms of device time)
+        needs when eight ranks share the host's cores.  Graphs are keyed by the input buffers; the
+        first step at a new batch size runs eagerly (allocations), tracing (ops.trace) always does."""
+        graphable = (self.use_graph and self.grad_accum == 1 and ops._TRACE is None
+                     and not ((self.use_gmd and self.injected_A is None)
+                              or (self.use_igmd and self.injected_A_igmd is None)))
+        B = frames.shape[0]
+        if not graphable or self._warm_B != B:
+            self.zero_grad()
+            self.forward(frames, gaze, actions)
+            self.backward()
+            self._warm_B = B if B == self.B else 0
+            return self.buf["losses"]
+        key = (frames.data_ptr(), gaze.data_ptr(), actions.data_ptr(), tuple(frames.shape), tuple(actions.shape))
+        g = self._graphs.get(key)
+        if g is None:
+            if len(self._graphs) >= 8:
+                self._graphs.clear()
+            g = self._graphs[key] = self._capture(frames, gaze, actions)
+        g[0].replay()
         if self.on_heads_grads_ready is not None:
             self.on_heads_grads_ready()
-        self._encoder_bwd()
-        self._accum_count += 1
+        g[1].replay()
         if self.on_all_grads_ready is not None:
             self.on_all_grads_ready()
+        return self.buf["losses"]
+
+    def _capture(self, frames, gaze, actions):
+        torch.cuda.synchronize(self.device)
+        ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(ga, capture_error_mode="thread_local"):
+            self.zero_grad()
+            self.forward(frames, gaze, actions)
+            self._backward_heads()
+        with torch.cuda.graph(gb, pool=ga.pool(), capture_error_mode="thread_local"):
+            self._encoder_bwd()
+        self._keep = getattr(self, "_keep", []) + [(frames, gaze, actions)]   # the graphs hold raw pointers
+        return ga, gb
 
     def _encoder_bwd(self):
         """Backward of the encoder from b["dz"] (gradient w.r.t. z) to every encoder weight gradient."""

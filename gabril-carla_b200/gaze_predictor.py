@@ -25,6 +25,7 @@ class GazePredictorEngine(StepEngine):
                  grayscale: bool = True, frame_stack: int = 2, grad_accum: int = 1):
         super().__init__(spec, arena, gaze_pre, gaze_method="None", dp_method="None", grayscale=grayscale,
                          frame_stack=frame_stack, grad_accum=grad_accum)
+        self.use_graph = False   # StepEngine.train_step's graph split follows the policy's backward
 
     def _alloc(self, B):
         super()._alloc(B)

@@ -367,13 +367,29 @@ class BCTrainer(BaseTrainer):
         actions = batch["actions"].to(dev, non_blocking=True)
         if gaze.dim() == 4:
             gaze = gaze.reshape(gaze.shape[0], gaze.shape[1], -1)
-        losses = self.engine.forward(frames.contiguous(), gaze.contiguous().float(), actions.float())
+        if bool(self.cfg.training.get("cuda_graph", False)) and self.engine.grad_accum == 1:
+            # training.cuda_graph=true: the whole step (zero_grad + forward + backward) is replayed from
+            # CUDA graphs captured over static input buffers (StepEngine.train_step); the later
+            # loss.backward() then has nothing left to launch
+            st = getattr(self, "_static_in", None)
+            if st is None or st[0].shape != frames.shape or st[2].shape != actions.shape:
+                st = self._static_in = (torch.empty_like(frames, memory_format=torch.contiguous_format),
+                                        torch.empty_like(gaze, dtype=torch.float32, memory_format=torch.contiguous_format),
+                                        torch.empty_like(actions, dtype=torch.float32, memory_format=torch.contiguous_format))
+            st[0].copy_(frames); st[1].copy_(gaze); st[2].copy_(actions)
+            losses = self.engine.train_step(*st)
+            self._bwd_done = True
+        else:
+            losses = self.engine.forward(frames.contiguous(), gaze.contiguous().float(), actions.float())
         actor, reg, total = self.engine.losses_host()        # one D2H read (the reference does three)
         anchor = torch.zeros((), device=dev, requires_grad=True)
         loss = _StepLoss.apply(anchor, self, losses[2])
         return loss, int(frames.shape[0]), {"Loss/actor": actor, "Loss/reg": reg, "Loss/total": total}
 
     def _run_backward(self):
+        if getattr(self, "_bwd_done", False):
+            self._bwd_done = False
+            return
         self.engine.backward()
 
     def zero_grad(self):

@@ -159,3 +159,38 @@ def test_checkpoint_layout_roundtrip(tmp_path):
     arena2 = ParamArena(spec, DEV)
     arena2.load_reference({m: torch.load(tmp_path / f"ep1_{m}.pth", weights_only=True) for m in sds})
     assert torch.equal(arena2.p, arena.p)
+
+
+@pytest.mark.parametrize("dp", ["None", "GMD"])
+def test_graphed_train_step_matches_eager(dp):
+    """StepEngine.train_step by CUDA-graph replay == the eager zero_grad/forward/backward, including a
+    second replay on fresh input values in the same buffers and the hook order of the bucket reducer."""
+    batch = tuple(t.to(DEV) for t in make_batch(8, seed=3))
+    other = tuple(t.to(DEV) for t in make_batch(8, seed=4))
+    A = torch.rand(8, 760, generator=torch.Generator().manual_seed(1)).to(DEV)
+    out = {}
+    for mode in ("eager", "graph"):
+        spec, arena, eng = build(True, "Reg", dp, seed=2)
+        eng.use_graph = mode == "graph"
+        eng.injected_A = A
+        calls = []
+        eng.on_heads_grads_ready = lambda: calls.append("heads")
+        eng.on_all_grads_ready = lambda: calls.append("all")
+        bufs = tuple(t.clone() for t in batch)
+        res = []
+        for step in range(3):
+            if step == 2:                      # new values, same buffers: the graph must see them
+                for dst, src in zip(bufs, other):
+                    dst.copy_(src)
+            eng.train_step(*bufs)
+            torch.cuda.synchronize()
+            res.append((eng.buf["losses"].clone(), eng.buf["z"].clone(), arena.g.clone()))
+        assert calls == ["heads", "all"] * 3
+        if mode == "graph":
+            assert len(eng._graphs) == 1       # step 0 eager (allocation), steps 1-2 replays
+        out[mode] = res
+    for (l0, z0, g0), (l1, z1, g1) in zip(out["eager"], out["graph"]):
+        assert torch.equal(z0, z1)
+        assert torch.allclose(l0, l1, rtol=2e-4, atol=0)
+        assert (g0 - g1).abs().max().item() <= 1e-2 * g0.abs().max().item()
+    assert not torch.equal(out["graph"][1][1], out["graph"][2][1])

@@ -87,3 +87,30 @@ def test_unsupported_methods_raise(tmp_path):
         BCTrainer(make_cfg(tmp_path, "gaze.method=AGIL"))
     with pytest.raises(NotImplementedError):
         BCTrainer(make_cfg(tmp_path, "dropout.method=Oreo"))
+
+
+def test_cuda_graph_step_matches_eager_loop(tmp_path):
+    """training.cuda_graph=true: the reference-style loop driven by graph replays gives the eager
+    loop's losses (batch-dict feed, the HBM store materialised per batch) and the same weights."""
+    from gabril_carla_b200.trainer import BCTrainer
+    finals = {}
+    for mode in ("false", "true"):
+        tr = BCTrainer(make_cfg(tmp_path / mode, f"training.cuda_graph={mode}", "training.epochs=1"))
+        tr.fused_feed = False
+        tr.train_loader.fused = False
+        tr.set_train_mode()
+        losses = []
+        for batch in tr.train_loader:
+            tr.zero_grad()
+            loss, bs, m = tr.compute_loss(batch)
+            loss.backward()
+            tr.optimizer_step()
+            losses.append(m["Loss/total"])
+        torch.cuda.synchronize()
+        if mode == "true":
+            assert len(tr.engine._graphs) == 1
+        finals[mode] = (losses, tr.arena.p.clone())
+    for a, b in zip(finals["false"][0], finals["true"][0]):
+        assert abs(a - b) <= 2e-3 * abs(a), (finals["false"][0], finals["true"][0])
+    pa, pb = finals["false"][1], finals["true"][1]
+    assert (pa - pb).abs().max().item() <= 2e-3   # three Adam steps at lr 1e-4 apart at most
