@@ -207,6 +207,8 @@ def main_ours(args):
     eng = StepEngine(spec, arena, pre, gaze_method=args.gaze_method, dp_method=args.dp_method,
                      grayscale=gray, seed=1234 + rank)
     red = ddp.attach(eng, arena)
+    # CUDA-graph replays of the step: on by default (GABRIL_GRAPH=0 / --no-graph for eager launches)
+    eng.use_graph = os.environ.get("GABRIL_GRAPH", "1") != "0"
     if args.graph:
         eng.use_graph = True
     if args.no_graph:

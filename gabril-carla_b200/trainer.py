@@ -377,6 +377,7 @@ class BCTrainer(BaseTrainer):
                                         torch.empty_like(gaze, dtype=torch.float32, memory_format=torch.contiguous_format),
                                         torch.empty_like(actions, dtype=torch.float32, memory_format=torch.contiguous_format))
             st[0].copy_(frames); st[1].copy_(gaze); st[2].copy_(actions)
+            self.engine.use_graph = True
             losses = self.engine.train_step(*st)
             self._bwd_done = True
         else:
