@@ -239,9 +239,12 @@ def main_ours(args):
     for _ in range(max(3, args.warmup)):
         step(dev_batch)
     barrier()
+    # the traced step runs eagerly and serially (no side stream), so that every launch is timed alone
+    overlap, eng.overlap = eng.overlap, False
     with ops.trace() as tr:
         step(dev_batch)
     rows = tr.rows()
+    eng.overlap = overlap
     launches_per_step = len(rows) + (2 if args.dp_method == "GMD" else 0)
     tc_ms = sum(r[4] for r in rows if r[0] == "tc_gemm_kernel")
     tc_flop = sum(r[2] for r in rows if r[0] == "tc_gemm_kernel")
