@@ -93,6 +93,11 @@ class GradReducer:
         else:
             self.pending.append(dist.all_reduce(view, op=dist.ReduceOp.SUM, async_op=True))
 
+    def flush(self):
+        """Reduce every bucket now (gradients of an accumulation window that did not close)."""
+        for i in range(len(self.bounds) - 1):
+            self.reduce_bucket(i)
+
     def finish(self):
         """Order the optimizer after every outstanding bucket (stream-level wait, no host sync on CUDA)."""
         for w in self.pending:
@@ -110,13 +115,8 @@ def attach(engine, arena) -> GradReducer:
     split = arena.offset_of("enc.conv6.w")
     red = GradReducer(arena.g, [0, split, arena.n])
 
-    def heads_ready():
-        if engine._accum_count + 1 >= engine.grad_accum:  # only on the micro-step that closes the window
-            red.reduce_bucket(0)
-
-    def all_ready():
-        if engine._accum_count >= engine.grad_accum:
-            red.reduce_bucket(1)
-    engine.on_heads_grads_ready = heads_ready
-    engine.on_all_grads_ready = all_ready
+    # the engine calls the hooks only on the micro-step that closes an accumulation window (and on
+    # every CUDA-graph replayed step), so they carry no condition of their own
+    engine.on_heads_grads_ready = lambda: red.reduce_bucket(0)
+    engine.on_all_grads_ready = lambda: red.reduce_bucket(1)
     return red

@@ -367,12 +367,15 @@ class StepEngine:
     # ------------------------------------------------------------------------------------------
     def backward(self):
         """The rest of loss.backward(): every weight / bias gradient accumulated into arena.g."""
+        # the bucket hooks fire only on the micro-step that closes the accumulation window (DDP's
+        # no_sync semantics); the engine decides, the hooks themselves are unconditional
+        closing = self._accum_count + 1 >= self.grad_accum
         self._backward_heads()
-        if self.on_heads_grads_ready is not None:
+        if closing and self.on_heads_grads_ready is not None:
             self.on_heads_grads_ready()
         self._encoder_bwd()
         self._accum_count += 1
-        if self.on_all_grads_ready is not None:
+        if closing and self.on_all_grads_ready is not None:
             self.on_all_grads_ready()
 
     def _backward_heads(self):
@@ -424,10 +427,13 @@ class StepEngine:
             if len(self._graphs) >= 8:
                 self._graphs.clear()
             g = self._graphs[key] = self._capture(frames, gaze, actions)
+        # graphs exist only for grad_accum == 1: every replayed step closes its window, so both
+        # bucket hooks fire on every step (the captured zero_grad never runs on the host)
         g[0].replay()
         if self.on_heads_grads_ready is not None:
             self.on_heads_grads_ready()
         g[1].replay()
+        self._accum_count = 1
         if self.on_all_grads_ready is not None:
             self.on_all_grads_ready()
         return self.buf["losses"]

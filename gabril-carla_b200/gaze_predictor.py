@@ -110,11 +110,12 @@ class GazePredictorEngine(StepEngine):
         ops.colsum_bf16(dt, a.G("dec.conv1.b"))
         ops.conv_wgrad(dt, b["z"], a.G("dec.conv1.w"), 3, 3, 1, 1)
         ops.conv_dgrad(dt, a.WB("dec.conv1.w"), b["dz"], 3, 3, 1, 1)
-        if self.on_heads_grads_ready is not None:   # decoder gradients complete: first all-reduce bucket
+        closing = self._accum_count + 1 >= self.grad_accum    # hooks fire on the window-closing micro-step
+        if closing and self.on_heads_grads_ready is not None:   # decoder gradients complete: first all-reduce bucket
             self.on_heads_grads_ready()
         self._encoder_bwd()
         self._accum_count += 1
-        if self.on_all_grads_ready is not None:
+        if closing and self.on_all_grads_ready is not None:
             self.on_all_grads_ready()
 
     def output(self) -> torch.Tensor:

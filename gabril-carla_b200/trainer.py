@@ -213,6 +213,20 @@ class BaseTrainer:
     def zero_grad(self):
         raise NotImplementedError
 
+    def flush_grads(self):
+        """All-reduce gradients of an unfinished accumulation window (epoch tail)."""
+        red = getattr(self, "reducer", None)
+        if red is not None:
+            red.flush()
+
+    def poll_device_errors(self):
+        """Once per epoch: raise if a tcgen05 kernel reported an mbarrier-wait timeout (the kernels
+        only set a device flag), instead of checkpointing silently corrupt weights."""
+        if self.device.type == "cuda":
+            from . import _lib
+            torch.cuda.synchronize(self.device)
+            _lib.poll_error()
+
     # setup ----------------------------------------------------------------------------------
     def _set_seed(self, seed: int):
         import numpy as np
@@ -234,7 +248,9 @@ class BaseTrainer:
             nbytes = store.images.numel()
             store = store.to(self.device) if nbytes < 0.5 * free else store.pin()
         self.train_dataset = store
-        self.train_loader = ShardedBatches(store, int(c.data.batch_size), self.rank, self.world_size,
+        # micro-batch = data.batch_size // gradient_accumulation_steps (train/common/data.py:64)
+        accum = max(1, int(c.training.gradient_accumulation_steps))
+        self.train_loader = ShardedBatches(store, max(1, int(c.data.batch_size) // accum), self.rank, self.world_size,
                                            seed=int(c.training.seed), shuffle=True,
                                            fused=getattr(self, "fused_feed", False))
         self.train_sampler = self.train_loader
@@ -252,8 +268,9 @@ class BaseTrainer:
         c = self.cfg
         accum = max(1, int(c.training.gradient_accumulation_steps))
         for epoch in range(int(c.training.epochs)):
-            if self.is_distributed:
-                self.train_sampler.set_epoch(epoch)
+            # the reference reshuffles every epoch on one GPU too (DataLoader(shuffle=sampler is None),
+            # train/common/data.py:62-66), so the permutation seed advances unconditionally
+            self.train_sampler.set_epoch(epoch)
             self.set_train_mode()
             epoch_total, epoch_count, sums = 0.0, 0, {}
             self.zero_grad()
@@ -272,9 +289,15 @@ class BaseTrainer:
                 for k, v in metrics.items():
                     if k != "Loss/total":
                         sums[k] = sums.get(k, 0.0) + float(v) * bs
-            if (i + 1) % accum != 0:       # tail micro-steps of the epoch
+            # epoch tail (base_trainer.py:161-167): the reference steps when the SAMPLE count is not a
+            # multiple of accum; with no pending micro-step its gradients are None and the step is a
+            # no-op.  Pending micro-steps were not all-reduced yet (the bucket hooks fire only when a
+            # window closes), so flush the reducer first: DDP reduces on every backward.
+            if epoch_count % accum != 0 and (i + 1) % accum != 0:
+                self.flush_grads()
                 self.optimizer_step()
-                self.zero_grad()
+            self.zero_grad()
+            self.poll_device_errors()
             avg = epoch_total / max(1, epoch_count)
             if not self.batch_scheduler_update:
                 self.schedule.step()

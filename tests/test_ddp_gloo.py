@@ -45,6 +45,23 @@ def _worker(rank, world, port, q):
         expect = torch.arange(n, dtype=torch.float32) * sum(range(1, world + 1))
         assert torch.equal(g, expect)
         assert red.grad_scale == 1.0 / world and red.bytes_reduced == 4 * n
+        # --- flush(): every bucket at once (epoch-tail micro-steps of an unfinished accumulation window)
+        g3 = torch.ones(10) * (rank + 1)
+        red3 = ddp.GradReducer(g3, [0, 4, 10])
+        red3.flush()
+        red3.finish()
+        assert torch.all(g3 == float(sum(range(1, world + 1)))) and red3.bytes_reduced == 40
+        # --- attach(): the hooks are unconditional; the engine decides when a window closes
+        class _Eng:
+            on_heads_grads_ready = on_all_grads_ready = None
+        class _Arena:
+            g = torch.ones(8) * (rank + 1); n = 8
+            @staticmethod
+            def offset_of(name): return 3
+        e = _Eng()
+        red4 = ddp.attach(e, _Arena)
+        e.on_heads_grads_ready(); e.on_all_grads_ready(); red4.finish()
+        assert torch.all(_Arena.g == float(sum(range(1, world + 1)))) and red4.bytes_reduced == 32
         # --- shard semantics with the oracle's losses (checker only)
         from oracle import gabril_oracle as O
         from tests.synth import make_batch, make_weights

@@ -132,3 +132,79 @@ def test_arena_reference_layout_round_trip(cin):
     arena.load_reference({"actor": {"module._orig_mod." + k: v for k, v in w["actor"].items()}})
     with pytest.raises(RuntimeError):
         arena.load_reference({"actor": {"0.weight": w["actor"]["0.weight"]}})
+
+
+# ---- trainer loop (host logic on CPU with recording hooks) ----------------------------------------
+class _LoopProbe:
+    """BaseTrainer with the five hooks replaced by recorders: exercises the epoch / accumulation /
+    tail / scheduler logic of base_trainer.py:122-192 without a GPU."""
+
+    @staticmethod
+    def make(tmp_path, *extra):
+        from gabril_carla_b200.trainer import BaseTrainer
+
+        class Probe(BaseTrainer):
+            def build_models(self):
+                self.log = []
+
+                class Red:
+                    def __init__(s): s.flushed = 0
+                    def flush(s): s.flushed += 1
+                self.reducer = Red()
+
+            def set_train_mode(self): pass
+
+            def compute_loss(self, batch):
+                idx = batch["actions"].shape[0]
+                self.log.append(("loss", idx, batch["actions"][:, -1, 0].clone()))
+                t = torch.zeros((), requires_grad=True)
+                return t * 1.0, idx, {"Loss/total": 0.0}
+
+            def optimizer_step(self): self.log.append(("step", self.schedule.lr))
+            def zero_grad(self): pass
+            def save_for_epoch(self, epoch): self.log.append(("save", epoch))
+        cfg = C.load_config(["data.hdf5_path=synthetic:40", "data.img_height=18", "data.img_width=32",
+                             f"logging.checkpoint_dir={tmp_path}", f"logging.log_dir={tmp_path}",
+                             "training.device=cpu", *extra])
+        return Probe(cfg)
+
+
+def test_single_gpu_epochs_reshuffle(tmp_path):
+    tr = _LoopProbe.make(tmp_path, "data.batch_size=8", "training.epochs=2", "scheduler.type=none")
+    tr.train()
+    losses = [e for e in tr.log if e[0] == "loss"]
+    assert len(losses) == 10                                           # 5 batches x 2 epochs
+    ep0 = torch.cat([e[2] for e in losses[:5]]); ep1 = torch.cat([e[2] for e in losses[5:]])
+    assert not torch.equal(ep0, ep1) and torch.equal(ep0.sort().values, ep1.sort().values)
+    sb = tr.train_loader
+    sb.set_epoch(0); a = sb.indices().clone(); sb.set_epoch(1)
+    assert not torch.equal(a, sb.indices())
+
+
+def test_accumulation_micro_batch_tail_and_schedule(tmp_path):
+    # batch 8 with accum 2 -> micro-batch 4 (data.py:64): 40 samples = 10 micro-steps = 5 optimizer steps
+    tr = _LoopProbe.make(tmp_path, "data.batch_size=8", "training.gradient_accumulation_steps=2",
+                         "training.epochs=1", "scheduler.warmup_steps=2")
+    assert tr.train_loader.bs == 4 and len(tr.train_loader) == 10
+    tr.train()
+    steps = [e for e in tr.log if e[0] == "step"]
+    assert len(steps) == 5 and tr.reducer.flushed == 0
+    # cosine_warmup over total = len(loader) * epochs // accum = 5 optimizer steps, lr(0) = 0
+    ref = [5e-4 * O_factor(i, 2, 5, 1e-6, 5e-4) for i in range(5)]
+    assert [s[1] for s in steps] == pytest.approx(ref, rel=1e-12, abs=1e-18)
+    # 36 samples, micro-batch 4, accum 2 -> 9 micro-steps: the tail window holds one micro-step, but the
+    # reference steps only when the SAMPLE count is not a multiple of accum (36 % 2 == 0: no tail step)
+    tr = _LoopProbe.make(tmp_path, "data.hdf5_path=synthetic:36", "data.batch_size=8", "scheduler.type=none",
+                         "training.gradient_accumulation_steps=2", "training.epochs=1")
+    tr.train()
+    assert len([e for e in tr.log if e[0] == "step"]) == 4 and tr.reducer.flushed == 0
+    # 35 samples: 9 micro-steps (the last one of 3 samples), 35 % 2 != 0 -> flush the reducer, then step
+    tr = _LoopProbe.make(tmp_path, "data.hdf5_path=synthetic:35", "data.batch_size=8", "scheduler.type=none",
+                         "training.gradient_accumulation_steps=2", "training.epochs=1")
+    tr.train()
+    assert len([e for e in tr.log if e[0] == "step"]) == 5 and tr.reducer.flushed == 1
+
+
+def O_factor(step, warm, total, eta_min, base):
+    from oracle.gabril_oracle import cosine_warmup_factor
+    return cosine_warmup_factor(step, warm, total, eta_min, base)
