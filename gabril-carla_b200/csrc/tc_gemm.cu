@@ -41,7 +41,7 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
   int cls = 0;
   while (cls + 1 < p.n_classes && mi >= p.tiles_m[cls]) { mi -= p.tiles_m[cls]; ++cls; }
   r.cls = cls;
-  r.m0 = mi * 128;
+  r.m0 = mi * 128 * p.m_sub;
   int n_tile = y, tg = 0;
   if (p.kind == KIND_WGRAD) {
     n_tile = fdiv(y, p.fd_tap_groups);
@@ -60,7 +60,7 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
 // and the MMA issuer work on tile i+1 while the epilogue warps drain tile i.
 __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_constant__ Params p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 5];
+  __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 2 * kMaxAcc + 1];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -68,8 +68,8 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
   const uint32_t full0 = ptx::smem_u32(&bars[0]);
   const uint32_t empty0 = ptx::smem_u32(&bars[kMaxStages]);
   const uint32_t tfull0 = ptx::smem_u32(&bars[2 * kMaxStages]);
-  const uint32_t tempty0 = ptx::smem_u32(&bars[2 * kMaxStages + 2]);
-  const uint32_t wfull = ptx::smem_u32(&bars[2 * kMaxStages + 4]);  // resident weights landed
+  const uint32_t tempty0 = ptx::smem_u32(&bars[2 * kMaxStages + kMaxAcc]);
+  const uint32_t wfull = ptx::smem_u32(&bars[2 * kMaxStages + 2 * kMaxAcc]);  // resident weights landed
   const uint32_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
 
   if (threadIdx.x == 0) {
@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       ptx::mbar_init(full0 + 8 * s, 1);
       ptx::mbar_init(empty0 + 8 * s, 1);
     }
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < p.acc_bufs; ++b) {
       ptx::mbar_init(tfull0 + 8 * b, 1);
       ptx::mbar_init(tempty0 + 8 * b, 4);  // one arrival per epilogue warp
     }
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       bool ok = true;
       const int mma_k = p.mma_k, mma_groups = p.mma_groups, g_taps = p.g_taps;
       const uint32_t a_kstep = p.a_kstep, b_kstep = p.b_kstep, b_gstep = p.b_gstep, d_gstep = p.d_gstep;
-      const uint32_t a_gstep = p.swap_ab ? p.a_gstep : 0u;
+      const uint32_t a_gstep = p.a_gstep;  // swapped wgrad: per tap; FWD with m_sub = 2: per 128-row sub-tile
       const uint32_t a_hi32 = (uint32_t)(p.desc_a_hi >> 32), b_hi32 = (uint32_t)(p.desc_b_hi >> 32);
       const uint32_t stage16 = stage_bytes >> 4;
       const uint32_t a_lo_const = (uint32_t)p.desc_a_hi + (smem_base >> 4);
@@ -320,8 +320,8 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       for (int t = blockIdx.x; t < p.total_tiles && ok; t += gridDim.x, ++tcount) {
         const long long c0 = prof ? clock64() : 0;
         const Tile tl = decode_tile(p, t);
-        const int buf = (p.acc_bufs == 2) ? (tcount & 1) : 0;
-        const int use = (p.acc_bufs == 2) ? (tcount >> 1) : tcount;
+        const int buf = tcount & (p.acc_bufs - 1);
+        const int use = tcount >> p.acc_shift;
         // the epilogue must have drained this accumulator buffer
         if (!ptx::mbar_wait(tempty0 + 8 * buf, (use & 1) ^ 1)) { report_timeout(p, 105); break; }
         ptx::tc_fence_after();
@@ -424,9 +424,11 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tcount) {
       const Tile tl = decode_tile(p, t);
       const int cls = tl.cls, n0 = tl.n0;
-      const int buf = (p.acc_bufs == 2) ? (tcount & 1) : 0;
-      const int use = (p.acc_bufs == 2) ? (tcount >> 1) : tcount;
-      const int row = tl.m0 + q * 32 + lane;
+      const int buf = tcount & (p.acc_bufs - 1);
+      const int use = tcount >> p.acc_shift;
+      bool dead = false;
+      for (int sub = 0; sub < p.m_sub; ++sub) {   // 128-row sub-tiles of this tile (FWD regime: 1 or 2)
+      const int row = tl.m0 + sub * 128 + q * 32 + lane;
       bool row_ok = row < p.M_total[cls];
       long long orow = row;
       if (p.remap && row_ok) {
@@ -478,12 +480,14 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
           for (int i = 0; i < 4; ++i) rpre[i] = __ldg(r4 + i);
         }
       }
-      bool ok = ptx::mbar_wait(tfull0 + 8 * buf, use & 1);
-      if (!ok) report_timeout(p, 104);
-      ok = __all_sync(0xffffffffu, ok);
-      if (!ok) break;
-      ptx::tc_fence_after();
-      const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + buf * p.acc_stride;
+      if (sub == 0) {
+        bool ok = ptx::mbar_wait(tfull0 + 8 * buf, use & 1);
+        if (!ok) report_timeout(p, 104);
+        ok = __all_sync(0xffffffffu, ok);
+        if (!ok) { dead = true; break; }
+        ptx::tc_fence_after();
+      }
+      const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + buf * p.acc_stride + sub * p.block_n;
       // The chunk loop is deliberately NOT unrolled: one epilogue warp runs alone on its SM
       // sub-partition, so straight-line code is instruction-fetch bound (ncu: half of the epilogue's
       // stall samples were stall_no_inst with the loop unrolled four times); a rolled body of a few
@@ -613,6 +617,8 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
           }
         }
       }
+      }  // sub
+      if (dead) break;
       // accumulator buffer drained: hand it back to the MMA issuer
       ptx::tc_fence_before();
       __syncwarp();
@@ -663,6 +669,14 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     }
     return f;
   };
+  if (p.m_sub < 1) p.m_sub = 1;
+  if (p.acc_bufs < 1) p.acc_bufs = 1;
+  p.acc_shift = 0;
+  while ((1 << p.acc_shift) < p.acc_bufs) ++p.acc_shift;
+  if ((1 << p.acc_shift) != p.acc_bufs || p.acc_bufs > kMaxAcc || p.acc_bufs * p.acc_stride > 512) {
+    gabril_set_error("tc::launch: accumulator ring must be a power of two <= 8 buffers within 512 TMEM columns");
+    return GABRIL_ERR_BAD_SHAPE;
+  }
   p.fd_tiles_m = magic(p.tiles_m_total);
   p.fd_n_tiles = magic(p.n_tiles);
   p.fd_tap_groups = magic(p.tap_groups);

@@ -18,6 +18,7 @@
 namespace tc {
 
 constexpr int kMaxStages = 8;
+constexpr int kMaxAcc = 8;             // TMEM accumulator ring depth (power of two)
 constexpr int kProducers = 3;          // TMA-issuing warps
 constexpr int kMmaWarp = 0;            // TMEM owner + single-thread MMA issuer
 constexpr int kFirstEpilogueWarp = 1;  // 4 epilogue warps (TMEM lane quarter = warp % 4)
@@ -113,7 +114,12 @@ struct Params {
   uint32_t resident_off;    // offset of the resident weight region from the aligned smem base
   // persistent tile schedule: tile -> (m tile [classes concatenated], n tile, split)
   int tiles_m[4], tiles_m_total, n_tiles, n_splits, total_tiles;
-  int acc_bufs, acc_stride;  // TMEM accumulator ring (1 or 2 buffers of acc_stride columns)
+  int acc_bufs, acc_stride;  // TMEM accumulator ring (1, 2, 4 or 8 buffers of acc_stride columns)
+  int acc_shift;             // log2(acc_bufs), filled by launch()
+  // FWD regime: 128-row sub-tiles per CTA tile (1 or 2).  With 2, one A box of 256 rows and ONE weight
+  // tile feed two accumulators (columns [0, block_n) and [block_n, 2*block_n) of the buffer), which cuts
+  // the shared-memory fill per MAC by a quarter for 128-wide layers (the L2 -> SM path bounds them).
+  int m_sub;
   long long tap_stride;  // WGRAD: element (m, tap, n) at out + m*ldo + tap*tap_stride + n
   // magic numbers of the divisions above, filled by launch() from the fields they belong to
   FastDiv fd_tiles_m, fd_n_tiles, fd_tap_groups, fd_border_w, fd_border_h, fd_border_hw;

@@ -30,6 +30,15 @@ int g_num_sms = 148;
 int* g_err_flag = nullptr;  // device int, polled by gabril_poll_error
 
 int resolve_driver() {
+  // cuTensorMapEncode* are driver entry points and need a context current on the CALLING thread.  A
+  // host thread that never issued a runtime call (autograd's backward thread on device 0: torch skips
+  // cudaSetDevice when the device already is the thread's default) has none -> error 201; cudaFree(0)
+  // binds the primary context of the thread's current device.  Once per thread.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    cudaFree(0);
+    ctx_bound = true;
+  }
   if (g_encode_tiled && g_encode_im2col) return GABRIL_OK;
   cudaDriverEntryPointQueryResult qres;
   void* fn = nullptr;
@@ -179,7 +188,13 @@ void finalize_schedule(tc::Params& p, const int* m_tiles, int n_tiles_y, int spl
   p.n_splits = splits;
   p.total_tiles = p.tiles_m_total * n_tiles_y * splits;
   p.acc_stride = (int)pow2_cols((uint32_t)acc_cols);
-  p.acc_bufs = (p.acc_stride * 2 <= 512 / occ) ? 2 : 1;
+  // as many accumulator buffers as this CTA's share of TMEM holds (GABRIL_TC_ACC caps it): a tile's
+  // buffer is busy from its first MMA until the epilogue has drained it, and for short-K tiles that
+  // round trip (MMA latency + tcgen05.ld + stores) is several times the MMA issue time of the tile
+  static int acc_max = 0;
+  if (!acc_max) { const char* e = getenv("GABRIL_TC_ACC"); acc_max = e ? std::max(1, std::min(atoi(e), tc::kMaxAcc)) : tc::kMaxAcc; }
+  p.acc_bufs = 1;
+  while (p.acc_bufs * 2 <= acc_max && p.acc_stride * p.acc_bufs * 2 <= 512 / occ) p.acc_bufs *= 2;
   p.tmem_cols = (uint32_t)(p.acc_stride * p.acc_bufs);
 }
 
@@ -187,13 +202,23 @@ struct ActDims { int N, H, W, C; };
 
 // Common K-major / MN-major schedule helpers ---------------------------------------------------
 // FWD regime: A K-major with kc elements per k-block; B K-major or MN-major.
-void fwd_schedule(tc::Params& p, int kc, int block_n, int b_mn) {
+// 128-row sub-tiles per CTA tile for a FWD-regime launch over M rows (GABRIL_TC_MSUB: 1, 2; default 2):
+// two only when every SM still gets several tiles and the accumulators fit a single-occupancy CTA.
+int pick_m_sub(long long M, int block_n) {
+  static int want = 0;
+  if (!want) { const char* e = getenv("GABRIL_TC_MSUB"); want = (e && atoi(e) == 1) ? 1 : 2; }
+  if (want == 1 || block_n > 128) return 1;
+  return (M >= 256ll * 4 * g_num_sms) ? 2 : 1;
+}
+
+void fwd_schedule(tc::Params& p, int kc, int block_n, int b_mn, int m_sub = 1) {
   const int a_sw = kc * 2;  // 128 or 64 byte swizzle span
   p.kc = kc;
   p.block_n = block_n;
   p.n_acc = 1;
+  p.m_sub = m_sub;
   p.a_boxes = 1;
-  p.a_box_bytes = 128 * a_sw;
+  p.a_box_bytes = 128 * m_sub * a_sw;
   p.a_stage_bytes = round_up(p.a_box_bytes, 1024);
   p.desc_a_hi = desc_hi(16, 8 * a_sw, layout_type_for_bytes(a_sw));
   if (!b_mn) {
@@ -211,12 +236,14 @@ void fwd_schedule(tc::Params& p, int kc, int block_n, int b_mn) {
   }
   p.b_stage_bytes = round_up(p.b_boxes * p.b_box_bytes, 1024);
   p.mma_k = kc / 16;
-  p.mma_groups = 1;
-  p.g_taps = 1;
+  // one MMA group per sub-tile: A start advances by one 128-row tile, the accumulator by block_n columns
+  p.mma_groups = m_sub;
+  p.g_taps = m_sub > 1 ? 0 : 1;
+  p.a_gstep = m_sub > 1 ? (uint32_t)((128 * a_sw) >> 4) : 0u;
   p.a_kstep = 32 >> 4;
   p.b_kstep = (uint32_t)((b_mn ? 16 * (std::min(64, block_n) * 2) : 32) >> 4);
   p.b_gstep = 0;
-  p.d_gstep = 0;
+  p.d_gstep = m_sub > 1 ? (uint32_t)block_n : 0u;
   p.idesc = make_idesc(0, b_mn, 128, block_n);
 }
 
@@ -274,10 +301,11 @@ static int conv_fwd_impl(const void* x, const void* w, const float* bias, const 
   p.kind = tc::KIND_FWD;
   p.n_classes = 1;
   p.b_mn = 0;
-  fwd_schedule(p, kc, block_n, 0);
+  const long long M = (long long)N * OH * OW;
+  const int m_sub = (out_f32_atomic || splits > 1) ? 1 : pick_m_sub(M, block_n);
+  fwd_schedule(p, kc, block_n, 0, m_sub);
   const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
   p.a_im2col = plain ? 0 : 1;
-  const long long M = (long long)N * OH * OW;
   p.M_total[0] = (int)M;
   p.N_total = Cout;
   p.taps = R * S;
@@ -293,10 +321,10 @@ static int conv_fwd_impl(const void* x, const void* w, const float* bias, const 
   if (plain) {
     uint64_t dims[2] = {(uint64_t)Cin, (uint64_t)M};
     uint64_t strides[1] = {(uint64_t)Cin * 2};
-    uint32_t box[2] = {(uint32_t)kc, 128};
+    uint32_t box[2] = {(uint32_t)kc, (uint32_t)(128 * m_sub)};
     rc = tiled_map(&p.mapA[0], x, 2, dims, strides, box, kc * 2);
   } else {
-    rc = im2col_map(&p.mapA[0], x, N, H, W, Cin, -pad, -pad, pad - (S - 1), pad - (R - 1), kc, 128,
+    rc = im2col_map(&p.mapA[0], x, N, H, W, Cin, -pad, -pad, pad - (S - 1), pad - (R - 1), kc, 128 * m_sub,
                     stride);
   }
   if (rc) return rc;
@@ -308,10 +336,10 @@ static int conv_fwd_impl(const void* x, const void* w, const float* bias, const 
   p.relu = relu;
   p.err_flag = g_err_flag;
   size_t smem;
-  const int occ = occ_setting();
+  const int occ = m_sub > 1 ? 1 : occ_setting();
   pick_stages(p, &smem, occ);
-  const int mt[1] = {(int)((M + 127) / 128)};
-  finalize_schedule(p, mt, Cout / block_n, splits, block_n, occ);
+  const int mt[1] = {(int)((M + 128 * m_sub - 1) / (128 * m_sub))};
+  finalize_schedule(p, mt, Cout / block_n, splits, m_sub * block_n, occ);
   return tc::launch(p, g_num_sms * occ, smem, stream);
 }
 
@@ -339,7 +367,9 @@ static int conv_dgrad_impl(const void* dy, const void* w, const float* bias, int
   zero_params(p);
   p.kind = tc::KIND_FWD;
   p.b_mn = 1;
-  fwd_schedule(p, kc, block_n, 1);
+  const int m_sub = pick_m_sub((long long)N * H * W / (stride * stride), block_n);
+  const int tile_rows = 128 * m_sub;
+  fwd_schedule(p, kc, block_n, 1, m_sub);
   p.N_total = Cin;
   p.chunks_per_tap = Cout / kc;
   p.trav_stride_w = 1; p.trav_stride_h = 1;
@@ -358,11 +388,11 @@ static int conv_dgrad_impl(const void* dy, const void* w, const float* bias, int
     if (plain) {
       uint64_t dims[2] = {(uint64_t)Cout, (uint64_t)M};
       uint64_t strides[1] = {(uint64_t)Cout * 2};
-      uint32_t box[2] = {(uint32_t)kc, 128};
+      uint32_t box[2] = {(uint32_t)kc, (uint32_t)tile_rows};
       rc = tiled_map(&p.mapA[0], dy, 2, dims, strides, box, kc * 2);
     } else {
       rc = im2col_map(&p.mapA[0], dy, N, OH, OW, Cout, p.lower_w[0], p.lower_h[0], -pad, -pad, kc,
-                      128, 1);
+                      tile_rows, 1);
     }
     if (rc) return rc;
   } else if (stride == 2 && R == 4 && S == 4 && (pad == 1 || pad == 0)) {
@@ -388,7 +418,7 @@ static int conv_dgrad_impl(const void* dy, const void* w, const float* bias, int
       p.r_base[c] = bh + 2; p.s_base[c] = bw_ + 2;
       const int upper_w = p.lower_w[c] + Ws - OW, upper_h = p.lower_h[c] + Hs - OH;
       rc = im2col_map(&p.mapA[c], dy, N, OH, OW, Cout, p.lower_w[c], p.lower_h[c], upper_w,
-                      upper_h, kc, 128, 1);
+                      upper_h, kc, tile_rows, 1);
       if (rc) return rc;
     }
   } else {
@@ -404,11 +434,11 @@ static int conv_dgrad_impl(const void* dy, const void* w, const float* bias, int
   p.relu = relu;
   p.err_flag = g_err_flag;
   size_t smem;
-  const int occ = occ_setting();
+  const int occ = m_sub > 1 ? 1 : occ_setting();
   pick_stages(p, &smem, occ);
   int mt[4] = {0, 0, 0, 0};
-  for (int c = 0; c < p.n_classes; ++c) mt[c] = (p.M_total[c] + 127) / 128;
-  finalize_schedule(p, mt, Cin / block_n, 1, block_n, occ);
+  for (int c = 0; c < p.n_classes; ++c) mt[c] = (p.M_total[c] + tile_rows - 1) / tile_rows;
+  finalize_schedule(p, mt, Cin / block_n, 1, m_sub * block_n, occ);
   return tc::launch(p, g_num_sms * occ, smem, stream);
 }
 
@@ -853,9 +883,10 @@ int gabril_conv1_s2d_fwd_masked(const void* patches, const void* w, const float*
   zero_params(p);
   p.kind = tc::KIND_FWD;
   p.n_classes = 1;
-  fwd_schedule(p, kc, block_n, 0);
   const long long M = (long long)N * SH * SW * 4;
   if (M >= (1ll << 31)) return GABRIL_ERR_BAD_SHAPE;
+  const int m_sub = pick_m_sub(M, block_n);
+  fwd_schedule(p, kc, block_n, 0, m_sub);
   p.M_total[0] = (int)M;
   p.N_total = Cout;
   p.taps = 1; p.S = 1; p.S_w = 1; p.r_step = 1; p.s_step = 1;
@@ -866,7 +897,7 @@ int gabril_conv1_s2d_fwd_masked(const void* patches, const void* w, const float*
   p.trav_stride_w = 1; p.trav_stride_h = 1;
   uint64_t dims[2] = {(uint64_t)Kp, (uint64_t)M};
   uint64_t strides[1] = {(uint64_t)Kp * 2};
-  uint32_t box[2] = {(uint32_t)kc, 128};
+  uint32_t box[2] = {(uint32_t)kc, (uint32_t)(128 * m_sub)};
   rc = tiled_map(&p.mapA[0], patches, 2, dims, strides, box, kc * 2);
   if (rc) return rc;
   rc = weight_map(&p.mapB, w, Cout, 1, Kp, 0, kc, block_n);
@@ -877,10 +908,10 @@ int gabril_conv1_s2d_fwd_masked(const void* patches, const void* w, const float*
   p.border_h = SH; p.border_w = SW; p.s2d_H = img_h; p.s2d_W = img_w;
   p.err_flag = g_err_flag;
   size_t smem;
-  const int occ = occ_setting();
+  const int occ = m_sub > 1 ? 1 : occ_setting();
   pick_stages(p, &smem, occ);
-  const int mt[1] = {(int)((M + 127) / 128)};
-  finalize_schedule(p, mt, Cout / block_n, 1, block_n, occ);
+  const int mt[1] = {(int)((M + 128 * m_sub - 1) / (128 * m_sub))};
+  finalize_schedule(p, mt, Cout / block_n, 1, m_sub * block_n, occ);
   return tc::launch(p, g_num_sms * occ, smem, stream);
 }
 
