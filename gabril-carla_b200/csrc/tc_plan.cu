@@ -205,10 +205,10 @@ struct ActDims { int N, H, W, C; };
 // 128-row sub-tiles per CTA tile for a FWD-regime launch over M rows (GABRIL_TC_MSUB: 1, 2; default 2):
 // two only when every SM still gets several tiles and the accumulators fit a single-occupancy CTA.
 int pick_m_sub(long long M, int block_n) {
-  static int want = 0;
-  if (!want) { const char* e = getenv("GABRIL_TC_MSUB"); want = (e && atoi(e) == 1) ? 1 : 2; }
+  static int want = 0;   // 1: never, 2 (default): when the launch is large enough, 3: always (tests)
+  if (!want) { const char* e = getenv("GABRIL_TC_MSUB"); want = e ? std::max(1, std::min(atoi(e), 3)) : 2; }
   if (want == 1 || block_n > 128) return 1;
-  return (M >= 256ll * 4 * g_num_sms) ? 2 : 1;
+  return (want == 3 || M >= 256ll * 4 * g_num_sms) ? 2 : 1;
 }
 
 void fwd_schedule(tc::Params& p, int kc, int block_n, int b_mn, int m_sub = 1) {
