@@ -8,7 +8,9 @@ import os
 
 import torch
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libgabril_b200.so")
+# GABRIL_B200_LIB: another build of the same library (A/B experiments of kernel variants)
+_LIB_PATH = os.environ.get("GABRIL_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)),
+                                                              "libgabril_b200.so")
 _lib = None
 
 c_void_p = ctypes.c_void_p

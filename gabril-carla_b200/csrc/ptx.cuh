@@ -154,6 +154,60 @@ __device__ __forceinline__ void tmem_ld_wait() {
 }
 
 // ----------------------------------------------------------------------------
+// packed arithmetic and 32-byte global accesses for the epilogue
+// ----------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t pack2(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {   // two fp32 adds, one instruction
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// {lo, hi} fp32 pair -> packed bf16x2 (round to nearest even), lo in the low half
+__device__ __forceinline__ uint32_t cvt_bf16x2(uint64_t a) {
+  uint32_t r;
+  asm("{\n\t.reg .b32 lo, hi;\n\t"
+      "mov.b64 {lo, hi}, %1;\n\t"
+      "cvt.rn.bf16x2.f32 %0, hi, lo;\n\t}"
+      : "=r"(r) : "l"(a));
+  return r;
+}
+__device__ __forceinline__ uint32_t relu_bf16x2(uint32_t a) {
+  uint32_t r;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(0u));
+  return r;
+}
+// 0xffff in every half whose bf16 value is > 0
+__device__ __forceinline__ uint32_t gt0_mask_bf16x2(uint32_t a) {
+  uint32_t r;
+  asm("set.gt.u32.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(0u));
+  return r;
+}
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+  return r;
+}
+__device__ __forceinline__ void ldg256(const void* p, uint32_t* r) {   // p 32-byte aligned
+  asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "l"(p));
+}
+__device__ __forceinline__ void stg256(void* p, const uint32_t* r) {    // p 32-byte aligned
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(r[0]), "r"(r[1]),
+               "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+               : "memory");
+}
+
+// ----------------------------------------------------------------------------
 // misc
 // ----------------------------------------------------------------------------
 __device__ __forceinline__ void red_add_f32(float* addr, float v) {

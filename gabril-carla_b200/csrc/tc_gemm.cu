@@ -17,7 +17,7 @@ namespace tc {
 // ---------------------------------------------------------------------------------------------
 // device
 // ---------------------------------------------------------------------------------------------
-__device__ unsigned long long g_prof[8];
+__device__ unsigned long long g_prof[16];
 
 __device__ __forceinline__ void report_timeout(const Params& p, int code) {
   if (p.err_flag) atomicExch(p.err_flag, code);
@@ -62,6 +62,9 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 2 * kMaxAcc + 1];
   __shared__ uint32_t tmem_base_s;
+  // bias vector of the layer: read by every epilogue item; from global memory each read was an exposed
+  // L1 / L2 round trip on a warp that has nothing else to issue (ncu: a quarter of the epilogue's samples)
+  __shared__ __align__(16) float bias_s[kBiasSmem];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -79,7 +82,8 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
     }
     for (int b = 0; b < p.acc_bufs; ++b) {
       ptx::mbar_init(tfull0 + 8 * b, 1);
-      ptx::mbar_init(tempty0 + 8 * b, 4);  // one arrival per epilogue warp
+      // one arrival per epilogue warp that drains the buffer: every group, or only the tile's owner
+      ptx::mbar_init(tempty0 + 8 * b, p.epi_tile_split ? 4 : 4 * kEpiGroups);
     }
     ptx::mbar_init(wfull, 1);
     ptx::fence_mbar_init();
@@ -88,12 +92,22 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
     ptx::tmem_alloc(ptx::smem_u32(&tmem_base_s), p.tmem_cols);
     ptx::tmem_relinquish();
   }
+  const bool bias_sm = p.bias != nullptr && p.N_total <= kBiasSmem;
+  if (warp >= kFirstEpilogueWarp && bias_sm)
+    for (int i = threadIdx.x - 32 * kFirstEpilogueWarp; i < p.N_total; i += 128 * kEpiGroups) bias_s[i] = p.bias[i];
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+#if GABRIL_EPI_GROUPS == 2
+  // 384 threads, two CTAs per SM: the kernel starts at 80 registers per thread; the MMA / producer
+  // warpgroup (one active thread per warp, uniform-datapath code) gives most of its share to the two
+  // epilogue warpgroups: 4 x 48 + 8 x 104 = 1024 registers per lane slot = half the file per CTA.
+  if (warp < kFirstEpilogueWarp) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
+  else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
+#endif
 
-  if (warp >= kFirstProducerWarp) {
+  if (warp >= kFirstProducerWarp && warp < kFirstEpilogueWarp) {
     // ===================== TMA producers (one thread per warp) =====================
     // Issuing a tensor-map copy costs the issuing thread hundreds of cycles, so the smem stages
     // are dealt round-robin to kProducers threads in different warps.  A stage is always served
@@ -418,177 +432,169 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
       }
     }
   } else {
-    // ===================== epilogue (4 warps, one TMEM lane quarter each) =====================
+    // ===================== epilogue (kEpiGroups x 4 warps, one TMEM lane quarter each) =====================
+    // Work item = one 32-row x 32-column chunk of an accumulator.  The warp is alone (or nearly) on its
+    // scheduler, so its cost is INSTRUCTIONS (measured: ~2.5 clk per instruction): the bf16 path works
+    // on packed pairs (f32x2 adds, bf16x2 max / compare), gates through byte-permute sign replication
+    // and moves 32 bytes per access.  With two groups the items of a tile alternate between them (or
+    // whole tiles do, when a tile is a single item).
     const int q = warp & 3;
+    const int grp = (warp - kFirstEpilogueWarp) >> 2;
     int tcount = 0;
+    const bool eprof = (p.debug & 4) != 0 && warp == kFirstEpilogueWarp && lane == 0;
+    const bool dbg_nostore = (p.debug & 8) != 0, dbg_nobias = (p.debug & 16) != 0;
+    long long e_wait = 0, e_ld = 0, e_tile = 0, e_n = 0, e_pre = 0, e_math = 0, e_st = 0;
+    const int n_chunks = (p.block_n + 31) >> 5;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tcount) {
+      if (p.epi_tile_split && (tcount & (kEpiGroups - 1)) != grp) continue;   // the other group's tile
+      const long long ec0 = eprof ? clock64() : 0;
       const Tile tl = decode_tile(p, t);
       const int cls = tl.cls, n0 = tl.n0;
       const int buf = tcount & (p.acc_bufs - 1);
       const int use = tcount >> p.acc_shift;
       bool dead = false;
+      int item = 0;
       for (int sub = 0; sub < p.m_sub; ++sub) {   // 128-row sub-tiles of this tile (FWD regime: 1 or 2)
-      const int row = tl.m0 + sub * 128 + q * 32 + lane;
-      bool row_ok = row < p.M_total[cls];
-      long long orow = row;
-      if (p.remap && row_ok) {
-        const int hw = p.Hs[cls] * p.Ws[cls];
-        const int n = fdiv(row, p.fd_hw[cls]);
-        const int rem = row - n * hw;
-        const int jh = fdiv(rem, p.fd_ws[cls]);
-        const int jw = rem - jh * p.Ws[cls];
-        orow = ((long long)n * p.OHf + (jh * p.remap_sh + p.ah[cls])) * p.OWf +
-               (jw * p.remap_sw + p.aw[cls]);
-        if (p.valid_h > 0 && (jh >= p.valid_h || jw >= p.valid_w)) row_ok = false;
-      }
-      bool zero_row = false;
-      if (p.s2d_H > 0 && row_ok) {
-        const int qd = row & 3, sp = row >> 2;
-        const int spr = fdiv(sp, p.fd_border_w);
-        const int sw = sp - spr * p.border_w, sh = spr - fdiv(spr, p.fd_border_h) * p.border_h;
-        const int ih = 2 * sh + (qd >> 1) - 1, iw = 2 * sw + (qd & 1) - 1;
-        zero_row = ih < 0 || ih >= p.s2d_H || iw < 0 || iw >= p.s2d_W;
-      } else if (p.border_h > 0 && row_ok) {
-        const int hw = p.border_h * p.border_w;
-        const int rem = row - fdiv(row, p.fd_border_hw) * hw;
-        const int y = fdiv(rem, p.fd_border_w);
-        const int x = rem - y * p.border_w;
-        zero_row = (y == 0) || (y == p.border_h - 1) || (x == 0) || (x == p.border_w - 1);
-      }
-      const float rmask = (p.rowmask && row_ok) ? p.rowmask[orow] : 1.0f;
-      const long long off0 = orow * p.ldo + n0;
-      // gate / residual operands of the first 32 columns are fetched BEFORE waiting for the MMAs:
-      // their global-memory latency hides behind the main loop of this tile
-      uint4 gpre[4], rpre[4];
-      uint32_t gw[4] = {0u, 0u, 0u, 0u};
-      if (p.out_mode == OUT_BF16 && row_ok) {
-        if (p.gate_bits) {
-          // the sign words of every 32-column chunk of this row: 4 bytes per chunk instead of 64
+        const int row = tl.m0 + sub * 128 + q * 32 + lane;
+        bool row_ok = row < p.M_total[cls];
+        long long orow = row;
+        if (p.remap && row_ok) {
+          const int hw = p.Hs[cls] * p.Ws[cls];
+          const int n = fdiv(row, p.fd_hw[cls]);
+          const int rem = row - n * hw;
+          const int jh = fdiv(rem, p.fd_ws[cls]);
+          const int jw = rem - jh * p.Ws[cls];
+          orow = ((long long)n * p.OHf + (jh * p.remap_sh + p.ah[cls])) * p.OWf +
+                 (jw * p.remap_sw + p.aw[cls]);
+          if (p.valid_h > 0 && (jh >= p.valid_h || jw >= p.valid_w)) row_ok = false;
+        }
+        bool zero_row = false;
+        if (p.s2d_H > 0 && row_ok) {
+          const int qd = row & 3, sp = row >> 2;
+          const int spr = fdiv(sp, p.fd_border_w);
+          const int sw = sp - spr * p.border_w, sh = spr - fdiv(spr, p.fd_border_h) * p.border_h;
+          const int ih = 2 * sh + (qd >> 1) - 1, iw = 2 * sw + (qd & 1) - 1;
+          zero_row = ih < 0 || ih >= p.s2d_H || iw < 0 || iw >= p.s2d_W;
+        } else if (p.border_h > 0 && row_ok) {
+          const int hw = p.border_h * p.border_w;
+          const int rem = row - fdiv(row, p.fd_border_hw) * hw;
+          const int y = fdiv(rem, p.fd_border_w);
+          const int x = rem - y * p.border_w;
+          zero_row = (y == 0) || (y == p.border_h - 1) || (x == 0) || (x == p.border_w - 1);
+        }
+        const float rmask = (p.rowmask && row_ok) ? p.rowmask[orow] : 1.0f;
+        const uint64_t rmask2 = ptx::pack2(__float_as_uint(rmask), __float_as_uint(rmask));
+        const uint32_t keep = zero_row ? 0u : 0xffffffffu;
+        const long long off0 = orow * p.ldo + n0;
+        // the sign words of every 32-column chunk of this row: 4 bytes per chunk instead of 64
+        uint32_t gw[4] = {0u, 0u, 0u, 0u};
+        if (p.out_mode == OUT_BF16 && row_ok && p.gate_bits) {
           const uint32_t* gb = p.gate_bits + (off0 >> 5);
 #pragma unroll
           for (int ci = 0; ci < 4; ++ci)
             if (ci * 32 < p.block_n && n0 + ci * 32 < p.N_total) gw[ci] = __ldg(gb + ci);
         }
-        if (p.gate) {
-          const uint4* g4 = reinterpret_cast<const uint4*>(p.gate + off0);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) gpre[i] = __ldg(g4 + i);
+        if (sub == 0) {
+          const long long ec1 = eprof ? clock64() : 0;
+          if (eprof) e_pre += ec1 - ec0;
+          bool ok = ptx::mbar_wait(tfull0 + 8 * buf, use & 1);
+          if (eprof) e_wait += clock64() - ec1;
+          if (!ok) report_timeout(p, 104);
+          ok = __all_sync(0xffffffffu, ok);
+          if (!ok) { dead = true; break; }
+          ptx::tc_fence_after();
         }
-        if (p.resid) {
-          const uint4* r4 = reinterpret_cast<const uint4*>(p.resid + off0);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) rpre[i] = __ldg(r4 + i);
-        }
-      }
-      if (sub == 0) {
-        bool ok = ptx::mbar_wait(tfull0 + 8 * buf, use & 1);
-        if (!ok) report_timeout(p, 104);
-        ok = __all_sync(0xffffffffu, ok);
-        if (!ok) { dead = true; break; }
-        ptx::tc_fence_after();
-      }
-      const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + buf * p.acc_stride + sub * p.block_n;
-      // The chunk loop is deliberately NOT unrolled: one epilogue warp runs alone on its SM
-      // sub-partition, so straight-line code is instruction-fetch bound (ncu: half of the epilogue's
-      // stall samples were stall_no_inst with the loop unrolled four times); a rolled body of a few
-      // hundred instructions stays in the instruction cache across chunks and tiles.
-      const int n_chunks = (p.block_n + 31) >> 5;
-      for (int a = 0; a < tl.ntaps; ++a) {
+        const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + buf * p.acc_stride + sub * p.block_n;
+        // The item loop is deliberately NOT unrolled: a rolled body of ~150 instructions stays in the
+        // instruction cache across chunks and tiles.
+        for (int a = 0; a < tl.ntaps; ++a) {
 #pragma unroll 1
-        for (int ci = 0; ci < n_chunks; ++ci) {
-          const int c = ci * 32;
-          {
+          for (int ci = 0; ci < n_chunks; ++ci, ++item) {
+            if (!p.epi_tile_split && (item & (kEpiGroups - 1)) != grp) continue;   // the other group's chunk
+            const int c = ci * 32;
+            const int col0 = n0 + c;
+            const bool live = row_ok && col0 < p.N_total;
             uint32_t v[32];
-            if (p.out_mode == OUT_BF16 && row_ok && (ci > 0 || a > 0)) {  // chunk 0 was fetched before the wait
-              if (p.gate) {
-                const uint4* g4 = reinterpret_cast<const uint4*>(p.gate + off0 + c);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) gpre[i] = __ldg(g4 + i);
-              }
-              if (p.resid) {
-                const uint4* r4 = reinterpret_cast<const uint4*>(p.resid + off0 + c);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) rpre[i] = __ldg(r4 + i);
-              }
+            // residual / gate operands of this chunk: issued before the accumulator read so that their
+            // global-memory latency overlaps it
+            uint32_t rp[16], gp[16];
+            if (p.out_mode == OUT_BF16 && live) {
+              if (p.resid) { ptx::ldg256(p.resid + off0 + c, rp); ptx::ldg256(p.resid + off0 + c + 16, rp + 8); }
+              if (p.gate) { ptx::ldg256(p.gate + off0 + c, gp); ptx::ldg256(p.gate + off0 + c + 16, gp + 8); }
             }
             __syncwarp();
+            const long long ec2 = eprof ? clock64() : 0;
             ptx::tmem_ld_32x32(t_lane + a * p.block_n + c, v);
             ptx::tmem_ld_wait();
-            const int col0 = n0 + c;
-            if (row_ok && col0 < p.N_total) {
+            const long long ec3 = eprof ? clock64() : 0;
+            if (eprof) e_ld += ec3 - ec2;
+            if (!live) continue;
+            if (p.out_mode == OUT_BF16) {
+              const long long off = off0 + c;
+              uint64_t acc[16];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) acc[i] = ptx::pack2(v[2 * i], v[2 * i + 1]);
+              if (p.bias && !dbg_nobias) {
+                const float4* b4 = bias_sm ? reinterpret_cast<const float4*>(bias_s + col0)
+                                           : reinterpret_cast<const float4*>(p.bias + col0);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  const float4 b = b4[i];
+                  acc[2 * i] = ptx::add2(acc[2 * i], ptx::pack2(__float_as_uint(b.x), __float_as_uint(b.y)));
+                  acc[2 * i + 1] = ptx::add2(acc[2 * i + 1], ptx::pack2(__float_as_uint(b.z), __float_as_uint(b.w)));
+                }
+              }
+              if (p.resid) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i)   // bf16 -> fp32 is a shift / mask of the packed word
+                  acc[i] = ptx::add2(acc[i], ptx::pack2(rp[i] << 16, rp[i] & 0xffff0000u));
+              }
+              if (p.rowmask) {   // masks are >= 0, so scaling before the ReLU equals scaling after it
+#pragma unroll
+                for (int i = 0; i < 16; ++i) acc[i] = ptx::mul2(acc[i], rmask2);
+              }
+              uint32_t w[16];
+#pragma unroll
+              for (int i = 0; i < 16; ++i) w[i] = ptx::cvt_bf16x2(acc[i]);
+              if (p.relu) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) w[i] = ptx::relu_bf16x2(w[i]);
+              }
+              if (p.gate) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) w[i] &= ptx::gt0_mask_bf16x2(gp[i]);
+              }
+              if (p.gate_bits) {
+                // sign word layout: bit k = element 2k, bit 16 + k = element 2k + 1 (the two halves of
+                // packed word k).  Shift the pair of bits to the top of bytes 0/2 (k < 8) or 1/3, then one
+                // byte permute with sign replication expands them to a 0xffff / 0 mask per half.
+                const uint32_t g = ci == 0 ? gw[0] : ci == 1 ? gw[1] : ci == 2 ? gw[2] : gw[3];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) w[i] &= ptx::prmt(g << (7 - i), 0u, 0xaa88u);
+#pragma unroll
+                for (int i = 8; i < 16; ++i) w[i] &= ptx::prmt(g << (15 - i), 0u, 0xbb99u);
+              }
+              if (p.border_h > 0) {   // border / padding pixels of a zero-bordered output store exact zeros
+#pragma unroll
+                for (int i = 0; i < 16; ++i) w[i] &= keep;
+              }
+              bf16* o = reinterpret_cast<bf16*>(p.out) + off;
+              const long long ec4 = eprof ? clock64() : 0;
+              if (eprof) e_math += ec4 - ec3;
+              if (!dbg_nostore || w[15] == 0x12345678u) { ptx::stg256(o, w); ptx::stg256(o + 16, w + 8); }
+              if (p.bits_out) {
+                // ReLU's backward predicate on the stored bf16 value
+                uint32_t sign_word = 0u;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) sign_word |= ptx::gt0_mask_bf16x2(w[i]) & (0x00010001u << i);
+                p.bits_out[off >> 5] = sign_word;
+              }
+              if (eprof) e_st += clock64() - ec4;
+            } else {
               float f[32];
 #pragma unroll
               for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
-              if (p.out_mode == OUT_BF16) {
-                const long long off = off0 + c;
-                if (p.bias) {
-                  const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
-#pragma unroll
-                  for (int i = 0; i < 8; ++i) {
-                    const float4 b = __ldg(b4 + i);
-                    f[4 * i + 0] += b.x; f[4 * i + 1] += b.y; f[4 * i + 2] += b.z; f[4 * i + 3] += b.w;
-                  }
-                }
-                if (p.resid) {
-#pragma unroll
-                  for (int i = 0; i < 4; ++i) {
-                    const uint4 r = rpre[i];
-                    f[8 * i + 0] += bf16lo(r.x); f[8 * i + 1] += bf16hi(r.x);
-                    f[8 * i + 2] += bf16lo(r.y); f[8 * i + 3] += bf16hi(r.y);
-                    f[8 * i + 4] += bf16lo(r.z); f[8 * i + 5] += bf16hi(r.z);
-                    f[8 * i + 6] += bf16lo(r.w); f[8 * i + 7] += bf16hi(r.w);
-                  }
-                }
-                if (p.relu) {
-#pragma unroll
-                  for (int i = 0; i < 32; ++i) f[i] = fmaxf(f[i], 0.0f);
-                }
-                if (p.gate) {
-#pragma unroll
-                  for (int i = 0; i < 4; ++i) {
-                    const uint4 g = gpre[i];
-                    f[8 * i + 0] = bf16lo(g.x) > 0.f ? f[8 * i + 0] : 0.f;
-                    f[8 * i + 1] = bf16hi(g.x) > 0.f ? f[8 * i + 1] : 0.f;
-                    f[8 * i + 2] = bf16lo(g.y) > 0.f ? f[8 * i + 2] : 0.f;
-                    f[8 * i + 3] = bf16hi(g.y) > 0.f ? f[8 * i + 3] : 0.f;
-                    f[8 * i + 4] = bf16lo(g.z) > 0.f ? f[8 * i + 4] : 0.f;
-                    f[8 * i + 5] = bf16hi(g.z) > 0.f ? f[8 * i + 5] : 0.f;
-                    f[8 * i + 6] = bf16lo(g.w) > 0.f ? f[8 * i + 6] : 0.f;
-                    f[8 * i + 7] = bf16hi(g.w) > 0.f ? f[8 * i + 7] : 0.f;
-                  }
-                }
-                if (p.gate_bits) {
-                  const uint32_t g = ci == 0 ? gw[0] : ci == 1 ? gw[1] : ci == 2 ? gw[2] : gw[3];
-#pragma unroll
-                  for (int i = 0; i < 32; ++i) f[i] = ((g >> i) & 1u) ? f[i] : 0.f;
-                }
-                if (p.rowmask) {
-#pragma unroll
-                  for (int i = 0; i < 32; ++i) f[i] *= rmask;
-                }
-                if (zero_row) {
-#pragma unroll
-                  for (int i = 0; i < 32; ++i) f[i] = 0.f;
-                }
-                uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(p.out) + off);
-                uint32_t sign_word = 0u;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  uint4 o;
-                  o.x = pack_bf16x2(f[8 * i + 0], f[8 * i + 1]);
-                  o.y = pack_bf16x2(f[8 * i + 2], f[8 * i + 3]);
-                  o.z = pack_bf16x2(f[8 * i + 4], f[8 * i + 5]);
-                  o.w = pack_bf16x2(f[8 * i + 6], f[8 * i + 7]);
-                  o4[i] = o;
-                }
-                if (p.bits_out) {
-                  // ReLU's backward predicate on the fp32 value (the stored bf16 is > 0 exactly when
-                  // it is, except below bf16's smallest subnormal, where this follows the fp32 reference)
-#pragma unroll
-                  for (int i = 0; i < 32; ++i) sign_word |= (f[i] > 0.f) ? (1u << i) : 0u;
-                }
-                if (p.bits_out) p.bits_out[off >> 5] = sign_word;
-              } else if (p.swap_ab) {
+              if (p.swap_ab) {
                 // lane = cin (row), column = cout: 32 lanes write 32 consecutive cin of one cout
                 float* o = reinterpret_cast<float*>(p.out) + (long long)col0 * p.ldo +
                            (long long)(tl.tap0 + a) * p.tap_stride + orow;
@@ -616,13 +622,19 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
             }
           }
         }
-      }
       }  // sub
       if (dead) break;
+      if (eprof) { e_tile += clock64() - ec0; ++e_n; }
       // accumulator buffer drained: hand it back to the MMA issuer
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty0 + 8 * buf);
+    }
+    if (eprof) {
+      atomicAdd(&g_prof[8], (unsigned long long)e_pre); atomicAdd(&g_prof[9], (unsigned long long)e_wait);
+      atomicAdd(&g_prof[10], (unsigned long long)e_ld); atomicAdd(&g_prof[11], (unsigned long long)e_tile);
+      atomicAdd(&g_prof[12], (unsigned long long)e_n); atomicAdd(&g_prof[13], (unsigned long long)e_math);
+      atomicAdd(&g_prof[14], (unsigned long long)e_st);
     }
   }
 
@@ -677,6 +689,13 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     gabril_set_error("tc::launch: accumulator ring must be a power of two <= 8 buffers within 512 TMEM columns");
     return GABRIL_ERR_BAD_SHAPE;
   }
+  // a tile that is a single 32-column item cannot be shared by two epilogue groups: they alternate tiles
+  p.epi_tile_split = (kEpiGroups > 1 && p.kind == KIND_FWD && p.m_sub == 1 && p.block_n <= 32 && p.acc_bufs >= 2) ? 1 : 0;
+  if (p.out_mode == OUT_BF16 &&
+      ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.resid) | reinterpret_cast<uintptr_t>(p.gate)) & 31)) {
+    gabril_set_error("tc::launch: bf16 output / residual / gate tensors must be 32-byte aligned");
+    return GABRIL_ERR_BAD_SHAPE;
+  }
   p.fd_tiles_m = magic(p.tiles_m_total);
   p.fd_n_tiles = magic(p.n_tiles);
   p.fd_tap_groups = magic(p.tap_groups);
@@ -692,7 +711,7 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(g_attr_once, [] {
     attr_err = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    227 * 1024 - 256);
+                                    227 * 1024 - 2048);  // static smem: barriers, TMEM base, bias vector (< 2 KB)
   });
   if (attr_err != cudaSuccess) return gabril_set_cuda_error(attr_err);
   if (p.total_tiles <= 0) return GABRIL_OK;
@@ -705,8 +724,8 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
 
 }  // namespace tc
 
-extern "C" int gabril_tc_prof(unsigned long long* out8, int reset) {
-  if (cudaMemcpyFromSymbol(out8, tc::g_prof, 8 * sizeof(unsigned long long)) != cudaSuccess) return -1;
-  if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(tc::g_prof, z, sizeof(z)); }
+extern "C" int gabril_tc_prof(unsigned long long* out16, int reset) {
+  if (cudaMemcpyFromSymbol(out16, tc::g_prof, 16 * sizeof(unsigned long long)) != cudaSuccess) return -1;
+  if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(tc::g_prof, z, sizeof(z)); }
   return 0;
 }

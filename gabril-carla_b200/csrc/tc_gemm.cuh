@@ -7,8 +7,8 @@
 //              (forward conv, dgrad as a conv over dY, linear)     B K-major or MN-major weight tile
 //   KIND_WGRAD D[Cout, Cin]    = dY[pixels, Cout]^T * X[pixels, Cin]   both MN-major, contraction
 //              (one accumulator per filter tap, several per CTA)       over pixels, split over CTAs
-// Warp roles (256 threads): warp0 = TMEM owner + single-thread MMA issuer, warps1..4 = epilogue,
-// warps5..7 = TMA producers (tcgen05.ld -> fused bias/residual/ReLU/gate/mask -> global).
+// Warp roles: warp0 = TMEM owner + single-thread MMA issuer, warps1..3 = TMA producers, warps 4.. =
+// epilogue (tcgen05.ld -> fused bias/residual/ReLU/gate/mask -> global), one or two groups of four.
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -19,11 +19,16 @@ namespace tc {
 
 constexpr int kMaxStages = 8;
 constexpr int kMaxAcc = 8;             // TMEM accumulator ring depth (power of two)
+constexpr int kBiasSmem = 256;         // bias vectors up to this many columns are staged in shared memory
 constexpr int kProducers = 3;          // TMA-issuing warps
 constexpr int kMmaWarp = 0;            // TMEM owner + single-thread MMA issuer
-constexpr int kFirstEpilogueWarp = 1;  // 4 epilogue warps (TMEM lane quarter = warp % 4)
-constexpr int kFirstProducerWarp = 5;
-constexpr int kThreads = 32 * (kFirstProducerWarp + kProducers);
+constexpr int kFirstProducerWarp = 1;  // warps 1..3
+#ifndef GABRIL_EPI_GROUPS
+#define GABRIL_EPI_GROUPS 1
+#endif
+constexpr int kEpiGroups = GABRIL_EPI_GROUPS;   // 1 or 2 groups of 4 epilogue warps (TMEM lane quarter = warp % 4)
+constexpr int kFirstEpilogueWarp = 4;  // warps 4..7 (group 0), 8..11 (group 1): aligned warpgroups
+constexpr int kThreads = 32 * (kFirstEpilogueWarp + 4 * kEpiGroups);
 
 enum Kind { KIND_FWD = 0, KIND_WGRAD = 1 };
 enum OutMode { OUT_BF16 = 0, OUT_F32_STORE = 1, OUT_F32_ATOMIC = 2 };
@@ -120,6 +125,8 @@ struct Params {
   // tile feed two accumulators (columns [0, block_n) and [block_n, 2*block_n) of the buffer), which cuts
   // the shared-memory fill per MAC by a quarter for 128-wide layers (the L2 -> SM path bounds them).
   int m_sub;
+  // epilogue groups split the work by whole tiles (a tile is a single 32-column item) instead of by items
+  int epi_tile_split;
   long long tap_stride;  // WGRAD: element (m, tap, n) at out + m*ldo + tap*tap_stride + n
   // magic numbers of the divisions above, filled by launch() from the fields they belong to
   FastDiv fd_tiles_m, fd_n_tiles, fd_tap_groups, fd_border_w, fd_border_h, fd_border_hw;

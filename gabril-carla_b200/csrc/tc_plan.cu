@@ -204,11 +204,15 @@ struct ActDims { int N, H, W, C; };
 // FWD regime: A K-major with kc elements per k-block; B K-major or MN-major.
 // 128-row sub-tiles per CTA tile for a FWD-regime launch over M rows (GABRIL_TC_MSUB: 1, 2; default 2):
 // two only when every SM still gets several tiles and the accumulators fit a single-occupancy CTA.
-int pick_m_sub(long long M, int block_n) {
-  static int want = 0;   // 1: never, 2 (default): when the launch is large enough, 3: always (tests)
+// Measured at batch 1024 (tools/exp_tiles.sh): 256-row tiles pay off only where the k loop is long and
+// the tile wide (conv_5 fwd / dgrad: K = 3200, N = 128: 0.54 -> 0.48 ms); shorter or narrower layers lose
+// more to the single-occupancy CTA (no second CTA to hide the epilogue) than the smaller feed saves.
+int pick_m_sub(long long M, int block_n, int kb_total) {
+  static int want = 0;   // 1: never, 2 (default): where it pays, 3: always (tests)
   if (!want) { const char* e = getenv("GABRIL_TC_MSUB"); want = e ? std::max(1, std::min(atoi(e), 3)) : 2; }
   if (want == 1 || block_n > 128) return 1;
-  return (want == 3 || M >= 256ll * 4 * g_num_sms) ? 2 : 1;
+  if (want == 3) return 2;
+  return (block_n == 128 && kb_total >= 40 && M >= 256ll * 4 * g_num_sms) ? 2 : 1;
 }
 
 void fwd_schedule(tc::Params& p, int kc, int block_n, int b_mn, int m_sub = 1) {
@@ -302,7 +306,7 @@ static int conv_fwd_impl(const void* x, const void* w, const float* bias, const 
   p.n_classes = 1;
   p.b_mn = 0;
   const long long M = (long long)N * OH * OW;
-  const int m_sub = (out_f32_atomic || splits > 1) ? 1 : pick_m_sub(M, block_n);
+  const int m_sub = (out_f32_atomic || splits > 1) ? 1 : pick_m_sub(M, block_n, R * S * (Cin / kc));
   fwd_schedule(p, kc, block_n, 0, m_sub);
   const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
   p.a_im2col = plain ? 0 : 1;
@@ -367,7 +371,8 @@ static int conv_dgrad_impl(const void* dy, const void* w, const float* bias, int
   zero_params(p);
   p.kind = tc::KIND_FWD;
   p.b_mn = 1;
-  const int m_sub = pick_m_sub((long long)N * H * W / (stride * stride), block_n);
+  const int m_sub = pick_m_sub((long long)N * H * W / (stride * stride), block_n,
+                               (stride == 1 ? R * S : 4) * (Cout / kc));
   const int tile_rows = 128 * m_sub;
   fwd_schedule(p, kc, block_n, 1, m_sub);
   p.N_total = Cin;
@@ -885,7 +890,7 @@ int gabril_conv1_s2d_fwd_masked(const void* patches, const void* w, const float*
   p.n_classes = 1;
   const long long M = (long long)N * SH * SW * 4;
   if (M >= (1ll << 31)) return GABRIL_ERR_BAD_SHAPE;
-  const int m_sub = pick_m_sub(M, block_n);
+  const int m_sub = pick_m_sub(M, block_n, Kp / kc);
   fwd_schedule(p, kc, block_n, 0, m_sub);
   p.M_total[0] = (int)M;
   p.N_total = Cout;

@@ -51,8 +51,9 @@ int gabril_poll_error(void);
 /* Launch attribute of the NEXT conv / linear call below made by the calling host thread (consumed
  * by it; the call must produce a bf16 output whose channel count is a multiple of 32).
  * Packed ReLU sign bits: one uint32 word per 32 consecutive channels of one pixel, word index =
- * (element offset into the output tensor) / 32, bit i = (element i of the chunk, as stored in
- * bf16, > 0) — the predicate of nn.ReLU's backward (linear_models.py:78-102,191-207 ReLU calls).
+ * (element offset into the output tensor) / 32; bit j (j < 16) = (element 2j of the chunk, as stored
+ * in bf16, > 0), bit 16 + j = (element 2j + 1 > 0) — i.e. the low / high halves of the chunk's sixteen
+ * packed bf16x2 words — the predicate of nn.ReLU's backward (linear_models.py:78-102,191-207).
  *   sign_bits_out: the call also writes the sign words of everything it stores (forward);
  *   gate_bits:     the call reads these words instead of its `gate` tensor (backward): 4 bytes of
  *                  HBM traffic per 32 channels instead of 64.

@@ -36,9 +36,12 @@ def rel(a, b):
 
 
 def pack_signs(t):
-    """Host restatement of the sign words: word k covers elements 32k .. 32k+31, bit i = (element > 0)."""
+    """Host restatement of the sign words (include/gabril_b200.h): word k covers elements 32k .. 32k+31,
+    bit j (j < 16) = (element 2j > 0), bit 16 + j = (element 2j + 1 > 0) -- the low / high halves of the
+    sixteen packed bf16x2 words the epilogue holds."""
     pos = (t.float().reshape(-1, 32) > 0).to(torch.int64)
-    words = (pos << torch.arange(32, dtype=torch.int64)).sum(1)
+    e = torch.arange(32, dtype=torch.int64)
+    words = (pos << ((e % 2) * 16 + e // 2)).sum(1)
     return torch.where(words >= 2 ** 31, words - 2 ** 32, words).to(torch.int32)
 
 

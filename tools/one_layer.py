@@ -21,18 +21,25 @@ y = torch.empty(N, OH, OW, Cout, device=dev, dtype=bf)
 dy = (torch.randn(N, OH, OW, Cout, device=dev) * 0.1).to(bf)
 dx = torch.empty_like(x)
 dw = torch.zeros(Cout, R * R, Cin, device=dev)
+bias = torch.randn(Cout, device=dev)
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
 for _ in range(reps):
     if what == "fwd":
-        ops.conv_fwd(x, w, None, y, R, R, stride, pad, relu=True)
+        ops.conv_fwd(x, w, bias, y, R, R, stride, pad, relu=True)
     elif what == "dgrad":
         ops.conv_dgrad(dy, w, dx, R, R, stride, pad, gate=x)
     else:
         ops.conv_wgrad(dy, x, dw, R, R, stride, pad)
+e1.record()
 torch.cuda.synchronize()
-print("ok", name, what, N, "err flag", _lib.load().gabril_poll_error())
+print("ok", name, what, N, f"{e0.elapsed_time(e1) / reps:.3f} ms/launch (first launch included)", "TC_DEBUG", os.environ.get("GABRIL_TC_DEBUG"),
+      "err flag", _lib.load().gabril_poll_error())
 import ctypes
-buf = (ctypes.c_ulonglong * 8)()
+buf = (ctypes.c_ulonglong * 16)()
 if hasattr(_lib.load(), "gabril_tc_prof"):
     _lib.load().gabril_tc_prof(buf, 1)
     n = max(1, buf[4])
+    m = max(1, buf[12])
+    print(f"epilogue warp 1 per tile: pre {buf[8]/m:.0f} wait_tfull {buf[9]/m:.0f} tmem_ld {buf[10]/m:.0f} math {buf[13]/m:.0f} stores {buf[14]/m:.0f} total {buf[11]/m:.0f} clk; tiles {buf[12]}")
     print(f"MMA thread per k-block: wait_full {buf[0]/n:.0f} issue {buf[1]/n:.0f} commit {buf[2]/n:.0f} clk; per-tile pre {buf[3]/max(1,n)*1.0:.1f}/kb; kblocks {buf[4]}")
