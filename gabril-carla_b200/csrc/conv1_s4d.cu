@@ -1,0 +1,197 @@
+// conv_1 (k4 / s2 / p1 over the raw frame stack) without a patch matrix.
+//
+// Reference ops replaced: _gather_last_s_frames + _format_obs_image
+// (vlm_gaze/data_utils/data_loader_robomimic.py:144-157,179-202) feeding Encoder._conv_1 + ReLU
+// (vlm_gaze/models/linear_models.py:141-146,191-193).
+//
+// The frames are written ONCE as a 4x4 space-to-depth bf16 image X4 on the SAME [SH, SW] grid as
+// conv_1's space-to-depth output a1s (SH = H/4 + 2, SW = W/4 + 2 for 180x320: 47 x 82):
+//     X4[n, u, v, (a*4 + b)*C0 + ci] = obs[n, ci, 4(u-1) + a, 4(v-1) + b]        (0 outside the image)
+// Output super-pixel (sh, sw) = the four conv_1 pixels (2sh+qh-1, 2sw+qw-1) reads input rows
+// 4sh-3 .. 4sh+2, i.e. cells (sh + r', sw + s'), r', s' in {0, 1}: conv_1 + space-to-depth is a 2x2
+// stride-1 convolution over X4 with 4*C1 output channels (qh, qw, co) whose weights
+//     W4[(qh,qw,co)][r'][(s', a, b, ci)] = W1[co, ci, 4r' + a - 2qh - 1, 4s' + b - 2qw - 1]   (0 if out of 0..3)
+// are a 4x zero-inflated copy of conv_1's (tensor work is 0.6 % of the step; HBM bytes are what this
+// layer costs).  Cells of row u = 0 / column v = 0 are all zero, so the flat (wrapping) index q + SW + 1
+// needs no extra border, and two horizontally adjacent cells are ONE row of an overlapping-row tensor
+// map (row pitch = one cell), which makes (s', a, b, ci) a single 64-channel (gray) contraction chunk.
+// Traffic per sample (gray, stack 2): 345.6 KB u8 read + 247 KB written, instead of the 864 KB patch
+// matrix written once and read by conv_1 forward and conv_1 wgrad.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ int frame_index(int s, int S, int center, int L) {
+  return min(max(center - S + 1 + s, 0), L - 1);   // data_loader_robomimic.py:151-152
+}
+__device__ __forceinline__ float to_gray(float r, float g, float b) {
+  // ((0.299 R) + (0.587 G)) + (0.114 B), every op rounded separately (data_loader_robomimic.py:192-193)
+  return __fadd_rn(__fadd_rn(__fmul_rn(0.299f, r), __fmul_rn(0.587f, g)), __fmul_rn(0.114f, b));
+}
+
+// One thread = one cell row (u, v, a): 4 pixels x S frames -> 4*C0 consecutive bf16 of the cell.
+template <int S_, bool GRAY>
+__global__ void __launch_bounds__(256)
+obs_s4d_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__ widx,
+               bf16* __restrict__ out, long long cells, int L, int center, int H, int W, int SH, int SW,
+               int Cp) {
+  constexpr int CP = GRAY ? 1 : 3;
+  constexpr int C0 = S_ * CP;
+  __shared__ float lut[256];   // u8 / 255.0f, correctly rounded (same bits as the division)
+  lut[threadIdx.x & 255] = __fdiv_rn((float)(threadIdx.x & 255), 255.0f);
+  __syncthreads();
+  const long long total = cells * 4;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int a = (int)(idx & 3);
+    const long long cell = idx >> 2;
+    const int v = (int)(cell % SW);
+    const long long t = cell / SW;
+    const int u = (int)(t % SH);
+    const long long b = t / SH;
+    const int y = 4 * (u - 1) + a, x0 = 4 * (v - 1);
+    const bool ok = u >= 1 && v >= 1 && y < H && x0 < W;
+    float px[4][C0];
+#pragma unroll
+    for (int fs = 0; fs < S_; ++fs) {
+      uint32_t wv[3] = {0u, 0u, 0u};
+      if (ok) {
+        // batch layout [B, L, H, W, 3], or (widx != NULL) a frame store [N, H, W, 3] addressed through
+        // the window table widx[b][fs] of gabril_store_windows
+        const long long fr = widx ? __ldg(widx + b * S_ + fs) : b * L + frame_index(fs, S_, center, L);
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(frames + ((fr * H + y) * (long long)W + x0) * 3);
+        wv[0] = __ldg(src); wv[1] = __ldg(src + 1); wv[2] = __ldg(src + 2);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float ch[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const int byte = 3 * k + c;
+          ch[c] = lut[(wv[byte >> 2] >> (8 * (byte & 3))) & 0xffu];
+        }
+        if (GRAY) {
+          px[k][fs] = ok ? to_gray(ch[0], ch[1], ch[2]) : 0.f;
+        } else {
+          px[k][fs * 3 + 0] = ok ? ch[0] : 0.f;
+          px[k][fs * 3 + 1] = ok ? ch[1] : 0.f;
+          px[k][fs * 3 + 2] = ok ? ch[2] : 0.f;
+        }
+      }
+    }
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(out + cell * Cp + a * (4 * C0));
+    const float* pf = &px[0][0];
+    if ((C0 & 1) == 0) {   // 4*C0 bf16 = C0/2 16-byte stores
+      uint4* d4 = reinterpret_cast<uint4*>(d32);
+#pragma unroll
+      for (int k = 0; k < C0 / 2; ++k)
+        d4[k] = make_uint4(pack_bf16x2(pf[8 * k], pf[8 * k + 1]), pack_bf16x2(pf[8 * k + 2], pf[8 * k + 3]),
+                           pack_bf16x2(pf[8 * k + 4], pf[8 * k + 5]), pack_bf16x2(pf[8 * k + 6], pf[8 * k + 7]));
+    } else {
+#pragma unroll
+      for (int k = 0; k < 2 * C0; ++k) d32[k] = pack_bf16x2(pf[2 * k], pf[2 * k + 1]);
+    }
+    if (a == 3)   // channel padding of the cell (RGB: 96 -> 128)
+      for (int k = 16 * C0; k < Cp; k += 2) *reinterpret_cast<uint32_t*>(out + cell * Cp + k) = 0u;
+  }
+}
+
+// W4[(q, co)][r'][(s', a, b, ci)] (bf16) from the fp32 master W1[co][(kh*4 + kw)*C0 + ci] (row pitch K1p).
+__global__ void conv1_expand_kernel(const float* __restrict__ w1, bf16* __restrict__ w4, int C1, int C0,
+                                    int K1p, int Cp) {
+  const int total = 4 * C1 * 2 * 2 * Cp;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int kk = i % (2 * Cp);
+    const int rp = (i / (2 * Cp)) & 1;
+    const int m = i / (4 * Cp);
+    const int q = m / C1, co = m - q * C1;
+    const int qh = q >> 1, qw = q & 1;
+    const int sp = kk / Cp, k = kk - sp * Cp;
+    float val = 0.f;
+    if (k < 16 * C0) {
+      const int ab = k / C0, ci = k - ab * C0;
+      const int kh = 4 * rp + (ab >> 2) - 2 * qh - 1, kw = 4 * sp + (ab & 3) - 2 * qw - 1;
+      if (kh >= 0 && kh < 4 && kw >= 0 && kw < 4) val = w1[(long long)co * K1p + (kh * 4 + kw) * C0 + ci];
+    }
+    w4[i] = __float2bfloat16(val);
+  }
+}
+
+// dW1[co][(kh*4 + kw)*C0 + ci] += sum over the four quadrants of dW4 (fixed order: deterministic)
+__global__ void conv1_fold_kernel(const float* __restrict__ dw4, float* __restrict__ dw1, int C1, int C0,
+                                  int K1p, int Cp) {
+  const int total = C1 * 16 * C0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int ci = i % C0;
+    const int tap = (i / C0) & 15;
+    const int co = i / (16 * C0);
+    const int kh = tap >> 2, kw = tap & 3;
+    float acc = 0.f;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int eh = kh + 2 * (q >> 1) + 1, ew = kw + 2 * (q & 1) + 1;
+      const int rp = eh >> 2, a = eh & 3, sp = ew >> 2, b = ew & 3;
+      acc += dw4[((long long)(q * C1 + co) * 2 + rp) * (2 * Cp) + sp * Cp + (a * 4 + b) * C0 + ci];
+    }
+    dw1[(long long)co * K1p + tap * C0 + ci] += acc;
+  }
+}
+
+int obs_s4d_impl(const uint8_t* frames, const long long* widx, void* x4, int B, int L, int S, int center, int H,
+                 int W, int grayscale, int Cp, int SH, int SW, cudaStream_t stream) {
+  const int C0 = S * (grayscale ? 1 : 3);
+  if (!frames || !x4 || B <= 0 || S < 1 || S > 4 || (W & 3) || (H & 3) || SH != H / 4 + 2 || SW != W / 4 + 2 ||
+      Cp < 16 * C0 || (Cp & 7))
+    return GABRIL_ERR_BAD_SHAPE;
+  const long long cells = (long long)B * SH * SW;
+  const int grid = (int)std::min<long long>((cells * 4 + 255) / 256, 148 * 16);
+#define LAUNCH_S4D(SS, GG)                                                                              \
+  obs_s4d_kernel<SS, GG><<<grid, 256, 0, stream>>>(frames, widx, (bf16*)x4, cells, L, center, H, W, SH, \
+                                                   SW, Cp)
+  if (grayscale) {
+    switch (S) { case 1: LAUNCH_S4D(1, true); break; case 2: LAUNCH_S4D(2, true); break;
+                 case 3: LAUNCH_S4D(3, true); break; default: LAUNCH_S4D(4, true); break; }
+  } else {
+    switch (S) { case 1: LAUNCH_S4D(1, false); break; case 2: LAUNCH_S4D(2, false); break;
+                 case 3: LAUNCH_S4D(3, false); break; default: LAUNCH_S4D(4, false); break; }
+  }
+#undef LAUNCH_S4D
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gabril_obs_s4d(const uint8_t* frames, void* x4, int B, int L, int S, int center, int H, int W,
+                   int grayscale, int Cp, int SH, int SW, cudaStream_t stream) {
+  if (L < 1 || center < 0) return GABRIL_ERR_BAD_SHAPE;
+  return obs_s4d_impl(frames, nullptr, x4, B, L, S, center, H, W, grayscale, Cp, SH, SW, stream);
+}
+
+int gabril_obs_s4d_store(const uint8_t* store, const long long* widx, void* x4, int B, int S, int H, int W,
+                         int grayscale, int Cp, int SH, int SW, cudaStream_t stream) {
+  if (!widx) return GABRIL_ERR_BAD_SHAPE;
+  return obs_s4d_impl(store, widx, x4, B, S, S, S - 1, H, W, grayscale, Cp, SH, SW, stream);
+}
+
+int gabril_conv1_s4d_expand(const float* w1, void* w4, int C1, int C0, int K1p, int Cp, cudaStream_t stream) {
+  if (!w1 || !w4 || C1 <= 0 || C0 <= 0 || K1p < 16 * C0 || Cp < 16 * C0) return GABRIL_ERR_BAD_SHAPE;
+  const int total = 4 * C1 * 4 * Cp;
+  conv1_expand_kernel<<<(total + 255) / 256, 256, 0, stream>>>(w1, (bf16*)w4, C1, C0, K1p, Cp);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_conv1_s4d_fold(const float* dw4, float* dw1, int C1, int C0, int K1p, int Cp, cudaStream_t stream) {
+  if (!dw4 || !dw1 || C1 <= 0 || C0 <= 0 || K1p < 16 * C0 || Cp < 16 * C0) return GABRIL_ERR_BAD_SHAPE;
+  const int total = C1 * 16 * C0;
+  conv1_fold_kernel<<<(total + 255) / 256, 256, 0, stream>>>(dw4, dw1, C1, C0, K1p, Cp);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+}  // extern "C"

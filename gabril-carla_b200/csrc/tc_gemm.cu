@@ -58,7 +58,12 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
 // Persistent CTA: tiles blockIdx.x, blockIdx.x + gridDim.x, ...  The smem stage ring runs across
 // tile boundaries and the accumulator lives in a ring of acc_bufs TMEM buffers, so the producer
 // and the MMA issuer work on tile i+1 while the epilogue warps drain tile i.
-__global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_constant__ Params p) {
+// kEpiGroups = 1: 256 threads, two CTAs per SM (each other's epilogue hides behind the other's MMAs);
+// kEpiGroups = 2: 384 threads for the single-occupancy launches (flat-slab layers with resident weights,
+// 256-row tiles, 512-column wgrad accumulators), where nothing else covers the epilogue's latencies.
+template <int kEpiGroups>
+__global__ void __launch_bounds__(32 * (kFirstEpilogueWarp + 4 * kEpiGroups), kEpiGroups == 1 ? 2 : 1)
+tc_gemm_kernel(const __grid_constant__ Params p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * kMaxStages + 2 * kMaxAcc + 1];
   __shared__ uint32_t tmem_base_s;
@@ -94,18 +99,12 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
   }
   const bool bias_sm = p.bias != nullptr && p.N_total <= kBiasSmem;
   if (warp >= kFirstEpilogueWarp && bias_sm)
-    for (int i = threadIdx.x - 32 * kFirstEpilogueWarp; i < p.N_total; i += 128 * kEpiGroups) bias_s[i] = p.bias[i];
+    for (int i = threadIdx.x - 32 * kFirstEpilogueWarp; i < p.N_total; i += 128 * kEpiGroups)
+      bias_s[i] = p.bias[p.bias_mod > 0 ? i % p.bias_mod : i];
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
-#if GABRIL_EPI_GROUPS == 2
-  // 384 threads, two CTAs per SM: the kernel starts at 80 registers per thread; the MMA / producer
-  // warpgroup (one active thread per warp, uniform-datapath code) gives most of its share to the two
-  // epilogue warpgroups: 4 x 48 + 8 x 104 = 1024 registers per lane slot = half the file per CTA.
-  if (warp < kFirstEpilogueWarp) asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");
-  else asm volatile("setmaxnreg.inc.sync.aligned.u32 104;");
-#endif
 
   if (warp >= kFirstProducerWarp && warp < kFirstEpilogueWarp) {
     // ===================== TMA producers (one thread per warp) =====================
@@ -469,7 +468,12 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
           if (p.valid_h > 0 && (jh >= p.valid_h || jw >= p.valid_w)) row_ok = false;
         }
         bool zero_row = false;
-        if (p.s2d_H > 0 && row_ok) {
+        int q_sh = 0, q_sw = 0;   // quadrant mode: super-pixel coordinates of this row
+        if (p.quad_C > 0) {
+          const int spr = fdiv(row, p.fd_border_w);
+          q_sw = row - spr * p.border_w;
+          q_sh = spr - fdiv(spr, p.fd_border_h) * p.border_h;
+        } else if (p.s2d_H > 0 && row_ok) {
           const int qd = row & 3, sp = row >> 2;
           const int spr = fdiv(sp, p.fd_border_w);
           const int sw = sp - spr * p.border_w, sh = spr - fdiv(spr, p.fd_border_h) * p.border_h;
@@ -482,9 +486,16 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
           const int x = rem - y * p.border_w;
           zero_row = (y == 0) || (y == p.border_h - 1) || (x == 0) || (x == p.border_w - 1);
         }
-        const float rmask = (p.rowmask && row_ok) ? p.rowmask[orow] : 1.0f;
-        const uint64_t rmask2 = ptx::pack2(__float_as_uint(rmask), __float_as_uint(rmask));
-        const uint32_t keep = zero_row ? 0u : 0xffffffffu;
+        float rm4[4] = {1.0f, 1.0f, 1.0f, 1.0f};   // rm4[0]: the row's multiplier; quadrant mode: one per quadrant
+        if (p.rowmask && row_ok) {
+          if (p.quad_C > 0) {
+            const float4 r4 = __ldg(reinterpret_cast<const float4*>(p.rowmask) + orow);
+            rm4[0] = r4.x; rm4[1] = r4.y; rm4[2] = r4.z; rm4[3] = r4.w;
+          } else {
+            rm4[0] = p.rowmask[orow];
+          }
+        }
+        const uint32_t keep_row = zero_row ? 0u : 0xffffffffu;
         const long long off0 = orow * p.ldo + n0;
         // the sign words of every 32-column chunk of this row: 4 bytes per chunk instead of 64
         uint32_t gw[4] = {0u, 0u, 0u, 0u};
@@ -514,6 +525,15 @@ __global__ void __launch_bounds__(kThreads, 2) tc_gemm_kernel(const __grid_const
             const int c = ci * 32;
             const int col0 = n0 + c;
             const bool live = row_ok && col0 < p.N_total;
+            uint32_t keep = keep_row;
+            float rmask = rm4[0];
+            if (p.quad_C > 0) {
+              const int qd = fdiv(col0, p.fd_quad);
+              const int ih = 2 * q_sh + (qd >> 1) - 1, iw = 2 * q_sw + (qd & 1) - 1;
+              keep = (ih < 0 || ih >= p.s2d_H || iw < 0 || iw >= p.s2d_W) ? 0u : 0xffffffffu;
+              rmask = qd == 0 ? rm4[0] : qd == 1 ? rm4[1] : qd == 2 ? rm4[2] : rm4[3];
+            }
+            const uint64_t rmask2 = ptx::pack2(__float_as_uint(rmask), __float_as_uint(rmask));
             uint32_t v[32];
             // residual / gate operands of this chunk: issued before the accumulator read so that their
             // global-memory latency overlaps it
@@ -690,7 +710,8 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     return GABRIL_ERR_BAD_SHAPE;
   }
   // a tile that is a single 32-column item cannot be shared by two epilogue groups: they alternate tiles
-  p.epi_tile_split = (kEpiGroups > 1 && p.kind == KIND_FWD && p.m_sub == 1 && p.block_n <= 32 && p.acc_bufs >= 2) ? 1 : 0;
+  if (p.epi_groups != 2) p.epi_groups = 1;
+  p.epi_tile_split = (p.epi_groups > 1 && p.kind == KIND_FWD && p.m_sub == 1 && p.block_n <= 32 && p.acc_bufs >= 2) ? 1 : 0;
   if (p.out_mode == OUT_BF16 &&
       ((reinterpret_cast<uintptr_t>(p.out) | reinterpret_cast<uintptr_t>(p.resid) | reinterpret_cast<uintptr_t>(p.gate)) & 31)) {
     gabril_set_error("tc::launch: bf16 output / residual / gate tensors must be 32-byte aligned");
@@ -702,6 +723,7 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
   p.fd_border_w = magic(p.border_w);
   p.fd_border_h = magic(p.border_h);
   p.fd_border_hw = magic(p.border_h * p.border_w);
+  p.fd_quad = magic(p.quad_C);
   for (int c = 0; c < 4; ++c) {
     p.fd_hw[c] = magic(p.Hs[c] * p.Ws[c]);
     p.fd_ws[c] = magic(p.Ws[c]);
@@ -710,14 +732,17 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
   }
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(g_attr_once, [] {
-    attr_err = cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    227 * 1024 - 2048);  // static smem: barriers, TMEM base, bias vector (< 2 KB)
+    // static smem: barriers, TMEM base, bias vector (< 2 KB)
+    attr_err = cudaFuncSetAttribute(tc_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(tc_gemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
   });
   if (attr_err != cudaSuccess) return gabril_set_cuda_error(attr_err);
   if (p.total_tiles <= 0) return GABRIL_OK;
   // one persistent CTA per SM (smem / TMEM are sized for single occupancy)
   const unsigned grid = (unsigned)std::min(p.total_tiles, num_sms);
-  tc_gemm_kernel<<<grid, kThreads, smem_bytes, stream>>>(p);
+  if (p.epi_groups == 2) tc_gemm_kernel<2><<<grid, 32 * (kFirstEpilogueWarp + 8), smem_bytes, stream>>>(p);
+  else tc_gemm_kernel<1><<<grid, 32 * (kFirstEpilogueWarp + 4), smem_bytes, stream>>>(p);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
 }

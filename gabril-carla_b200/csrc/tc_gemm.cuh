@@ -23,12 +23,7 @@ constexpr int kBiasSmem = 256;         // bias vectors up to this many columns a
 constexpr int kProducers = 3;          // TMA-issuing warps
 constexpr int kMmaWarp = 0;            // TMEM owner + single-thread MMA issuer
 constexpr int kFirstProducerWarp = 1;  // warps 1..3
-#ifndef GABRIL_EPI_GROUPS
-#define GABRIL_EPI_GROUPS 1
-#endif
-constexpr int kEpiGroups = GABRIL_EPI_GROUPS;   // 1 or 2 groups of 4 epilogue warps (TMEM lane quarter = warp % 4)
-constexpr int kFirstEpilogueWarp = 4;  // warps 4..7 (group 0), 8..11 (group 1): aligned warpgroups
-constexpr int kThreads = 32 * (kFirstEpilogueWarp + 4 * kEpiGroups);
+constexpr int kFirstEpilogueWarp = 4;  // warps 4..7 (group 0), 8..11 (group 1); TMEM lane quarter = warp % 4
 
 enum Kind { KIND_FWD = 0, KIND_WGRAD = 1 };
 enum OutMode { OUT_BF16 = 0, OUT_F32_STORE = 1, OUT_F32_ATOMIC = 2 };
@@ -103,6 +98,10 @@ struct Params {
   // s2d_H/W > 0 instead: rows are (super-pixel, quadrant) of a border_h x border_w space-to-depth
   // grid over an s2d_H x s2d_W image padded by one pixel; rows of padding pixels store 0.
   int border_h, border_w, s2d_H, s2d_W;
+  // quad_C > 0 (with border_h/w = the grid and s2d_H/W = the image): rows are super-pixels (n, sh, sw) and
+  // the columns four quadrants (qh, qw) of quad_C channels = pixels (2sh+qh-1, 2sw+qw-1) of the image;
+  // quadrants outside it store 0, rowmask is indexed [row*4 + quadrant], bias by column % bias_mod.
+  int quad_C, bias_mod;
   // remap validity: rows with jh >= valid_h or jw >= valid_w are not stored (0 = no check)
   int valid_h, valid_w;
   // flat-slab mode: the A rows (FWD) / B rows (WGRAD) are the flat pixels of a zero-bordered
@@ -127,9 +126,10 @@ struct Params {
   int m_sub;
   // epilogue groups split the work by whole tiles (a tile is a single 32-column item) instead of by items
   int epi_tile_split;
+  int epi_groups;   // 1 (256 threads, two CTAs per SM) or 2 (384 threads, single-occupancy launches)
   long long tap_stride;  // WGRAD: element (m, tap, n) at out + m*ldo + tap*tap_stride + n
   // magic numbers of the divisions above, filled by launch() from the fields they belong to
-  FastDiv fd_tiles_m, fd_n_tiles, fd_tap_groups, fd_border_w, fd_border_h, fd_border_hw;
+  FastDiv fd_tiles_m, fd_n_tiles, fd_tap_groups, fd_border_w, fd_border_h, fd_border_hw, fd_quad;
   FastDiv fd_hw[4], fd_ws[4];    // remap: Hs*Ws, Ws per class
   FastDiv fd_ohw[4], fd_ow[4];   // im2col traversal: OHW, OW per class
   int* err_flag;

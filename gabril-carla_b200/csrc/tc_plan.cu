@@ -196,6 +196,10 @@ void finalize_schedule(tc::Params& p, const int* m_tiles, int n_tiles_y, int spl
   p.acc_bufs = 1;
   while (p.acc_bufs * 2 <= acc_max && p.acc_stride * p.acc_bufs * 2 <= 512 / occ) p.acc_bufs *= 2;
   p.tmem_cols = (uint32_t)(p.acc_stride * p.acc_bufs);
+  // single-occupancy launches get a second group of epilogue warps (GABRIL_TC_EPI=1 switches it off)
+  static int epi_max = 0;
+  if (!epi_max) { const char* e = getenv("GABRIL_TC_EPI"); epi_max = (e && atoi(e) == 1) ? 1 : 2; }
+  p.epi_groups = (occ == 1 && epi_max == 2) ? 2 : 1;
 }
 
 struct ActDims { int N, H, W, C; };
@@ -705,11 +709,16 @@ int gabril_conv_flat(const void* x, const void* w, const float* bias, const void
 
 // rowmask: per OUTPUT-STORAGE pixel multiplier (index = pixel index of y after the remap), applied
 // after bias / ReLU - the in-encoder gaze dropout of linear_models.py:194-199.
-int gabril_conv_flat_masked(const void* x, const void* w, const float* bias, const void* resid,
-                            const void* gate, const float* rowmask, void* y, int N, int Hg, int Wg,
-                            int Cx, int Cy, int R, int S, int valid_h, int valid_w, int o_rows,
-                            int o_pitch, int o_off_h, int o_off_w, int relu, int transpose_w,
-                            cudaStream_t stream) {
+// x_pitch_c: channel pitch between consecutive flat rows of x (0 = Cx).  A pitch below Cx makes rows
+// overlap: row q = cells q and q + 1 of a tensor with x_pitch_c channels per cell (conv1_s4d.cu).
+// quad_C > 0: the output columns are four quadrants (qh, qw) of quad_C channels, i.e. row (n, sh, sw) holds
+// the pixels (2sh+qh-1, 2sw+qw-1) of a quad_H x quad_W image; pixels outside it store zeros, the bias
+// vector has quad_C entries, and rowmask has one entry per (row, quadrant).
+static int conv_flat_impl(const void* x, const void* w, const float* bias, const void* resid,
+                          const void* gate, const float* rowmask, void* y, int N, int Hg, int Wg,
+                          int Cx, int Cy, int R, int S, int valid_h, int valid_w, int o_rows,
+                          int o_pitch, int o_off_h, int o_off_w, int relu, int transpose_w,
+                          int x_pitch_c, int quad_C, int quad_H, int quad_W, cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
   if (Cx % 64 || N <= 0 || R < 1 || S < 1 || S > 8) return GABRIL_ERR_BAD_SHAPE;
@@ -738,7 +747,7 @@ int gabril_conv_flat_masked(const void* x, const void* w, const float* bias, con
   const int slab_rows = 128 + S - 1;
   {
     uint64_t dims[2] = {(uint64_t)Cx, (uint64_t)M};
-    uint64_t strides[1] = {(uint64_t)Cx * 2};
+    uint64_t strides[1] = {(uint64_t)(x_pitch_c > 0 ? x_pitch_c : Cx) * 2};
     uint32_t box[2] = {(uint32_t)kc, (uint32_t)slab_rows};
     rc = tiled_map(&p.mapA[0], x, 2, dims, strides, box, kc * 2);
     if (rc) return rc;
@@ -773,17 +782,42 @@ int gabril_conv_flat_masked(const void* x, const void* w, const float* bias, con
     p.Hs[0] = Hg; p.Ws[0] = Wg; p.OHf = o_rows; p.OWf = o_pitch; p.ah[0] = o_off_h; p.aw[0] = o_off_w;
     p.valid_h = valid_h; p.valid_w = valid_w;
   }
+  if (quad_C > 0) {
+    if (quad_C % 32 || 4 * quad_C != Cy || valid_h > 0) return GABRIL_ERR_BAD_SHAPE;
+    p.quad_C = quad_C;
+    p.border_h = Hg; p.border_w = Wg; p.s2d_H = quad_H; p.s2d_W = quad_W;
+    p.bias_mod = quad_C;
+  }
   p.err_flag = g_err_flag;
   const int mt[1] = {(int)((M + 127) / 128)};
   finalize_schedule(p, mt, n_tiles, 1, block_n, 1);
   return tc::launch(p, g_num_sms, smem, stream);
 }
 
+int gabril_conv_flat_masked(const void* x, const void* w, const float* bias, const void* resid,
+                            const void* gate, const float* rowmask, void* y, int N, int Hg, int Wg,
+                            int Cx, int Cy, int R, int S, int valid_h, int valid_w, int o_rows,
+                            int o_pitch, int o_off_h, int o_off_w, int relu, int transpose_w,
+                            cudaStream_t stream) {
+  return conv_flat_impl(x, w, bias, resid, gate, rowmask, y, N, Hg, Wg, Cx, Cy, R, S, valid_h, valid_w, o_rows,
+                        o_pitch, o_off_h, o_off_w, relu, transpose_w, 0, 0, 0, 0, stream);
+}
+
+// conv_1 + ReLU over the 4x4 space-to-depth frame image (conv1_s4d.cu): x4 [N*SH*SW (+1), Cp] bf16,
+// w4 [4*C1][2][2*Cp] bf16 (gabril_conv1_s4d_expand), bias fp32 [C1], rowmask fp32 [N*SH*SW*4] or NULL
+// (in-encoder gaze dropout, one entry per conv_1 pixel in space-to-depth order) -> y [N, SH, SW, 4*C1].
+int gabril_conv1_s4d_fwd(const void* x4, const void* w4, const float* bias, const float* rowmask, void* y,
+                         int N, int SH, int SW, int Cp, int C1, int img_h, int img_w, int relu,
+                         cudaStream_t stream) {
+  return conv_flat_impl(x4, w4, bias, nullptr, nullptr, rowmask, y, N, SH, SW, 2 * Cp, 4 * C1, 2, 1, 0, 0, SH,
+                        SW, 0, 0, relu, 0, Cp, C1, img_h, img_w, stream);
+}
+
 // dw[Cy][R*S][Cx] (fp32) += sum_q dy_flat[q + dy_row_off, Cy]^T . x_flat[q + r*Wg + s, Cx]
 // over every flat pixel q of the [N, Hg, Wg] grid; dy and x are zero-bordered tensors with that
 // same grid (rows past the end read as zero).  The caller zeroes dw.
-int gabril_conv_wgrad_flat(const void* dy, const void* x, float* dw, int N, int Hg, int Wg, int Cx,
-                           int Cy, int R, int S, int dy_row_off, cudaStream_t stream) {
+static int conv_wgrad_flat_impl(const void* dy, const void* x, float* dw, int N, int Hg, int Wg, int Cx,
+                                int Cy, int R, int S, int dy_row_off, int x_pitch_c, cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
   if (!mn_ok(Cx) || Cx < 64 || Cy % 32 || N <= 0 || S > 8) return GABRIL_ERR_BAD_SHAPE;
@@ -841,7 +875,7 @@ int gabril_conv_wgrad_flat(const void* dy, const void* x, float* dw, int N, int 
   }
   {
     uint64_t dims[2] = {(uint64_t)Cx, (uint64_t)P};
-    uint64_t strides[1] = {(uint64_t)Cx * 2};
+    uint64_t strides[1] = {(uint64_t)(x_pitch_c > 0 ? x_pitch_c : Cx) * 2};
     uint32_t box[2] = {64u, (uint32_t)slab_rows};
     rc = tiled_map(&p.mapB, x, 2, dims, strides, box, 128);
     if (rc) return rc;
@@ -863,6 +897,18 @@ int gabril_conv_wgrad_flat(const void* dy, const void* x, float* dw, int N, int 
   p.acc_bufs = 1;
   p.tmem_cols = (uint32_t)p.acc_stride;
   return tc::launch(p, 1 << 30, smem, stream);
+}
+
+int gabril_conv_wgrad_flat(const void* dy, const void* x, float* dw, int N, int Hg, int Wg, int Cx,
+                           int Cy, int R, int S, int dy_row_off, cudaStream_t stream) {
+  return conv_wgrad_flat_impl(dy, x, dw, N, Hg, Wg, Cx, Cy, R, S, dy_row_off, 0, stream);
+}
+
+// dw4 [4*C1][2][2*Cp] fp32 += da1s [N, SH, SW, 4*C1]^T . (overlapping rows of x4): the weight gradient of
+// gabril_conv1_s4d_fwd; gabril_conv1_s4d_fold sums its four quadrants into conv_1's own gradient.
+int gabril_conv1_s4d_wgrad(const void* dy, const void* x4, float* dw4, int N, int SH, int SW, int Cp, int C1,
+                           cudaStream_t stream) {
+  return conv_wgrad_flat_impl(dy, x4, dw4, N, SH, SW, 2 * Cp, 4 * C1, 2, 1, 0, Cp, stream);
 }
 
 // conv_1 as a patch GEMM whose rows are in space-to-depth order: row = ((n*SH + sh)*SW + sw)*4 + q

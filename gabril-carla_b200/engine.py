@@ -84,7 +84,12 @@ class StepEngine:
         self.SH, self.SW = s.H2 + 2, s.W2 + 2
         assert s.H1 % 2 == 0 and s.W1 % 2 == 0 and (4 * s.C1) % 64 == 0 and s.C2 % 64 == 0
         zact = lambda h, w, c: torch.zeros(B, h, w, c, device=dev, dtype=bf)  # noqa: E731
-        b["patches"] = torch.zeros(B * self.SH * self.SW * 4, s.K1p, device=dev, dtype=bf)
+        # conv_1 input: the frames as a 4x4 space-to-depth bf16 image on the [SH, SW] grid (csrc/conv1_s4d.cu),
+        # one spare zero cell at the end (rows of the overlapping-row tensor map span two cells)
+        assert s.H % 4 == 0 and s.W % 4 == 0 and self.SH == s.H // 4 + 2 and self.SW == s.W // 4 + 2
+        b["x4"] = torch.zeros(B * self.SH * self.SW + 1, s.K1p, device=dev, dtype=bf)
+        b["w4"] = torch.zeros(4 * s.C1, 2, 2 * s.K1p, device=dev, dtype=bf)
+        b["dw4"] = torch.zeros(4 * s.C1, 2, 2 * s.K1p, device=dev, dtype=f32)
         b["a1s"], b["a2p"] = zact(self.SH, self.SW, 4 * s.C1), zact(self.SH, self.SW, s.C2)
         b["a3"] = act(s.H3, s.W3, s.NH)
         b["r-1"] = act(s.h, s.w, s.NH)  # relu(conv_4): the input of the first Residual
@@ -151,7 +156,7 @@ class StepEngine:
         b = self.buf
         center = L - 1
         # ---- preprocessing (prepare_for_bc, data_loader_robomimic.py:318-360) ----
-        ops.obs_patches_s2d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["patches"])
+        ops.obs_s4d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["x4"])
         # ---- which samples use gaze (train_bc.py:230-240); all of them at gaze.ratio >= 1 ----
         self.sel = self.sel_stats = None
         if self.gaze_ratio < 1.0 and (self.use_reg or self.use_gmd or self.use_igmd):
@@ -178,7 +183,7 @@ class StepEngine:
         center = self.S - 1
         widx = ops.store_windows(step_idx.to(self.device, torch.int64).contiguous(), store.first, self.S,
                                  out=b["widx"])
-        ops.obs_patches_s2d_store(store.images, widx, self.grayscale, self.SH, self.SW, b["patches"])
+        ops.obs_s4d_store(store.images, widx, self.grayscale, self.SH, self.SW, b["x4"])
         self.sel = self.sel_stats = None
         if self.gaze_ratio < 1.0 and (self.use_reg or self.use_gmd or self.use_igmd):
             self.sel, self.sel_stats = ops.ivg_select_store(store.images, widx, self.grayscale,
@@ -200,7 +205,7 @@ class StepEngine:
         if B != self.B:
             self._alloc(B)
         b = self.buf
-        ops.obs_patches_s2d(frames, self.S, L - 1, self.grayscale, self.SH, self.SW, b["patches"])
+        ops.obs_s4d(frames, self.S, L - 1, self.grayscale, self.SH, self.SW, b["x4"])
         rowmask = igmd = None
         if self.use_gmd or self.use_igmd:
             if g is None:
@@ -270,9 +275,11 @@ class StepEngine:
         fused into conv_6's epilogue; igmd = (mask after conv_1, mask after conv_2): the stored a1 / a2
         are the dropped-out activations, so their `> 0` gates carry the mask through the backward."""
         s, a, b, B = self.spec, self.arena, self.buf, self.B
-        ops.conv1_s2d_fwd(b["patches"], a.WB("enc.conv1.w"), a.P("enc.conv1.b"), b["a1s"], B, self.SH,
-                          self.SW, s.H1, s.W1, relu=True, rowmask=igmd[0] if igmd else None,
-                          bits_out=b["sb_a1s"])
+        # conv_1 = a 2x2 flat convolution over the 4x4 space-to-depth frame image; its zero-inflated
+        # weights are re-derived from the fp32 master every step (16 K elements)
+        ops.conv1_s4d_expand(a.P("enc.conv1.w"), b["w4"], s.C0)
+        ops.conv1_s4d_fwd(b["x4"], b["w4"], a.P("enc.conv1.b"), b["a1s"], B, self.SH, self.SW, s.H1, s.W1,
+                          relu=True, rowmask=igmd[0] if igmd else None, bits_out=b["sb_a1s"])
         ops.conv_flat(b["a1s"], a.WB("enc.conv2.w"), b["a2p"], 2, 2, bias=a.P("enc.conv2.b"),
                       valid=(s.H2, s.W2), out_geom=(self.SH, self.SW, 1, 1), relu=True,
                       rowmask=igmd[1] if igmd else None, bits_out=b["sb_a2p"])
@@ -487,8 +494,9 @@ class StepEngine:
                       flop_pixels=B * s.H2 * s.W2)  # algorithmic FLOPs of the k4/s2 dgrad
         M1 = B * self.SH * self.SW * 4
         self._colsum(b["da1s"].view(M1, s.C1), a.G("enc.conv1.b"))
-        ops.conv_wgrad(b["da1s"].view(M1, 1, 1, s.C1), b["patches"].view(M1, 1, 1, s.K1p),
-                       a.G("enc.conv1.w"), 1, 1, 1, 0)
+        b["dw4"].zero_()
+        ops.conv1_s4d_wgrad(b["da1s"], b["x4"], b["dw4"], B, self.SH, self.SW, s.H1, s.W1)
+        ops.conv1_s4d_fold(b["dw4"], a.G("enc.conv1.w"), s.C0)
         if self._colsum_pending:
             main = torch.cuda.current_stream(self.device)
             self._ev["colsum"].record(self._side)

@@ -56,7 +56,7 @@ class GazePredictorEngine(StepEngine):
         b = self.buf
         center = L - 1
         # prepare_for_gaze_predictor: image stack + causally aggregated heat maps, last one is the target
-        ops.obs_patches_s2d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["patches"])
+        ops.obs_s4d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["x4"])
         self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=True)
         self._encoder_fwd(None)
         # ---- Decoder.forward (linear_models.py:271-282) ----

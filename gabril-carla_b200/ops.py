@@ -221,6 +221,77 @@ def obs_patches_s2d(frames, S, center, grayscale, SH, SW, out):
     return out
 
 
+# ---- conv_1 over the 4x4 space-to-depth frame image (csrc/conv1_s4d.cu) ------------------------
+def obs_s4d(frames, S, center, grayscale, SH, SW, out):
+    """uint8 [B,L,H,W,3] -> bf16 cells [B*SH*SW (+1), Cp] (gather + /255 + gray + space-to-depth)."""
+    _chk(frames, torch.uint8, "frames")
+    B, L, H, W, C = frames.shape
+    Cp = out.shape[1]
+    assert out.shape[0] >= B * SH * SW + 1 and out.dtype == torch.bfloat16 and C == 3
+    _call("gabril_obs_s4d", ptr(frames), ptr(out), c_int(B), c_int(L), c_int(S), c_int(center), c_int(H), c_int(W),
+          c_int(int(grayscale)), c_int(Cp), c_int(SH), c_int(SW), stream(),
+          work=float(B * S * H * W * 3 + B * SH * SW * Cp * 2))
+    return out
+
+
+def obs_s4d_store(store_frames, widx, grayscale, SH, SW, out):
+    """obs_s4d reading frame widx[b,s] of the uint8 store [N,H,W,3] (no batch tensor)."""
+    _chk(store_frames, torch.uint8, "store_frames"); _chk(widx, torch.int64, "widx")
+    N, H, W, C = store_frames.shape
+    B, S = widx.shape
+    Cp = out.shape[1]
+    assert out.shape[0] >= B * SH * SW + 1 and out.dtype == torch.bfloat16
+    _call("gabril_obs_s4d_store", ptr(store_frames), ptr(widx), ptr(out), c_int(B), c_int(S), c_int(H), c_int(W),
+          c_int(int(grayscale)), c_int(Cp), c_int(SH), c_int(SW), stream(),
+          work=float(B * S * H * W * 3 + B * SH * SW * Cp * 2))
+    return out
+
+
+def conv1_s4d_expand(w1, w4, C0):
+    """fp32 master conv_1 weight [C1,1,K1p] -> bf16 [4*C1, 2, 2*Cp] weights of the 2x2 convolution."""
+    _chk(w1, torch.float32, "w1"); _chk_bf16(w4, "w4")
+    C1, K1p = w1.shape[0], w1.shape[-1]
+    Cp = w4.shape[2] // 2
+    assert w4.shape == (4 * C1, 2, 2 * Cp)
+    _call("gabril_conv1_s4d_expand", ptr(w1), ptr(w4), c_int(C1), c_int(C0), c_int(K1p), c_int(Cp), stream())
+    return w4
+
+
+def conv1_s4d_fwd(x4, w4, bias, y, N, SH, SW, img_h, img_w, relu=True, rowmask=None, bits_out=None):
+    """x4 bf16 cells, w4 [4*C1,2,2*Cp] -> y [N,SH,SW,4*C1]: conv_1 + ReLU in space-to-depth storage."""
+    _chk_bf16(x4, "x4"); _chk_bf16(w4, "w4"); _chk_bf16(y, "y")
+    Cp, C1 = x4.shape[1], w4.shape[0] // 4
+    assert w4.shape[2] == 2 * Cp and y.numel() == N * SH * SW * 4 * C1 and x4.shape[0] >= N * SH * SW + 1
+    with _span("tc_gemm_kernel", f"fwd-s4d {16 * Cp // 16}->{C1} k4s2", 2.0 * N * img_h * img_w * C1 * Cp, "flop"):
+        _epilogue_bits(None, bits_out, y)
+        st = _lib.init().gabril_conv1_s4d_fwd(ptr(x4), ptr(w4), ptr(bias), ptr(rowmask), ptr(y), c_int(N), c_int(SH),
+                                              c_int(SW), c_int(Cp), c_int(C1), c_int(img_h), c_int(img_w),
+                                              c_int(int(relu)), stream())
+    _lib.check(st, "gabril_conv1_s4d_fwd")
+    return y
+
+
+def conv1_s4d_wgrad(dy, x4, dw4, N, SH, SW, img_h, img_w):
+    """dw4 fp32 [4*C1,2,2*Cp] += dy [N,SH,SW,4*C1]^T . x4 windows."""
+    _chk_bf16(dy, "dy"); _chk_bf16(x4, "x4"); _chk(dw4, torch.float32, "dw4")
+    Cp, C1 = x4.shape[1], dw4.shape[0] // 4
+    assert dw4.shape == (4 * C1, 2, 2 * Cp) and dy.numel() == N * SH * SW * 4 * C1
+    with _span("tc_gemm_kernel", f"wgrad-s4d {Cp}x{C1} k4s2", 2.0 * N * img_h * img_w * C1 * Cp, "flop"):
+        st = _lib.init().gabril_conv1_s4d_wgrad(ptr(dy), ptr(x4), ptr(dw4), c_int(N), c_int(SH), c_int(SW), c_int(Cp),
+                                                c_int(C1), stream())
+    _lib.check(st, "gabril_conv1_s4d_wgrad")
+    return dw4
+
+
+def conv1_s4d_fold(dw4, dw1, C0):
+    """dw1 fp32 [C1,1,K1p] += the four quadrants of dw4."""
+    _chk(dw4, torch.float32, "dw4"); _chk(dw1, torch.float32, "dw1")
+    C1, K1p = dw1.shape[0], dw1.shape[-1]
+    Cp = dw4.shape[2] // 2
+    _call("gabril_conv1_s4d_fold", ptr(dw4), ptr(dw1), c_int(C1), c_int(C0), c_int(K1p), c_int(Cp), stream())
+    return dw1
+
+
 def s2d_weight_taps():
     """Permutation of the 16 taps of a k4/s2 filter into (r', s', qh, qw) order: the 2x2 stride-1
     filter over the space-to-depth input has tap (r', s') = [W(2r'+qh, 2s'+qw) for qh, qw]."""

@@ -255,6 +255,31 @@ int gabril_conv1_s2d_fwd_masked(const void* patches, const void* w, const float*
                                 const float* rowmask, void* y, int N, int SH, int SW, int img_h,
                                 int img_w, int Kp, int Cout, int relu, cudaStream_t stream);
 
+/* ---- conv_1 without a patch matrix (csrc/conv1_s4d.cu) ------------------------------------------
+ * Replaces _gather_last_s_frames + _format_obs_image (data_loader_robomimic.py:144-157,179-202)
+ * feeding Encoder._conv_1 + ReLU (linear_models.py:141-146,191-193).  The uint8 frames are written
+ * once as a 4x4 space-to-depth bf16 image on conv_1's own space-to-depth grid,
+ *   x4[n, u, v, (a*4 + b)*C0 + ci] = obs[n, ci, 4(u-1) + a, 4(v-1) + b]   (0 outside), SH = H/4 + 2,
+ *   SW = W/4 + 2, Cp >= 16*C0 channels per cell; the buffer holds N*SH*SW + 1 cells (the last one zero);
+ * conv_1 is then a 2x2 stride-1 flat convolution with 4*C1 output channels (quadrant, co) whose weights
+ * w4 [4*C1][2][2*Cp] (bf16) gabril_conv1_s4d_expand derives from the fp32 master w1 [C1][K1p]
+ * (column (kh*4 + kw)*C0 + ci); gabril_conv1_s4d_wgrad accumulates dw4 (fp32, same shape) and
+ * gabril_conv1_s4d_fold adds its four quadrants into dw1 [C1][K1p].  rowmask: one multiplier per
+ * conv_1 pixel in space-to-depth order [N, SH, SW, 4] (in-encoder gaze dropout) or NULL. */
+int gabril_obs_s4d(const uint8_t* frames, void* x4, int B, int L, int S, int center, int H, int W,
+                   int grayscale, int Cp, int SH, int SW, cudaStream_t stream);
+int gabril_obs_s4d_store(const uint8_t* store, const long long* widx, void* x4, int B, int S, int H,
+                         int W, int grayscale, int Cp, int SH, int SW, cudaStream_t stream);
+int gabril_conv1_s4d_expand(const float* w1, void* w4, int C1, int C0, int K1p, int Cp,
+                            cudaStream_t stream);
+int gabril_conv1_s4d_fwd(const void* x4, const void* w4, const float* bias, const float* rowmask,
+                         void* y, int N, int SH, int SW, int Cp, int C1, int img_h, int img_w, int relu,
+                         cudaStream_t stream);
+int gabril_conv1_s4d_wgrad(const void* dy, const void* x4, float* dw4, int N, int SH, int SW, int Cp,
+                           int C1, cudaStream_t stream);
+int gabril_conv1_s4d_fold(const float* dw4, float* dw1, int C1, int C0, int K1p, int Cp,
+                          cudaStream_t stream);
+
 /* ---- gaze-predictor pre-training (train_gaze_predictor.py:83-101): AutoEncoder = Encoder + Decoder
  * (linear_models.py:210-282, 356-367), MSE against the last aggregated heat map.
  * nn.ConvTranspose2d with weight Wt[Cin_t][Cout_t][R][S] runs on the convolution kernels through the

@@ -184,3 +184,85 @@ def test_conv_flat_fwd_dgrad_wgrad(ops, layer, N):
     wref = ops.w_oihw_to_internal(torch.nn.grad.conv2d_weight(x64, (Cout, Cin, R, R), dy64, padding=pad))
     assert rel(dw.cpu(), wref) <= 2e-5
     _lib.poll_error()
+
+
+# ---- conv_1 over the 4x4 space-to-depth frame image (csrc/conv1_s4d.cu) ---------------------------
+@pytest.mark.parametrize("gray,S,L", [(True, 2, 2), (False, 2, 3), (True, 1, 2), (True, 3, 5)])
+def test_obs_s4d_bit_exact(ops, gray, S, L):
+    """u8 frames -> bf16 cells: window gather (integer, bit-exact), /255, gray, rounding, cell layout."""
+    from oracle import gabril_oracle as O
+    from tests.synth import make_batch
+    img, _, _ = make_batch(3, L=L, seed=2, smooth=False)
+    B, _, H, W, _ = img.shape
+    SH, SW = H // 4 + 2, W // 4 + 2
+    C0 = S * (1 if gray else 3)
+    Cp = ops.conv1_kp(S, gray)
+    x4 = torch.full((B * SH * SW + 1, Cp), float("nan"), device=DEV, dtype=torch.bfloat16)
+    x4[-1] = 0
+    ops.obs_s4d(img.to(DEV), S, L - 1, gray, SH, SW, x4)
+    obs = O.format_obs(O.gather_stack(img, L - 1, S), gray)            # [B, C0, H, W] fp32
+    canvas = torch.zeros(B, C0, 4 * SH, 4 * SW)
+    canvas[:, :, 4:4 + H, 4:4 + W] = obs                               # cell (u, v) = rows 4(u-1) .. of the image
+    ref = canvas.reshape(B, C0, SH, 4, SW, 4).permute(0, 2, 4, 3, 5, 1).reshape(B * SH * SW, 16 * C0)
+    got = x4[:-1].float().cpu()
+    assert torch.equal(got[:, :16 * C0], ref.to(torch.bfloat16).float())
+    assert torch.count_nonzero(got[:, 16 * C0:]) == 0                  # channel padding (RGB: 96 -> 128)
+
+
+@pytest.mark.parametrize("gray,N", [(True, 3), (False, 2)])
+def test_conv1_s4d_fwd_wgrad(ops, gray, N):
+    """conv_1 + ReLU as a 2x2 flat convolution over the cells vs fp64 F.conv2d of the same bf16 operands:
+    forward in space-to-depth storage (zero border quadrants, sign words), per-pixel mask, and the
+    weight gradient folded back to conv_1's own layout."""
+    S, H, W, C1 = 2, 180, 320, 32
+    C0 = S * (1 if gray else 3)
+    Cp = ops.conv1_kp(S, gray)
+    SH, SW, H1, W1 = H // 4 + 2, W // 4 + 2, H // 2, W // 2
+    g = torch.Generator().manual_seed(11)
+    x = torch.rand(N, C0, H, W, generator=g).to(torch.bfloat16)
+    w = (torch.randn(C1, C0, 4, 4, generator=g) * 0.3).to(torch.bfloat16)
+    bias = torch.randn(C1, generator=g) * 0.2
+    canvas = torch.zeros(N, C0, 4 * SH, 4 * SW, dtype=torch.bfloat16)
+    canvas[:, :, 4:4 + H, 4:4 + W] = x
+    x4 = torch.zeros(N * SH * SW + 1, Cp, dtype=torch.bfloat16)
+    x4[:-1, :16 * C0] = canvas.reshape(N, C0, SH, 4, SW, 4).permute(0, 2, 4, 3, 5, 1).reshape(N * SH * SW, 16 * C0)
+    x4 = x4.to(DEV)
+    w1 = torch.zeros(C1, 1, Cp)
+    w1[:, 0, :16 * C0] = w.float().permute(0, 2, 3, 1).reshape(C1, 16 * C0)      # master layout (kh, kw, ci)
+    w4 = torch.empty(4 * C1, 2, 2 * Cp, device=DEV, dtype=torch.bfloat16)
+    ops.conv1_s4d_expand(w1.to(DEV), w4, C0)
+    rowmask = (torch.rand(N * SH * SW * 4, generator=g) > 0.3).float() * 0.5 + 0.25
+    y = torch.full((N, SH, SW, 4 * C1), float("nan"), device=DEV, dtype=torch.bfloat16)
+    sb = torch.full((y.numel() // 32,), -1, device=DEV, dtype=torch.int32)
+    ops.conv1_s4d_fwd(x4, w4, bias.to(DEV), y, N, SH, SW, H1, W1, relu=True, rowmask=rowmask.to(DEV), bits_out=sb)
+    torch.cuda.synchronize()
+    ref = F.relu(F.conv2d(x.double(), w.double(), bias.double(), stride=2, padding=1))          # [N, C1, H1, W1]
+    refp = torch.zeros(N, C1, 2 * SH, 2 * SW, dtype=torch.float64)
+    refp[:, :, 1:1 + H1, 1:1 + W1] = ref
+    ref_s2d = refp.reshape(N, C1, SH, 2, SW, 2).permute(0, 2, 4, 3, 5, 1).reshape(N, SH, SW, 4 * C1)
+    ref_s2d = ref_s2d * rowmask.double().reshape(N, SH, SW, 4, 1).expand(N, SH, SW, 4, C1).reshape(N, SH, SW, 4 * C1)
+    got = y.float().cpu()
+    assert torch.isfinite(got).all()
+    assert rel(got, ref_s2d) <= 4e-3
+    border = refp.reshape(N, C1, SH, 2, SW, 2).permute(0, 2, 4, 3, 5, 1).reshape(N, SH, SW, 4 * C1) == 0
+    inside = torch.zeros(N, 1, 2 * SH, 2 * SW, dtype=torch.bool)
+    inside[:, :, 1:1 + H1, 1:1 + W1] = True
+    inside = inside.reshape(N, 1, SH, 2, SW, 2).permute(0, 2, 4, 3, 5, 1).expand(N, SH, SW, 2, 2, C1).reshape(N, SH, SW, 4 * C1)
+    assert torch.count_nonzero(got[~inside]) == 0                      # padding pixels store exact zeros
+    assert torch.equal(sb.cpu(), pack_signs(y.cpu()))
+    # weight gradient: dy in the same storage (zero at padding pixels, like the gated gradient)
+    dy = (torch.randn(N, SH, SW, 4 * C1, generator=g) * 0.1).to(torch.bfloat16) * inside
+    dw4 = torch.zeros(4 * C1, 2, 2 * Cp, device=DEV)
+    ops.conv1_s4d_wgrad(dy.to(DEV), x4, dw4, N, SH, SW, H1, W1)
+    dw1 = torch.zeros(C1, 1, Cp, device=DEV)
+    dw1[:, 0, 0] = 1.0                                                  # fold accumulates
+    ops.conv1_s4d_fold(dw4, dw1, C0)
+    dyi = dy.double().reshape(N, SH, SW, 2, 2, C1).permute(0, 5, 1, 3, 2, 4).reshape(N, C1, 2 * SH, 2 * SW)
+    dyi = dyi[:, :, 1:1 + H1, 1:1 + W1]
+    wd = w.double().requires_grad_(True)
+    (F.conv2d(x.double(), wd, None, stride=2, padding=1) * dyi).sum().backward()
+    ref_dw = wd.grad.permute(0, 2, 3, 1).reshape(C1, 16 * C0)
+    got_dw = dw1.cpu()[:, 0].double()
+    got_dw[:, 0] -= 1.0
+    assert rel(got_dw[:, :16 * C0], ref_dw) <= 2e-3
+    assert torch.count_nonzero(got_dw[:, 16 * C0:]) == 0

@@ -90,27 +90,46 @@ def test_unsupported_methods_raise(tmp_path):
 
 
 def test_cuda_graph_step_matches_eager_loop(tmp_path):
-    """training.cuda_graph=true: the reference-style loop driven by graph replays gives the eager
-    loop's losses (batch-dict feed, the HBM store materialised per batch) and the same weights."""
+    """training.cuda_graph=true: the reference-style loop driven by graph replays computes the eager
+    loop's step.  The two trainers are compared STEP BY STEP FROM IDENTICAL WEIGHTS (the graph trainer's
+    arena is overwritten with the eager trainer's before every step): fp32 atomics (split-K wgrad, bias
+    column sums, the split-K pre_actor GEMM) make any two runs of the same step differ by ~1e-7 relative
+    (tools/determinism.py, profiles/r2_determinism.txt: eager vs eager == eager vs graph), and Adam's
+    first steps are sign-like (p -= lr * g / |g|), so a free-running 3-step trajectory amplifies one
+    flipped near-zero gradient element chaotically (loss 4 -> 53 -> 2.8 at this lr): that comparison
+    (rounds 1's version of this test) is unsound at any fixed bound.  Per step the bounds are tight."""
     from gabril_carla_b200.trainer import BCTrainer
-    finals = {}
+    lr = 1e-4
+    trs = {}
     for mode in ("false", "true"):
         tr = BCTrainer(make_cfg(tmp_path / mode, f"training.cuda_graph={mode}", "training.epochs=1"))
         tr.fused_feed = False
         tr.train_loader.fused = False
         tr.set_train_mode()
-        losses = []
-        for batch in tr.train_loader:
+        trs[mode] = tr
+    eager, graph = trs["false"], trs["true"]
+    assert torch.equal(eager.arena.p, graph.arena.p)          # same seed -> same initial weights
+    n_steps = 0
+    for be, bg in zip(eager.train_loader, graph.train_loader):
+        assert torch.equal(be["actions"], bg["actions"])      # same sampler stream
+        for name in ("p", "m", "v", "wb"):                    # identical weights / Adam state before the step
+            getattr(graph.arena, name).copy_(getattr(eager.arena, name))
+        out = {}
+        for tag, tr, batch in (("eager", eager, be), ("graph", graph, bg)):
             tr.zero_grad()
             loss, bs, m = tr.compute_loss(batch)
             loss.backward()
+            torch.cuda.synchronize()
+            g = tr.arena.g.clone()
             tr.optimizer_step()
-            losses.append(m["Loss/total"])
-        torch.cuda.synchronize()
-        if mode == "true":
-            assert len(tr.engine._graphs) == 1
-        finals[mode] = (losses, tr.arena.p.clone())
-    for a, b in zip(finals["false"][0], finals["true"][0]):
-        assert abs(a - b) <= 2e-3 * abs(a), (finals["false"][0], finals["true"][0])
-    pa, pb = finals["false"][1], finals["true"][1]
-    assert (pa - pb).abs().max().item() <= 2e-3   # three Adam steps at lr 1e-4 apart at most
+            torch.cuda.synchronize()
+            out[tag] = (m, g, tr.arena.p.clone())
+        (me, ge, pe), (mg, gg, pg) = out["eager"], out["graph"]
+        for k in ("Loss/actor", "Loss/reg", "Loss/total"):
+            assert abs(me[k] - mg[k]) <= 1e-5 * abs(me[k]), (k, me[k], mg[k])
+        assert ((ge - gg).norm() / ge.norm()).item() <= 1e-5
+        assert (pe - pg).abs().max().item() <= 2 * lr * 1.01   # one sign-like Adam step apart at most
+        assert ((pe - pg).norm() / pe.norm()).item() <= 1e-6
+        n_steps += 1
+    assert n_steps == 3 and len(graph.engine._graphs) == 1
+    assert all(v == v for v in me.values())                   # finite after three steps
