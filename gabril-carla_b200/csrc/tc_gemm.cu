@@ -24,7 +24,7 @@ __device__ __forceinline__ void report_timeout(const Params& p, int code) {
 }
 
 struct Tile {
-  int cls, m0, n0, tap0, ntaps, kb_begin, kb_end;
+  int cls, m0, n0, tap0, ntaps, kb_begin, kb_end, split;
 };
 
 __device__ __forceinline__ int fdiv(int n, const FastDiv& d) {
@@ -50,6 +50,7 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
   r.n0 = n_tile * p.block_n;
   r.tap0 = tg * p.n_acc;
   r.ntaps = (p.kind == KIND_WGRAD) ? min(p.n_acc, p.taps - r.tap0) : 1;
+  r.split = split;
   r.kb_begin = split * p.kb_per_split;
   r.kb_end = min(r.kb_begin + p.kb_per_split, p.kb_total);
   return r;
@@ -627,7 +628,7 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
                 }
               } else {
                 float* o = reinterpret_cast<float*>(p.out) + orow * p.ldo +
-                           (long long)(tl.tap0 + a) * p.tap_stride + col0;
+                           (long long)(tl.tap0 + a) * p.tap_stride + col0 + tl.split * p.split_stride;
                 if (p.out_mode == OUT_F32_STORE) {
                   float4* o4 = reinterpret_cast<float4*>(o);
 #pragma unroll

@@ -128,6 +128,7 @@ struct Params {
   int epi_tile_split;
   int epi_groups;   // 1 (256 threads, two CTAs per SM) or 2 (384 threads, single-occupancy launches)
   long long tap_stride;  // WGRAD: element (m, tap, n) at out + m*ldo + tap*tap_stride + n
+  long long split_stride;  // FWD split-K with plain stores: split s writes its partial at out + s*split_stride
   // magic numbers of the divisions above, filled by launch() from the fields they belong to
   FastDiv fd_tiles_m, fd_n_tiles, fd_tap_groups, fd_border_w, fd_border_h, fd_border_hw, fd_quad;
   FastDiv fd_hw[4], fd_ws[4];    // remap: Hs*Ws, Ws per class

@@ -338,7 +338,11 @@ static int conv_fwd_impl(const void* x, const void* w, const float* bias, const 
   if (rc) return rc;
   rc = weight_map(&p.mapB, w, Cout, R * S, Cin, 0, kc, block_n);
   if (rc) return rc;
-  p.out_mode = out_f32_atomic ? tc::OUT_F32_ATOMIC : tc::OUT_BF16;
+  // out_f32_atomic: 0 = bf16 output with the fused epilogue; 1 = fp32 atomic accumulation into y (the
+  // caller zeroes it); 2 = fp32 plain stores, split s into its own plane y[s][M][Cout] (deterministic:
+  // gabril_bias_act_cast_planes sums the planes in order; y holds gabril_conv_fwd_splits(...) planes)
+  p.out_mode = out_f32_atomic == 1 ? tc::OUT_F32_ATOMIC : out_f32_atomic == 2 ? tc::OUT_F32_STORE : tc::OUT_BF16;
+  if (out_f32_atomic == 2) p.split_stride = M * Cout;
   p.out = y; p.ldo = Cout;
   p.bias = bias; p.resid = (const bf16*)resid; p.gate = (const bf16*)gate; p.rowmask = rowmask;
   p.relu = relu;
@@ -349,6 +353,16 @@ static int conv_fwd_impl(const void* x, const void* w, const float* bias, const 
   const int mt[1] = {(int)((M + 128 * m_sub - 1) / (128 * m_sub))};
   finalize_schedule(p, mt, Cout / block_n, splits, m_sub * block_n, occ);
   return tc::launch(p, g_num_sms * occ, smem, stream);
+}
+
+// Number of split-K planes gabril_conv_fwd uses for a requested split count (planes of the
+// out_f32_atomic = 2 mode).
+int gabril_conv_fwd_splits(int Cin, int R, int S, int splits) {
+  const int kc = (Cin % 64 == 0) ? 64 : 32;
+  const int kb_total = R * S * (Cin / kc);
+  if (splits < 1) splits = 1;
+  const int per = (kb_total + splits - 1) / splits;
+  return (kb_total + per - 1) / per;
 }
 
 int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void* resid,

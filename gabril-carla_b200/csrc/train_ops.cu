@@ -51,12 +51,17 @@ colsum_bf16_kernel(const bf16* __restrict__ dy, float* __restrict__ db, long lon
 // y = act(x + bias) as bf16;  x fp32 [M, C] (C % 4 == 0)
 __global__ void __launch_bounds__(256)
 bias_act_cast_kernel(const float* __restrict__ x, const float* __restrict__ bias,
-                     bf16* __restrict__ y, float* __restrict__ y_f32, long long M, int C, int relu) {
+                     bf16* __restrict__ y, float* __restrict__ y_f32, long long M, int C, int relu,
+                     int planes) {
   const long long total4 = M * C / 4;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)((i * 4) % C);
     float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+    for (int s = 1; s < planes; ++s) {   // split-K partial planes, summed in a fixed order (deterministic)
+      const float4 t = __ldg(reinterpret_cast<const float4*>(x) + s * total4 + i);
+      v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+    }
     if (bias) {
       const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + c));
       v.x += bb.x; v.y += bb.y; v.z += bb.z; v.w += bb.w;
@@ -211,11 +216,16 @@ int gabril_colsum_bf16(const void* dy, float* db, long long M, int C, cudaStream
 
 int gabril_bias_act_cast(const float* x, const float* bias, void* y_bf16, float* y_f32, long long M,
                          int C, int relu, cudaStream_t stream) {
+  return gabril_bias_act_cast_planes(x, 1, bias, y_bf16, y_f32, M, C, relu, stream);
+}
+
+int gabril_bias_act_cast_planes(const float* x, int planes, const float* bias, void* y_bf16, float* y_f32,
+                                long long M, int C, int relu, cudaStream_t stream) {
   if (!x || !y_bf16) return GABRIL_ERR_NULL;
-  if (C % 4 || M <= 0) return GABRIL_ERR_BAD_SHAPE;
+  if (C % 4 || M <= 0 || planes < 1) return GABRIL_ERR_BAD_SHAPE;
   const int grid = blocks_for(M * C / 4, 256, 148 * 8);
   bias_act_cast_kernel<<<grid, 256, 0, stream>>>(x, bias, reinterpret_cast<bf16*>(y_bf16), y_f32, M,
-                                                 C, relu);
+                                                 C, relu, planes);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
 }

@@ -115,7 +115,13 @@ class StepEngine:
             b["K1"] = torch.empty(B, s.H1 * s.W1, device=dev, dtype=f32)
             b["K2"] = torch.empty(B, s.H2 * s.W2, device=dev, dtype=f32)
         b["mnmx"] = torch.empty(2, device=dev, dtype=torch.int32)
-        b["zf_raw"] = torch.empty(B, s.Z, device=dev, dtype=f32)
+        # split-K for the pre_actor GEMM: enough CTAs to cover the machine; every split stores its partial
+        # product into its own plane and bias_act_cast sums the planes in order (deterministic forward)
+        m_tiles = (B + 127) // 128
+        n_tiles = s.Z // 128 if s.Z >= 128 else 1
+        self.pre_splits = max(1, min(s.flat // 64, (2 * 148) // max(1, m_tiles * n_tiles)))
+        self.pre_planes = ops.conv_fwd_planes(s.flat, 1, 1, self.pre_splits)
+        b["zf_raw"] = torch.empty(self.pre_planes, B, s.Z, device=dev, dtype=f32)
         b["zf"] = torch.empty(B, s.Z, device=dev, dtype=bf)
         b["act1"] = torch.empty(B, s.Z, device=dev, dtype=bf)
         b["lg_raw"] = torch.empty(B, s.AP, device=dev, dtype=f32)
@@ -136,10 +142,6 @@ class StepEngine:
         b["da3"] = act(s.H3, s.W3, s.NH)
         b["da2p"], b["da1s"] = zact(self.SH, self.SW, s.C2), zact(self.SH, self.SW, 4 * s.C1)
         self.buf, self.B = b, B
-        # split-K for the pre_actor GEMM: enough CTAs to cover the machine
-        m_tiles = (B + 127) // 128
-        n_tiles = s.Z // 128 if s.Z >= 128 else 1
-        self.pre_splits = max(1, min(s.flat // 64, (2 * 148) // max(1, m_tiles * n_tiles)))
 
     # ------------------------------------------------------------------------------------------
     def zero_grad(self):
@@ -338,9 +340,8 @@ class StepEngine:
     def _heads_logits(self):
         """pre_actor + actor up to the raw (bias-free) logits (train_bc.py:79-82,290-291)."""
         s, a, b, B = self.spec, self.arena, self.buf, self.B
-        b["zf_raw"].zero_()
         ops.conv_fwd(b["z"].view(B, 1, 1, s.flat), a.WB("pre.w"), None, b["zf_raw"], 1, 1, 1, 0,
-                     out_f32_atomic=True, splits=self.pre_splits)
+                     out_f32_atomic=2, splits=self.pre_splits)
         ops.bias_act_cast(b["zf_raw"], a.P("pre.b"), b["zf"], relu=False)
         ops.conv_fwd(b["zf"].view(B, 1, 1, s.Z), a.WB("act.0.w"), a.P("act.0.b"), b["act1"], 1, 1, 1, 0,
                      relu=True)

@@ -92,6 +92,11 @@ def conv_out_hw(H, W, R, S, stride, pad):
     return (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
 
 
+def conv_fwd_planes(Cin, R, S, splits):
+    """Split-K planes conv_fwd(out_f32_atomic=2) writes for a requested split count."""
+    return int(_lib.load().gabril_conv_fwd_splits(c_int(Cin), c_int(R), c_int(S), c_int(splits)))
+
+
 def conv_fwd(x, w, bias, y, R, S, stride, pad, relu=False, resid=None, rowmask=None,
              out_f32_atomic=False, splits=1, bits_out=None):
     """x [N,H,W,Cin] bf16, w [Cout,R*S,Cin] bf16, bias fp32[Cout] or None -> y [N,OH,OW,Cout]."""
@@ -100,14 +105,15 @@ def conv_fwd(x, w, bias, y, R, S, stride, pad, relu=False, resid=None, rowmask=N
     Cout = w.shape[0]
     assert w.shape[1] == R * S and w.shape[2] == Cin, (w.shape, R, S, Cin)
     OH, OW = conv_out_hw(H, W, R, S, stride, pad)
-    assert y.numel() == N * OH * OW * Cout, (y.shape, N, OH, OW, Cout)
+    planes = conv_fwd_planes(Cin, R, S, splits) if int(out_f32_atomic) == 2 else 1
+    assert y.numel() == planes * N * OH * OW * Cout, (y.shape, planes, N, OH, OW, Cout)
     assert y.dtype == (torch.float32 if out_f32_atomic else torch.bfloat16)
     with _span("tc_gemm_kernel", f"fwd {Cin}->{Cout} k{R}s{stride}", 2.0 * N * OH * OW * Cout * R * S * Cin, "flop"):
         _epilogue_bits(None, bits_out, y)
         st = _fn("gabril_conv_fwd")(ptr(x), ptr(w), ptr(bias), ptr(resid), ptr(rowmask), ptr(y),
                                     c_int(N), c_int(H), c_int(W), c_int(Cin), c_int(Cout), c_int(R),
                                     c_int(S), c_int(stride), c_int(pad), c_int(int(relu)),
-                                    c_int(int(out_f32_atomic)), c_int(splits), stream())
+                                    c_int(int(out_f32_atomic)), c_int(splits), stream())  # 0 / 1 atomic / 2 planes
     _lib.check(st, "gabril_conv_fwd")
     return y
 
@@ -607,9 +613,11 @@ def colsum_bf16(dy, db):
 
 
 def bias_act_cast(x, bias, y_bf16, relu=False, y_f32=None):
+    """y = act(sum_planes x + bias) as bf16; x fp32 [M, C] or split-K planes [planes, M, C] (summed in order)."""
     _chk(x, torch.float32, "x"); _chk(y_bf16, torch.bfloat16, "y")
-    M, C = x.shape
-    _call("gabril_bias_act_cast", ptr(x), ptr(bias), ptr(y_bf16), ptr(y_f32), c_ll(M), c_int(C),
+    planes = x.shape[0] if x.dim() == 3 else 1
+    M, C = x.shape[-2], x.shape[-1]
+    _call("gabril_bias_act_cast_planes", ptr(x), c_int(planes), ptr(bias), ptr(y_bf16), ptr(y_f32), c_ll(M), c_int(C),
           c_int(int(relu)), stream())
 
 

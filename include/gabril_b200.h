@@ -61,8 +61,12 @@ int gabril_poll_error(void);
  * (zero borders). */
 int gabril_conv_epilogue_bits(const void* gate_bits, void* sign_bits_out);
 /* nn.Conv2d / nn.Linear forward — linear_models.py:141-207, train_bc.py:79-82.
- * y = relu?( conv(x, w) + bias + resid ) * rowmask ; out_f32_atomic: y is fp32 and the raw
- * products are atomically added (split-K linear), epilogue terms are then ignored. */
+ * y = relu?( conv(x, w) + bias + resid ) * rowmask ; out_f32_atomic = 1: y is fp32 and the raw
+ * products are atomically added (split-K linear; the caller zeroes y); = 2: y is fp32
+ * [planes][rows][Cout], every split stores its partial product into its own plane with plain
+ * stores (deterministic; planes = gabril_conv_fwd_splits(Cin, R, S, splits), summed in order by
+ * gabril_bias_act_cast_planes).  Epilogue terms are ignored in both fp32 modes. */
+int gabril_conv_fwd_splits(int Cin, int R, int S, int splits);
 int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void* resid,
                     const float* rowmask, void* y, int N, int H, int W, int Cin, int Cout, int R,
                     int S, int stride, int pad, int relu, int out_f32_atomic, int splits,
@@ -206,6 +210,10 @@ int gabril_colsum_bf16(const void* dy, float* db, long long M, int C, cudaStream
 /* y = act(x + bias) cast to bf16 (and optionally kept in fp32); x fp32 [M, C]. */
 int gabril_bias_act_cast(const float* x, const float* bias, void* y_bf16, float* y_f32, long long M,
                          int C, int relu, cudaStream_t stream);
+/* The same over `planes` split-K partial planes x[s][M][C] (gabril_conv_fwd with out_f32_atomic = 2),
+ * summed in plane order: a deterministic replacement of the fp32 atomic accumulation. */
+int gabril_bias_act_cast_planes(const float* x, int planes, const float* bias, void* y_bf16, float* y_f32,
+                                long long M, int C, int relu, cudaStream_t stream);
 /* nn.MSELoss on the action head (train_bc.py:292): logits = raw[:, :A] + bias;
  * part[b] = sum_k (logits - actions)^2; dlogits (bf16 [B, ld_d], zero padded) = 2 (l - a) gscale;
  * dbias[k] += sum_b dlogits. */
