@@ -27,6 +27,90 @@ struct Tile {
   int cls, m0, n0, tap0, ntaps, kb_begin, kb_end, split;
 };
 
+// ---------------------------------------------------------------------------------------------
+// bf16 epilogue of one 32-row x 32-column accumulator chunk (one warp).
+// The epilogue warp is alone (or nearly) on its scheduler: every instruction's fixed latency, every
+// branch on a runtime flag and every parameter load from the constant bank is exposed (ncu: stall_wait /
+// branch_resolving / short_scoreboard dominate, not memory).  So the chunk is compiled once per
+// COMBINATION of epilogue terms that the network uses (straight-line code, in-place packed math) and the
+// kernel picks the variant with one switch per chunk; EF_RUNTIME keeps the general form for the rest.
+// ---------------------------------------------------------------------------------------------
+template <uint32_t F>
+__device__ __forceinline__ void epi_item_bf16(uint32_t rt, uint32_t taddr, bool live, const float* bias,
+                                              const bf16* resid, const bf16* gate, uint32_t gword, float rmask,
+                                              uint32_t keep, bf16* out, uint32_t* bits) {
+  constexpr bool RT = (F & EF_RUNTIME) != 0;
+#define EPI_HAS(flag) (RT ? ((rt & (flag)) != 0u) : ((F & (flag)) != 0u))
+  uint32_t v[32];
+  // residual / gate operands: issued before the accumulator read so that their latency overlaps it
+  uint32_t rp[16], gp[16];
+  if (EPI_HAS(EF_RESID) && live) { ptx::ldg256(resid, rp); ptx::ldg256(resid + 16, rp + 8); }
+  if (EPI_HAS(EF_GATE) && live) { ptx::ldg256(gate, gp); ptx::ldg256(gate + 16, gp + 8); }
+  __syncwarp();
+  ptx::tmem_ld_32x32(taddr, v);
+  ptx::tmem_ld_wait();
+  if (!live) return;
+  uint64_t acc[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) acc[i] = ptx::pack2(v[2 * i], v[2 * i + 1]);
+  if (EPI_HAS(EF_BIAS)) {
+    const float4* b4 = reinterpret_cast<const float4*>(bias);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 b = b4[i];
+      acc[2 * i] = ptx::add2(acc[2 * i], ptx::pack2(__float_as_uint(b.x), __float_as_uint(b.y)));
+      acc[2 * i + 1] = ptx::add2(acc[2 * i + 1], ptx::pack2(__float_as_uint(b.z), __float_as_uint(b.w)));
+    }
+  }
+  if (EPI_HAS(EF_RESID)) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i)   // bf16 -> fp32 is a shift / mask of the packed word
+      acc[i] = ptx::add2(acc[i], ptx::pack2(rp[i] << 16, rp[i] & 0xffff0000u));
+  }
+  if (EPI_HAS(EF_RMASK)) {   // masks are >= 0, so scaling before the ReLU equals scaling after it
+    const uint64_t rmask2 = ptx::pack2(__float_as_uint(rmask), __float_as_uint(rmask));
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc[i] = ptx::mul2(acc[i], rmask2);
+  }
+  uint32_t w[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) w[i] = ptx::cvt_bf16x2(acc[i]);
+  if (EPI_HAS(EF_RELU)) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = ptx::relu_bf16x2(w[i]);
+  }
+  if (EPI_HAS(EF_GATE)) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] &= ptx::gt0_mask_bf16x2(gp[i]);
+  }
+  if (EPI_HAS(EF_GBITS)) {
+    // sign word layout: bit k = element 2k, bit 16 + k = element 2k + 1 (the two halves of packed word
+    // k).  Shift the pair of bits to the top of bytes 0/2 (k < 8) or 1/3, then one byte permute with sign
+    // replication expands them to a 0xffff / 0 mask per half.
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] &= ptx::prmt(gword << (7 - i), 0u, 0xaa88u);
+#pragma unroll
+    for (int i = 8; i < 16; ++i) w[i] &= ptx::prmt(gword << (15 - i), 0u, 0xbb99u);
+  }
+  if (EPI_HAS(EF_KEEP)) {   // border / padding pixels of a zero-bordered output store exact zeros
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] &= keep;
+  }
+  ptx::stg256(out, w);
+  ptx::stg256(out + 16, w + 8);
+  if (EPI_HAS(EF_BITS)) {
+    // ReLU's backward predicate on the stored bf16 value; two partial words keep the OR chains short
+    uint32_t s0 = 0u, s1 = 0u;
+#pragma unroll
+    for (int i = 0; i < 16; i += 2) {
+      s0 |= ptx::gt0_mask_bf16x2(w[i]) & (0x00010001u << i);
+      s1 |= ptx::gt0_mask_bf16x2(w[i + 1]) & (0x00010001u << (i + 1));
+    }
+    *bits = s0 | s1;
+  }
+#undef EPI_HAS
+}
+
 __device__ __forceinline__ int fdiv(int n, const FastDiv& d) {
   return (int)((__umulhi((uint32_t)n, d.mul) + (uint32_t)n) >> d.shr);
 }
@@ -62,7 +146,9 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
 // kEpiGroups = 1: 256 threads, two CTAs per SM (each other's epilogue hides behind the other's MMAs);
 // kEpiGroups = 2: 384 threads for the single-occupancy launches (flat-slab layers with resident weights,
 // 256-row tiles, 512-column wgrad accumulators), where nothing else covers the epilogue's latencies.
-template <int kEpiGroups>
+// kEF: the epilogue this instantiation is compiled for: one EPI_VARIANTS mask (bf16 output, straight-line
+// code), EF_F32 (fp32 stores / atomics only: wgrad, split-K), or EF_RUNTIME (everything, runtime flags).
+template <int kEpiGroups, uint32_t kEF>
 __global__ void __launch_bounds__(32 * (kFirstEpilogueWarp + 4 * kEpiGroups), kEpiGroups == 1 ? 2 : 1)
 tc_gemm_kernel(const __grid_constant__ Params p) {
   extern __shared__ uint8_t smem_raw[];
@@ -442,9 +528,14 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
     const int grp = (warp - kFirstEpilogueWarp) >> 2;
     int tcount = 0;
     const bool eprof = (p.debug & 4) != 0 && warp == kFirstEpilogueWarp && lane == 0;
-    const bool dbg_nostore = (p.debug & 8) != 0, dbg_nobias = (p.debug & 16) != 0;
-    long long e_wait = 0, e_ld = 0, e_tile = 0, e_n = 0, e_pre = 0, e_math = 0, e_st = 0;
+    long long e_wait = 0, e_tile = 0, e_n = 0, e_pre = 0;
     const int n_chunks = (p.block_n + 31) >> 5;
+    const bool out_bf16 = p.out_mode == OUT_BF16;
+    const uint32_t epi_flags = p.epi_flags;
+    const float* bias_base = bias_sm ? bias_s : p.bias;
+    const bf16* resid_base = p.resid;
+    const bf16* gate_base = p.gate;
+    uint32_t* bits_base = p.bits_out;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tcount) {
       if (p.epi_tile_split && (tcount & (kEpiGroups - 1)) != grp) continue;   // the other group's tile
       const long long ec0 = eprof ? clock64() : 0;
@@ -534,84 +625,23 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
               keep = (ih < 0 || ih >= p.s2d_H || iw < 0 || iw >= p.s2d_W) ? 0u : 0xffffffffu;
               rmask = qd == 0 ? rm4[0] : qd == 1 ? rm4[1] : qd == 2 ? rm4[2] : rm4[3];
             }
-            const uint64_t rmask2 = ptx::pack2(__float_as_uint(rmask), __float_as_uint(rmask));
-            uint32_t v[32];
-            // residual / gate operands of this chunk: issued before the accumulator read so that their
-            // global-memory latency overlaps it
-            uint32_t rp[16], gp[16];
-            if (p.out_mode == OUT_BF16 && live) {
-              if (p.resid) { ptx::ldg256(p.resid + off0 + c, rp); ptx::ldg256(p.resid + off0 + c + 16, rp + 8); }
-              if (p.gate) { ptx::ldg256(p.gate + off0 + c, gp); ptx::ldg256(p.gate + off0 + c + 16, gp + 8); }
+            if constexpr ((kEF & EF_F32) == 0u) {
+              if ((kEF & EF_RUNTIME) == 0u || out_bf16) {
+                const long long off = off0 + c;
+                const uint32_t gword = ci == 0 ? gw[0] : ci == 1 ? gw[1] : ci == 2 ? gw[2] : gw[3];
+                epi_item_bf16<kEF>(epi_flags, t_lane + a * p.block_n + c, live, bias_base + col0, resid_base + off,
+                                   gate_base + off, gword, rmask, keep, reinterpret_cast<bf16*>(p.out) + off,
+                                   bits_base + (off >> 5));
+                continue;
+              }
             }
+            if constexpr ((kEF & (EF_F32 | EF_RUNTIME)) != 0u) {
+            uint32_t v[32];
             __syncwarp();
-            const long long ec2 = eprof ? clock64() : 0;
             ptx::tmem_ld_32x32(t_lane + a * p.block_n + c, v);
             ptx::tmem_ld_wait();
-            const long long ec3 = eprof ? clock64() : 0;
-            if (eprof) e_ld += ec3 - ec2;
             if (!live) continue;
-            if (p.out_mode == OUT_BF16) {
-              const long long off = off0 + c;
-              uint64_t acc[16];
-#pragma unroll
-              for (int i = 0; i < 16; ++i) acc[i] = ptx::pack2(v[2 * i], v[2 * i + 1]);
-              if (p.bias && !dbg_nobias) {
-                const float4* b4 = bias_sm ? reinterpret_cast<const float4*>(bias_s + col0)
-                                           : reinterpret_cast<const float4*>(p.bias + col0);
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                  const float4 b = b4[i];
-                  acc[2 * i] = ptx::add2(acc[2 * i], ptx::pack2(__float_as_uint(b.x), __float_as_uint(b.y)));
-                  acc[2 * i + 1] = ptx::add2(acc[2 * i + 1], ptx::pack2(__float_as_uint(b.z), __float_as_uint(b.w)));
-                }
-              }
-              if (p.resid) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i)   // bf16 -> fp32 is a shift / mask of the packed word
-                  acc[i] = ptx::add2(acc[i], ptx::pack2(rp[i] << 16, rp[i] & 0xffff0000u));
-              }
-              if (p.rowmask) {   // masks are >= 0, so scaling before the ReLU equals scaling after it
-#pragma unroll
-                for (int i = 0; i < 16; ++i) acc[i] = ptx::mul2(acc[i], rmask2);
-              }
-              uint32_t w[16];
-#pragma unroll
-              for (int i = 0; i < 16; ++i) w[i] = ptx::cvt_bf16x2(acc[i]);
-              if (p.relu) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) w[i] = ptx::relu_bf16x2(w[i]);
-              }
-              if (p.gate) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) w[i] &= ptx::gt0_mask_bf16x2(gp[i]);
-              }
-              if (p.gate_bits) {
-                // sign word layout: bit k = element 2k, bit 16 + k = element 2k + 1 (the two halves of
-                // packed word k).  Shift the pair of bits to the top of bytes 0/2 (k < 8) or 1/3, then one
-                // byte permute with sign replication expands them to a 0xffff / 0 mask per half.
-                const uint32_t g = ci == 0 ? gw[0] : ci == 1 ? gw[1] : ci == 2 ? gw[2] : gw[3];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) w[i] &= ptx::prmt(g << (7 - i), 0u, 0xaa88u);
-#pragma unroll
-                for (int i = 8; i < 16; ++i) w[i] &= ptx::prmt(g << (15 - i), 0u, 0xbb99u);
-              }
-              if (p.border_h > 0) {   // border / padding pixels of a zero-bordered output store exact zeros
-#pragma unroll
-                for (int i = 0; i < 16; ++i) w[i] &= keep;
-              }
-              bf16* o = reinterpret_cast<bf16*>(p.out) + off;
-              const long long ec4 = eprof ? clock64() : 0;
-              if (eprof) e_math += ec4 - ec3;
-              if (!dbg_nostore || w[15] == 0x12345678u) { ptx::stg256(o, w); ptx::stg256(o + 16, w + 8); }
-              if (p.bits_out) {
-                // ReLU's backward predicate on the stored bf16 value
-                uint32_t sign_word = 0u;
-#pragma unroll
-                for (int i = 0; i < 16; ++i) sign_word |= ptx::gt0_mask_bf16x2(w[i]) & (0x00010001u << i);
-                p.bits_out[off >> 5] = sign_word;
-              }
-              if (eprof) e_st += clock64() - ec4;
-            } else {
+            {
               float f[32];
 #pragma unroll
               for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]);
@@ -641,6 +671,7 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
                 }
               }
             }
+            }   // fp32 output path
           }
         }
       }  // sub
@@ -653,9 +684,7 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
     }
     if (eprof) {
       atomicAdd(&g_prof[8], (unsigned long long)e_pre); atomicAdd(&g_prof[9], (unsigned long long)e_wait);
-      atomicAdd(&g_prof[10], (unsigned long long)e_ld); atomicAdd(&g_prof[11], (unsigned long long)e_tile);
-      atomicAdd(&g_prof[12], (unsigned long long)e_n); atomicAdd(&g_prof[13], (unsigned long long)e_math);
-      atomicAdd(&g_prof[14], (unsigned long long)e_st);
+      atomicAdd(&g_prof[11], (unsigned long long)e_tile); atomicAdd(&g_prof[12], (unsigned long long)e_n);
     }
   }
 
@@ -711,6 +740,13 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     return GABRIL_ERR_BAD_SHAPE;
   }
   // a tile that is a single 32-column item cannot be shared by two epilogue groups: they alternate tiles
+  p.epi_flags = (p.bias ? EF_BIAS : 0u) | (p.resid ? EF_RESID : 0u) | (p.relu ? EF_RELU : 0u) |
+                (p.gate_bits ? EF_GBITS : 0u) | (p.rowmask ? EF_RMASK : 0u) | (p.border_h > 0 ? EF_KEEP : 0u) |
+                (p.bits_out ? EF_BITS : 0u) | (p.gate ? EF_GATE : 0u);
+  p.epi_mode = 0;
+#define EPI_PICK(idx, F) if (p.epi_flags == (F)) p.epi_mode = idx;
+  EPI_VARIANTS(EPI_PICK)
+#undef EPI_PICK
   if (p.epi_groups != 2) p.epi_groups = 1;
   p.epi_tile_split = (p.epi_groups > 1 && p.kind == KIND_FWD && p.m_sub == 1 && p.block_n <= 32 && p.acc_bufs >= 2) ? 1 : 0;
   if (p.out_mode == OUT_BF16 &&
@@ -731,19 +767,34 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     p.fd_ohw[c] = magic(p.OHW[c]);
     p.fd_ow[c] = magic(p.OW[c]);
   }
+  // kernel table: [group count - 1][variant]; variant 0 = general form, EPI_VARIANTS indices, last = fp32 only
+  typedef void (*KernelFn)(const Params);
+  constexpr int kF32Slot = 12;
+#define EPI_FN(idx, F) tc_gemm_kernel<kG, (F)>,
+  static const KernelFn table[2][kF32Slot + 1] = {
+#define kG 1
+      {tc_gemm_kernel<1, EF_RUNTIME>, EPI_VARIANTS(EPI_FN) tc_gemm_kernel<1, EF_F32>},
+#undef kG
+#define kG 2
+      {tc_gemm_kernel<2, EF_RUNTIME>, EPI_VARIANTS(EPI_FN) tc_gemm_kernel<2, EF_F32>},
+#undef kG
+  };
+#undef EPI_FN
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(g_attr_once, [] {
     // static smem: barriers, TMEM base, bias vector (< 2 KB)
-    attr_err = cudaFuncSetAttribute(tc_gemm_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(tc_gemm_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
+    for (int g = 0; g < 2 && attr_err == cudaSuccess; ++g)
+      for (int v = 0; v <= kF32Slot && attr_err == cudaSuccess; ++v)
+        attr_err = cudaFuncSetAttribute(reinterpret_cast<const void*>(table[g][v]),
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048);
   });
   if (attr_err != cudaSuccess) return gabril_set_cuda_error(attr_err);
   if (p.total_tiles <= 0) return GABRIL_OK;
   // one persistent CTA per SM (smem / TMEM are sized for single occupancy)
   const unsigned grid = (unsigned)std::min(p.total_tiles, num_sms);
-  if (p.epi_groups == 2) tc_gemm_kernel<2><<<grid, 32 * (kFirstEpilogueWarp + 8), smem_bytes, stream>>>(p);
-  else tc_gemm_kernel<1><<<grid, 32 * (kFirstEpilogueWarp + 4), smem_bytes, stream>>>(p);
+  const int slot = (p.debug & 32) ? 0 : (p.out_mode != OUT_BF16 ? kF32Slot : p.epi_mode);
+  const KernelFn fn = table[p.epi_groups - 1][slot];
+  fn<<<grid, 32 * (kFirstEpilogueWarp + 4 * p.epi_groups), smem_bytes, stream>>>(p);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
 }

@@ -26,6 +26,25 @@ constexpr int kFirstProducerWarp = 1;  // warps 1..3
 constexpr int kFirstEpilogueWarp = 4;  // warps 4..7 (group 0), 8..11 (group 1); TMEM lane quarter = warp % 4
 
 enum Kind { KIND_FWD = 0, KIND_WGRAD = 1 };
+
+// Terms of the bf16 epilogue (see epi_item_bf16 in tc_gemm.cu) and the combinations compiled as
+// straight-line variants (index, mask): every conv / linear launch of the training step hits one of them.
+enum : uint32_t {
+  EF_BIAS = 1u, EF_RESID = 2u, EF_RELU = 4u, EF_GBITS = 8u, EF_RMASK = 16u, EF_KEEP = 32u, EF_BITS = 64u,
+  EF_GATE = 128u, EF_F32 = 1u << 30, EF_RUNTIME = 1u << 31
+};
+#define EPI_VARIANTS(X)                                                                     \
+  X(1, EF_BIAS | EF_RELU | EF_BITS)             /* conv_2 .. conv_5 forward */              \
+  X(2, EF_BIAS | EF_RELU | EF_BITS | EF_KEEP)   /* conv_1 forward (zero border quadrants) */ \
+  X(3, EF_RELU | EF_BITS)                       /* residual 3x3 forward */                  \
+  X(4, EF_RESID | EF_RELU | EF_BITS)            /* residual 1x1 forward + skip */           \
+  X(5, EF_GBITS)                                /* data gradients through a ReLU */         \
+  X(6, EF_RESID | EF_GBITS)                     /* residual 3x3 dgrad + skip gradient */    \
+  X(7, EF_BIAS)                                 /* conv_6 forward */                        \
+  X(8, EF_BIAS | EF_RMASK)                      /* conv_6 forward with the GMD mask */      \
+  X(9, EF_RESID)                                /* pre_actor dgrad + regulariser gradient */ \
+  X(10, 0u)                                     /* plain dgrad */                           \
+  X(11, EF_BIAS | EF_RELU)                      /* actor.0 forward */
 enum OutMode { OUT_BF16 = 0, OUT_F32_STORE = 1, OUT_F32_ATOMIC = 2 };
 
 // n / d for 0 <= n < 2^31 as (umulhi(n, mul) + n) >> shr (round-up multiplier, Granlund-Montgomery):
@@ -127,6 +146,8 @@ struct Params {
   // epilogue groups split the work by whole tiles (a tile is a single 32-column item) instead of by items
   int epi_tile_split;
   int epi_groups;   // 1 (256 threads, two CTAs per SM) or 2 (384 threads, single-occupancy launches)
+  uint32_t epi_flags;   // EF_* terms of this launch's bf16 epilogue, filled by launch()
+  int epi_mode;         // index into EPI_VARIANTS, 0 = general form
   long long tap_stride;  // WGRAD: element (m, tap, n) at out + m*ldo + tap*tap_stride + n
   long long split_stride;  // FWD split-K with plain stores: split s writes its partial at out + s*split_stride
   // magic numbers of the divisions above, filled by launch() from the fields they belong to
