@@ -53,7 +53,7 @@ def default_tree() -> Dict[str, Any]:
         "scheduler": {"type": "cosine_warmup", "step_size": 50, "gamma": 0.5, "eta_min": 1e-6,
                       "warmup_steps": 500, "T_0": 10, "T_mult": 1, "pct_start": 0.3,
                       "anneal_strategy": "cos", "div_factor": 25.0, "final_div_factor": 10000.0},
-        "training": {"seed": 42, "epochs": 500, "device": "cuda:0", "use_amp": True, "use_compile": True, "cuda_graph": False,
+        "training": {"seed": 42, "epochs": 500, "device": "cuda:0", "use_amp": True, "use_compile": True, "cuda_graph": True,
                      "compile_backend": "inductor", "compile_mode": "default",
                      "gradient_accumulation_steps": 1, "save_interval": 50,
                      "distributed": {"enabled": False, "backend": "nccl", "find_unused_parameters": False,

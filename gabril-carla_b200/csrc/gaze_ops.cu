@@ -380,8 +380,27 @@ __global__ void gmd_init_kernel(unsigned int* mnmx) {
   mnmx[1] = 0u;
 }
 
+// Philox4x32-10 (Salmon et al., SC'11): counter (c0..c3), key (k0, k1) -> four uniform 32-bit words.
+// Used for GMD's uniform draw A ~ U[0,1) (gaze_utils.py:36 draws it with torch.rand) when the caller
+// passes no A: the draw then lives inside the kernel, so a GMD / IGMD step is CUDA-graph capturable.
+// The stream is (seed, step counter read from device memory, draw id, element / 4).
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+
+__global__ void gmd_rng_advance_kernel(unsigned long long* rng) { rng[1] += 1ull; }
+
 __global__ void __launch_bounds__(256)
 gmd_mask_kernel(const float* __restrict__ K, const float* __restrict__ A,
+                const unsigned long long* __restrict__ rng, int draw_id,
                 const unsigned int* __restrict__ mnmx, float* __restrict__ rowmask,
                 float* __restrict__ keep_out, long long total, float drop_p, int test_mode,
                 int layout, int h, int w, int SH, int SW) {
@@ -404,7 +423,21 @@ gmd_mask_kernel(const float* __restrict__ K, const float* __restrict__ A,
               ? ((b * SH + (oy >> 1)) * SW + (ox >> 1)) * 4 + ((oy & 1) * 2 + (ox & 1))
               : (b * SH + oy) * SW + ox;
     }
-    rowmask[o] = test_mode ? kt : ((A[idx] < kt) ? 1.f : 0.f);
+    float a_draw = 0.f;
+    if (!test_mode) {
+      if (A) {
+        a_draw = A[idx];
+      } else {
+        const unsigned long long seed = rng[0], step = rng[1];
+        const uint4 r = philox4x32_10(make_uint4((uint32_t)(idx >> 2), (uint32_t)(idx >> 34), (uint32_t)step,
+                                                 (uint32_t)(step >> 32) ^ ((uint32_t)draw_id << 24)),
+                                      make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+        const int lane4 = (int)(idx & 3);
+        const uint32_t bits = lane4 == 0 ? r.x : lane4 == 1 ? r.y : lane4 == 2 ? r.z : r.w;
+        a_draw = (float)(bits >> 8) * (1.0f / 16777216.0f);   // 24 random mantissa bits: [0, 1)
+      }
+    }
+    rowmask[o] = test_mode ? kt : ((a_draw < kt) ? 1.f : 0.f);
   }
 }
 
@@ -1022,16 +1055,31 @@ int gabril_gmd_mask_layout(const float* g, const float* sel, const float* A, flo
                            unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B, int S,
                            int H, int W, int h, int w, float drop_p, int test_mode, int layout,
                            int SH, int SW, cudaStream_t stream) {
+  return gabril_gmd_mask_rng(g, sel, A, nullptr, 0, K_ws, mnmx_ws, rowmask, keep_out, B, S, H, W, h, w, drop_p,
+                             test_mode, layout, SH, SW, stream);
+}
+
+int gabril_rng_advance(unsigned long long* rng_state, cudaStream_t stream) {
+  if (!rng_state) return GABRIL_ERR_NULL;
+  gmd_rng_advance_kernel<<<1, 1, 0, stream>>>(rng_state);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_gmd_mask_rng(const float* g, const float* sel, const float* A, const unsigned long long* rng_state,
+                        int draw_id, float* K_ws, unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B,
+                        int S, int H, int W, int h, int w, float drop_p, int test_mode, int layout, int SH, int SW,
+                        cudaStream_t stream) {
   if (layout == GABRIL_MASK_S2D && (2 * SH < h + 2 || 2 * SW < w + 2)) return GABRIL_ERR_BAD_SHAPE;
   if (layout == GABRIL_MASK_BORDERED && (SH < h + 2 || SW < w + 2)) return GABRIL_ERR_BAD_SHAPE;
   if (layout < GABRIL_MASK_PLAIN || layout > GABRIL_MASK_BORDERED) return GABRIL_ERR_BAD_SHAPE;
-  if (!g || !K_ws || !mnmx_ws || !rowmask || (!A && !test_mode)) return GABRIL_ERR_NULL;
+  if (!g || !K_ws || !mnmx_ws || !rowmask || (!A && !rng_state && !test_mode)) return GABRIL_ERR_NULL;
   if (B <= 0 || S < 1) return GABRIL_ERR_BAD_SHAPE;
   const long long total = (long long)B * h * w;
   gmd_init_kernel<<<1, 1, 0, stream>>>(mnmx_ws);
   gmd_keep_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(g, sel, K_ws, mnmx_ws, B, S, H, W, h, w);
-  gmd_mask_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(K_ws, A, mnmx_ws, rowmask, keep_out,
-                                                                     total, drop_p, test_mode, layout,
+  gmd_mask_kernel<<<grid_for(total, 256, 148 * 8), 256, 0, stream>>>(K_ws, A, rng_state, draw_id, mnmx_ws, rowmask,
+                                                                     keep_out, total, drop_p, test_mode, layout,
                                                                      h, w, SH, SW);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;

@@ -43,8 +43,9 @@ class StepEngine:
         self.device = arena.device
         self.B = 0
         self.buf: Dict[str, torch.Tensor] = {}
-        self.rng = torch.Generator(device=self.device)
-        self.rng.manual_seed(seed)
+        # GMD / IGMD uniform draws: a Philox stream inside the mask kernel, (seed, step) kept in device
+        # memory so that the draw is part of the captured step (gaze_utils.py:36 draws with torch.rand)
+        self.rng_state = torch.tensor([int(seed) & 0x7FFFFFFFFFFFFFFF, 0], dtype=torch.int64, device=self.device)
         self.injected_A: Optional[torch.Tensor] = None  # parity tests inject GMD's uniform draw
         self.injected_A_igmd = None                     # ... and IGMD's pair ([B,H1*W1], [B,H2*W2])
         if prob_dist_type not in ops.DIST_KINDS:
@@ -61,7 +62,8 @@ class StepEngine:
         self._ev = {k: torch.cuda.Event() for k in ("in", "heat", "z", "head", "reg")} if self._side else {}
         self._reg_pending = False
         self.use_graph = os.environ.get("GABRIL_GRAPH", "0") == "1"      # train_step() only
-        self._graphs, self._warm_B = {}, 0
+        self._graphs, self._warm_B, self._warm_store_B = {}, 0, 0
+        self._own_in, self._own_inputs = {}, False
         self._colsum_pending, self._cs_i = False, 0
         self._cs_ev = [torch.cuda.Event() for _ in range(8)] if self._side else []
         if self._side:
@@ -248,26 +250,26 @@ class StepEngine:
                 self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
         rowmask = None
         if self.use_gmd:
-            # A is drawn before the interpolation, like gaze_utils.py:36
-            A = self.injected_A if self.injected_A is not None else torch.rand(
-                B, s.n, device=self.device, dtype=torch.float32, generator=self.rng)
-            ops.gmd_mask(b["heat"], A.reshape(B, s.n), s.h, s.w, 0.7, False, rowmask=b["rowmask"],
-                         ws=(b["K"], b["mnmx"]), sel=self.sel)
+            # A ~ U[0,1) (gaze_utils.py:36): injected by the parity tests, else drawn inside the kernel
+            A = self.injected_A.reshape(B, s.n) if self.injected_A is not None else None
+            ops.gmd_mask(b["heat"], A, s.h, s.w, 0.7, False, rowmask=b["rowmask"],
+                         ws=(b["K"], b["mnmx"]), sel=self.sel, rng_state=self.rng_state, draw_id=0)
             rowmask = b["rowmask"]
         igmd = None
         if self.use_igmd:
             # apply_gmd_dropout after conv_1 + ReLU (90x160) and conv_2 + ReLU (45x80): the same keep
             # map as GMD, interpolated to each size, its own uniform draw per layer
+            A1 = A2 = None
             if self.injected_A_igmd is not None:
-                A1, A2 = self.injected_A_igmd
-            else:
-                A1 = torch.rand(B, s.H1 * s.W1, device=self.device, dtype=torch.float32, generator=self.rng)
-                A2 = torch.rand(B, s.H2 * s.W2, device=self.device, dtype=torch.float32, generator=self.rng)
-            ops.gmd_mask(b["heat"], A1.reshape(B, -1), s.H1, s.W1, 0.7, False, rowmask=b["rm1"],
-                         ws=(b["K1"], b["mnmx"]), sel=self.sel, layout="s2d", grid=(self.SH, self.SW))
-            ops.gmd_mask(b["heat"], A2.reshape(B, -1), s.H2, s.W2, 0.7, False, rowmask=b["rm2"],
-                         ws=(b["K2"], b["mnmx"]), sel=self.sel, layout="bordered", grid=(self.SH, self.SW))
+                A1, A2 = (t.reshape(B, -1) for t in self.injected_A_igmd)
+            ops.gmd_mask(b["heat"], A1, s.H1, s.W1, 0.7, False, rowmask=b["rm1"], ws=(b["K1"], b["mnmx"]),
+                         sel=self.sel, layout="s2d", grid=(self.SH, self.SW), rng_state=self.rng_state, draw_id=1)
+            ops.gmd_mask(b["heat"], A2, s.H2, s.W2, 0.7, False, rowmask=b["rm2"], ws=(b["K2"], b["mnmx"]),
+                         sel=self.sel, layout="bordered", grid=(self.SH, self.SW), rng_state=self.rng_state,
+                         draw_id=2)
             igmd = (b["rm1"], b["rm2"])
+        if self.use_gmd or self.use_igmd:
+            ops.rng_advance(self.rng_state)     # next step draws a fresh stream
         self._encoder_fwd(rowmask, igmd)
         self._heads_fwd(actions, center)
         return b["losses"]
@@ -412,16 +414,19 @@ class StepEngine:
             self._mask_rows(b["dz"], rowmask)
 
     # ------------------------------------------------------------------------------------------
+    GRAPH_KEYS = 4   # pointer-keyed graphs kept before the engine switches to its own input buffers
+
     def train_step(self, frames: torch.Tensor, gaze: torch.Tensor, actions: torch.Tensor):
-        """zero_grad + forward + backward.  With use_graph (and nothing that draws random numbers or
-        accumulates over micro-batches) the step is two CUDA-graph replays, split at the point where
-        the heads' gradients are complete so that the data-parallel bucket hooks still fire between
-        them: ~60 kernel launches become 2, which is what a 128-sample shard (1.6 ms of device time)
-        needs when eight ranks share the host's cores.  Graphs are keyed by the input buffers; the
-        first step at a new batch size runs eagerly (allocations), tracing (ops.trace) always does."""
-        graphable = (self.use_graph and self.grad_accum == 1 and ops._TRACE is None
-                     and not ((self.use_gmd and self.injected_A is None)
-                              or (self.use_igmd and self.injected_A_igmd is None)))
+        """zero_grad + forward + backward.  With use_graph (and no gradient accumulation over
+        micro-batches) the step is two CUDA-graph replays, split at the point where the heads'
+        gradients are complete so that the data-parallel bucket hooks still fire between them: ~60
+        kernel launches become 2, which is what a 128-sample shard (1.6 ms of device time) needs when
+        eight ranks share the host's cores.  GMD / IGMD steps are captured too (the uniform draw is a
+        Philox stream inside the mask kernel).  Graphs are keyed by the input buffers; a caller that
+        hands fresh tensors every step (more than GRAPH_KEYS distinct buffer sets) is served from
+        engine-owned input buffers instead (one device-to-device copy, one graph), so the cache is
+        bounded.  The first step at a new batch size runs eagerly (allocations), tracing always does."""
+        graphable = self.use_graph and self.grad_accum == 1 and ops._TRACE is None
         B = frames.shape[0]
         if not graphable or self._warm_B != B:
             self.zero_grad()
@@ -432,9 +437,46 @@ class StepEngine:
         key = (frames.data_ptr(), gaze.data_ptr(), actions.data_ptr(), tuple(frames.shape), tuple(actions.shape))
         g = self._graphs.get(key)
         if g is None:
-            if len(self._graphs) >= 8:
-                self._graphs.clear()
-            g = self._graphs[key] = self._capture(frames, gaze, actions)
+            n_ptr_keys = sum(1 for k in self._graphs if k[0] != "own")
+            if n_ptr_keys >= self.GRAPH_KEYS or self._own_inputs:
+                # unstable input pointers: stage into our own buffers, one graph per shape
+                self._own_inputs = True
+                key = ("own", tuple(frames.shape), tuple(gaze.shape), tuple(actions.shape))
+                st = self._own_in.get(key)
+                if st is None:
+                    st = self._own_in[key] = tuple(torch.empty_like(t, memory_format=torch.contiguous_format)
+                                                   for t in (frames, gaze, actions))
+                for dst, src in zip(st, (frames, gaze, actions)):
+                    dst.copy_(src, non_blocking=True)
+                frames, gaze, actions = st
+                g = self._graphs.get(key)
+            if g is None:
+                g = self._graphs[key] = self._capture(lambda: self.forward(frames, gaze, actions),
+                                                      keep=(frames, gaze, actions))
+        return self._replay(g)
+
+    def train_step_store(self, store, step_idx: torch.Tensor):
+        """train_step for the device-resident feed (forward_store): the sampled step indices are copied
+        into a static buffer, so one graph per (store, batch size) serves every step."""
+        graphable = self.use_graph and self.grad_accum == 1 and ops._TRACE is None
+        B = step_idx.numel()
+        if not graphable or self._warm_store_B != B:
+            self.zero_grad()
+            self.forward_store(store, step_idx)
+            self.backward()
+            self._warm_store_B = B if B == self.B else 0
+            return self.buf["losses"]
+        key = ("store", id(store), B)
+        st = self._own_in.get(key)
+        if st is None:
+            st = self._own_in[key] = torch.empty(B, device=self.device, dtype=torch.int64)
+        st.copy_(step_idx.reshape(-1), non_blocking=True)
+        g = self._graphs.get(key)
+        if g is None:
+            g = self._graphs[key] = self._capture(lambda: self.forward_store(store, st), keep=(store, st))
+        return self._replay(g)
+
+    def _replay(self, g):
         # graphs exist only for grad_accum == 1: every replayed step closes its window, so both
         # bucket hooks fire on every step (the captured zero_grad never runs on the host)
         g[0].replay()
@@ -446,17 +488,16 @@ class StepEngine:
             self.on_all_grads_ready()
         return self.buf["losses"]
 
-    def _capture(self, frames, gaze, actions):
+    def _capture(self, forward_fn, keep=()):
         torch.cuda.synchronize(self.device)
         ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
         with torch.cuda.graph(ga, capture_error_mode="thread_local"):
             self.zero_grad()
-            self.forward(frames, gaze, actions)
+            forward_fn()
             self._backward_heads()
         with torch.cuda.graph(gb, pool=ga.pool(), capture_error_mode="thread_local"):
             self._encoder_bwd()
-        self._keep = getattr(self, "_keep", []) + [(frames, gaze, actions)]   # the graphs hold raw pointers
-        return ga, gb
+        return ga, gb, keep   # the graphs hold raw pointers: `keep` pins the captured input tensors
 
     def _encoder_bwd(self):
         """Backward of the encoder from b["dz"] (gradient w.r.t. z) to every encoder weight gradient."""

@@ -444,13 +444,19 @@ def gaze_splat(gaze, out, ktab, Lk_host, agg_coeff, step_coeff, normalize_base, 
 MASK_LAYOUTS = {"plain": 0, "s2d": 1, "bordered": 2}
 
 
+def rng_advance(rng_state):
+    """Bump the step counter of the device-side Philox state (int64 [2] = seed, step)."""
+    _chk(rng_state, torch.int64, "rng_state")
+    _call("gabril_rng_advance", ptr(rng_state), stream())
+
+
 def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=None, ws=None, sel=None,
-             layout="plain", grid=(0, 0)):
+             layout="plain", grid=(0, 0), rng_state=None, draw_id=0):
     """g fp32 [B,S,H,W], A fp32 [B,h*w] -> rowmask fp32 [B,h*w] (gaze_utils.py:33-52); sel fp32 [B]
     (optional): samples with sel <= 0 see a zero heat map (train_bc.py:258).  layout / grid=(SH, SW):
     storage order of the mask (include/gabril_b200.h, gabril_gmd_mask_layout); rowmask must then be
     given, sized for that storage."""
-    _chk(g, torch.float32, "g"); _chk(A, torch.float32, "A")
+    _chk(g, torch.float32, "g"); _chk(A, torch.float32, "A"); _chk(rng_state, torch.int64, "rng_state")
     B, S, H, W = g.shape
     if rowmask is None:
         rowmask = torch.empty(B, h * w, device=g.device, dtype=torch.float32)
@@ -458,7 +464,8 @@ def gmd_mask(g, A, h, w, drop_p=0.7, test_mode=False, rowmask=None, keep_out=Non
         ws = (torch.empty(B, h * w, device=g.device, dtype=torch.float32),
               torch.empty(2, device=g.device, dtype=torch.int32))
     assert layout == "plain" or rowmask is not None
-    _call("gabril_gmd_mask_layout", ptr(g), ptr(sel), ptr(A), ptr(ws[0]), ptr(ws[1]), ptr(rowmask), ptr(keep_out),
+    _call("gabril_gmd_mask_rng", ptr(g), ptr(sel), ptr(A), ptr(rng_state), c_int(draw_id), ptr(ws[0]), ptr(ws[1]),
+          ptr(rowmask), ptr(keep_out),
           c_int(B), c_int(S), c_int(H), c_int(W), c_int(h), c_int(w), c_float(drop_p),
           c_int(int(test_mode)), c_int(MASK_LAYOUTS[layout]), c_int(grid[0]), c_int(grid[1]), stream(), work=float(B * h * w * (16 * S * 4 + 16)))
     return rowmask

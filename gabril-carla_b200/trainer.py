@@ -378,8 +378,14 @@ class BCTrainer(BaseTrainer):
         train_bc.py:203-299.  The returned tensor's .backward() runs the kernel backward."""
         gaze_key = self.cfg.data.get("gaze_key", "gaze_coords")
         dev = self.device
+        use_graph = bool(self.cfg.training.get("cuda_graph", True)) and self.engine.grad_accum == 1
         if "store" in batch:   # device-resident feed (data.ShardedBatches(fused=True))
-            losses = self.engine.forward_store(batch["store"], batch["step_idx"])
+            if use_graph:
+                self.engine.use_graph = True
+                losses = self.engine.train_step_store(batch["store"], batch["step_idx"])
+                self._bwd_done = True
+            else:
+                losses = self.engine.forward_store(batch["store"], batch["step_idx"])
             actor, reg, total = self.engine.losses_host()
             anchor = torch.zeros((), device=dev, requires_grad=True)
             loss = _StepLoss.apply(anchor, self, losses[2])
@@ -390,7 +396,7 @@ class BCTrainer(BaseTrainer):
         actions = batch["actions"].to(dev, non_blocking=True)
         if gaze.dim() == 4:
             gaze = gaze.reshape(gaze.shape[0], gaze.shape[1], -1)
-        if bool(self.cfg.training.get("cuda_graph", False)) and self.engine.grad_accum == 1:
+        if use_graph:
             # training.cuda_graph=true: the whole step (zero_grad + forward + backward) is replayed from
             # CUDA graphs captured over static input buffers (StepEngine.train_step); the later
             # loss.backward() then has nothing left to launch

@@ -145,6 +145,15 @@ int gabril_gmd_mask_layout(const float* g, const float* sel, const float* A, flo
                            unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B, int S,
                            int H, int W, int h, int w, float drop_p, int test_mode, int layout,
                            int SH, int SW, cudaStream_t stream);
+/* The same with GMD's uniform draw made inside the kernel when A is NULL (train mode): Philox4x32-10 keyed
+ * by rng_state[0] (seed) with the counter (rng_state[1] = step, draw_id, element index), 24-bit uniforms in
+ * [0, 1) like torch.rand (gaze_utils.py:36).  The state lives in device memory and gabril_rng_advance
+ * bumps the step once per training step, so the whole step (draw included) is CUDA-graph capturable. */
+int gabril_gmd_mask_rng(const float* g, const float* sel, const float* A, const unsigned long long* rng_state,
+                        int draw_id, float* K_ws, unsigned int* mnmx_ws, float* rowmask, float* keep_out, int B,
+                        int S, int H, int W, int h, int w, float drop_p, int test_mode, int layout, int SH, int SW,
+                        cudaStream_t stream);
+int gabril_rng_advance(unsigned long long* rng_state, cudaStream_t stream);
 /* out[b, c, j] = z[b, c, j] * rowmask[b, j] on the reference's fp32 NCHW layout. */
 int gabril_rowmask_apply_nchw(const float* z, const float* rowmask, float* out, int B, int C, int n,
                               cudaStream_t stream);

@@ -146,6 +146,46 @@ def test_gmd_mask(G):
     assert (out_t - O.gmd_dropout(z, heat, A, test_mode=True)).abs().max().item() <= 1e-5
 
 
+def test_gmd_in_kernel_philox_statistics(G):
+    """A ~ U[0,1) drawn inside the mask kernel (Philox4x32-10 keyed by a device-resident (seed, step)): the
+    mask is a Bernoulli(K~) field — empirical keep rate within 4 sigma of mean(K~) overall and per K~ bin —
+    reproducible for a given state, different after gabril_rng_advance and for another draw id or seed."""
+    B = 64
+    _, gaze, _ = make_batch(B, seed=9)
+    heat = O.stack_heatmaps(gaze, 2, 1, 180, 320, 30.0).to(DEV)
+    keep = torch.empty(B, 760, device=DEV)
+    st = torch.tensor([1234, 0], dtype=torch.int64, device=DEV)
+    m0 = G.ops.gmd_mask(heat, None, 20, 38, 0.7, False, keep_out=keep, rng_state=st, draw_id=0).clone()
+    m0b = G.ops.gmd_mask(heat, None, 20, 38, 0.7, False, rng_state=st, draw_id=0).clone()
+    assert torch.equal(m0, m0b) and set(m0.unique().tolist()) <= {0.0, 1.0}
+    m_other_draw = G.ops.gmd_mask(heat, None, 20, 38, 0.7, False, rng_state=st, draw_id=1).clone()
+    G.ops.rng_advance(st)
+    assert st.tolist() == [1234, 1]
+    m1 = G.ops.gmd_mask(heat, None, 20, 38, 0.7, False, rng_state=st, draw_id=0).clone()
+    st2 = torch.tensor([99, 0], dtype=torch.int64, device=DEV)
+    m_seed = G.ops.gmd_mask(heat, None, 20, 38, 0.7, False, rng_state=st2, draw_id=0).clone()
+    K = keep.cpu().double().flatten()
+    n = K.numel()
+    for m in (m0, m1, m_other_draw, m_seed):
+        x = m.cpu().double().flatten()
+        sigma = (K * (1 - K)).sum().sqrt() / n
+        assert abs(x.mean() - K.mean()) <= 4 * sigma, (x.mean().item(), K.mean().item(), sigma.item())
+        for lo, hi in ((0.3, 0.35), (0.35, 0.6), (0.6, 1.01)):        # keep rate follows K~ bin by bin
+            sel = (K >= lo) & (K < hi)
+            if sel.sum() > 2000:
+                s_bin = (K[sel] * (1 - K[sel])).sum().sqrt() / sel.sum()
+                assert abs(x[sel].mean() - K[sel].mean()) <= 4.5 * s_bin
+    # independent streams: agreement rate between two masks = E[K^2 + (1-K)^2], not 1
+    expect = (K * K + (1 - K) * (1 - K)).mean().item()
+    for other in (m1, m_other_draw, m_seed):
+        agree = (m0 == other).double().mean().item()
+        assert abs(agree - expect) <= 0.02, (agree, expect)
+    # neighbouring elements are uncorrelated (lag-1 autocorrelation of the uniform-ised residual)
+    r = (m0.cpu().double().flatten() - K)
+    ac = (r[1:] * r[:-1]).mean() / (r * r).mean()
+    assert abs(ac.item()) <= 0.02
+
+
 def test_get_gaze_mask_fwd_bwd(G):
     g = torch.Generator().manual_seed(8)
     z = torch.randn(6, 64, 20, 38, generator=g) * 3.0

@@ -130,3 +130,48 @@ def test_trainer_uses_the_fused_feed(tmp_path):
     for k in logs:               # split-K heads: see test_forward_store_equals_...
         assert abs(logs[k] - logs2[k]) <= 2e-4 * abs(logs[k]), (k, logs[k], logs2[k])
     assert b["obs"]["image"].shape == (16, 2, 180, 320, 3)     # reference keys on demand
+
+
+def test_store_feed_and_gmd_steps_replay_from_graphs():
+    """CUDA-graph replay of the modes users run: the device-resident store feed (step indices staged into
+    a static buffer) and GMD with the in-kernel uniform draw; and the graph cache stays bounded when a
+    caller hands fresh input tensors every step."""
+    import gabril_carla_b200  # noqa: F401
+    from gabril_carla_b200.data import synthetic_store
+    from gabril_carla_b200.engine import StepEngine
+    from gabril_carla_b200.gaze import GazePreprocessor
+    from gabril_carla_b200.model import ParamArena, PolicySpec
+    st = synthetic_store(64, 2, seed=3).to(DEV)
+    spec = PolicySpec(2)
+    out = {}
+    for mode in ("eager", "graph"):
+        arena = ParamArena(spec, DEV)
+        arena.init_reference_style(seed=1)
+        eng = StepEngine(spec, arena, GazePreprocessor(device=DEV), gaze_method="Reg", dp_method="GMD", seed=5)
+        eng.use_graph = mode == "graph"
+        losses = []
+        g = torch.Generator().manual_seed(0)
+        for step in range(4):
+            idx = torch.randint(0, 64, (8,), generator=g).to(DEV)       # a fresh index tensor every step
+            eng.train_step_store(st, idx)
+            losses.append(eng.buf["losses"].clone())
+        out[mode] = (torch.stack(losses), arena.g.clone(), eng)
+    le, ge, _ = out["eager"]
+    lg, gg, eng = out["graph"]
+    assert len(eng._graphs) == 1                                        # one graph, replayed on steps 3 and 4
+    assert torch.equal(le, lg), (le, lg)          # same Philox stream (seed, step) and a deterministic forward
+    assert ((ge - gg).norm() / ge.norm()).item() <= 1e-5
+    assert eng.rng_state.tolist()[1] == 4                               # the step counter advanced inside the graphs
+    # bounded cache: more distinct buffer sets than GRAPH_KEYS -> engine-owned inputs, one more graph
+    from tests.synth import make_batch
+    eng2 = StepEngine(spec, out["graph"][2].arena, GazePreprocessor(device=DEV), gaze_method="Reg")
+    eng2.use_graph = True
+    ref = None
+    for i in range(StepEngine.GRAPH_KEYS + 4):
+        batch = tuple(t.to(DEV) for t in make_batch(4, seed=40))        # new tensors, same values
+        eng2.train_step(*batch)
+        torch.cuda.synchronize()
+        cur = eng2.buf["losses"].clone()
+        ref = cur if ref is None else ref
+        assert torch.equal(cur, ref)
+    assert eng2._own_inputs and len(eng2._graphs) <= StepEngine.GRAPH_KEYS + 1
