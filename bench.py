@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--graph", action="store_true", help="CUDA-graph replays of the step (StepEngine.train_step)")
     ap.add_argument("--no-graph", action="store_true", help="eager launches")
     ap.add_argument("--no-store-feed", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the short runs of the other configurations")
     ap.add_argument("--store-steps", type=int, default=8192, help="steps held by the HBM-resident store leg")
     ap.add_argument("--trace-out", default="")
     return ap.parse_args()
@@ -125,42 +126,118 @@ def main_reference(args):
 # GPU leg
 # ------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    """SM clock / power / throttle reasons sampled DURING the timed regions: NVML every 5 ms (a short
+    timed region still gets tens of samples), nvidia-smi as the fallback."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop_flag = index, [], False
+        self.index, self.rows, self.stop_flag, self.source = index, [], False, "nvml"
+        self.sm_max = None
 
-    def run(self):
+    def _nvml_loop(self):
+        import pynvml as N
+        N.nvmlInit()
+        h = N.nvmlDeviceGetHandleByIndex(self.index)
+        self.sm_max = float(N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM))
+        bits = [getattr(N, n, 0) for n in ("nvmlClocksEventReasonHwSlowdown", "nvmlClocksEventReasonHwThermalSlowdown",
+                                           "nvmlClocksEventReasonSwThermalSlowdown", "nvmlClocksEventReasonSwPowerCap")]
+        if not all(bits):
+            bits = [getattr(N, n, 0) for n in ("nvmlClocksThrottleReasonHwSlowdown", "nvmlClocksThrottleReasonHwThermalSlowdown",
+                                               "nvmlClocksThrottleReasonSwThermalSlowdown", "nvmlClocksThrottleReasonSwPowerCap")]
+        get_reasons = getattr(N, "nvmlDeviceGetCurrentClocksEventReasons", None) or N.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            r = get_reasons(h)
+            self.rows.append((float(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)), N.nvmlDeviceGetPowerUsage(h) / 1e3,
+                              [bool(r & b) for b in bits]))
+            time.sleep(0.005)
+
+    def _smi_loop(self):
+        self.source = "nvidia-smi"
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                       "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                parts = [p.strip() for p in out.strip().split(",")]
-                if len(parts) >= 7:
-                    self.rows.append(parts)
+                p = [x.strip() for x in out.strip().split(",")]
+                if len(p) >= 7:
+                    self.sm_max = float(p[1])
+                    self.rows.append((float(p[0]), float(p[2]), [x.lower().startswith("active") for x in p[3:7]]))
             except Exception:
                 pass
             time.sleep(0.1)
 
+    def run(self):
+        try:
+            self._nvml_loop()
+        except Exception:
+            self._smi_loop()
+
     def summary(self):
         if not self.rows:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        sm = sorted(float(r[0]) for r in self.rows)
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
-                "samples": len(self.rows), "power_w_max": max(float(r[2]) for r in self.rows)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock samples"]}
+        sm = sorted(r[0] for r in self.rows)
+        reasons = [n for i, n in enumerate(self.NAMES) if any(r[2][i] for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.sm_max, "reasons": reasons, "samples": len(self.rows),
+                "power_w_max": max(r[1] for r in self.rows), "source": self.source}
+
+
+def synth_batch(B, seed):
+    """B DISTINCT synthetic Bench2Drive-shaped samples (tests.synth.make_batch in chunks of 64, one seed per
+    chunk), pinned on the host."""
+    import torch
+    from tests.synth import make_batch
+    parts = [make_batch(min(64, B - lo), seed=seed + 7919 * (lo // 64)) for lo in range(0, B, 64)]
+    return tuple(torch.cat([p[i] for p in parts]).contiguous().pin_memory() for i in range(3))
+
+
+def quick_run(device, gaze_method, dp_method, rgb, B, steps=10, warmup=3, seed=0):
+    """Short device-timed run of another configuration (CUDA-graph replays, inputs resident in HBM)."""
+    import torch
+    from gabril_carla_b200.engine import StepEngine
+    from gabril_carla_b200.gaze import GazePreprocessor
+    from gabril_carla_b200.model import ParamArena, PolicySpec
+    spec = PolicySpec(6 if rgb else 2)
+    arena = ParamArena(spec, device)
+    arena.init_reference_style(seed=42)
+    eng = StepEngine(spec, arena, GazePreprocessor(device=str(device)), gaze_method=gaze_method,
+                     dp_method=dp_method, grayscale=not rgb, seed=seed)
+    eng.use_graph = True
+    base = synth_batch(min(B, 256), seed=300)
+    reps = (B + base[0].shape[0] - 1) // base[0].shape[0]
+    batch = tuple(t.repeat((reps,) + (1,) * (t.dim() - 1))[:B].contiguous().to(device) for t in base)
+    n = [0]
+
+    def step():
+        n[0] += 1
+        eng.train_step(*batch)
+        eng.adam_step(n[0], 5e-4)
+    for _ in range(max(3, warmup)):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    losses = eng.losses_host()
+    del eng, arena, batch
+    torch.cuda.empty_cache()
+    return {"value": B / (ms * 1e-3), "unit": "samples/s", "ms_per_step": ms, "per_gpu_batch": B,
+            "gaze_method": gaze_method, "dp_method": dp_method, "rgb": bool(rgb), "steps": steps,
+            "cuda_graph": True, "loss_total": losses[2]}
 
 
 def load_tc_traffic(args, B):
     """dram__bytes_read.sum + dram__bytes_write.sum of every tc_gemm_kernel launch of ONE step, from the
     committed ncu pass (profiles/r1_tc_traffic.json); only quoted for the configuration it was taken on."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_tc_traffic.json")) as f:
+        name = "r2_tc_traffic.json" if os.path.exists(os.path.join(ROOT, "profiles", "r2_tc_traffic.json")) else "r1_tc_traffic.json"
+        with open(os.path.join(ROOT, "profiles", name)) as f:
             t = json.load(f)
         if B == 1024 and not args.rgb and args.gaze_method == "Reg" and args.dp_method == "None":
             return t["dram_bytes_per_step"], t["source"]
@@ -214,10 +291,8 @@ def main_ours(args):
     if args.no_graph:
         eng.use_graph = False
 
-    # synthetic batch of this rank's shard: 64 distinct samples tiled to B, pinned on the host
-    base = make_batch(min(B, 64), seed=100 + rank)
-    reps = (B + base[0].shape[0] - 1) // base[0].shape[0]
-    host = tuple(t.repeat((reps,) + (1,) * (t.dim() - 1))[:B].contiguous().pin_memory() for t in base)
+    # synthetic batch of this rank's shard: B distinct samples, pinned on the host
+    host = synth_batch(B, seed=100 + 1000 * rank)
     dev_batch = tuple(t.to(device) for t in host)
     h2d = sum(t.numel() * t.element_size() for t in host)
     lr, step_no = 5e-4, [0]
@@ -302,9 +377,7 @@ def main_ours(args):
 
         def store_step(idx):
             step_no[0] += 1
-            eng.zero_grad()
-            eng.forward_store(store, idx)
-            eng.backward()
+            eng.train_step_store(store, idx)   # graph replays: the step indices are staged into a static buffer
             red.finish()
             eng.adam_step(step_no[0], lr, grad_scale=red.grad_scale)
 
@@ -351,7 +424,9 @@ def main_ours(args):
         "roofline": {"bound": "tensor", "kernel": "tc_gemm_kernel (every conv / linear fwd, dgrad, wgrad launch of one step)",
                      "achieved": achieved, "peak": tf_sust, "unit": "TFLOP/s", "frac": achieved / tf_sust,
                      "peak_source": f"bf16_tflops_sustained, {how}", "traffic": traffic,
-                     "traffic_unit": "bytes per step (all tc_gemm_kernel launches), like achieved", "traffic_source": traffic_src,
+                     "traffic_unit": "bytes per step (all tc_gemm_kernel launches), like achieved",
+                     "traffic_source": (f"CONSTANT from a committed ncu pass, not measured in this run: {traffic_src}"
+                                        if traffic_src else None),
                      "algorithmic_flop_per_step": tc_flop,
                      "tc_ms_per_step": tc_ms, "all_traced_ms_per_step": traced_ms,
                      "step_flop_frac_of_peak": FLOP_PER_SAMPLE[gray] * B / (ms * 1e-3) / 1e12 / tf_sust},
@@ -361,7 +436,20 @@ def main_ours(args):
         line["store_feed"] = {"value": total / (store_ms * 1e-3), "unit": "samples/s", "ms_per_step": store_ms,
                               "store_steps": args.store_steps, "h2d_bytes_per_step": 0,
                               "note": "HBM-resident uint8 frame store, random step indices per step, "
-                                      "StepEngine.forward_store (window table + patch kernel reading the store)"}
+                                      "StepEngine.train_step_store (window table + frame kernel reading the store)"}
+    # ---- the other BASELINE.json configurations on one GPU (short runs; the headline stays cfg2 / 1024) ----
+    if world == 1 and not args.no_extra:
+        extra = {}
+        for key, (gm, dpm, rgb, bb) in {"cfg3_gmd": ("Reg", "GMD", False, B), "cfg1_bc": ("None", "None", False, B),
+                                       "rgb": (args.gaze_method, args.dp_method, True, B),
+                                       "b128": (args.gaze_method, args.dp_method, False, 128),
+                                       "b512": (args.gaze_method, args.dp_method, False, 512),
+                                       "b2000": (args.gaze_method, args.dp_method, False, 2000)}.items():
+            try:
+                extra[key] = quick_run(device, gm, dpm, rgb, bb)
+            except Exception as e:  # noqa: BLE001
+                extra[key] = {"error": repr(e)[:200]}
+        line["extra_configs"] = extra
     if args.trace_out:
         agg = {}
         for k, lab, work, unit, t_ms in rows:
