@@ -11,12 +11,8 @@ import torch
 from . import _lib
 from ._lib import c_int, ptr, stream
 
-_NAIVE = os.environ.get("GABRIL_NAIVE_CONV", "0") == "1"
-
-
 def _fn(name):
-    lib = _lib.init()
-    return getattr(lib, name + ("_naive" if _NAIVE else ""))
+    return getattr(_lib.init(), name)
 
 
 # ---- optional per-launch tracing (bench.py's roofline leg): CUDA events around every call ----
@@ -77,8 +73,6 @@ def _epilogue_bits(gate_bits, bits_out, out):
             continue
         if t.dtype != torch.int32 or not t.is_cuda or not t.is_contiguous() or t.numel() * 32 != out.numel():
             raise ValueError(f"{name}: expected contiguous CUDA int32 tensor of {out.numel() // 32} words")
-    if _NAIVE:
-        raise RuntimeError("sign-bit gates exist only on the tcgen05 path")
     _lib.check(_lib.init().gabril_conv_epilogue_bits(ptr(gate_bits), ptr(bits_out)), "gabril_conv_epilogue_bits")
 
 

@@ -80,18 +80,6 @@ int gabril_conv_dgrad(const void* dy, const void* w, const void* addend, const v
 int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int Cin,
                       int Cout, int R, int S, int stride, int pad, int direct_store,
                       cudaStream_t stream);
-/* CUDA-core cross-check versions of the three contracts (bring-up only). */
-int gabril_conv_fwd_naive(const void* x, const void* w, const float* bias, const void* resid,
-                          const float* rowmask, void* y, int N, int H, int W, int Cin, int Cout,
-                          int R, int S, int stride, int pad, int relu, int out_f32_atomic,
-                          int splits, cudaStream_t stream);
-int gabril_conv_dgrad_naive(const void* dy, const void* w, const void* addend, const void* gate,
-                            const float* rowmask, void* dx, int N, int H, int W, int Cin, int Cout,
-                            int R, int S, int stride, int pad, cudaStream_t stream);
-int gabril_conv_wgrad_naive(const void* dy, const void* x, float* dw, int N, int H, int W, int Cin,
-                            int Cout, int R, int S, int stride, int pad, int direct_store,
-                            cudaStream_t stream);
-
 /* ---- frame formatting: data_loader_robomimic.py:144-157 (_gather_last_s_frames) + :179-202
  * (_format_obs_image).  frames: uint8 [B, L, H, W, 3]; the S frames ending at `center` are taken
  * (indices clamped into [0, L-1], bit-exact integer gather). ---------------------------------- */
