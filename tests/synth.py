@@ -110,3 +110,13 @@ def make_weights_gp(c_in, seed=9):
                 fan_in //= 4
             dec[k] = torch.randn(shp, generator=g) * ((2.0 / fan_in) ** 0.5)
     return {"encoder": enc, "decoder": dec}
+
+
+def make_weights_gril(seed=9, z_dim=256, max_points=5):
+    """Deterministic weights of the GRIL gaze-coordinate head nn.Sequential(Linear(z, z), ReLU, Linear(z, 2P))
+    (train_bc.py:84-86), reference state_dict keys."""
+    g = torch.Generator().manual_seed(seed)
+    return {"0.weight": torch.randn(z_dim, z_dim, generator=g) / z_dim ** 0.5,
+            "0.bias": (torch.rand(z_dim, generator=g) - 0.5) * 0.1,
+            "2.weight": torch.randn(2 * max_points, z_dim, generator=g) / z_dim ** 0.5,
+            "2.bias": (torch.rand(2 * max_points, generator=g) - 0.5) * 0.1}
