@@ -32,13 +32,17 @@ __device__ __forceinline__ float to_gray(float r, float g, float b) {
 }
 
 // One thread = one cell row (u, v, a): 4 pixels x S frames -> 4*C0 consecutive bf16 of the cell.
-template <int S_, bool GRAY>
+// MODE (gray stacks only; train_bc.py:252-264, heat = the gaze heat maps [B, S, H, W], sel = ivg or NULL = all):
+//   1  gaze.method = Mask / AGIL's second encoder: obs * (ivg * heat + (1 - ivg))
+//   2  gaze.method = ViSaRL: channels (obs_0 .. obs_S-1, ivg*heat_0 .. ivg*heat_S-1), C0 = 2 S
+template <int S_, bool GRAY, int MODE>
 __global__ void __launch_bounds__(256)
 obs_s4d_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__ widx,
+               const float* __restrict__ heat, const float* __restrict__ sel,
                bf16* __restrict__ out, long long cells, int L, int center, int H, int W, int SH, int SW,
                int Cp) {
   constexpr int CP = GRAY ? 1 : 3;
-  constexpr int C0 = S_ * CP;
+  constexpr int C0 = S_ * CP * (MODE == 2 ? 2 : 1);
   __shared__ float lut[256];   // u8 / 255.0f, correctly rounded (same bits as the division)
   lut[threadIdx.x & 255] = __fdiv_rn((float)(threadIdx.x & 255), 255.0f);
   __syncthreads();
@@ -74,6 +78,19 @@ obs_s4d_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__
         }
         if (GRAY) {
           px[k][fs] = ok ? to_gray(ch[0], ch[1], ch[2]) : 0.f;
+          if (MODE != 0) {
+            float gv = 0.f, iv = 1.f;
+            if (ok) {
+              gv = __ldg(heat + ((b * S_ + fs) * H + y) * (long long)W + x0 + k);
+              if (sel) iv = __ldg(sel + b) > 0.f ? 1.f : 0.f;
+            }
+            if (MODE == 1) {   // x * (ivg * g + (1 - ivg) * 1), every op rounded like the reference's torch ops
+              const float m = __fadd_rn(__fmul_rn(iv, gv), __fsub_rn(1.f, iv));
+              px[k][fs] = __fmul_rn(px[k][fs], m);
+            } else {
+              px[k][S_ + fs] = ok ? __fmul_rn(iv, gv) : 0.f;
+            }
+          }
         } else {
           px[k][fs * 3 + 0] = ok ? ch[0] : 0.f;
           px[k][fs * 3 + 1] = ok ? ch[1] : 0.f;
@@ -139,24 +156,29 @@ __global__ void conv1_fold_kernel(const float* __restrict__ dw4, float* __restri
   }
 }
 
-int obs_s4d_impl(const uint8_t* frames, const long long* widx, void* x4, int B, int L, int S, int center, int H,
-                 int W, int grayscale, int Cp, int SH, int SW, cudaStream_t stream) {
-  const int C0 = S * (grayscale ? 1 : 3);
+int obs_s4d_impl(const uint8_t* frames, const long long* widx, const float* heat, const float* sel, int mode,
+                 void* x4, int B, int L, int S, int center, int H, int W, int grayscale, int Cp, int SH, int SW,
+                 cudaStream_t stream) {
+  const int C0 = S * (grayscale ? 1 : 3) * (mode == 2 ? 2 : 1);
   if (!frames || !x4 || B <= 0 || S < 1 || S > 4 || (W & 3) || (H & 3) || SH != H / 4 + 2 || SW != W / 4 + 2 ||
-      Cp < 16 * C0 || (Cp & 7))
+      Cp < 16 * C0 || (Cp & 7) || mode < 0 || mode > 2)
     return GABRIL_ERR_BAD_SHAPE;
+  // the reference multiplies / concatenates a [B, S, H, W] heat-map stack with the [B, S*C', H, W] frames: the
+  // shapes only agree for grayscale stacks (train_bc.py:261,264 raise for RGB)
+  if (mode != 0 && (!grayscale || !heat)) return GABRIL_ERR_BAD_SHAPE;
   const long long cells = (long long)B * SH * SW;
   const int grid = (int)std::min<long long>((cells * 4 + 255) / 256, 148 * 16);
-#define LAUNCH_S4D(SS, GG)                                                                              \
-  obs_s4d_kernel<SS, GG><<<grid, 256, 0, stream>>>(frames, widx, (bf16*)x4, cells, L, center, H, W, SH, \
-                                                   SW, Cp)
-  if (grayscale) {
-    switch (S) { case 1: LAUNCH_S4D(1, true); break; case 2: LAUNCH_S4D(2, true); break;
-                 case 3: LAUNCH_S4D(3, true); break; default: LAUNCH_S4D(4, true); break; }
-  } else {
-    switch (S) { case 1: LAUNCH_S4D(1, false); break; case 2: LAUNCH_S4D(2, false); break;
-                 case 3: LAUNCH_S4D(3, false); break; default: LAUNCH_S4D(4, false); break; }
-  }
+#define LAUNCH_S4D(SS, GG, MM)                                                                            \
+  obs_s4d_kernel<SS, GG, MM><<<grid, 256, 0, stream>>>(frames, widx, heat, sel, (bf16*)x4, cells, L, center, H, \
+                                                       W, SH, SW, Cp)
+#define LAUNCH_S4D_S(GG, MM)                                                                       \
+  switch (S) { case 1: LAUNCH_S4D(1, GG, MM); break; case 2: LAUNCH_S4D(2, GG, MM); break;         \
+               case 3: LAUNCH_S4D(3, GG, MM); break; default: LAUNCH_S4D(4, GG, MM); break; }
+  if (!grayscale) { LAUNCH_S4D_S(false, 0) }
+  else if (mode == 0) { LAUNCH_S4D_S(true, 0) }
+  else if (mode == 1) { LAUNCH_S4D_S(true, 1) }
+  else { LAUNCH_S4D_S(true, 2) }
+#undef LAUNCH_S4D_S
 #undef LAUNCH_S4D
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
@@ -169,13 +191,21 @@ extern "C" {
 int gabril_obs_s4d(const uint8_t* frames, void* x4, int B, int L, int S, int center, int H, int W,
                    int grayscale, int Cp, int SH, int SW, cudaStream_t stream) {
   if (L < 1 || center < 0) return GABRIL_ERR_BAD_SHAPE;
-  return obs_s4d_impl(frames, nullptr, x4, B, L, S, center, H, W, grayscale, Cp, SH, SW, stream);
+  return obs_s4d_impl(frames, nullptr, nullptr, nullptr, 0, x4, B, L, S, center, H, W, grayscale, Cp, SH, SW, stream);
+}
+
+int gabril_obs_s4d_gaze(const uint8_t* frames, const long long* widx, const float* heat, const float* sel, int mode,
+                        void* x4, int B, int L, int S, int center, int H, int W, int grayscale, int Cp, int SH,
+                        int SW, cudaStream_t stream) {
+  if (!widx && (L < 1 || center < 0)) return GABRIL_ERR_BAD_SHAPE;
+  return obs_s4d_impl(frames, widx, heat, sel, mode, x4, B, widx ? S : L, S, widx ? S - 1 : center, H, W, grayscale,
+                      Cp, SH, SW, stream);
 }
 
 int gabril_obs_s4d_store(const uint8_t* store, const long long* widx, void* x4, int B, int S, int H, int W,
                          int grayscale, int Cp, int SH, int SW, cudaStream_t stream) {
   if (!widx) return GABRIL_ERR_BAD_SHAPE;
-  return obs_s4d_impl(store, widx, x4, B, S, S, S - 1, H, W, grayscale, Cp, SH, SW, stream);
+  return obs_s4d_impl(store, widx, nullptr, nullptr, 0, x4, B, S, S, S - 1, H, W, grayscale, Cp, SH, SW, stream);
 }
 
 int gabril_conv1_s4d_expand(const float* w1, void* w4, int C1, int C0, int K1p, int Cp, cudaStream_t stream) {

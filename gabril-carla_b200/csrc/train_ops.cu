@@ -101,6 +101,82 @@ mse_head_kernel(const float* __restrict__ raw, int ld_raw, const float* __restri
   if (dbias && threadIdx.x < A) atomicAdd(dbias + threadIdx.x, sdb[threadIdx.x]);
 }
 
+// GRIL (train_bc.py:182-192): pred = raw[:, :P2] + bias over the samples that use gaze (sel > 0 or sel NULL);
+// reg = clamp(mean((pred - target)^2) + 1e-8, 0, 100) -> reg_part[0] (the other entries 0, so that
+// finalize_losses reads it with reg_scale 1); dpred (bf16 [B, ld_d], zero padded) = d(gscale * reg)/dpred,
+// zero when the clamp saturates or no sample uses gaze; dbias[k] += sum_b dpred.  One block: fixed order.
+__global__ void __launch_bounds__(1024)
+gril_head_kernel(const float* __restrict__ raw, int ld_raw, const float* __restrict__ bias,
+                 const float* __restrict__ target, long long tgt_bstride, const float* __restrict__ sel, int P2,
+                 bf16* __restrict__ dpred, int ld_d, float* __restrict__ dbias, float* __restrict__ reg_part, int B,
+                 float gscale) {
+  __shared__ float s_sq[1024], s_n[1024], s_db[32];
+  float sq = 0.f, n = 0.f;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    if (sel && sel[b] <= 0.f) continue;
+    n += 1.f;
+    for (int k = 0; k < P2; ++k) {
+      const float d = raw[(long long)b * ld_raw + k] + bias[k] - target[(long long)b * tgt_bstride + k];
+      sq = fmaf(d, d, sq);
+    }
+  }
+  s_sq[threadIdx.x] = sq; s_n[threadIdx.x] = n;
+  if (threadIdx.x < 32) s_db[threadIdx.x] = 0.f;
+  __syncthreads();
+  for (int o = blockDim.x / 2; o > 0; o >>= 1) {
+    if (threadIdx.x < o) { s_sq[threadIdx.x] += s_sq[threadIdx.x + o]; s_n[threadIdx.x] += s_n[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  const float n_sel = s_n[0];
+  const float mse = n_sel > 0.f ? s_sq[0] / (n_sel * (float)P2) + 1e-8f : 0.f;
+  const bool live = n_sel > 0.f && mse >= 0.f && mse <= 100.f;      // inside the clamp: gradient flows
+  const float gs = live ? 2.f * gscale / (n_sel * (float)P2) : 0.f;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) {
+    reg_part[b] = (b == 0) ? (n_sel > 0.f ? fminf(fmaxf(mse, 0.f), 100.f) : 0.f) : 0.f;
+    const bool use = !(sel && sel[b] <= 0.f);
+    for (int k = 0; k < ld_d; ++k) {
+      float g = 0.f;
+      if (use && k < P2) {
+        g = gs * (raw[(long long)b * ld_raw + k] + bias[k] - target[(long long)b * tgt_bstride + k]);
+        if (dbias) atomicAdd(&s_db[k], g);
+      }
+      dpred[(long long)b * ld_d + k] = __float2bfloat16(g);
+    }
+  }
+  __syncthreads();
+  if (dbias && threadIdx.x < P2) dbias[threadIdx.x] += s_db[threadIdx.x];
+}
+
+// gaze.method = AGIL (train_bc.py:268-272): z = where(ivg > 0, 0.5 (z + z_agil), z) [* rowmask], bf16 NHWC in place
+__global__ void __launch_bounds__(256)
+agil_combine_kernel(bf16* __restrict__ z, const bf16* __restrict__ z2, const float* __restrict__ sel,
+                    const float* __restrict__ rowmask, long long total2, int per_sample2, int C2) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total2;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long b = i / per_sample2;
+    const uint32_t a = reinterpret_cast<const uint32_t*>(z)[i], c = reinterpret_cast<const uint32_t*>(z2)[i];
+    float lo = bf16lo(a), hi = bf16hi(a);
+    if (!sel || sel[b] > 0.f) { lo = 0.5f * (lo + bf16lo(c)); hi = 0.5f * (hi + bf16hi(c)); }
+    if (rowmask) { const float m = rowmask[i / C2]; lo *= m; hi *= m; }
+    reinterpret_cast<uint32_t*>(z)[i] = pack_bf16x2(lo, hi);
+  }
+}
+
+// its backward: dz_agil = [ivg > 0] 0.5 dz; dz = (ivg > 0 ? 0.5 : 1) dz (in place)
+__global__ void __launch_bounds__(256)
+agil_split_kernel(bf16* __restrict__ dz, bf16* __restrict__ dz2, const float* __restrict__ sel, long long total2,
+                  int per_sample2) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total2;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long b = i / per_sample2;
+    const uint32_t a = reinterpret_cast<const uint32_t*>(dz)[i];
+    const bool use = !sel || sel[b] > 0.f;
+    const float lo = bf16lo(a), hi = bf16hi(a);
+    reinterpret_cast<uint32_t*>(dz2)[i] = use ? pack_bf16x2(0.5f * lo, 0.5f * hi) : 0u;
+    if (use) reinterpret_cast<uint32_t*>(dz)[i] = pack_bf16x2(0.5f * lo, 0.5f * hi);
+  }
+}
+
 // losses[0] = actor = sum(actor_part) / (B*A); losses[1] = reg = sum(reg_part) * reg_scale;
 // losses[2] = lambda * reg + actor.  One block, fixed summation order (deterministic).
 __global__ void __launch_bounds__(256)
@@ -239,6 +315,38 @@ int gabril_mse_head(const float* raw, int ld_raw, const float* bias, const float
                                                        logits_out,
                                                        reinterpret_cast<bf16*>(dlogits_bf16), ld_d,
                                                        dbias, part, B, gscale);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_gril_head(const float* raw, int ld_raw, const float* bias, const float* target, long long tgt_bstride,
+                     const float* sel, int P2, void* dpred_bf16, int ld_d, float* dbias, float* reg_part, int B,
+                     float gscale, cudaStream_t stream) {
+  if (!raw || !bias || !target || !dpred_bf16 || !reg_part) return GABRIL_ERR_NULL;
+  if (P2 < 1 || P2 > 32 || ld_d < P2 || B <= 0) return GABRIL_ERR_BAD_SHAPE;
+  gril_head_kernel<<<1, 1024, 0, stream>>>(raw, ld_raw, bias, target, tgt_bstride, sel, P2,
+                                           reinterpret_cast<bf16*>(dpred_bf16), ld_d, dbias, reg_part, B, gscale);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_agil_combine(void* z, const void* z_agil, const float* sel, const float* rowmask, int B, int n, int C,
+                        cudaStream_t stream) {
+  if (!z || !z_agil) return GABRIL_ERR_NULL;
+  if (B <= 0 || (C & 1)) return GABRIL_ERR_BAD_SHAPE;
+  const long long total2 = (long long)B * n * C / 2;
+  agil_combine_kernel<<<blocks_for(total2, 256, 148 * 8), 256, 0, stream>>>(
+      reinterpret_cast<bf16*>(z), reinterpret_cast<const bf16*>(z_agil), sel, rowmask, total2, n * C / 2, C / 2);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+int gabril_agil_split(void* dz, void* dz_agil, const float* sel, int B, int n, int C, cudaStream_t stream) {
+  if (!dz || !dz_agil) return GABRIL_ERR_NULL;
+  if (B <= 0 || (C & 1)) return GABRIL_ERR_BAD_SHAPE;
+  const long long total2 = (long long)B * n * C / 2;
+  agil_split_kernel<<<blocks_for(total2, 256, 148 * 8), 256, 0, stream>>>(
+      reinterpret_cast<bf16*>(dz), reinterpret_cast<bf16*>(dz_agil), sel, total2, n * C / 2);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
 }

@@ -26,15 +26,35 @@ class StepEngine:
                  frame_stack: int = 2, beta: float = 50.0, lam: float = 10.0,
                  aggregate: bool = True, grad_accum: int = 1, seed: int = 0,
                  prob_dist_type: str = "MSE", gaze_ratio: float = 1.0):
-        if gaze_method not in ("None", "Reg", "Teacher"):
-            raise NotImplementedError(f"gaze.method={gaze_method} is outside the B200 hot path "
-                                      "(supported: None, Reg, Teacher)")
+        if gaze_method in ("Contrastive",) or dp_method == "Oreo":
+            # recorded from the unmodified reference by tests/golden/make_golden_n4.py
+            raise NotImplementedError(
+                f"gaze.method={gaze_method} / dropout.method={dp_method}: this path raises inside the reference "
+                "itself (Contrastive feeds the encoder an empty channel slice of the heat-map stack, "
+                "train_bc.py:173-176; Oreo rearranges a 2-D index tensor with a 3-D einops pattern, train_bc.py:280)")
+        if gaze_method not in ("None", "Reg", "Teacher", "Mask", "ViSaRL", "AGIL", "GRIL"):
+            raise NotImplementedError(f"gaze.method={gaze_method} is not a method of the reference "
+                                      "(None, Teacher, Reg, Mask, ViSaRL, AGIL, GRIL)")
+        if gaze_method in ("Mask", "ViSaRL", "AGIL") and not grayscale:
+            # xx [B, S*3, H, W] * gg [B, S, H, W] / cat to 2x channels: the reference's own shapes disagree for RGB
+            raise NotImplementedError(f"gaze.method={gaze_method} needs model.grayscale=true (train_bc.py:261,264,270 "
+                                      "multiply / concatenate the [B,S,H,W] heat maps with the frame stack)")
         if dp_method not in ("None", "GMD", "IGMD"):
             raise NotImplementedError(f"dropout.method={dp_method} is outside the B200 hot path "
                                       "(supported: None, GMD, IGMD)")
         _lib.init()
         self.spec, self.arena, self.gaze_pre = spec, arena, gaze_pre
         self.use_reg = gaze_method in ("Reg", "Teacher")
+        self.gaze_method = gaze_method
+        # how the heat maps enter conv_1's input (csrc/conv1_s4d.cu): 1 = multiplied in (Mask), 2 = concatenated (ViSaRL)
+        self.in_mode = {"Mask": 1, "ViSaRL": 2}.get(gaze_method, 0)
+        self.use_agil, self.use_gril = gaze_method == "AGIL", gaze_method == "GRIL"
+        want_c0 = frame_stack * (1 if grayscale else 3) * (2 if gaze_method == "ViSaRL" else 1)
+        if spec.C0 != want_c0:
+            raise ValueError(f"PolicySpec has {spec.C0} input channels, gaze.method={gaze_method} needs {want_c0} "
+                             "(train_bc.py:60-61)")
+        self.needs_heat = self.use_reg or dp_method in ("GMD", "IGMD") or self.in_mode != 0 or self.use_agil
+        self.needs_sel = self.needs_heat or self.use_gril
         self.use_gmd = dp_method == "GMD"
         self.use_igmd = dp_method == "IGMD"   # in-encoder dropout, linear_models.py:194-199
         self.grayscale, self.S = grayscale, frame_stack
@@ -78,32 +98,46 @@ class StepEngine:
 
         def act(h, w, c):
             return torch.empty(B, h, w, c, device=dev, dtype=bf)
-        b = {}
         # conv_1 / conv_2 live on a space-to-depth grid: a1s[B,SH,SW,(qh,qw,C1)] holds conv_1 output
         # pixel (2*sh+qh-1, 2*sw+qw-1) (a one-pixel zero border included), so that the k4/s2/p1
         # conv_2 is a 2x2 stride-1 flat-slab convolution; a2p / da2p are conv_2's output and its
         # gradient with a one-pixel zero border on the same [SH, SW] grid (conv_3 reads them with pad 0).
         self.SH, self.SW = s.H2 + 2, s.W2 + 2
         assert s.H1 % 2 == 0 and s.W1 % 2 == 0 and (4 * s.C1) % 64 == 0 and s.C2 % 64 == 0
-        zact = lambda h, w, c: torch.zeros(B, h, w, c, device=dev, dtype=bf)  # noqa: E731
-        # conv_1 input: the frames as a 4x4 space-to-depth bf16 image on the [SH, SW] grid (csrc/conv1_s4d.cu),
-        # one spare zero cell at the end (rows of the overlapping-row tensor map span two cells)
         assert s.H % 4 == 0 and s.W % 4 == 0 and self.SH == s.H // 4 + 2 and self.SW == s.W // 4 + 2
-        b["x4"] = torch.zeros(B * self.SH * self.SW + 1, s.K1p, device=dev, dtype=bf)
-        b["w4"] = torch.zeros(4 * s.C1, 2, 2 * s.K1p, device=dev, dtype=bf)
-        b["dw4"] = torch.zeros(4 * s.C1, 2, 2 * s.K1p, device=dev, dtype=f32)
-        b["a1s"], b["a2p"] = zact(self.SH, self.SW, 4 * s.C1), zact(self.SH, self.SW, s.C2)
-        b["a3"] = act(s.H3, s.W3, s.NH)
-        b["r-1"] = act(s.h, s.w, s.NH)  # relu(conv_4): the input of the first Residual
-        for i in range(s.NR):
-            b[f"h{i}"] = act(s.h, s.w, s.RH)
-            b[f"r{i}"] = act(s.h, s.w, s.NH)
-        b["a5"], b["z"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.E)
-        # packed ReLU sign words of every rectified activation (1 bit per element, written by the
-        # forward epilogues, read by the dgrad epilogues in place of the activation itself); zeroed:
-        # words of never-stored border pixels must read as "not positive"
-        for name in ["a1s", "a2p", "a3", "a5"] + [f"r{i}" for i in range(-1, s.NR)] + [f"h{i}" for i in range(s.NR)]:
-            b["sb_" + name] = ops.sign_bits_like(b[name])
+        zact = lambda h, w, c: torch.zeros(B, h, w, c, device=dev, dtype=bf)  # noqa: E731
+
+        def encoder_bufs(k1p):
+            """Activations, sign words and gradient tensors of one encoder pass."""
+            e = {}
+            # conv_1 input: the frames as a 4x4 space-to-depth bf16 image on the [SH, SW] grid (csrc/conv1_s4d.cu),
+            # one spare zero cell at the end (rows of the overlapping-row tensor map span two cells)
+            e["x4"] = torch.zeros(B * self.SH * self.SW + 1, k1p, device=dev, dtype=bf)
+            e["w4"] = torch.zeros(4 * s.C1, 2, 2 * k1p, device=dev, dtype=bf)
+            e["dw4"] = torch.zeros(4 * s.C1, 2, 2 * k1p, device=dev, dtype=f32)
+            e["a1s"], e["a2p"] = zact(self.SH, self.SW, 4 * s.C1), zact(self.SH, self.SW, s.C2)
+            e["a3"] = act(s.H3, s.W3, s.NH)
+            e["r-1"] = act(s.h, s.w, s.NH)  # relu(conv_4): the input of the first Residual
+            for i in range(s.NR):
+                e[f"h{i}"] = act(s.h, s.w, s.RH)
+                e[f"r{i}"] = act(s.h, s.w, s.NH)
+            e["a5"], e["z"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.E)
+            # packed ReLU sign words of every rectified activation (1 bit per element, written by the
+            # forward epilogues, read by the dgrad epilogues in place of the activation itself); zeroed:
+            # words of never-stored border pixels must read as "not positive"
+            for name in ["a1s", "a2p", "a3", "a5"] + [f"r{i}" for i in range(-1, s.NR)] + [f"h{i}" for i in range(s.NR)]:
+                e["sb_" + name] = ops.sign_bits_like(e[name])
+            # gradients (same shapes as the activations they belong to)
+            e["dz"] = act(s.h, s.w, s.E)
+            e["da5"] = act(s.h, s.w, s.NH)
+            e["dt_a"], e["dt_b"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.NH)
+            e["dh"] = act(s.h, s.w, s.RH)
+            e["da3"] = act(s.H3, s.W3, s.NH)
+            e["da2p"], e["da1s"] = zact(self.SH, self.SW, s.C2), zact(self.SH, self.SW, 4 * s.C1)
+            return e
+        b = encoder_bufs(s.K1p)
+        # gaze.method=AGIL: a second encoder pass with its own weights (prefix "agil") and buffers
+        self.buf2 = encoder_bufs(s.k1p_of(s.C0a)) if self.use_agil else None
         b["heat"] = torch.empty(B, self.S, s.H, s.W, device=dev, dtype=f32)
         b["rowmask"] = torch.empty(B, s.n, device=dev, dtype=f32)
         b["sel"] = torch.empty(B, device=dev, dtype=f32)
@@ -137,12 +171,12 @@ class StepEngine:
         b["dact1"] = torch.empty(B, s.Z, device=dev, dtype=bf)
         b["dzf"] = torch.empty(B, s.Z, device=dev, dtype=bf)
         b["dz_reg"] = act(s.h, s.w, s.E)
-        b["dz"] = act(s.h, s.w, s.E)
-        b["da5"] = act(s.h, s.w, s.NH)
-        b["dt_a"], b["dt_b"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.NH)
-        b["dh"] = act(s.h, s.w, s.RH)
-        b["da3"] = act(s.H3, s.W3, s.NH)
-        b["da2p"], b["da1s"] = zact(self.SH, self.SW, s.C2), zact(self.SH, self.SW, 4 * s.C1)
+        if self.use_gril:
+            b["g_h"] = torch.empty(B, s.Z, device=dev, dtype=bf)
+            b["g_raw"] = torch.empty(B, s.AP, device=dev, dtype=f32)
+            b["g_dpred"] = torch.empty(B, s.AP, device=dev, dtype=bf)
+            b["g_dh"] = torch.empty(B, s.Z, device=dev, dtype=bf)
+            b["g_dzf"] = torch.empty(B, s.Z, device=dev, dtype=bf)
         self.buf, self.B = b, B
 
     # ------------------------------------------------------------------------------------------
@@ -160,12 +194,22 @@ class StepEngine:
         b = self.buf
         center = L - 1
         # ---- preprocessing (prepare_for_bc, data_loader_robomimic.py:318-360) ----
-        ops.obs_s4d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["x4"])
         # ---- which samples use gaze (train_bc.py:230-240); all of them at gaze.ratio >= 1 ----
         self.sel = self.sel_stats = None
-        if self.gaze_ratio < 1.0 and (self.use_reg or self.use_gmd or self.use_igmd):
+        if self.gaze_ratio < 1.0 and self.needs_sel:
             self.sel, self.sel_stats = ops.ivg_select(frames, self.S, center, self.grayscale,
                                                       self.gaze_ratio, b["sel"], b["sel_stats"])
+        self._heat_done = False
+        if self.in_mode or self.use_agil:
+            # the heat maps are part of conv_1's input (Mask / ViSaRL / AGIL's second encoder): splat first
+            self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
+            self._heat_done = True
+        if self.in_mode:
+            ops.obs_s4d_gaze(frames, None, b["heat"], self.sel, self.in_mode, self.S, center, self.SH, self.SW, b["x4"])
+        else:
+            ops.obs_s4d(frames, self.S, center, self.grayscale, self.SH, self.SW, b["x4"])
+        if self.use_agil:
+            ops.obs_s4d_gaze(frames, None, b["heat"], self.sel, 1, self.S, center, self.SH, self.SW, self.buf2["x4"])
         return self._forward_rest(gaze, actions, center)
 
     def forward_store(self, store, step_idx: torch.Tensor):
@@ -187,13 +231,22 @@ class StepEngine:
         center = self.S - 1
         widx = ops.store_windows(step_idx.to(self.device, torch.int64).contiguous(), store.first, self.S,
                                  out=b["widx"])
-        ops.obs_s4d_store(store.images, widx, self.grayscale, self.SH, self.SW, b["x4"])
         self.sel = self.sel_stats = None
-        if self.gaze_ratio < 1.0 and (self.use_reg or self.use_gmd or self.use_igmd):
+        if self.gaze_ratio < 1.0 and self.needs_sel:
             self.sel, self.sel_stats = ops.ivg_select_store(store.images, widx, self.grayscale,
                                                             self.gaze_ratio, b["sel"], b["sel_stats"])
         gaze = ops.store_gather_rows(store.gaze, widx)
         actions = ops.store_gather_rows(store.actions, widx)
+        self._heat_done = False
+        if self.in_mode or self.use_agil:
+            self.gaze_pre.splat_into(gaze, self.S, center, b["heat"], aggregate=self.aggregate)
+            self._heat_done = True
+        if self.in_mode:
+            ops.obs_s4d_gaze(store.images, widx, b["heat"], self.sel, self.in_mode, self.S, center, self.SH, self.SW, b["x4"])
+        else:
+            ops.obs_s4d_store(store.images, widx, self.grayscale, self.SH, self.SW, b["x4"])
+        if self.use_agil:
+            ops.obs_s4d_gaze(store.images, widx, b["heat"], self.sel, 1, self.S, center, self.SH, self.SW, self.buf2["x4"])
         return self._forward_rest(gaze, actions, center)
 
     def predict(self, frames: torch.Tensor, g: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -209,7 +262,25 @@ class StepEngine:
         if B != self.B:
             self._alloc(B)
         b = self.buf
-        ops.obs_s4d(frames, self.S, L - 1, self.grayscale, self.SH, self.SW, b["x4"])
+        if self.in_mode or self.use_agil:
+            # bc_agent.py:274-289: the gaze predictor's clipped map takes the heat maps' place (Mask / AGIL: broadcast
+            # over the stack; ViSaRL concatenates it, which only fits the trained 2S-channel conv_1 if g has S channels)
+            if g is None:
+                raise RuntimeError(f"gaze.method={self.gaze_method} needs the predicted gaze map g at inference "
+                                   "(bc_agent.py:274-277)")
+            gh = g.float().clamp(0.0, 1.0)
+            if self.in_mode == 2 and gh.shape[1] != self.S:
+                raise RuntimeError(f"ViSaRL: cat([obs, g]) has {self.S + gh.shape[1]} channels, the encoder {s.C0} "
+                                   "(bc_agent.py:281 has the same mismatch)")
+            gh = gh.expand(B, self.S, s.H, s.W).contiguous()
+            if self.in_mode:
+                ops.obs_s4d_gaze(frames, None, gh, None, self.in_mode, self.S, L - 1, self.SH, self.SW, b["x4"])
+            else:
+                ops.obs_s4d(frames, self.S, L - 1, self.grayscale, self.SH, self.SW, b["x4"])
+            if self.use_agil:
+                ops.obs_s4d_gaze(frames, None, gh, None, 1, self.S, L - 1, self.SH, self.SW, self.buf2["x4"])
+        else:
+            ops.obs_s4d(frames, self.S, L - 1, self.grayscale, self.SH, self.SW, b["x4"])
         rowmask = igmd = None
         if self.use_gmd or self.use_igmd:
             if g is None:
@@ -226,7 +297,12 @@ class StepEngine:
                 ops.gmd_mask(gl, b["K2"], s.H2, s.W2, 0.7, True, rowmask=b["rm2"], ws=(b["K2"], b["mnmx"]),
                              layout="bordered", grid=(self.SH, self.SW))
                 igmd = (b["rm1"], b["rm2"])
-        self._encoder_fwd(rowmask, igmd)
+        if self.use_agil:        # z = (z + encoder_agil(obs * g)) / 2, then GMD's test-mode scaling (bc_agent.py:291-295)
+            self._encoder_fwd(None, igmd)
+            self._encoder_fwd(None, None, pfx="agil", b=self.buf2, c0=s.C0a)
+            ops.agil_combine(b["z"], self.buf2["z"], None, rowmask.view(-1) if rowmask is not None else None)
+        else:
+            self._encoder_fwd(rowmask, igmd)
         self._heads_logits()
         ops.mse_head(b["lg_raw"], a.P("act.2.b"), b["logits"], s.A, b["actor_part"], 0.0,
                      logits_out=b["logits"])
@@ -234,7 +310,7 @@ class StepEngine:
 
     def _forward_rest(self, gaze, actions, center):
         s, a, b, B = self.spec, self.arena, self.buf, self.B
-        if self.use_reg or self.use_gmd or self.use_igmd:
+        if self.needs_heat and not self._heat_done:
             if self.overlap:
                 main = torch.cuda.current_stream(self.device)
                 self._ev["in"].record(main)
@@ -270,40 +346,50 @@ class StepEngine:
             igmd = (b["rm1"], b["rm2"])
         if self.use_gmd or self.use_igmd:
             ops.rng_advance(self.rng_state)     # next step draws a fresh stream
-        self._encoder_fwd(rowmask, igmd)
+        if self.use_agil:
+            # second encoder on obs * gg_for_mul; z = 0.5 (z + z_agil) for the samples that use gaze; GMD's
+            # mask (applied to the combined z in the reference, train_bc.py:273-274) rides on the combine
+            self._encoder_fwd(None, igmd)
+            self._encoder_fwd(None, None, pfx="agil", b=self.buf2, c0=s.C0a)
+            ops.agil_combine(b["z"], self.buf2["z"], self.sel, rowmask.view(-1) if rowmask is not None else None)
+        else:
+            self._encoder_fwd(rowmask, igmd)
+        self._gaze_seq, self._center = gaze, center      # GRIL's targets: the raw coordinates at the centre step
         self._heads_fwd(actions, center)
         return b["losses"]
 
-    def _encoder_fwd(self, rowmask=None, igmd=None):
+    def _encoder_fwd(self, rowmask=None, igmd=None, pfx="enc", b=None, c0=None):
         """Encoder.forward (linear_models.py:191-207) from the patch matrix to z.  rowmask: GMD mask
         fused into conv_6's epilogue; igmd = (mask after conv_1, mask after conv_2): the stored a1 / a2
         are the dropped-out activations, so their `> 0` gates carry the mask through the backward."""
-        s, a, b, B = self.spec, self.arena, self.buf, self.B
+        s, a, B = self.spec, self.arena, self.B
+        b = self.buf if b is None else b
+        c0 = s.C0 if c0 is None else c0
         # conv_1 = a 2x2 flat convolution over the 4x4 space-to-depth frame image; its zero-inflated
         # weights are re-derived from the fp32 master every step (16 K elements)
-        ops.conv1_s4d_expand(a.P("enc.conv1.w"), b["w4"], s.C0)
-        ops.conv1_s4d_fwd(b["x4"], b["w4"], a.P("enc.conv1.b"), b["a1s"], B, self.SH, self.SW, s.H1, s.W1,
+        ops.conv1_s4d_expand(a.P(f"{pfx}.conv1.w"), b["w4"], c0)
+        ops.conv1_s4d_fwd(b["x4"], b["w4"], a.P(f"{pfx}.conv1.b"), b["a1s"], B, self.SH, self.SW, s.H1, s.W1,
                           relu=True, rowmask=igmd[0] if igmd else None, bits_out=b["sb_a1s"])
-        ops.conv_flat(b["a1s"], a.WB("enc.conv2.w"), b["a2p"], 2, 2, bias=a.P("enc.conv2.b"),
+        ops.conv_flat(b["a1s"], a.WB(f"{pfx}.conv2.w"), b["a2p"], 2, 2, bias=a.P(f"{pfx}.conv2.b"),
                       valid=(s.H2, s.W2), out_geom=(self.SH, self.SW, 1, 1), relu=True,
                       rowmask=igmd[1] if igmd else None, bits_out=b["sb_a2p"])
-        ops.conv_fwd(b["a2p"], a.WB("enc.conv3.w"), a.P("enc.conv3.b"), b["a3"], 4, 4, 2, 0, relu=True,
+        ops.conv_fwd(b["a2p"], a.WB(f"{pfx}.conv3.w"), a.P(f"{pfx}.conv3.b"), b["a3"], 4, 4, 2, 0, relu=True,
                      bits_out=b["sb_a3"])
         # conv_4 has no activation of its own; the first Residual's in-place ReLU rectifies it (F7)
-        ops.conv_fwd(b["a3"], a.WB("enc.conv4.w"), a.P("enc.conv4.b"), b["r-1"], 3, 3, 1, 0, relu=True,
+        ops.conv_fwd(b["a3"], a.WB(f"{pfx}.conv4.w"), a.P(f"{pfx}.conv4.b"), b["r-1"], 3, 3, 1, 0, relu=True,
                      bits_out=b["sb_r-1"])
         for i in range(s.NR):
             prev = b[f"r{i - 1}"]
-            ops.conv_fwd(prev, a.WB(f"enc.res{i}.c3.w"), None, b[f"h{i}"], 3, 3, 1, 1, relu=True,
+            ops.conv_fwd(prev, a.WB(f"{pfx}.res{i}.c3.w"), None, b[f"h{i}"], 3, 3, 1, 1, relu=True,
                          bits_out=b[f"sb_h{i}"])
             # relu(x) + block(x); the next consumer (next Residual / the stack's final ReLU)
             # rectifies it again, so the rectified value is what gets stored
-            ops.conv_fwd(b[f"h{i}"], a.WB(f"enc.res{i}.c1.w"), None, b[f"r{i}"], 1, 1, 1, 0, relu=True,
+            ops.conv_fwd(b[f"h{i}"], a.WB(f"{pfx}.res{i}.c1.w"), None, b[f"r{i}"], 1, 1, 1, 0, relu=True,
                          resid=prev, bits_out=b[f"sb_r{i}"])
         last = b[f"r{s.NR - 1}"]
-        ops.conv_fwd(last, a.WB("enc.conv5.w"), a.P("enc.conv5.b"), b["a5"], 5, 5, 1, 2, relu=True,
+        ops.conv_fwd(last, a.WB(f"{pfx}.conv5.w"), a.P(f"{pfx}.conv5.b"), b["a5"], 5, 5, 1, 2, relu=True,
                      bits_out=b["sb_a5"])
-        ops.conv_fwd(b["a5"], a.WB("enc.conv6.w"), a.P("enc.conv6.b"), b["z"], 5, 5, 1, 2, relu=False,
+        ops.conv_fwd(b["a5"], a.WB(f"{pfx}.conv6.w"), a.P(f"{pfx}.conv6.b"), b["z"], 5, 5, 1, 2, relu=False,
                      rowmask=rowmask.view(-1) if rowmask is not None else None)
 
     def _heads_fwd(self, actions, center):
@@ -355,6 +441,19 @@ class StepEngine:
         s, a, b, B = self.spec, self.arena, self.buf, self.B
         # ---- regulariser (train_bc.py:145-150,168-169) on the (post-dropout) z ----
         reg_scale = 0.0
+        if self.use_gril:
+            # gaze-coordinate head on z_flat (train_bc.py:84-86,182-192): Linear -> ReLU -> Linear, clamped MSE
+            # against the raw gaze coordinates of the centre step over the samples that use gaze
+            ops.conv_fwd(b["zf"].view(B, 1, 1, s.Z), a.WB("gril.0.w"), a.P("gril.0.b"), b["g_h"], 1, 1, 1, 0, relu=True)
+            b["g_raw"].zero_()
+            ops.conv_fwd(b["g_h"].view(B, 1, 1, s.Z), a.WB("gril.2.w"), None, b["g_raw"], 1, 1, 1, 0,
+                         out_f32_atomic=True, splits=1)
+            gz = self._gaze_seq
+            tgt = gz[:, self._center] if gz.dim() >= 3 else gz
+            assert tgt.stride(-1) == 1 and tgt.dtype == torch.float32 and tgt.shape[-1] >= 2 * s.GP
+            ops.gril_head(b["g_raw"], a.P("gril.2.b"), tgt, 2 * s.GP, self.sel, b["g_dpred"], a.G("gril.2.b"),
+                          b["reg_part"], self.lam * scale)
+            return 1.0
         if self.use_reg:
             # mean over the selected samples (and, for MSE, their pixels); with gaze.ratio < 1 the
             # number selected is a device scalar: sel_stats[1] = B / n_selected rescales both uses
@@ -368,7 +467,7 @@ class StepEngine:
 
     def _finalize(self, reg_scale):
         s, b, B = self.spec, self.buf, self.B
-        ops.finalize_losses(b["actor_part"], b["reg_part"] if self.use_reg else None, B,
+        ops.finalize_losses(b["actor_part"], b["reg_part"] if (self.use_reg or self.use_gril) else None, B,
                             1.0 / (B * s.A), reg_scale, self.lam, b["losses"],
                             reg_scale_dev=(self.sel_stats[1:] if self.use_reg and self.sel_stats is not None
                                            else None))
@@ -383,7 +482,7 @@ class StepEngine:
         self._backward_heads()
         if closing and self.on_heads_grads_ready is not None:
             self.on_heads_grads_ready()
-        self._encoder_bwd()
+        self._backward_encoders()
         self._accum_count += 1
         if closing and self.on_all_grads_ready is not None:
             self.on_all_grads_ready()
@@ -401,7 +500,17 @@ class StepEngine:
         # actor.0
         ops.colsum_bf16(b["dact1"], a.G("act.0.b"))
         ops.conv_wgrad(b["dact1"].view(B, 1, 1, s.Z), b["zf"].view(B, 1, 1, s.Z), a.G("act.0.w"), 1, 1, 1, 0)
-        ops.conv_dgrad(b["dact1"].view(B, 1, 1, s.Z), a.WB("act.0.w"), b["dzf"].view(B, 1, 1, s.Z), 1, 1, 1, 0)
+        zf_addend = None
+        if self.use_gril:   # the coordinate head's share of d z_flat
+            ops.conv_wgrad(b["g_dpred"].view(B, 1, 1, s.AP), b["g_h"].view(B, 1, 1, s.Z), a.G("gril.2.w"), 1, 1, 1, 0)
+            ops.conv_dgrad(b["g_dpred"].view(B, 1, 1, s.AP), a.WB("gril.2.w"), b["g_dh"].view(B, 1, 1, s.Z),
+                           1, 1, 1, 0, gate=b["g_h"].view(B, 1, 1, s.Z))
+            ops.colsum_bf16(b["g_dh"], a.G("gril.0.b"))
+            ops.conv_wgrad(b["g_dh"].view(B, 1, 1, s.Z), b["zf"].view(B, 1, 1, s.Z), a.G("gril.0.w"), 1, 1, 1, 0)
+            ops.conv_dgrad(b["g_dh"].view(B, 1, 1, s.Z), a.WB("gril.0.w"), b["g_dzf"].view(B, 1, 1, s.Z), 1, 1, 1, 0)
+            zf_addend = b["g_dzf"].view(B, 1, 1, s.Z)
+        ops.conv_dgrad(b["dact1"].view(B, 1, 1, s.Z), a.WB("act.0.w"), b["dzf"].view(B, 1, 1, s.Z), 1, 1, 1, 0,
+                       addend=zf_addend)
         # pre_actor
         self._join_reg()                                    # dz_reg, losses (side stream)
         ops.colsum_bf16(b["dzf"], a.G("pre.b"))
@@ -496,49 +605,60 @@ class StepEngine:
             forward_fn()
             self._backward_heads()
         with torch.cuda.graph(gb, pool=ga.pool(), capture_error_mode="thread_local"):
-            self._encoder_bwd()
+            self._backward_encoders()
         return ga, gb, keep   # the graphs hold raw pointers: `keep` pins the captured input tensors
 
-    def _encoder_bwd(self):
+    def _backward_encoders(self):
+        """Encoder backward from b["dz"]; gaze.method=AGIL: both encoders, dz split by the where() of the combine."""
+        if self.use_agil:
+            ops.agil_split(self.buf["dz"], self.buf2["dz"], self.sel)
+            self._encoder_bwd()
+            self._encoder_bwd(pfx="agil", b=self.buf2, c0=self.spec.C0a)
+        else:
+            self._encoder_bwd()
+
+    def _encoder_bwd(self, pfx="enc", b=None, c0=None):
         """Backward of the encoder from b["dz"] (gradient w.r.t. z) to every encoder weight gradient."""
-        s, a, b, B = self.spec, self.arena, self.buf, self.B
+        s, a, B = self.spec, self.arena, self.B
+        b = self.buf if b is None else b
+        c0 = s.C0 if c0 is None else c0
         # conv_6 / conv_5
         last, sb_last = b[f"r{s.NR - 1}"], b[f"sb_r{s.NR - 1}"]
-        self._colsum(b["dz"], a.G("enc.conv6.b"))
-        ops.conv_wgrad(b["dz"], b["a5"], a.G("enc.conv6.w"), 5, 5, 1, 2)
-        ops.conv_dgrad(b["dz"], a.WB("enc.conv6.w"), b["da5"], 5, 5, 1, 2, gate_bits=b["sb_a5"])
-        self._colsum(b["da5"], a.G("enc.conv5.b"))
-        ops.conv_wgrad(b["da5"], last, a.G("enc.conv5.w"), 5, 5, 1, 2)
+        self._colsum(b["dz"], a.G(f"{pfx}.conv6.b"))
+        ops.conv_wgrad(b["dz"], b["a5"], a.G(f"{pfx}.conv6.w"), 5, 5, 1, 2)
+        ops.conv_dgrad(b["dz"], a.WB(f"{pfx}.conv6.w"), b["da5"], 5, 5, 1, 2, gate_bits=b["sb_a5"])
+        self._colsum(b["da5"], a.G(f"{pfx}.conv5.b"))
+        ops.conv_wgrad(b["da5"], last, a.G(f"{pfx}.conv5.w"), 5, 5, 1, 2)
         dt, other = b["dt_a"], b["dt_b"]
-        ops.conv_dgrad(b["da5"], a.WB("enc.conv5.w"), dt, 5, 5, 1, 2, gate_bits=sb_last)
+        ops.conv_dgrad(b["da5"], a.WB(f"{pfx}.conv5.w"), dt, 5, 5, 1, 2, gate_bits=sb_last)
         # residual stack, last block first
         for i in reversed(range(s.NR)):
             prev = b[f"r{i - 1}"]
-            ops.conv_wgrad(dt, b[f"h{i}"], a.G(f"enc.res{i}.c1.w"), 1, 1, 1, 0)
-            ops.conv_dgrad(dt, a.WB(f"enc.res{i}.c1.w"), b["dh"], 1, 1, 1, 0, gate_bits=b[f"sb_h{i}"])
-            ops.conv_wgrad(b["dh"], prev, a.G(f"enc.res{i}.c3.w"), 3, 3, 1, 1)
-            ops.conv_dgrad(b["dh"], a.WB(f"enc.res{i}.c3.w"), other, 3, 3, 1, 1, addend=dt,
+            ops.conv_wgrad(dt, b[f"h{i}"], a.G(f"{pfx}.res{i}.c1.w"), 1, 1, 1, 0)
+            ops.conv_dgrad(dt, a.WB(f"{pfx}.res{i}.c1.w"), b["dh"], 1, 1, 1, 0, gate_bits=b[f"sb_h{i}"])
+            ops.conv_wgrad(b["dh"], prev, a.G(f"{pfx}.res{i}.c3.w"), 3, 3, 1, 1)
+            ops.conv_dgrad(b["dh"], a.WB(f"{pfx}.res{i}.c3.w"), other, 3, 3, 1, 1, addend=dt,
                            gate_bits=b[f"sb_r{i - 1}"])
             dt, other = other, dt
         # conv_4 .. conv_1
-        self._colsum(dt, a.G("enc.conv4.b"))
-        ops.conv_wgrad(dt, b["a3"], a.G("enc.conv4.w"), 3, 3, 1, 0)
-        ops.conv_dgrad(dt, a.WB("enc.conv4.w"), b["da3"], 3, 3, 1, 0, gate_bits=b["sb_a3"])
-        self._colsum(b["da3"], a.G("enc.conv3.b"))
+        self._colsum(dt, a.G(f"{pfx}.conv4.b"))
+        ops.conv_wgrad(dt, b["a3"], a.G(f"{pfx}.conv4.w"), 3, 3, 1, 0)
+        ops.conv_dgrad(dt, a.WB(f"{pfx}.conv4.w"), b["da3"], 3, 3, 1, 0, gate_bits=b["sb_a3"])
+        self._colsum(b["da3"], a.G(f"{pfx}.conv3.b"))
         # conv_3 over the zero-bordered a2p (pad 0): the border gradients are gated to zero by a2p itself
-        ops.conv_wgrad(b["da3"], b["a2p"], a.G("enc.conv3.w"), 4, 4, 2, 0)
-        ops.conv_dgrad(b["da3"], a.WB("enc.conv3.w"), b["da2p"], 4, 4, 2, 0, gate_bits=b["sb_a2p"])
-        self._colsum(b["da2p"], a.G("enc.conv2.b"))
+        ops.conv_wgrad(b["da3"], b["a2p"], a.G(f"{pfx}.conv3.w"), 4, 4, 2, 0)
+        ops.conv_dgrad(b["da3"], a.WB(f"{pfx}.conv3.w"), b["da2p"], 4, 4, 2, 0, gate_bits=b["sb_a2p"])
+        self._colsum(b["da2p"], a.G(f"{pfx}.conv2.b"))
         # conv_2 on the space-to-depth grid: dY pixel (i, j) sits at flat row q + SW + 1
-        ops.conv_wgrad_flat(b["da2p"], b["a1s"], a.G("enc.conv2.w"), 2, 2, self.SW + 1,
+        ops.conv_wgrad_flat(b["da2p"], b["a1s"], a.G(f"{pfx}.conv2.w"), 2, 2, self.SW + 1,
                             flop_pixels=B * s.H2 * s.W2)
-        ops.conv_flat(b["da2p"], a.WB("enc.conv2.w"), b["da1s"], 2, 2, gate_bits=b["sb_a1s"], transpose_w=True,
+        ops.conv_flat(b["da2p"], a.WB(f"{pfx}.conv2.w"), b["da1s"], 2, 2, gate_bits=b["sb_a1s"], transpose_w=True,
                       flop_pixels=B * s.H2 * s.W2)  # algorithmic FLOPs of the k4/s2 dgrad
         M1 = B * self.SH * self.SW * 4
-        self._colsum(b["da1s"].view(M1, s.C1), a.G("enc.conv1.b"))
+        self._colsum(b["da1s"].view(M1, s.C1), a.G(f"{pfx}.conv1.b"))
         b["dw4"].zero_()
         ops.conv1_s4d_wgrad(b["da1s"], b["x4"], b["dw4"], B, self.SH, self.SW, s.H1, s.W1)
-        ops.conv1_s4d_fold(b["dw4"], a.G("enc.conv1.w"), s.C0)
+        ops.conv1_s4d_fold(b["dw4"], a.G(f"{pfx}.conv1.w"), c0)
         if self._colsum_pending:
             main = torch.cuda.current_stream(self.device)
             self._ev["colsum"].record(self._side)

@@ -48,7 +48,13 @@ class PolicySpec:
 
     def __init__(self, in_channels: int, H: int = 180, W: int = 320, embedding_dim: int = 64,
                  num_hiddens: int = 128, num_residual_layers: int = 2,
-                 num_residual_hiddens: int = 32, z_dim: int = 256, action_dim: int = 7):
+                 num_residual_hiddens: int = 32, z_dim: int = 256, action_dim: int = 7,
+                 agil_channels: int = 0, gril_points: int = 0):
+        # agil_channels > 0: gaze.method=AGIL's second encoder `encoder_agil` (train_bc.py:70-77) with that many
+        # input channels; gril_points > 0: GRIL's gaze-coordinate head on z_flat (train_bc.py:84-86), 2*points outputs
+        self.C0a, self.GP = int(agil_channels), int(gril_points)
+        if self.GP * 2 > 32:
+            raise NotImplementedError("gaze.max_points > 16")
         self.C0, self.H, self.W = in_channels, H, W
         self.E, self.NH, self.NR, self.RH = embedding_dim, num_hiddens, num_residual_layers, num_residual_hiddens
         self.Z, self.A = z_dim, action_dim
@@ -74,6 +80,12 @@ class PolicySpec:
         s = self
         e: List[Entry] = []
         # --- reverse execution order ---
+        if s.GP:
+            g = "gril_gaze_coord_predictor"
+            e.append(Entry("gril.2.w", g, "2.weight", "head", (2 * s.GP, s.Z), (s.AP, 1, s.Z)))
+            e.append(Entry("gril.2.b", g, "2.bias", "head_bias", (2 * s.GP,), (s.AP,)))
+            e.append(Entry("gril.0.w", g, "0.weight", "linear", (s.Z, s.Z), (s.Z, 1, s.Z)))
+            e.append(Entry("gril.0.b", g, "0.bias", "bias", (s.Z,), (s.Z,)))
         e.append(Entry("act.2.w", "actor", "2.weight", "head", (s.A, s.Z), (s.AP, 1, s.Z)))
         e.append(Entry("act.2.b", "actor", "2.bias", "head_bias", (s.A,), (s.AP,)))
         e.append(Entry("act.0.w", "actor", "0.weight", "linear", (s.Z, s.Z), (s.Z, 1, s.Z)))
@@ -87,6 +99,8 @@ class PolicySpec:
         def bias(name, key, co):
             e.append(Entry(f"enc.{name}.b", "encoder", f"{key}.bias", "bias", (co,), (co,)))
         self._encoder_entries(e, conv, bias)
+        if s.C0a:   # second encoder: same layers, its own input width, module "encoder_agil"
+            self._encoder_entries(e, conv, bias, pfx="agil", module="encoder_agil", c0=s.C0a)
         off = 0
         for ent in e:
             ent.offset = off
@@ -94,8 +108,19 @@ class PolicySpec:
         self.total = off
         return e
 
-    def _encoder_entries(self, e, conv, bias):
+    def k1p_of(self, c0):
+        k1 = 16 * c0
+        return 32 if k1 <= 32 else 64 if k1 <= 64 else (k1 + 127) // 128 * 128
+
+    def _encoder_entries(self, e, conv, bias, pfx="enc", module="encoder", c0=None):
         s = self
+        if pfx != "enc":
+            def conv(name, key, co, ci, k):   # noqa: F811
+                e.append(Entry(f"{pfx}.{name}.w", module, f"{key}.weight", "conv", (co, ci, k, k), (co, k * k, ci)))
+
+            def bias(name, key, co):          # noqa: F811
+                e.append(Entry(f"{pfx}.{name}.b", module, f"{key}.bias", "bias", (co,), (co,)))
+        c0 = s.C0 if c0 is None else c0
         conv("conv6", "_conv_6", s.E, s.NH, 5); bias("conv6", "_conv_6", s.E)
         conv("conv5", "_conv_5", s.NH, s.NH, 5); bias("conv5", "_conv_5", s.NH)
         for i in reversed(range(s.NR)):
@@ -105,10 +130,10 @@ class PolicySpec:
         conv("conv3", "_conv_3", s.NH, s.C2, 4); bias("conv3", "_conv_3", s.NH)
         # conv_2 (k4/s2/p1) runs as a 2x2 stride-1 convolution over the space-to-depth conv_1 output:
         # its 16 taps are stored as [Cout][(r',s')][(qh,qw,cin)] with (kh, kw) = (2r'+qh, 2s'+qw)
-        e.append(Entry("enc.conv2.w", "encoder", "_conv_2.weight", "conv_s2d", (s.C2, s.C1, 4, 4),
+        e.append(Entry(f"{pfx}.conv2.w", module, "_conv_2.weight", "conv_s2d", (s.C2, s.C1, 4, 4),
                        (s.C2, 4, 4 * s.C1)))
         bias("conv2", "_conv_2", s.C2)
-        e.append(Entry("enc.conv1.w", "encoder", "_conv_1.weight", "conv1", (s.C1, s.C0, 4, 4), (s.C1, 1, s.K1p)))
+        e.append(Entry(f"{pfx}.conv1.w", module, "_conv_1.weight", "conv1", (s.C1, c0, 4, 4), (s.C1, 1, s.k1p_of(c0))))
         bias("conv1", "_conv_1", s.C1)
 
 
@@ -166,7 +191,7 @@ def to_internal(ent: Entry, t: torch.Tensor, spec: PolicySpec) -> torch.Tensor:
     if ent.kind == "conv1":
         co, ci, r, s_ = t.shape
         flat = t.permute(0, 2, 3, 1).reshape(co, r * s_ * ci)
-        out = t.new_zeros(co, 1, spec.K1p)
+        out = t.new_zeros(co, 1, ent.int_shape[2])
         out[:, 0, :flat.shape[1]] = flat
         return out
     if ent.kind == "patch16":  # ConvTranspose2d(C, 1, 4, 2, 1) weight [C,1,4,4] -> patch-GEMM matrix [C][1][32]
@@ -181,11 +206,11 @@ def to_internal(ent: Entry, t: torch.Tensor, spec: PolicySpec) -> torch.Tensor:
         z, _ = t.shape
         return t.reshape(z, spec.E, spec.n).permute(0, 2, 1).reshape(z, 1, spec.flat).contiguous()
     if ent.kind == "head":
-        out = t.new_zeros(spec.AP, 1, t.shape[1])
+        out = t.new_zeros(ent.int_shape[0], 1, t.shape[1])
         out[:t.shape[0], 0] = t
         return out
     if ent.kind == "head_bias":
-        out = t.new_zeros(spec.AP)
+        out = t.new_zeros(ent.int_shape[0])
         out[:t.shape[0]] = t
         return out
     return t.contiguous()
@@ -203,7 +228,7 @@ def to_reference(ent: Entry, t: torch.Tensor, spec: PolicySpec) -> torch.Tensor:
         return w.reshape(co, 4, 4, ci).permute(0, 3, 1, 2).contiguous()
     if ent.kind == "conv1":
         co, ci, r, s_ = ent.ref_shape
-        return t[:, 0, :spec.K1].reshape(co, r, s_, ci).permute(0, 3, 1, 2).contiguous()
+        return t[:, 0, :r * s_ * ci].reshape(co, r, s_, ci).permute(0, 3, 1, 2).contiguous()
     if ent.kind == "patch16":
         return t[:, 0, :16].reshape(ent.ref_shape).contiguous()
     if ent.kind == "linear":
@@ -316,7 +341,7 @@ class ParamArena:
 
 
 def _layer_rank(mod, key):
-    if mod not in ("encoder", "decoder"):
+    if mod not in ("encoder", "decoder", "encoder_agil"):
         return int(key.split(".")[0])
     if key.startswith("_conv_trans_"):
         return 200 + int(key.split(".")[0].split("_")[-1])

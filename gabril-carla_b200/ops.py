@@ -247,6 +247,23 @@ def obs_s4d_store(store_frames, widx, grayscale, SH, SW, out):
     return out
 
 
+def obs_s4d_gaze(frames, widx, heat, sel, mode, S, center, SH, SW, out):
+    """obs_s4d with the gaze heat maps folded in (gray stacks): mode 1 = obs * (ivg*heat + 1 - ivg)
+    (gaze.method Mask / AGIL's second encoder), mode 2 = channels (obs, ivg*heat) (ViSaRL).  frames: the uint8
+    batch [B,L,H,W,3] (widx None) or the frame store [N,H,W,3] read through widx int64 [B,S]."""
+    _chk(frames, torch.uint8, "frames"); _chk(heat, torch.float32, "heat"); _chk(sel, torch.float32, "sel")
+    _chk(widx, torch.int64, "widx")
+    if widx is None:
+        B, L, H, W, _ = frames.shape
+    else:
+        (_, H, W, _), (B, L) = frames.shape, widx.shape
+    assert heat.shape == (B, S, H, W) and out.shape[0] >= B * SH * SW + 1 and out.dtype == torch.bfloat16
+    _call("gabril_obs_s4d_gaze", ptr(frames), ptr(widx), ptr(heat), ptr(sel), c_int(mode), ptr(out), c_int(B), c_int(L),
+          c_int(S), c_int(center), c_int(H), c_int(W), c_int(1), c_int(out.shape[1]), c_int(SH), c_int(SW), stream(),
+          work=float(B * S * H * W * 7 + B * SH * SW * out.shape[1] * 2))
+    return out
+
+
 def conv1_s4d_expand(w1, w4, C0):
     """fp32 master conv_1 weight [C1,1,K1p] -> bf16 [4*C1, 2, 2*Cp] weights of the 2x2 convolution."""
     _chk(w1, torch.float32, "w1"); _chk_bf16(w4, "w4")
@@ -629,6 +646,28 @@ def mse_head(raw, bias, actions_view, A, part, gscale, dlogits=None, dbias=None,
     _call("gabril_mse_head", ptr(raw), c_int(ld), ptr(bias), ptr(actions_view),
           c_ll(actions_view.stride(0)), c_int(A), ptr(logits_out), ptr(dlogits), c_int(ld_d),
           ptr(dbias), ptr(part), c_int(B), c_float(gscale), stream())
+
+
+def gril_head(raw, bias, target_view, P2, sel, dpred, dbias, reg_part, gscale):
+    """GRIL coordinate loss (train_bc.py:182-192); target_view: fp32 view whose row b starts at data_ptr + b*stride(0)."""
+    B, ld = raw.shape
+    _call("gabril_gril_head", ptr(raw), c_int(ld), ptr(bias), ptr(target_view), c_ll(target_view.stride(0)), ptr(sel),
+          c_int(P2), ptr(dpred), c_int(dpred.shape[1]), ptr(dbias), ptr(reg_part), c_int(B), c_float(gscale), stream())
+
+
+def agil_combine(z, z_agil, sel, rowmask=None):
+    """z = where(sel > 0, 0.5 (z + z_agil), z) [* rowmask]; bf16 [B,h,w,C] in place (train_bc.py:268-272)."""
+    _chk_bf16(z, "z"); _chk_bf16(z_agil, "z_agil")
+    B, h, w, C = z.shape
+    _call("gabril_agil_combine", ptr(z), ptr(z_agil), ptr(sel), ptr(rowmask), c_int(B), c_int(h * w), c_int(C), stream(),
+          work=float(z.numel() * 6))
+
+
+def agil_split(dz, dz_agil, sel):
+    _chk_bf16(dz, "dz"); _chk_bf16(dz_agil, "dz_agil")
+    B, h, w, C = dz.shape
+    _call("gabril_agil_split", ptr(dz), ptr(dz_agil), ptr(sel), c_int(B), c_int(h * w), c_int(C), stream(),
+          work=float(dz.numel() * 6))
 
 
 def finalize_losses(actor_part, reg_part, B, actor_scale, reg_scale, lam, losses, reg_scale_dev=None):

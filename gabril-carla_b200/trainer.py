@@ -330,15 +330,14 @@ class BCTrainer(BaseTrainer):
         c = self.cfg
         if self.device.type != "cuda":
             raise RuntimeError("BCTrainer needs a CUDA device (sm_100a); there is no CPU fallback")
-        if c.gaze.method not in ("None", "Reg", "Teacher") or c.dropout.method not in ("None", "GMD", "IGMD"):
-            raise NotImplementedError(
-                f"gaze.method={c.gaze.method} / dropout.method={c.dropout.method}: the B200 hot path covers "
-                "gaze.method in {None, Reg, Teacher} x dropout.method in {None, GMD, IGMD} (SURVEY.md §8b, §8f N1)")
         S = int(c.model.frame_stack)
-        cin = S * (1 if c.model.grayscale else 3)
+        base_c = S * (1 if c.model.grayscale else 3)
+        cin = base_c * (2 if c.gaze.method == "ViSaRL" else 1)          # train_bc.py:60-61
         spec = PolicySpec(cin, int(c.data.img_height), int(c.data.img_width), int(c.model.embedding_dim),
                           int(c.model.num_hiddens), int(c.model.num_residual_layers),
-                          int(c.model.num_residual_hiddens), int(c.model.z_dim), int(c.data.action_dim))
+                          int(c.model.num_residual_hiddens), int(c.model.z_dim), int(c.data.action_dim),
+                          agil_channels=base_c if c.gaze.method == "AGIL" else 0,           # train_bc.py:70-77
+                          gril_points=int(c.gaze.max_points) if c.gaze.method == "GRIL" else 0)   # train_bc.py:84-86
         self.spec = spec
         self.arena = ParamArena(spec, self.device)
         self.arena.init_reference_style()          # RNG state set by _set_seed, like the reference
@@ -363,14 +362,19 @@ class BCTrainer(BaseTrainer):
         self.encoder = ArenaModule(self.arena, "encoder")
         self.pre_actor = ArenaModule(self.arena, "pre_actor")
         self.actor = ArenaModule(self.arena, "actor")
-        self.gril_gaze_coord_predictor = None
-        self.encoder_agil = None
+        self.gril_gaze_coord_predictor = (ArenaModule(self.arena, "gril_gaze_coord_predictor")
+                                          if c.gaze.method == "GRIL" else None)
+        self.encoder_agil = ArenaModule(self.arena, "encoder_agil") if c.gaze.method == "AGIL" else None
+
+    def _modules(self):
+        return [m for m in (self.encoder, self.pre_actor, self.actor, self.encoder_agil,
+                            self.gril_gaze_coord_predictor) if m is not None]
 
     def get_optim_params(self):
-        return self.encoder.parameters() + self.pre_actor.parameters() + self.actor.parameters()
+        return [p for m in self._modules() for p in m.parameters()]
 
     def set_train_mode(self):
-        for m in (self.encoder, self.pre_actor, self.actor):
+        for m in self._modules():
             m.train()
 
     def compute_loss(self, batch):
@@ -439,9 +443,11 @@ class BCTrainer(BaseTrainer):
         d = Path(self.checkpoint_dir)
         d.mkdir(parents=True, exist_ok=True)
         sds = self.arena.state_dicts()
-        for mod, fname in (("encoder", "encoder"), ("actor", "actor"), ("pre_actor", "pre_actor")):
-            torch.save({k: v.detach().float().cpu().contiguous() for k, v in sds[mod].items()},
-                       d / f"ep{epoch}_{fname}.pth")
+        # + ep{E}_gril_gaze_coord_predictor.pth / ep{E}_encoder_agil.pth when those modules exist (train_bc.py:310-315)
+        for mod in ("encoder", "actor", "pre_actor", "gril_gaze_coord_predictor", "encoder_agil"):
+            if mod in sds:
+                torch.save({k: v.detach().float().cpu().contiguous() for k, v in sds[mod].items()},
+                           d / f"ep{epoch}_{mod}.pth")
         if c.logging.get("save_params", True):
             self.experiment.save_params_json({
                 "gaze_method": c.gaze.method, "dp_method": c.dropout.method,

@@ -218,6 +218,17 @@ int gabril_mse_head(const float* raw, int ld_raw, const float* bias, const float
                     long long act_bstride, int A, float* logits_out, void* dlogits_bf16, int ld_d,
                     float* dbias, float* part, int B, float gscale, cudaStream_t stream);
 /* losses[0] = actor, [1] = reg, [2] = lambda * reg + actor (train_bc.py:297); deterministic. */
+/* gaze.method = GRIL (train_bc.py:84-86,182-192,293-294): loss of the gaze-coordinate head on z_flat.
+ * pred = raw[:, :P2] + bias over the samples with sel > 0 (sel NULL = all); reg = clamp(mse(pred, target) + 1e-8,
+ * 0, 100) -> reg_part[0] (rest 0); dpred (bf16 [B, ld_d]) = gscale * d reg / d pred; dbias += column sums. */
+int gabril_gril_head(const float* raw, int ld_raw, const float* bias, const float* target, long long tgt_bstride,
+                     const float* sel, int P2, void* dpred_bf16, int ld_d, float* dbias, float* reg_part, int B,
+                     float gscale, cudaStream_t stream);
+/* gaze.method = AGIL (train_bc.py:268-272): z = where(sel > 0, 0.5 (z + z_agil), z) [* rowmask per pixel], bf16
+ * [B, n, C] in place; and its backward: dz_agil = [sel > 0] 0.5 dz, dz = (sel > 0 ? 0.5 : 1) dz in place. */
+int gabril_agil_combine(void* z, const void* z_agil, const float* sel, const float* rowmask, int B, int n, int C,
+                        cudaStream_t stream);
+int gabril_agil_split(void* dz, void* dz_agil, const float* sel, int B, int n, int C, cudaStream_t stream);
 int gabril_finalize_losses(const float* actor_part, const float* reg_part, int B, float actor_scale,
                            float reg_scale, float lambda, float* losses, cudaStream_t stream);
 /* reg additionally multiplied by the device scalar reg_scale_dev[0] (NULL = 1). */
@@ -275,6 +286,14 @@ int gabril_obs_s4d(const uint8_t* frames, void* x4, int B, int L, int S, int cen
                    int grayscale, int Cp, int SH, int SW, cudaStream_t stream);
 int gabril_obs_s4d_store(const uint8_t* store, const long long* widx, void* x4, int B, int S, int H,
                          int W, int grayscale, int Cp, int SH, int SW, cudaStream_t stream);
+/* The same with the gaze heat maps folded in (gray stacks; heat fp32 [B, S, H, W], sel = ivg fp32 [B] or NULL;
+ * widx = NULL: batch layout, else the frame store through the window table):
+ *   mode 1  gaze.method = Mask (train_bc.py:260-261) and AGIL's second encoder (:270):
+ *           obs * (ivg * heat + (1 - ivg));
+ *   mode 2  gaze.method = ViSaRL (train_bc.py:262-264): channels (obs, ivg * heat), C0 = 2 S. */
+int gabril_obs_s4d_gaze(const uint8_t* frames, const long long* widx, const float* heat, const float* sel, int mode,
+                        void* x4, int B, int L, int S, int center, int H, int W, int grayscale, int Cp, int SH,
+                        int SW, cudaStream_t stream);
 int gabril_conv1_s4d_expand(const float* w1, void* w4, int C1, int C0, int K1p, int Cp,
                             cudaStream_t stream);
 int gabril_conv1_s4d_fwd(const void* x4, const void* w4, const float* bias, const float* rowmask,

@@ -83,10 +83,29 @@ def test_train_two_epochs_and_checkpoint_layout(tmp_path):
 
 def test_unsupported_methods_raise(tmp_path):
     from gabril_carla_b200.trainer import BCTrainer
+    # the two paths that raise inside the reference itself (tests/golden/make_golden_n4.py)
     with pytest.raises(NotImplementedError):
-        BCTrainer(make_cfg(tmp_path, "gaze.method=AGIL"))
+        BCTrainer(make_cfg(tmp_path, "gaze.method=Contrastive"))
     with pytest.raises(NotImplementedError):
         BCTrainer(make_cfg(tmp_path, "dropout.method=Oreo"))
+
+
+@pytest.mark.parametrize("method", ["Mask", "ViSaRL", "AGIL", "GRIL"])
+def test_other_gaze_methods_train_and_checkpoint(tmp_path, method):
+    """SURVEY §8f N4 through the trainer: one epoch, and the extra checkpoint files of train_bc.py:310-315."""
+    from gabril_carla_b200.trainer import BCTrainer
+    tr = BCTrainer(make_cfg(tmp_path, f"gaze.method={method}", "training.epochs=1"))
+    tr.train()
+    d = tr.checkpoint_dir
+    enc = torch.load(d / "ep1_encoder.pth", weights_only=True)
+    assert tuple(enc["_conv_1.weight"].shape) == (32, 4 if method == "ViSaRL" else 2, 4, 4)
+    assert (d / "ep1_encoder_agil.pth").exists() == (method == "AGIL")
+    assert (d / "ep1_gril_gaze_coord_predictor.pth").exists() == (method == "GRIL")
+    if method == "GRIL":
+        g = torch.load(d / "ep1_gril_gaze_coord_predictor.pth", weights_only=True)
+        assert {k: tuple(v.shape) for k, v in g.items()} == {"0.weight": (256, 256), "0.bias": (256,),
+                                                             "2.weight": (10, 256), "2.bias": (10,)}
+    assert tr.last_epoch_loss == tr.last_epoch_loss
 
 
 def test_cuda_graph_step_matches_eager_loop(tmp_path):
