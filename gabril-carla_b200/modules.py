@@ -97,7 +97,7 @@ class Encoder(nn.Module):
             spec = PolicySpec(c, H, W, e, nh, nr, rh)
             arena = ParamArena(spec, device)
             self._engine = StepEngine(spec, arena, GazePreprocessor(img_height=H, img_width=W, device=str(device)),
-                                      gaze_method="None", dp_method="None", grayscale=True, frame_stack=1)
+                                      gaze_method="None", dp_method="None", grayscale=True, frame_stack=c)
             self._versions = None
         return self._engine
 
