@@ -564,7 +564,9 @@ struct RegArgs {
 // and the row slab yq of YS.  Walking down a column the four source rows of the bicubic y-taps change
 // only every H/h rows, so their tmap values (and, in the backward pass, the four y-adjoint
 // accumulators) live in registers and shared memory is touched only when the tap window moves.
-template <bool NHWC_BF16, int MODE, int MAXT>
+// RC: rows handled per inner chunk = the length of a tap-window run (H / h = 9 for 180 -> 20): a chunk of 8
+// walked a 9-row run in two rounds of eight predicated bodies, i.e. 16 issue slots for 9 pixels.
+template <bool NHWC_BF16, int MODE, int MAXT, int RC>
 __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __grid_constant__ RegArgs a) {
   extern __shared__ __align__(16) float sm[];
   constexpr bool LOSS = MODE == MODE_MSE || MODE >= MODE_KL;  // fused loss + gradient modes
@@ -716,12 +718,17 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __
       const int y0 = max(ya, ystart[r]), y1 = min(yb, ystart[r + 1]);
       if (y0 >= y1) continue;
       load_window(y0);
-#pragma unroll 4
-      for (int y = y0; y < y1; ++y) {
-        const float u = u_of(wy4[y]);
-        if (u < vmin) { vmin = u; imin = y; }
-        if (u > vmax) { vmax = u; imax = y; }
-        if (DISTN) { usum += u; g1sum += __ldg(g1c + y * W); }
+      for (int yc = y0; yc < y1; yc += RC) {
+#pragma unroll
+        for (int k = 0; k < RC; ++k) {
+          const int y = yc + k;
+          if (y < y1) {
+            const float u = u_of(wy4[y]);
+            if (u < vmin) { vmin = u; imin = y; }
+            if (u > vmax) { vmax = u; imax = y; }
+            if (DISTN) { usum += u; g1sum += __ldg(g1c + y * W); }
+          }
+        }
       }
     }
     if (imin != 0x7fffffff) imin = imin * W + x;
@@ -801,12 +808,12 @@ __global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __
       if (y0 >= y1) continue;
       load_window(y0);
       float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-      for (int yc = y0; yc < y1; yc += 8) {
-        float gv[8];
+      for (int yc = y0; yc < y1; yc += RC) {
+        float gv[RC];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) gv[k] = (yc + k < y1) ? __ldg(gsrc + (yc + k) * W) : 0.f;
+        for (int k = 0; k < RC; ++k) gv[k] = (yc + k < y1) ? __ldg(gsrc + (yc + k) * W) : 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < RC; ++k) {
           if (yc + k < y1) {
             const float4 wv = wy4[yc + k];
             const float g2 = __fsub_rn(u_of(wv), mn) * inv_rng;
@@ -912,18 +919,25 @@ size_t reg_smem_bytes(int h, int w, int H, int W) {
   return sizeof(float) * (n4 + 3 * (size_t)h * W + 8 * (size_t)H + 8 * (size_t)W + n4 + 2 * (size_t)w + (size_t)H + 1);
 }
 
-template <bool NHWC, int MODE, int MAXT>
-int launch_reg_t(const RegArgs& a, int threads, size_t smem, cudaStream_t stream) {
+template <bool NHWC, int MODE, int MAXT, int RC>
+int launch_reg_rc(const RegArgs& a, int threads, size_t smem, cudaStream_t stream) {
   static bool attr_done = false;
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(reg_kernel<NHWC, MODE, MAXT>,
+    cudaError_t e = cudaFuncSetAttribute(reg_kernel<NHWC, MODE, MAXT, RC>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return gabril_set_cuda_error(e);
     attr_done = true;
   }
-  reg_kernel<NHWC, MODE, MAXT><<<a.B, threads, smem, stream>>>(a);
+  reg_kernel<NHWC, MODE, MAXT, RC><<<a.B, threads, smem, stream>>>(a);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
+}
+
+template <bool NHWC, int MODE, int MAXT>
+int launch_reg_t(const RegArgs& a, int threads, size_t smem, cudaStream_t stream) {
+  // tap-window runs are exactly H / h rows when h divides H (180 / 20 = 9): one chunk per run
+  if (a.H % a.h == 0 && a.H / a.h == 9) return launch_reg_rc<NHWC, MODE, MAXT, 9>(a, threads, smem, stream);
+  return launch_reg_rc<NHWC, MODE, MAXT, 8>(a, threads, smem, stream);
 }
 
 template <bool NHWC, int MODE>

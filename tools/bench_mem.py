@@ -41,6 +41,7 @@ def timeit(name, fn, nbytes, reps=10):
 
 timeit("gaze_splat", lambda: pre.splat_into(gaze, 2, 1, heat), B * (80 + 460800))
 timeit("reg_mse", lambda: ops.reg_mse(z, heat[:, 1], heat.stride(0), 180, 320, 50.0, 1e-6, dz, part, stats=stats), B * 424960)
-timeit("obs_patches", lambda: ops.obs_patches(frames, 2, 1, True, out=patches), B * (345600 + 921600))
+x4 = torch.zeros(B * 47 * 82 + 1, 32, device=dev, dtype=torch.bfloat16)
+timeit("obs_s4d", lambda: ops.obs_s4d(frames, 2, 1, True, 47, 82, x4), B * (345600 + 47 * 82 * 64))
 timeit("gmd_mask", lambda: ops.gmd_mask(heat, A, 20, 38), B * (460800 + 6080))
 timeit("colsum da1", lambda: ops.colsum_bf16(big, db), big.numel() * 2)
