@@ -207,6 +207,14 @@ __device__ __forceinline__ void stg256(void* p, const uint32_t* r) {    // p 32-
                : "memory");
 }
 
+// programmatic dependent launch (griddepcontrol): no-ops when the kernel was launched without the attribute
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ----------------------------------------------------------------------------
 // misc
 // ----------------------------------------------------------------------------

@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -180,10 +181,15 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
     ptx::mbar_init(wfull, 1);
     ptx::fence_mbar_init();
   }
+  // Programmatic dependent launch: let the next kernel of the stream be scheduled while this one runs (its
+  // CTAs become resident as ours retire and wait below), and wait for the previous kernel's results before
+  // the first global-memory access.  Launch latency and this prologue overlap the predecessor's tail.
+  ptx::pdl_launch_dependents();
   if (warp == kMmaWarp) {
     ptx::tmem_alloc(ptx::smem_u32(&tmem_base_s), p.tmem_cols);
     ptx::tmem_relinquish();
   }
+  ptx::pdl_wait();
   const bool bias_sm = p.bias != nullptr && p.N_total <= kBiasSmem;
   if (warp >= kFirstEpilogueWarp && bias_sm)
     for (int i = threadIdx.x - 32 * kFirstEpilogueWarp; i < p.N_total; i += 128 * kEpiGroups)
@@ -794,7 +800,22 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
   const unsigned grid = (unsigned)std::min(p.total_tiles, num_sms);
   const int slot = (p.debug & 32) ? 0 : (p.out_mode != OUT_BF16 ? kF32Slot : p.epi_mode);
   const KernelFn fn = table[p.epi_groups - 1][slot];
-  fn<<<grid, 32 * (kFirstEpilogueWarp + 4 * p.epi_groups), smem_bytes, stream>>>(p);
+  static int use_pdl = -1;
+  if (use_pdl < 0) { const char* e = getenv("GABRIL_TC_PDL"); use_pdl = (e && e[0] == '0') ? 0 : 1; }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(32 * (kFirstEpilogueWarp + 4 * p.epi_groups));
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = use_pdl ? 1 : 0;
+  void* args[1] = {(void*)&p};
+  cudaError_t le = cudaLaunchKernelExC(&cfg, reinterpret_cast<const void*>(fn), args);
+  if (le != cudaSuccess) return gabril_set_cuda_error(le);
+
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
 }
