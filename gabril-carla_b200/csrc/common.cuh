@@ -48,3 +48,28 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 }
 __device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+
+// ---- PyTorch upsample_bicubic2d index math (fp32, A = -0.75, align_corners = False) -------------
+__device__ __forceinline__ float cubic1(float x) {
+  const float A = -0.75f;
+  return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f;
+}
+__device__ __forceinline__ float cubic2(float x) {
+  const float A = -0.75f;
+  return ((A * x - 5.f * A) * x + 8.f * A) * x - 4.f * A;
+}
+// taps i0-1 .. i0+2 clamped into [0, in-1]; weights in tap order.
+__device__ __forceinline__ void bicubic_taps(int dst, float scale, int in_size, int idx[4],
+                                             float w[4]) {
+  const float src = scale * ((float)dst + 0.5f) - 0.5f;
+  const float fl = floorf(src);
+  const int i0 = (int)fl;
+  const float t = src - fl;
+  w[0] = cubic2(t + 1.f);
+  w[1] = cubic1(t);
+  const float t2 = 1.f - t;
+  w[2] = cubic1(t2);
+  w[3] = cubic2(t2 + 1.f);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) idx[k] = min(max(i0 - 1 + k, 0), in_size - 1);
+}

@@ -1,13 +1,11 @@
 // Memory-bound kernels of the GABRIL training step (sm_100a): frame formatting, gaze heat-map
-// synthesis, gaze-mask dropout and the activation-map regulariser (forward + backward).
+// synthesis and gaze-mask dropout (the activation-map regulariser lives in reg_dist.cu).
 // Reference ops replaced (Gonglitian/GABRIL-CARLA, vlm_gaze/):
 //   data_utils/data_loader_robomimic.py:144-157  _gather_last_s_frames      (integer, bit-exact)
 //   data_utils/data_loader_robomimic.py:179-202  _format_obs_image          gabril_obs_format / _patches
 //   data_utils/data_loader_robomimic.py:85-139   GazePreprocessor.forward   gabril_gaze_splat
 //   data_utils/data_loader_robomimic.py:204-278  build_stack_heatmaps       gabril_gaze_splat
-//   data_utils/gaze_utils.py:7-30                get_gaze_mask              gabril_gaze_mask_fwd/_bwd
 //   data_utils/gaze_utils.py:33-52               apply_gmd_dropout          gabril_gmd_keep / _mask
-//   train/train_bc.py:145-171                    Reg/Teacher MSE loss       gabril_reg_mse
 // All of them are HBM-bound: one pass over the inputs, 16-byte accesses, per-sample tables in
 // shared memory, warp-shuffle reductions.
 #include <cfloat>
@@ -54,31 +52,6 @@ __device__ __forceinline__ float block_min(float v, float* scratch) {
   float r = scratch[0];
   for (int i = 1; i < nw; ++i) r = fminf(r, scratch[i]);
   return r;
-}
-
-// ---- PyTorch upsample_bicubic2d index math (fp32, A = -0.75, align_corners = False) -------------
-__device__ __forceinline__ float cubic1(float x) {
-  const float A = -0.75f;
-  return ((A + 2.f) * x - (A + 3.f)) * x * x + 1.f;
-}
-__device__ __forceinline__ float cubic2(float x) {
-  const float A = -0.75f;
-  return ((A * x - 5.f * A) * x + 8.f * A) * x - 4.f * A;
-}
-// taps i0-1 .. i0+2 clamped into [0, in-1]; weights in tap order.
-__device__ __forceinline__ void bicubic_taps(int dst, float scale, int in_size, int idx[4],
-                                             float w[4]) {
-  const float src = scale * ((float)dst + 0.5f) - 0.5f;
-  const float fl = floorf(src);
-  const int i0 = (int)fl;
-  const float t = src - fl;
-  w[0] = cubic2(t + 1.f);
-  w[1] = cubic1(t);
-  const float t2 = 1.f - t;
-  w[2] = cubic1(t2);
-  w[3] = cubic2(t2 + 1.f);
-#pragma unroll
-  for (int k = 0; k < 4; ++k) idx[k] = min(max(i0 - 1 + k, 0), in_size - 1);
 }
 
 // =================================================================================================
@@ -534,428 +507,6 @@ __global__ void __launch_bounds__(256) ivg_count_kernel(const float* __restrict_
   if (threadIdx.x == 0) { stats[0] = c; stats[1] = __fdiv_rn((float)B, c); }
 }
 
-// =================================================================================================
-// K5: get_gaze_mask forward / backward and the fused Reg-MSE loss + gradient.
-// One CTA = one sample; thread x owns output column x (blockDim = W rounded to a warp multiple).
-// Shared: p[n] softmax, t[h][W] row-interpolated map, sacc[h][W] y-adjoint accumulators,
-// bicubic tap tables for both axes, dp[n].
-// =================================================================================================
-// MODE_KL / MODE_TV / MODE_JS: train_bc.py:152-167 - both maps divided by their (detached) sums
-// + 1e-8, then KL(g1 || g2), sum |g1 - g2| or the Jensen-Shannon form with eps = 1e-6 inside the logs;
-// loss_part[b] is the per-sample sum, the caller divides by the number of selected samples.
-enum { MODE_MSE = 0, MODE_MASK_FWD = 1, MODE_MASK_BWD = 2, MODE_KL = 3, MODE_TV = 4, MODE_JS = 5 };
-
-struct RegArgs {
-  const void* z;         // bf16 [B, n, C] (NHWC) or fp32 [B, C, n] (NCHW)
-  const float* g1;       // MODE_MSE: target plane of sample b at g1 + b * g1_bstride
-  long long g1_bstride;
-  const float* sel;      // optional [B]: 0 => sample skipped (gaze.ratio < 1)
-  float* mask_out;       // MODE_MASK_FWD: [B, H*W]
-  const float* grad_in;  // MODE_MASK_BWD: [B, H*W]
-  void* dz;              // gradient w.r.t. z, same layout as z (MODE_MSE / MODE_MASK_BWD)
-  float* loss_part;      // MODE_MSE: [B] per-sample sum of squared differences
-  float* stats;          // optional [B][4]: min, max, argmin, argmax of the up-sampled map
-  const float* scale_dev;  // optional device scalar multiplied into grad_scale (B / n_selected)
-  float beta, grad_scale;
-  int B, C, h, w, H, W;
-};
-
-// blockDim = Wr * YS (Wr = W rounded up to a warp multiple): thread (x, yq) owns output column x
-// and the row slab yq of YS.  Walking down a column the four source rows of the bicubic y-taps change
-// only every H/h rows, so their tmap values (and, in the backward pass, the four y-adjoint
-// accumulators) live in registers and shared memory is touched only when the tap window moves.
-// RC: rows handled per inner chunk = the length of a tap-window run (H / h = 9 for 180 -> 20): a chunk of 8
-// walked a 9-row run in two rounds of eight predicated bodies, i.e. 16 issue slots for 9 pixels.
-template <bool NHWC_BF16, int MODE, int MAXT, int RC>
-__global__ void __launch_bounds__(MAXT, MAXT <= 640 ? 2 : 1) reg_kernel(const __grid_constant__ RegArgs a) {
-  extern __shared__ __align__(16) float sm[];
-  constexpr bool LOSS = MODE == MODE_MSE || MODE >= MODE_KL;  // fused loss + gradient modes
-  constexpr bool DISTN = MODE >= MODE_KL;                     // sum-normalised divergences
-  const int h = a.h, w = a.w, H = a.H, W = a.W, C = a.C, n = h * w, n4 = (n + 3) & ~3;
-  float* p = sm;                                        // [n4]
-  float* tmap = p + n4;                                 // [h][W]
-  float* sacc = tmap + h * W;                           // [2][h][W] (one copy per row slab)
-  float* wyt = sacc + 2 * h * W;                        // [H][4]
-  int* iyt = reinterpret_cast<int*>(wyt + 4 * H);       // [H][4]
-  float* wxt = reinterpret_cast<float*>(iyt + 4 * H);   // [W][4]
-  int* ixt = reinterpret_cast<int*>(wxt + 4 * W);       // [W][4]
-  float* dp = reinterpret_cast<float*>(ixt + 4 * W);    // [n4]
-  int* xrange = reinterpret_cast<int*>(dp + n4);        // [w][2]
-  int* ystart = xrange + 2 * w;                         // [runs + 1] first row of every tap-window run
-  __shared__ float scratch[32];
-  __shared__ int nruns_s;
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarp = blockDim.x >> 5;
-  const int b = blockIdx.x;
-  const bool skip = (a.sel != nullptr) && (a.sel[b] <= 0.f);
-  const int Wr = (W + 31) & ~31, YS = blockDim.x / Wr;
-  const int x = tid % Wr, yq = tid / Wr;
-  const int Hq = (H + YS - 1) / YS;
-  const int ya = min(yq * Hq, H), yb = min(ya + Hq, H);
-
-  const bf16* zb16 = reinterpret_cast<const bf16*>(a.z) + (long long)b * n * C;
-  const float* zf32 = reinterpret_cast<const float*>(a.z) + (long long)b * n * C;
-
-  if (LOSS && skip) {
-    // sample not selected: zero gradient, zero loss
-    if (NHWC_BF16) {
-      uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(a.dz) + (long long)b * n * C);
-      for (int i = tid; i < n * C / 8; i += blockDim.x) d[i] = make_uint4(0, 0, 0, 0);
-    } else {
-      float* d = reinterpret_cast<float*>(a.dz) + (long long)b * n * C;
-      for (int i = tid; i < n * C; i += blockDim.x) d[i] = 0.f;
-    }
-    if (tid == 0) a.loss_part[b] = 0.f;
-    return;
-  }
-
-  // ---- tap tables ----
-  const float sy = (float)h / (float)H, sx = (float)w / (float)W;
-  for (int y = tid; y < H; y += blockDim.x) {
-    int id[4]; float wt[4];
-    bicubic_taps(y, sy, h, id, wt);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { iyt[4 * y + k] = id[k]; wyt[4 * y + k] = wt[k]; }
-  }
-  for (int xx = tid; xx < W; xx += blockDim.x) {
-    int id[4]; float wt[4];
-    bicubic_taps(xx, sx, w, id, wt);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { ixt[4 * xx + k] = id[k]; wxt[4 * xx + k] = wt[k]; }
-  }
-  if (tid < w) { xrange[2 * tid] = W; xrange[2 * tid + 1] = -1; }
-
-  // ---- s_j = sum_c |z| (fp32) ----
-  if (NHWC_BF16) {
-    // C/8 lanes per position, 16-byte loads, shuffle reduce inside the lane group
-    const int lpp = C >> 3;              // lanes per position (power of two <= 32)
-    const int ppw = 32 / lpp;            // positions per warp step
-    const int sub = lane % lpp, posl = lane / lpp;
-    for (int j0 = wid * ppw; j0 < n; j0 += nwarp * ppw) {
-      const int j = j0 + posl;
-      float acc = 0.f;
-      if (j < n) {
-        const uint4 v = __ldg(reinterpret_cast<const uint4*>(zb16 + (long long)j * C) + sub);
-        acc = fabsf(bf16lo(v.x)) + fabsf(bf16hi(v.x)) + fabsf(bf16lo(v.y)) + fabsf(bf16hi(v.y)) +
-              fabsf(bf16lo(v.z)) + fabsf(bf16hi(v.z)) + fabsf(bf16lo(v.w)) + fabsf(bf16hi(v.w));
-      }
-      for (int o = lpp >> 1; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-      if (j < n && sub == 0) p[j] = acc;
-    }
-  } else {
-    for (int j = tid; j < n; j += blockDim.x) {
-      float acc = 0.f;
-      for (int c = 0; c < C; ++c) acc += fabsf(__ldg(zf32 + (long long)c * n + j));
-      p[j] = acc;
-    }
-  }
-  __syncthreads();
-
-  // source columns x' <- the contiguous range of output columns whose taps touch it
-  if (MODE != MODE_MASK_FWD && tid < W) {
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      atomicMin(&xrange[2 * ixt[4 * tid + k]], tid);
-      atomicMax(&xrange[2 * ixt[4 * tid + k] + 1], tid);
-    }
-  }
-
-  // runs of consecutive output rows that share one y-tap window (H / h rows each)
-  if (wid == 0) {
-    int base = 0;
-    for (int c = 0; c < H; c += 32) {
-      const int y = c + lane;
-      bool f = false;
-      if (y < H) f = (y == 0) || iyt[4 * y] != iyt[4 * y - 4] || iyt[4 * y + 3] != iyt[4 * y - 1];
-      const unsigned m = __ballot_sync(0xffffffffu, f);
-      if (f) ystart[base + __popc(m & ((2u << lane) - 1u)) - 1] = y;
-      base += __popc(m);
-    }
-    if (lane == 0) { ystart[base] = H; nruns_s = base; }
-  }
-
-  // ---- softmax(s / beta) over the n positions ----
-  float lmax = -FLT_MAX;
-  for (int j = tid; j < n; j += blockDim.x) { const float v = __fdiv_rn(p[j], a.beta); p[j] = v; lmax = fmaxf(lmax, v); }
-  const float smax = block_max(lmax, scratch);
-  float lsum = 0.f;
-  for (int j = tid; j < n; j += blockDim.x) { const float e = expf(p[j] - smax); p[j] = e; lsum += e; }
-  const float ssum = block_sum(lsum, scratch);
-  for (int j = tid; j < n; j += blockDim.x) p[j] = __fdiv_rn(p[j], ssum);
-  __syncthreads();
-
-  // ---- x interpolation of every source row: tmap[y'][x] (rows dealt over the YS slabs) ----
-  const bool col_ok = x < W && yq < YS;
-  if (col_ok) {
-    const int4 ii = *reinterpret_cast<const int4*>(ixt + 4 * x);
-    const float4 ww = *reinterpret_cast<const float4*>(wxt + 4 * x);
-    for (int yy = yq; yy < h; yy += YS) {
-      const float* pr = p + yy * w;
-      tmap[yy * W + x] = pr[ii.x] * ww.x + pr[ii.y] * ww.y + pr[ii.z] * ww.z + pr[ii.w] * ww.w;
-      if (MODE != MODE_MASK_FWD) { sacc[yy * W + x] = 0.f; sacc[(h + yy) * W + x] = 0.f; }
-    }
-  }
-  __syncthreads();
-
-  const int4* iy4 = reinterpret_cast<const int4*>(iyt);
-  const float4* wy4 = reinterpret_cast<const float4*>(wyt);
-  const int nruns = nruns_s;
-  // register window over the four source rows of the current run
-  int4 cur = make_int4(0, 0, 0, 0);
-  float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
-  auto load_window = [&](int y) {
-    cur = iy4[y];
-    t0 = tmap[cur.x * W + x]; t1 = tmap[cur.y * W + x]; t2 = tmap[cur.z * W + x]; t3 = tmap[cur.w * W + x];
-  };
-  auto u_of = [&](const float4& wv) { return t0 * wv.x + t1 * wv.y + t2 * wv.z + t3 * wv.w; };
-
-  // ---- pass 1: extrema (first occurrence wins ties, like torch's CPU max/min) ----
-  float vmin = FLT_MAX, vmax = -FLT_MAX;
-  int imin = 0x7fffffff, imax = 0x7fffffff;
-  float usum = 0.f, g1sum = 0.f;  // DISTN: column sums of the raw map and of the target
-  if (col_ok) {
-    const float* g1c = DISTN ? a.g1 + (long long)b * a.g1_bstride + x : nullptr;
-    for (int r = 0; r < nruns; ++r) {
-      const int y0 = max(ya, ystart[r]), y1 = min(yb, ystart[r + 1]);
-      if (y0 >= y1) continue;
-      load_window(y0);
-      for (int yc = y0; yc < y1; yc += RC) {
-#pragma unroll
-        for (int k = 0; k < RC; ++k) {
-          const int y = yc + k;
-          if (y < y1) {
-            const float u = u_of(wy4[y]);
-            if (u < vmin) { vmin = u; imin = y; }
-            if (u > vmax) { vmax = u; imax = y; }
-            if (DISTN) { usum += u; g1sum += __ldg(g1c + y * W); }
-          }
-        }
-      }
-    }
-    if (imin != 0x7fffffff) imin = imin * W + x;
-    if (imax != 0x7fffffff) imax = imax * W + x;
-  }
-  // block arg-reduce
-  for (int o = 16; o > 0; o >>= 1) {
-    const float ov = __shfl_xor_sync(0xffffffffu, vmin, o);
-    const int oi = __shfl_xor_sync(0xffffffffu, imin, o);
-    if (ov < vmin || (ov == vmin && oi < imin)) { vmin = ov; imin = oi; }
-    const float ov2 = __shfl_xor_sync(0xffffffffu, vmax, o);
-    const int oi2 = __shfl_xor_sync(0xffffffffu, imax, o);
-    if (ov2 > vmax || (ov2 == vmax && oi2 < imax)) { vmax = ov2; imax = oi2; }
-  }
-  __shared__ float r_min[32], r_max[32];
-  __shared__ int r_imin[32], r_imax[32];
-  if (lane == 0) { r_min[wid] = vmin; r_imin[wid] = imin; r_max[wid] = vmax; r_imax[wid] = imax; }
-  __syncthreads();
-  vmin = r_min[0]; imin = r_imin[0]; vmax = r_max[0]; imax = r_imax[0];
-  for (int i = 1; i < nwarp; ++i) {
-    if (r_min[i] < vmin || (r_min[i] == vmin && r_imin[i] < imin)) { vmin = r_min[i]; imin = r_imin[i]; }
-    if (r_max[i] > vmax || (r_max[i] == vmax && r_imax[i] < imax)) { vmax = r_max[i]; imax = r_imax[i]; }
-  }
-  if (imin >= H * W) imin = 0;  // all-NaN map: keep the indices addressable, values stay NaN
-  if (imax >= H * W) imax = 0;
-  const float mn = vmin, mx = vmax;
-  const float rng = __fsub_rn(mx, mn);
-  if (a.stats && tid == 0) {
-    a.stats[4 * b + 0] = mn; a.stats[4 * b + 1] = mx;
-    a.stats[4 * b + 2] = (float)imin; a.stats[4 * b + 3] = (float)imax;
-  }
-
-  if (MODE == MODE_MASK_FWD) {
-    if (col_ok) {
-      float* mo = a.mask_out + (long long)b * H * W;
-      for (int r = 0; r < nruns; ++r) {
-        const int y0 = max(ya, ystart[r]), y1 = min(yb, ystart[r + 1]);
-        if (y0 >= y1) continue;
-        load_window(y0);
-        for (int y = y0; y < y1; ++y)  // reference-facing op: exact division
-          mo[y * W + x] = __fdiv_rn(__fsub_rn(u_of(wy4[y]), mn), rng);
-      }
-    }
-    return;
-  }
-
-  // ---- pass 2: g2, loss, d(loss)/du accumulated through the y-adjoint into sacc ----
-  // (training path: the two divisions by rng are multiplications by 1/rng; 0/0 still gives NaN)
-  const float inv_rng = __fdiv_rn(1.f, rng);
-  const float gs = a.scale_dev ? a.grad_scale * __ldg(a.scale_dev) : a.grad_scale;
-  float iS1 = 0.f, iS2 = 0.f;
-  if (DISTN) {
-    // S1 = sum g1 + 1e-8; S2 = sum (u - mn) / rng + 1e-8 (block sums in double: the second one
-    // is a difference of two sums of 57 600 terms)
-    __shared__ double dred[2][32];
-    double du = usum, dg = g1sum;
-    for (int o = 16; o > 0; o >>= 1) {
-      du += __shfl_xor_sync(0xffffffffu, du, o);
-      dg += __shfl_xor_sync(0xffffffffu, dg, o);
-    }
-    if (lane == 0) { dred[0][wid] = du; dred[1][wid] = dg; }
-    __syncthreads();
-    du = 0.0; dg = 0.0;
-    for (int i = 0; i < nwarp; ++i) { du += dred[0][i]; dg += dred[1][i]; }
-    const double S2 = (du - (double)(H * W) * (double)mn) / (double)rng + 1e-8;
-    const double S1 = dg + 1e-8;
-    iS1 = (float)(1.0 / S1);
-    iS2 = (float)(1.0 / S2);
-  }
-  float sq = 0.f, E = 0.f, F = 0.f;
-  if (col_ok) {
-    const float* gsrc = LOSS ? a.g1 + (long long)b * a.g1_bstride
-                                           : a.grad_in + (long long)b * H * W;
-    gsrc += x;
-    for (int r = 0; r < nruns; ++r) {
-      const int y0 = max(ya, ystart[r]), y1 = min(yb, ystart[r + 1]);
-      if (y0 >= y1) continue;
-      load_window(y0);
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-      for (int yc = y0; yc < y1; yc += RC) {
-        float gv[RC];
-#pragma unroll
-        for (int k = 0; k < RC; ++k) gv[k] = (yc + k < y1) ? __ldg(gsrc + (yc + k) * W) : 0.f;
-#pragma unroll
-        for (int k = 0; k < RC; ++k) {
-          if (yc + k < y1) {
-            const float4 wv = wy4[yc + k];
-            const float g2 = __fsub_rn(u_of(wv), mn) * inv_rng;
-            float e;
-            if (MODE == MODE_MSE) {
-              const float d = g2 - gv[k];
-              sq = fmaf(d, d, sq);
-              e = 2.f * d * gs;
-            } else if (MODE == MODE_TV) {
-              const float d = gv[k] * iS1 - g2 * iS2;
-              sq += fabsf(d);
-              e = (d > 0.f ? -iS2 : (d < 0.f ? iS2 : 0.f)) * gs;
-            } else if (MODE == MODE_KL) {
-              const float pa = gv[k] * iS1, pb = g2 * iS2;
-              const float ib = __fdiv_rn(1.f, pb + 1e-6f);
-              sq = fmaf(pa, logf((pa + 1e-6f) * ib), sq);
-              e = -pa * ib * iS2 * gs;
-            } else if (MODE == MODE_JS) {
-              const float pa = gv[k] * iS1, pb = g2 * iS2;
-              const float im = __fdiv_rn(1.f, 0.5f * (pa + pb) + 1e-6f);
-              const float la = logf((pa + 1e-6f) * im), lb = logf((pb + 1e-6f) * im);
-              sq += 0.5f * (pa * la + pb * lb);
-              // d/dpb of 0.5 [pa log((pa+e)/(m+e)) + pb log((pb+e)/(m+e))], m = (pa + pb) / 2
-              e = 0.5f * (lb + __fdiv_rn(pb, pb + 1e-6f) - 0.5f * (pa + pb) * im) * iS2 * gs;
-            } else {
-              e = gv[k];
-            }
-            E += e;
-            F = fmaf(e, g2, F);
-            const float du = e * inv_rng;
-            a0 = fmaf(wv.x, du, a0); a1 = fmaf(wv.y, du, a1); a2 = fmaf(wv.z, du, a2); a3 = fmaf(wv.w, du, a3);
-          }
-        }
-      }
-      // slab-private copy of the accumulators: plain read-modify-write, no atomics
-      float* sa = sacc + (yq & 1) * h * W + x;
-      sa[cur.x * W] += a0; sa[cur.y * W] += a1; sa[cur.z * W] += a2; sa[cur.w * W] += a3;
-    }
-  }
-  const float Esum = block_sum(E, scratch);
-  const float Fsum = block_sum(F, scratch);
-  if (LOSS) {
-    const float sqsum = block_sum(sq, scratch);
-    if (tid == 0) a.loss_part[b] = sqsum;
-  }
-  __syncthreads();
-  if (tid == 0) {
-    // max/min backward: the whole -sum term goes to the single arg index
-    const int ymin = imin / W, xmin = imin - ymin * W;
-    const int ymax = imax / W, xmax = imax - ymax * W;
-    const float dmin = -(Esum - Fsum) * inv_rng, dmax = -Fsum * inv_rng;
-    for (int k = 0; k < 4; ++k) sacc[iyt[4 * ymin + k] * W + xmin] += wyt[4 * ymin + k] * dmin;
-    for (int k = 0; k < 4; ++k) sacc[iyt[4 * ymax + k] * W + xmax] += wyt[4 * ymax + k] * dmax;
-  }
-  __syncthreads();
-  // ---- x-adjoint: dp[y'][x'] = sum_x sum_k [ix[x][k] == x'] wx[x][k] sacc[y'][x] ----
-  for (int j = tid; j < n; j += blockDim.x) {
-    const int yy = j / w, xs = j - yy * w;
-    float acc = 0.f;
-    for (int xx = xrange[2 * xs]; xx <= xrange[2 * xs + 1]; ++xx) {
-      const float sv = sacc[yy * W + xx] + sacc[(h + yy) * W + xx];
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (ixt[4 * xx + k] == xs) acc = fmaf(wxt[4 * xx + k], sv, acc);
-    }
-    dp[j] = acc;
-  }
-  __syncthreads();
-  // ---- softmax backward: ds_j = p_j (dp_j - sum_k p_k dp_k) / beta ----
-  float ldot = 0.f;
-  for (int j = tid; j < n; j += blockDim.x) ldot = fmaf(p[j], dp[j], ldot);
-  const float dot = block_sum(ldot, scratch);
-  for (int j = tid; j < n; j += blockDim.x) dp[j] = p[j] * (dp[j] - dot) / a.beta;
-  __syncthreads();
-  // ---- dz = sign(z) ds ----
-  if (NHWC_BF16) {
-    bf16* dzb = reinterpret_cast<bf16*>(a.dz) + (long long)b * n * C;
-    const int vec_per_pos = C >> 3;
-    for (int i = tid; i < n * vec_per_pos; i += blockDim.x) {
-      const int j = i / vec_per_pos;
-      const float ds = dp[j];
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(zb16) + i);
-      auto sg = [&](float zv) { return zv > 0.f ? ds : (zv < 0.f ? -ds : 0.f); };
-      uint4 o;
-      o.x = pack_bf16x2(sg(bf16lo(v.x)), sg(bf16hi(v.x)));
-      o.y = pack_bf16x2(sg(bf16lo(v.y)), sg(bf16hi(v.y)));
-      o.z = pack_bf16x2(sg(bf16lo(v.z)), sg(bf16hi(v.z)));
-      o.w = pack_bf16x2(sg(bf16lo(v.w)), sg(bf16hi(v.w)));
-      reinterpret_cast<uint4*>(dzb)[i] = o;
-    }
-  } else {
-    float* dzf = reinterpret_cast<float*>(a.dz) + (long long)b * n * C;
-    for (int i = tid; i < n * C; i += blockDim.x) {
-      const int j = i % n;
-      const float zv = __ldg(zf32 + i), ds = dp[j];
-      dzf[i] = zv > 0.f ? ds : (zv < 0.f ? -ds : 0.f);
-    }
-  }
-}
-
-size_t reg_smem_bytes(int h, int w, int H, int W) {
-  const size_t n4 = ((size_t)h * w + 3) & ~(size_t)3;
-  return sizeof(float) * (n4 + 3 * (size_t)h * W + 8 * (size_t)H + 8 * (size_t)W + n4 + 2 * (size_t)w + (size_t)H + 1);
-}
-
-template <bool NHWC, int MODE, int MAXT, int RC>
-int launch_reg_rc(const RegArgs& a, int threads, size_t smem, cudaStream_t stream) {
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(reg_kernel<NHWC, MODE, MAXT, RC>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e != cudaSuccess) return gabril_set_cuda_error(e);
-    attr_done = true;
-  }
-  reg_kernel<NHWC, MODE, MAXT, RC><<<a.B, threads, smem, stream>>>(a);
-  GABRIL_CHECK_LAUNCH();
-  return GABRIL_OK;
-}
-
-template <bool NHWC, int MODE, int MAXT>
-int launch_reg_t(const RegArgs& a, int threads, size_t smem, cudaStream_t stream) {
-  // tap-window runs are exactly H / h rows when h divides H (180 / 20 = 9): one chunk per run
-  if (a.H % a.h == 0 && a.H / a.h == 9) return launch_reg_rc<NHWC, MODE, MAXT, 9>(a, threads, smem, stream);
-  return launch_reg_rc<NHWC, MODE, MAXT, 8>(a, threads, smem, stream);
-}
-
-template <bool NHWC, int MODE>
-int launch_reg(const RegArgs& a, cudaStream_t stream) {
-  if (a.B <= 0 || a.W > 1024 || a.W < 1 || a.h < 1 || a.w < 1 || (a.W & 3)) return GABRIL_ERR_BAD_SHAPE;
-  if (NHWC) {
-    const int lpp = a.C / 8;
-    if (a.C % 8 || lpp > 32 || (lpp & (lpp - 1))) return GABRIL_ERR_BAD_SHAPE;
-  }
-  const size_t smem = reg_smem_bytes(a.h, a.w, a.H, a.W);
-  if (smem > 200 * 1024) return GABRIL_ERR_BAD_SHAPE;
-  const int Wr = ((a.W + 31) / 32) * 32;
-  // two row slabs per column when the block still fits twice on an SM
-  if (2 * Wr <= 640) return launch_reg_t<NHWC, MODE, 640>(a, 2 * Wr, smem, stream);
-  if (Wr <= 640) return launch_reg_t<NHWC, MODE, 640>(a, Wr, smem, stream);
-  return launch_reg_t<NHWC, MODE, 1024>(a, Wr, smem, stream);
-}
-
 int grid_for(long long total, int threads, int max_blocks = 148 * 16) {
   long long blocks = (total + threads - 1) / threads;
   if (blocks > max_blocks) blocks = max_blocks;
@@ -1106,56 +657,6 @@ int gabril_rowmask_apply_nchw(const float* z, const float* rowmask, float* out, 
   rowmask_apply_nchw_kernel<<<grid_for(total, 256, 148 * 16), 256, 0, stream>>>(z, rowmask, out, B, C, n);
   GABRIL_CHECK_LAUNCH();
   return GABRIL_OK;
-}
-
-int gabril_gaze_mask_fwd(const void* z, int z_nhwc_bf16, float* mask_out, float* stats, int B, int C,
-                         int h, int w, int H, int W, float beta, cudaStream_t stream) {
-  if (!z || !mask_out) return GABRIL_ERR_NULL;
-  RegArgs a = {};
-  a.z = z; a.mask_out = mask_out; a.stats = stats; a.beta = beta;
-  a.B = B; a.C = C; a.h = h; a.w = w; a.H = H; a.W = W;
-  return z_nhwc_bf16 ? launch_reg<true, MODE_MASK_FWD>(a, stream)
-                     : launch_reg<false, MODE_MASK_FWD>(a, stream);
-}
-
-int gabril_gaze_mask_bwd(const void* z, int z_nhwc_bf16, const float* grad_mask, void* dz, int B,
-                         int C, int h, int w, int H, int W, float beta, cudaStream_t stream) {
-  if (!z || !grad_mask || !dz) return GABRIL_ERR_NULL;
-  RegArgs a = {};
-  a.z = z; a.grad_in = grad_mask; a.dz = dz; a.beta = beta;
-  a.B = B; a.C = C; a.h = h; a.w = w; a.H = H; a.W = W;
-  return z_nhwc_bf16 ? launch_reg<true, MODE_MASK_BWD>(a, stream)
-                     : launch_reg<false, MODE_MASK_BWD>(a, stream);
-}
-
-int gabril_reg_mse(const void* z, int z_nhwc_bf16, const float* g1, long long g1_bstride,
-                   const float* sel, void* dz, float* loss_part, float* stats, int B, int C, int h,
-                   int w, int H, int W, float beta, float grad_scale, cudaStream_t stream) {
-  return gabril_reg_dist(z, z_nhwc_bf16, g1, g1_bstride, sel, nullptr, GABRIL_DIST_MSE, dz, loss_part,
-                         stats, B, C, h, w, H, W, beta, grad_scale, stream);
-}
-
-int gabril_reg_dist(const void* z, int z_nhwc_bf16, const float* g1, long long g1_bstride,
-                    const float* sel, const float* scale_dev, int dist, void* dz, float* loss_part,
-                    float* stats, int B, int C, int h, int w, int H, int W, float beta,
-                    float grad_scale, cudaStream_t stream) {
-  if (!z || !g1 || !dz || !loss_part) return GABRIL_ERR_NULL;
-  RegArgs a = {};
-  a.z = z; a.g1 = g1; a.g1_bstride = g1_bstride; a.sel = sel; a.dz = dz; a.loss_part = loss_part;
-  a.stats = stats; a.beta = beta; a.grad_scale = grad_scale; a.scale_dev = scale_dev;
-  a.B = B; a.C = C; a.h = h; a.w = w; a.H = H; a.W = W;
-  switch (dist) {
-    case GABRIL_DIST_MSE:
-      return z_nhwc_bf16 ? launch_reg<true, MODE_MSE>(a, stream) : launch_reg<false, MODE_MSE>(a, stream);
-    case GABRIL_DIST_KL:
-      return z_nhwc_bf16 ? launch_reg<true, MODE_KL>(a, stream) : launch_reg<false, MODE_KL>(a, stream);
-    case GABRIL_DIST_TV:
-      return z_nhwc_bf16 ? launch_reg<true, MODE_TV>(a, stream) : launch_reg<false, MODE_TV>(a, stream);
-    case GABRIL_DIST_JS:
-      return z_nhwc_bf16 ? launch_reg<true, MODE_JS>(a, stream) : launch_reg<false, MODE_JS>(a, stream);
-    default:
-      return GABRIL_ERR_BAD_SHAPE;
-  }
 }
 
 int gabril_ivg_select(const uint8_t* frames, float* sel, float* sel_stats, int B, int L, int S,
