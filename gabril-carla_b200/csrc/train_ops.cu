@@ -48,22 +48,39 @@ colsum_bf16_kernel(const bf16* __restrict__ dy, float* __restrict__ db, long lon
   }
 }
 
-// y = act(x + bias) as bf16;  x fp32 [M, C] (C % 4 == 0)
+// y = act(sum_s x[s] + bias) as bf16;  x fp32 [planes][M, C] (C % 4 == 0).
+// Eight lanes share one float4 of the output: lane l adds the split-K planes l, l + 8, ... in order (four loads
+// in flight), then a fixed xor-shuffle tree folds the eight partial sums: the summation order depends only on
+// `planes`, so the result is bit-reproducible, and a small batch (few outputs, up to 148 planes) still has
+// enough loads in flight to hide the memory latency.
 __global__ void __launch_bounds__(256)
 bias_act_cast_kernel(const float* __restrict__ x, const float* __restrict__ bias,
                      bf16* __restrict__ y, float* __restrict__ y_f32, long long M, int C, int relu,
                      int planes) {
   const long long total4 = M * C / 4;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)((i * 4) % C);
-    float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
-    for (int s = 1; s < planes; ++s) {   // split-K partial planes, summed in a fixed order (deterministic)
-      const float4 t = __ldg(reinterpret_cast<const float4*>(x) + s * total4 + i);
-      v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+  const int sub = threadIdx.x & 7;
+  const long long n_iter = (total4 + 31) / 32 * 32;   // whole warps stay in the loop: the shuffles need every lane
+  for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3; i < n_iter;
+       i += ((long long)gridDim.x * blockDim.x) >> 3) {
+    const bool live = i < total4;
+    const float4* src = reinterpret_cast<const float4*>(x) + (live ? i : 0);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s0 = sub; s0 < planes; s0 += 32) {
+      float4 t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        t[u] = (live && s0 + 8 * u < planes) ? __ldg(src + (long long)(s0 + 8 * u) * total4) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { v.x += t[u].x; v.y += t[u].y; v.z += t[u].z; v.w += t[u].w; }
     }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+      v.x += __shfl_xor_sync(0xffffffffu, v.x, o); v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+      v.z += __shfl_xor_sync(0xffffffffu, v.z, o); v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
+    }
+    if (!live || sub != 0) continue;
     if (bias) {
-      const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + c));
+      const float4 bb = __ldg(reinterpret_cast<const float4*>(bias + (int)((i * 4) % C)));
       v.x += bb.x; v.y += bb.y; v.z += bb.z; v.w += bb.w;
     }
     if (relu) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
@@ -82,17 +99,24 @@ mse_head_kernel(const float* __restrict__ raw, int ld_raw, const float* __restri
   if (threadIdx.x < 64) sdb[threadIdx.x] = 0.f;
   __syncthreads();
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b < B) {
-    float sq = 0.f;
-    for (int k = 0; k < A; ++k) {
+  const bool live = b < B;
+  float sq = 0.f;
+  for (int k = 0; k < A; ++k) {   // A is block-uniform: every lane reaches the shuffles
+    float g = 0.f;
+    if (live) {
       const float l = raw[(long long)b * ld_raw + k] + bias[k];
       const float d = l - actions[(long long)b * act_bstride + k];
       sq = fmaf(d, d, sq);
-      const float g = 2.f * d * gscale;
+      g = 2.f * d * gscale;
       if (logits_out) logits_out[(long long)b * A + k] = l;
       if (dlogits) dlogits[(long long)b * ld_d + k] = __float2bfloat16(g);
-      if (dbias) atomicAdd(&sdb[k], g);
     }
+    if (dbias) {   // one shared atomic per warp instead of one per sample
+      g = warp_sum(g);
+      if ((threadIdx.x & 31) == 0) atomicAdd(&sdb[k], g);
+    }
+  }
+  if (live) {
     if (dlogits)
       for (int k = A; k < ld_d; ++k) dlogits[(long long)b * ld_d + k] = __float2bfloat16(0.f);
     part[b] = sq;
@@ -299,7 +323,7 @@ int gabril_bias_act_cast_planes(const float* x, int planes, const float* bias, v
                                 long long M, int C, int relu, cudaStream_t stream) {
   if (!x || !y_bf16) return GABRIL_ERR_NULL;
   if (C % 4 || M <= 0 || planes < 1) return GABRIL_ERR_BAD_SHAPE;
-  const int grid = blocks_for(M * C / 4, 256, 148 * 8);
+  const int grid = blocks_for(M * C / 4 * 8, 256, 148 * 8);
   bias_act_cast_kernel<<<grid, 256, 0, stream>>>(x, bias, reinterpret_cast<bf16*>(y_bf16), y_f32, M,
                                                  C, relu, planes);
   GABRIL_CHECK_LAUNCH();
