@@ -402,3 +402,61 @@ extern "C" int gabril_gaze_splat(const float* gaze, float* out, float* ext_ws, c
 #undef GABRIL_SPLAT_CASE
   return GABRIL_ERR_BAD_SHAPE;
 }
+
+// ---- allocation-free variant ------------------------------------------------------------------
+// gabril_gaze_splat with the extrema workspace in a file-scope device array instead of a caller
+// buffer, for callers that cannot allocate (CUDA-graph capture, serving loops).  No counterpart in
+// the reference.  The array is 512 KB per GPU that
+// loads the library, held until exit.  Every call shares it: calls that overlap on the GPU (two
+// streams, two threads) race on it.  Nothing in it has to start at zero - the extrema launch writes
+// every slot [b][0..3][0..S) that the write launch reads - so it is never cleared.
+namespace {
+
+constexpr int kStaticMaxB = 4096;  // samples per call
+constexpr int kStaticMaxDev = 64;
+
+static __device__ __align__(256) float g_splat_ext_static[kStaticMaxB * 4 * kMaxS];
+
+// In host code g_splat_ext_static is only the symbol's host-side stand-in: its device address is
+// looked up once per device, with that device current, and that pointer is what the kernels get.
+float* splat_static_ws() {
+  static float* ws[kStaticMaxDev] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { gabril_set_cuda_error(e); return nullptr; }
+  if (dev < 0 || dev >= kStaticMaxDev) {
+    gabril_set_error("gabril_gaze_splat_static: device ordinal beyond 63");
+    return nullptr;
+  }
+  float* p = __atomic_load_n(&ws[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_splat_ext_static);
+    if (e != cudaSuccess || !sym) {
+      gabril_set_cuda_error(e != cudaSuccess ? e : cudaErrorInvalidSymbol);
+      return nullptr;
+    }
+    p = static_cast<float*>(sym);
+    __atomic_store_n(&ws[dev], p, __ATOMIC_RELEASE);  // racing threads store the same address
+  }
+  return p;
+}
+
+}  // namespace
+
+extern "C" int gabril_gaze_splat_static_max_batch(void) { return kStaticMaxB; }
+
+extern "C" int gabril_gaze_splat_static(const float* gaze, float* out, const float* ktab, const int* Lk,
+                                        int ktab_stride, const float* agg_coeff, const float* step_coeff,
+                                        int normalize_base, int aggregate, int B, int L, int S,
+                                        int center, int P, int H, int W, cudaStream_t stream) {
+  if (B > kStaticMaxB) {
+    gabril_set_error("gabril_gaze_splat_static: B exceeds the static workspace (4096 samples per call); "
+                     "split the batch or use gabril_gaze_splat with a caller workspace");
+    return GABRIL_ERR_BAD_SHAPE;
+  }
+  float* ws = splat_static_ws();
+  if (!ws) return GABRIL_ERR_CUDA;
+  return gabril_gaze_splat(gaze, out, ws, ktab, Lk, ktab_stride, agg_coeff, step_coeff, normalize_base,
+                           aggregate, B, L, S, center, P, H, W, stream);
+}

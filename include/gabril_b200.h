@@ -110,6 +110,23 @@ int gabril_gaze_splat(const float* gaze, float* out, float* ext_ws /* [B][32] fp
                       int ktab_stride, const float* agg_coeff, const float* step_coeff,
                       int normalize_base, int aggregate, int B, int L, int S, int center, int P,
                       int H, int W, cudaStream_t stream);
+/* Allocation-free variant of gabril_gaze_splat.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * gabril_gaze_splat minus ext_ws: the [B][32] fp32 extrema workspace is a file-scope
+ * `static __device__ __align__(256)` array inside the library (csrc/gaze_splat.cu), 512 KB, held by every
+ * GPU that loads the library until the process exits.  Limit: B <= gabril_gaze_splat_static_max_batch()
+ * = 4096 samples per call; a larger B returns GABRIL_ERR_BAD_SHAPE with a message in gabril_last_error().
+ * The call performs no cudaMalloc / cudaFree / allocating library routine; its set-up (once per device,
+ * on the first call with that device current) is one cudaGetSymbolAddress.  Every call shares the one
+ * array, which keeps the previous call's contents (nothing in it has to start at zero: each call
+ * rewrites every slot it reads): calls that OVERLAP on the GPU - different streams, or different host
+ * threads - race on it; serialise them on one stream or use gabril_gaze_splat with separate workspaces. */
+int gabril_gaze_splat_static(const float* gaze, float* out, const float* ktab, const int* Lk,
+                             int ktab_stride, const float* agg_coeff, const float* step_coeff,
+                             int normalize_base, int aggregate, int B, int L, int S, int center, int P,
+                             int H, int W, cudaStream_t stream);
+int gabril_gaze_splat_static_max_batch(void);
 
 /* ---- gaze-mask dropout: apply_gmd_dropout (gaze_utils.py:33-52).  g: fp32 [B, S, H, W];
  * A: the uniform draw fp32 [B, h*w]; K_ws: fp32 [B, h*w] workspace; mnmx_ws: 2 x uint32 workspace.
