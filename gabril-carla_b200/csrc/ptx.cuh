@@ -207,6 +207,16 @@ __device__ __forceinline__ void stg256(void* p, const uint32_t* r) {    // p 32-
                : "memory");
 }
 
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+// named barrier among `count` threads of the CTA (count a multiple of 32); id 0 is __syncthreads'
+__device__ __forceinline__ void bar_sync(int id, int count) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+
 // programmatic dependent launch (griddepcontrol): no-ops when the kernel was launched without the attribute
 __device__ __forceinline__ void pdl_launch_dependents() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");

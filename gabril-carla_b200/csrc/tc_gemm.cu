@@ -26,6 +26,7 @@ __device__ __forceinline__ void report_timeout(const Params& p, int code) {
 
 struct Tile {
   int cls, m0, n0, tap0, ntaps, kb_begin, kb_end, split;
+  int mi, y;   // m tile index over the concatenated classes; n tile [x tap group] index
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -123,6 +124,8 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
   int mi = t - rest * p.tiles_m_total;
   const int split = fdiv(rest, p.fd_n_tiles);
   const int y = rest - split * p.n_tiles;
+  r.mi = mi;
+  r.y = y;
   int cls = 0;
   while (cls + 1 < p.n_classes && mi >= p.tiles_m[cls]) { mi -= p.tiles_m[cls]; ++cls; }
   r.cls = cls;
@@ -168,10 +171,14 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
   const uint32_t wfull = ptx::smem_u32(&bars[2 * kMaxStages + 2 * kMaxAcc]);  // resident weights landed
   const uint32_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
 
+  // fused bias gradient (WGRAD, one tile per CTA): this CTA's epilogue warps also read the dY tile of every stage
+  const bool dbias_cta = p.dbias != nullptr;
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
       ptx::mbar_init(full0 + 8 * s, 1);
-      ptx::mbar_init(empty0 + 8 * s, 1);
+      // a stage is free once its MMAs have completed (tcgen05.commit) and, with the fused bias gradient, once
+      // every epilogue warp has read (or passed on) the dY tile
+      ptx::mbar_init(empty0 + 8 * s, dbias_cta ? 1 + 4 * kEpiGroups : 1);
     }
     for (int b = 0; b < p.acc_bufs; ++b) {
       ptx::mbar_init(tfull0 + 8 * b, 1);
@@ -532,6 +539,57 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
     // whole tiles do, when a tile is a single item).
     const int q = warp & 3;
     const int grp = (warp - kFirstEpilogueWarp) >> 2;
+    if (dbias_cta) {
+      // ---- bias gradient: column sums of the dY tiles of this CTA's split ----
+      // Every CTA that shares (m tile, split) - the tap groups and column tiles of the same dY rows - stages
+      // the same dY tiles: they deal the k-blocks round-robin, so nobody becomes the straggler of the launch
+      // (one reader CTA per group lengthened conv_5 / conv_6 by 20 %).
+      // Thread = (16-byte chunk column, pixel phase): it owns 8 consecutive channels and every pstep-th pixel.
+      // The eight lanes of a 16-byte-per-lane shared load phase read one pixel's 128 contiguous bytes
+      // (permuted by the swizzle XOR): conflict-free.
+      const Tile tl = decode_tile(p, blockIdx.x);
+      const int etid = threadIdx.x - 32 * kFirstEpilogueWarp, nthr = 128 * kEpiGroups;
+      const int nc = p.dy_cols >> 3;                 // chunk columns: 4, 8 or 16
+      const int cpb = p.dy_row_bytes >> 4;           // chunks per box row: 4 or 8
+      const int col = etid & (nc - 1), prow = etid / nc, pstep = nthr / nc;
+      const uint32_t cj = (uint32_t)(col & (cpb - 1));
+      const uint32_t tile_off = p.dy_off + (uint32_t)(col / cpb) * p.dy_box_bytes;
+      const bool wide = p.dy_row_bytes == 128;
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (etid < kBiasSmem) bias_s[etid] = 0.f;
+      ptx::bar_sync(1, nthr);
+      int s = 0;
+      uint32_t ph = 0;
+      const int share_n = p.swap_ab ? p.tiles_m_total * p.n_tiles : p.n_tiles;
+      int turn = p.swap_ab ? tl.mi * p.n_tiles + tl.y : tl.y;   // k-blocks until this CTA's next turn
+      for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+        if (!ptx::mbar_wait(full0 + 8 * s, ph)) { report_timeout(p, 110); break; }
+        const uint32_t st = smem_base + (uint32_t)s * stage_bytes + tile_off;
+        const bool mine = turn == 0;
+        turn = mine ? share_n - 1 : turn - 1;
+#pragma unroll 4
+        for (int px = prow; mine && px < p.kc; px += pstep) {
+          const uint32_t f = wide ? (uint32_t)(px & 7) : (uint32_t)((px >> 1) & 3);
+          const uint4 v = ptx::lds128(st + (uint32_t)px * (uint32_t)p.dy_row_bytes + ((cj ^ f) << 4));
+          acc[0] += bf16lo(v.x); acc[1] += bf16hi(v.x); acc[2] += bf16lo(v.y); acc[3] += bf16hi(v.y);
+          acc[4] += bf16lo(v.z); acc[5] += bf16hi(v.z); acc[6] += bf16lo(v.w); acc[7] += bf16hi(v.w);
+        }
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(empty0 + 8 * s);
+        if (++s == p.stages) { s = 0; ph ^= 1; }
+      }
+      for (int off = nc; off < 32; off <<= 1)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], off);
+      if (lane < nc)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) atomicAdd(&bias_s[col * 8 + i], acc[i]);
+      ptx::bar_sync(1, nthr);
+      if (etid < p.dy_cols && bias_s[etid] != 0.f) {
+        const int c = (p.swap_ab ? 0 : tl.m0) + etid;
+        ptx::red_add_f32(p.dbias + (p.dbias_mod > 0 ? c % p.dbias_mod : c), bias_s[etid]);
+      }
+    }
     int tcount = 0;
     const bool eprof = (p.debug & 4) != 0 && warp == kFirstEpilogueWarp && lane == 0;
     long long e_wait = 0, e_tile = 0, e_n = 0, e_pre = 0;
@@ -707,6 +765,14 @@ static std::once_flag g_attr_once;
 static thread_local const void* t_next_gate_bits = nullptr;
 static thread_local void* t_next_bits_out = nullptr;
 
+static thread_local float* t_next_dbias = nullptr;
+static thread_local int t_next_dbias_mod = 0;
+
+void set_next_dbias(float* dbias, int mod) {
+  t_next_dbias = dbias;
+  t_next_dbias_mod = mod;
+}
+
 void set_next_bits(const void* gate_bits, void* bits_out) {
   t_next_gate_bits = gate_bits;
   t_next_bits_out = bits_out;
@@ -726,6 +792,25 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     }
     if (gb) { p.gate_bits = (const uint32_t*)gb; p.gate = nullptr; }
     p.bits_out = (uint32_t*)bo;
+  }
+  if (t_next_dbias) {
+    float* db = t_next_dbias;
+    const int mod = t_next_dbias_mod;
+    t_next_dbias = nullptr;
+    t_next_dbias_mod = 0;
+    const int cols = p.swap_ab ? p.N_total : std::min(p.M_total[0], 128);
+    const int row_bytes = 2 * (p.swap_ab ? p.b_box_w : p.a_box_w);
+    if (p.kind != KIND_WGRAD || p.total_tiles > num_sms || p.kc != 64 || (row_bytes != 64 && row_bytes != 128) ||
+        (cols != 32 && cols != 64 && cols != 128) || (!p.swap_ab && p.M_total[0] % cols) || cols > kBiasSmem) {
+      gabril_set_error("gabril_conv_wgrad_dbias_next: the next launch is not a weight gradient with 32 / 64 / 128-wide dY tiles");
+      return GABRIL_ERR_BAD_SHAPE;
+    }
+    p.dbias = db;
+    p.dbias_mod = mod;
+    p.dy_cols = cols;
+    p.dy_row_bytes = row_bytes;
+    p.dy_off = p.swap_ab ? p.a_stage_bytes : 0u;
+    p.dy_box_bytes = p.swap_ab ? p.b_box_bytes : p.a_box_bytes;
   }
   auto magic = [](int d) {
     FastDiv f{0u, 0u};

@@ -154,6 +154,15 @@ struct Params {
   FastDiv fd_tiles_m, fd_n_tiles, fd_tap_groups, fd_border_w, fd_border_h, fd_border_hw, fd_quad;
   FastDiv fd_hw[4], fd_ws[4];    // remap: Hs*Ws, Ws per class
   FastDiv fd_ohw[4], fd_ow[4];   // im2col traversal: OHW, OW per class
+  // WGRAD: bias gradient fused into the weight-gradient launch (gabril_conv_wgrad_dbias_next).  The dY tile
+  // of every k-block is in shared memory anyway (A operand, or B in the exchanged form); the CTAs of tap
+  // group 0 / column tile 0 let their epilogue warps - idle until the k loop ends - add up its columns:
+  //   dbias[(col0 + c) % dbias_mod] += sum_pixels dY[pixel][c]
+  // which replaces a separate pass that re-read every dY from HBM (2.2 GB per step at batch 1024).
+  float* dbias;
+  int dbias_mod;
+  uint32_t dy_off, dy_box_bytes;   // the dY tile inside a stage: boxes of [kc pixels][dy_row_bytes / 2 channels]
+  int dy_row_bytes, dy_cols;       // 64 or 128 (= the TMA swizzle span); channels summed per tile (<= 128)
   int* err_flag;
   int debug;  // perf experiments only: bit0 = producer skips the TMA copies, bit1 = issuer skips the MMAs
 };
@@ -164,5 +173,7 @@ int launch(const Params& p, int num_sms, size_t smem_bytes, cudaStream_t stream)
 // Launch attribute of the NEXT launch() on the calling host thread (consumed by it): see
 // gabril_conv_epilogue_bits in include/gabril_b200.h.
 void set_next_bits(const void* gate_bits, void* bits_out);
+// Same mechanism: the next WGRAD launch() of this thread also accumulates the bias gradient into dbias.
+void set_next_dbias(float* dbias, int mod);
 
 }  // namespace tc

@@ -282,6 +282,11 @@ int gabril_conv_epilogue_bits(const void* gate_bits, void* sign_bits_out) {
   return GABRIL_OK;
 }
 
+int gabril_conv_wgrad_dbias_next(float* dbias, int mod) {
+  tc::set_next_dbias(dbias, mod);
+  return GABRIL_OK;
+}
+
 int gabril_poll_error(void) {
   if (!g_err_flag) return 0;
   int v = 0;

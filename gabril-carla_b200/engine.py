@@ -85,6 +85,7 @@ class StepEngine:
         self._graphs, self._warm_B, self._warm_store_B = {}, 0, 0
         self._own_in, self._own_inputs = {}, False
         self._colsum_pending, self._cs_i = False, 0
+        self.fused_dbias = os.environ.get("GABRIL_FUSED_DBIAS", "1") != "0"   # A/B switch: 0 = separate colsum passes
         self._cs_ev = [torch.cuda.Event() for _ in range(8)] if self._side else []
         if self._side:
             self._ev["colsum"] = torch.cuda.Event()
@@ -498,8 +499,11 @@ class StepEngine:
         ops.conv_dgrad(b["dlog"].view(B, 1, 1, s.AP), a.WB("act.2.w"), b["dact1"].view(B, 1, 1, s.Z),
                        1, 1, 1, 0, gate=b["act1"].view(B, 1, 1, s.Z))
         # actor.0
-        ops.colsum_bf16(b["dact1"], a.G("act.0.b"))
-        ops.conv_wgrad(b["dact1"].view(B, 1, 1, s.Z), b["zf"].view(B, 1, 1, s.Z), a.G("act.0.w"), 1, 1, 1, 0)
+        fb = self.fused_dbias
+        if not fb:
+            ops.colsum_bf16(b["dact1"], a.G("act.0.b"))
+        ops.conv_wgrad(b["dact1"].view(B, 1, 1, s.Z), b["zf"].view(B, 1, 1, s.Z), a.G("act.0.w"), 1, 1, 1, 0,
+                       dbias=a.G("act.0.b") if fb else None)
         zf_addend = None
         if self.use_gril:   # the coordinate head's share of d z_flat
             ops.conv_wgrad(b["g_dpred"].view(B, 1, 1, s.AP), b["g_h"].view(B, 1, 1, s.Z), a.G("gril.2.w"), 1, 1, 1, 0)
@@ -513,9 +517,10 @@ class StepEngine:
                        addend=zf_addend)
         # pre_actor
         self._join_reg()                                    # dz_reg, losses (side stream)
-        ops.colsum_bf16(b["dzf"], a.G("pre.b"))
+        if not fb:
+            ops.colsum_bf16(b["dzf"], a.G("pre.b"))
         ops.conv_wgrad(b["dzf"].view(B, 1, 1, s.Z), b["z"].view(B, 1, 1, s.flat), a.G("pre.w"), 1, 1, 1, 0,
-                       direct_store=direct)
+                       direct_store=direct, dbias=a.G("pre.b") if fb else None)
         ops.conv_dgrad(b["dzf"].view(B, 1, 1, s.Z), a.WB("pre.w"), b["dz"].view(B, 1, 1, s.flat), 1, 1, 1, 0,
                        addend=b["dz_reg"].view(B, 1, 1, s.flat) if self.use_reg else None)
         if rowmask is not None:
@@ -624,11 +629,14 @@ class StepEngine:
         c0 = s.C0 if c0 is None else c0
         # conv_6 / conv_5
         last, sb_last = b[f"r{s.NR - 1}"], b[f"sb_r{s.NR - 1}"]
-        self._colsum(b["dz"], a.G(f"{pfx}.conv6.b"))
-        ops.conv_wgrad(b["dz"], b["a5"], a.G(f"{pfx}.conv6.w"), 5, 5, 1, 2)
+        fb = self.fused_dbias   # bias gradients inside the weight-gradient launches (no separate pass over dY)
+        if not fb:
+            self._colsum(b["dz"], a.G(f"{pfx}.conv6.b"))
+        ops.conv_wgrad(b["dz"], b["a5"], a.G(f"{pfx}.conv6.w"), 5, 5, 1, 2, dbias=a.G(f"{pfx}.conv6.b") if fb else None)
         ops.conv_dgrad(b["dz"], a.WB(f"{pfx}.conv6.w"), b["da5"], 5, 5, 1, 2, gate_bits=b["sb_a5"])
-        self._colsum(b["da5"], a.G(f"{pfx}.conv5.b"))
-        ops.conv_wgrad(b["da5"], last, a.G(f"{pfx}.conv5.w"), 5, 5, 1, 2)
+        if not fb:
+            self._colsum(b["da5"], a.G(f"{pfx}.conv5.b"))
+        ops.conv_wgrad(b["da5"], last, a.G(f"{pfx}.conv5.w"), 5, 5, 1, 2, dbias=a.G(f"{pfx}.conv5.b") if fb else None)
         dt, other = b["dt_a"], b["dt_b"]
         ops.conv_dgrad(b["da5"], a.WB(f"{pfx}.conv5.w"), dt, 5, 5, 1, 2, gate_bits=sb_last)
         # residual stack, last block first
@@ -641,23 +649,29 @@ class StepEngine:
                            gate_bits=b[f"sb_r{i - 1}"])
             dt, other = other, dt
         # conv_4 .. conv_1
-        self._colsum(dt, a.G(f"{pfx}.conv4.b"))
-        ops.conv_wgrad(dt, b["a3"], a.G(f"{pfx}.conv4.w"), 3, 3, 1, 0)
+        if not fb:
+            self._colsum(dt, a.G(f"{pfx}.conv4.b"))
+        ops.conv_wgrad(dt, b["a3"], a.G(f"{pfx}.conv4.w"), 3, 3, 1, 0, dbias=a.G(f"{pfx}.conv4.b") if fb else None)
         ops.conv_dgrad(dt, a.WB(f"{pfx}.conv4.w"), b["da3"], 3, 3, 1, 0, gate_bits=b["sb_a3"])
-        self._colsum(b["da3"], a.G(f"{pfx}.conv3.b"))
+        if not fb:
+            self._colsum(b["da3"], a.G(f"{pfx}.conv3.b"))
         # conv_3 over the zero-bordered a2p (pad 0): the border gradients are gated to zero by a2p itself
-        ops.conv_wgrad(b["da3"], b["a2p"], a.G(f"{pfx}.conv3.w"), 4, 4, 2, 0)
+        ops.conv_wgrad(b["da3"], b["a2p"], a.G(f"{pfx}.conv3.w"), 4, 4, 2, 0, dbias=a.G(f"{pfx}.conv3.b") if fb else None)
         ops.conv_dgrad(b["da3"], a.WB(f"{pfx}.conv3.w"), b["da2p"], 4, 4, 2, 0, gate_bits=b["sb_a2p"])
-        self._colsum(b["da2p"], a.G(f"{pfx}.conv2.b"))
-        # conv_2 on the space-to-depth grid: dY pixel (i, j) sits at flat row q + SW + 1
+        if not fb:
+            self._colsum(b["da2p"], a.G(f"{pfx}.conv2.b"))
+        # conv_2 on the space-to-depth grid: dY pixel (i, j) sits at flat row q + SW + 1 (the rows before it are
+        # border cells: zero, so the fused column sums miss nothing)
         ops.conv_wgrad_flat(b["da2p"], b["a1s"], a.G(f"{pfx}.conv2.w"), 2, 2, self.SW + 1,
-                            flop_pixels=B * s.H2 * s.W2)
+                            flop_pixels=B * s.H2 * s.W2, dbias=a.G(f"{pfx}.conv2.b") if fb else None)
         ops.conv_flat(b["da2p"], a.WB(f"{pfx}.conv2.w"), b["da1s"], 2, 2, gate_bits=b["sb_a1s"], transpose_w=True,
                       flop_pixels=B * s.H2 * s.W2)  # algorithmic FLOPs of the k4/s2 dgrad
         M1 = B * self.SH * self.SW * 4
-        self._colsum(b["da1s"].view(M1, s.C1), a.G(f"{pfx}.conv1.b"))
+        if not fb:
+            self._colsum(b["da1s"].view(M1, s.C1), a.G(f"{pfx}.conv1.b"))
         b["dw4"].zero_()
-        ops.conv1_s4d_wgrad(b["da1s"], b["x4"], b["dw4"], B, self.SH, self.SW, s.H1, s.W1)
+        ops.conv1_s4d_wgrad(b["da1s"], b["x4"], b["dw4"], B, self.SH, self.SW, s.H1, s.W1,
+                            dbias=a.G(f"{pfx}.conv1.b") if fb else None)
         ops.conv1_s4d_fold(b["dw4"], a.G(f"{pfx}.conv1.w"), c0)
         if self._colsum_pending:
             main = torch.cuda.current_stream(self.device)

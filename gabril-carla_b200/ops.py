@@ -76,6 +76,16 @@ def _epilogue_bits(gate_bits, bits_out, out):
     _lib.check(_lib.init().gabril_conv_epilogue_bits(ptr(gate_bits), ptr(bits_out)), "gabril_conv_epilogue_bits")
 
 
+def _wgrad_dbias(dbias, cout, mod=0):
+    """Fuse the bias gradient into the next weight-gradient launch: dbias[c % mod] += column sums of dy."""
+    if dbias is None:
+        return
+    _chk(dbias, torch.float32, "dbias")
+    if dbias.numel() != (mod if mod else cout):
+        raise ValueError(f"dbias: expected {mod if mod else cout} elements, got {dbias.numel()}")
+    _lib.check(_lib.init().gabril_conv_wgrad_dbias_next(ptr(dbias), c_int(mod)), "gabril_conv_wgrad_dbias_next")
+
+
 def sign_bits_like(t):
     """Zeroed sign-word buffer for a bf16 activation tensor (1 bit per element)."""
     assert t.numel() % 32 == 0
@@ -129,8 +139,9 @@ def conv_dgrad(dy, w, dx, R, S, stride, pad, addend=None, gate=None, rowmask=Non
     return dx
 
 
-def conv_wgrad(dy, x, dw, R, S, stride, pad, direct_store=False):
-    """dw [Cout,R*S,Cin] fp32 += dy^T * im2col(x).  direct_store overwrites (no split)."""
+def conv_wgrad(dy, x, dw, R, S, stride, pad, direct_store=False, dbias=None):
+    """dw [Cout,R*S,Cin] fp32 += dy^T * im2col(x).  direct_store overwrites (no split).
+    dbias fp32 [Cout] (optional) += column sums of dy, inside the same launch."""
     _chk_bf16(dy, "dy"); _chk_bf16(x, "x")
     N, H, W, Cin = x.shape
     Cout = dw.shape[0]
@@ -138,6 +149,7 @@ def conv_wgrad(dy, x, dw, R, S, stride, pad, direct_store=False):
     OH, OW = conv_out_hw(H, W, R, S, stride, pad)
     assert dy.numel() == N * OH * OW * Cout, (dy.shape, N, OH, OW, Cout)
     with _span("tc_gemm_kernel", f"wgrad {Cin}x{Cout} k{R}s{stride}", 2.0 * N * OH * OW * Cout * R * S * Cin, "flop"):
+        _wgrad_dbias(dbias, Cout)
         st = _fn("gabril_conv_wgrad")(ptr(dy), ptr(x), ptr(dw), c_int(N), c_int(H), c_int(W),
                                       c_int(Cin), c_int(Cout), c_int(R), c_int(S), c_int(stride),
                                       c_int(pad), c_int(int(direct_store)), stream())
@@ -176,7 +188,7 @@ def conv_flat(x, w, y, R, S, *, bias=None, resid=None, gate=None, valid=None, ou
     return y
 
 
-def conv_wgrad_flat(dy, x, dw, R, S, dy_row_off, flop_pixels=None):
+def conv_wgrad_flat(dy, x, dw, R, S, dy_row_off, flop_pixels=None, dbias=None):
     """dw [Cy,R*S,Cx] fp32 += sum_q dy_flat[q + dy_row_off]^T x_flat[q + r*Wg + s]; dy [N,Hg,Wg,Cy] and
     x [N,Hg,Wg,Cx] share one zero-bordered grid."""
     _chk_bf16(dy, "dy"); _chk_bf16(x, "x")
@@ -185,6 +197,7 @@ def conv_wgrad_flat(dy, x, dw, R, S, dy_row_off, flop_pixels=None):
     assert dy.numel() == N * Hg * Wg * Cy and dw.dtype == torch.float32 and dw.numel() == Cy * R * S * Cx
     px = flop_pixels if flop_pixels is not None else N * Hg * Wg
     with _span("tc_gemm_kernel", f"wgrad-flat {Cx}x{Cy} k{R}x{S}", 2.0 * px * Cy * R * S * Cx, "flop"):
+        _wgrad_dbias(dbias, Cy)
         st = _fn("gabril_conv_wgrad_flat")(ptr(dy), ptr(x), ptr(dw), c_int(N), c_int(Hg), c_int(Wg), c_int(Cx),
                                            c_int(Cy), c_int(R), c_int(S), c_int(dy_row_off), stream())
     _lib.check(st, "gabril_conv_wgrad_flat")
@@ -288,12 +301,14 @@ def conv1_s4d_fwd(x4, w4, bias, y, N, SH, SW, img_h, img_w, relu=True, rowmask=N
     return y
 
 
-def conv1_s4d_wgrad(dy, x4, dw4, N, SH, SW, img_h, img_w):
-    """dw4 fp32 [4*C1,2,2*Cp] += dy [N,SH,SW,4*C1]^T . x4 windows."""
+def conv1_s4d_wgrad(dy, x4, dw4, N, SH, SW, img_h, img_w, dbias=None):
+    """dw4 fp32 [4*C1,2,2*Cp] += dy [N,SH,SW,4*C1]^T . x4 windows; dbias fp32 [C1] (optional) += column sums of
+    dy folded over its four quadrants."""
     _chk_bf16(dy, "dy"); _chk_bf16(x4, "x4"); _chk(dw4, torch.float32, "dw4")
     Cp, C1 = x4.shape[1], dw4.shape[0] // 4
     assert dw4.shape == (4 * C1, 2, 2 * Cp) and dy.numel() == N * SH * SW * 4 * C1
     with _span("tc_gemm_kernel", f"wgrad-s4d {Cp}x{C1} k4s2", 2.0 * N * img_h * img_w * C1 * Cp, "flop"):
+        _wgrad_dbias(dbias, 4 * C1, C1)
         st = _lib.init().gabril_conv1_s4d_wgrad(ptr(dy), ptr(x4), ptr(dw4), c_int(N), c_int(SH), c_int(SW), c_int(Cp),
                                                 c_int(C1), stream())
     _lib.check(st, "gabril_conv1_s4d_wgrad")

@@ -60,6 +60,14 @@ int gabril_poll_error(void);
  * Either may be NULL.  The buffers must be zero wherever the output tensor is never stored
  * (zero borders). */
 int gabril_conv_epilogue_bits(const void* gate_bits, void* sign_bits_out);
+/* Bias gradient fused into the NEXT weight-gradient launch of the calling host thread (gabril_conv_wgrad,
+ * gabril_conv_wgrad_flat, gabril_conv1_s4d_wgrad; consumed by it): dbias[c % mod] += sum over every output pixel
+ * of dy[pixel][c] (mod = 0: dbias[c]) - the bias gradient of nn.Conv2d / nn.Linear backward (linear_models.py:141-207,
+ * train_bc.py:79-82), taken from the dY tiles the launch stages in shared memory anyway instead of a separate
+ * gabril_colsum_bf16 pass over dy.  The caller zeroes dbias (it lives in the flat gradient arena).  Cout must be
+ * 32, 64 or a multiple of 128; conv_1's space-to-depth form passes mod = C1 (its 4*C1 columns are four quadrants
+ * of the same channels). */
+int gabril_conv_wgrad_dbias_next(float* dbias, int mod);
 /* nn.Conv2d / nn.Linear forward — linear_models.py:141-207, train_bc.py:79-82.
  * y = relu?( conv(x, w) + bias + resid ) * rowmask ; out_f32_atomic = 1: y is fp32 and the raw
  * products are atomically added (split-K linear; the caller zeroes y); = 2: y is fp32

@@ -92,6 +92,13 @@ def test_conv_fwd_dgrad_wgrad(ops, layer, N):
     ops.conv_wgrad(dy.to(DEV), xd, dw, R, S, stride, pad)
     wref = ops.w_oihw_to_internal(torch.nn.grad.conv2d_weight(x64, (Cout, Cin, R, S), dy64, stride=stride, padding=pad))
     assert rel(dw.cpu(), wref) <= 2e-5
+    # the same launch with the bias gradient fused in (gabril_conv_wgrad_dbias_next): db += column sums of dy
+    # (fp32 sums of the bf16 values, like gabril_colsum_bf16), dW unchanged up to the atomics' order
+    dw2 = torch.zeros_like(dw)
+    db = torch.full((Cout,), 0.5, device=DEV)
+    ops.conv_wgrad(dy.to(DEV), xd, dw2, R, S, stride, pad, dbias=db)
+    assert rel(dw2.cpu(), wref) <= 2e-5
+    assert rel(db.cpu() - 0.5, dy.double().sum((0, 1, 2))) <= 2e-5
     _lib.poll_error()
 
 
@@ -183,6 +190,11 @@ def test_conv_flat_fwd_dgrad_wgrad(ops, layer, N):
     ops.conv_wgrad_flat(dyg.to(DEV), xd, dw, R, R, 0)
     wref = ops.w_oihw_to_internal(torch.nn.grad.conv2d_weight(x64, (Cout, Cin, R, R), dy64, padding=pad))
     assert rel(dw.cpu(), wref) <= 2e-5
+    dw2 = torch.zeros_like(dw)
+    db = torch.zeros(Cout, device=DEV)
+    ops.conv_wgrad_flat(dyg.to(DEV), xd, dw2, R, R, 0, dbias=db)   # fused bias gradient
+    assert rel(dw2.cpu(), wref) <= 2e-5
+    assert rel(db.cpu(), dy.double().sum((0, 1, 2))) <= 2e-5
     _lib.poll_error()
 
 
@@ -266,3 +278,9 @@ def test_conv1_s4d_fwd_wgrad(ops, gray, N):
     got_dw[:, 0] -= 1.0
     assert rel(got_dw[:, :16 * C0], ref_dw) <= 2e-3
     assert torch.count_nonzero(got_dw[:, 16 * C0:]) == 0
+    # fused bias gradient: the 4*C1 columns fold onto conv_1's C1 channels
+    dw4b = torch.zeros_like(dw4)
+    db = torch.zeros(C1, device=DEV)
+    ops.conv1_s4d_wgrad(dy.to(DEV), x4, dw4b, N, SH, SW, H1, W1, dbias=db)
+    assert rel(dw4b.cpu(), dw4.double().cpu()) <= 2e-5
+    assert rel(db.cpu(), dy.double().reshape(-1, 4, C1).sum((0, 1))) <= 2e-5

@@ -69,3 +69,4 @@ run("full step", {})
 run("no colsum", {"colsum_bf16": nop})
 run("no reg_dist", {"reg_dist": nop, "reg_mse": nop})
 run("no colsum, no reg_dist", {"colsum_bf16": nop, "reg_dist": nop, "reg_mse": nop})
+run("no gaze_splat", {"gaze_splat": nop})
