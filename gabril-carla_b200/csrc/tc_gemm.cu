@@ -485,7 +485,9 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
                   for (int j = 0; j < 4; ++j) {
                     const uint64_t a_desc = ((uint64_t)a_hi32 << 32) | (uint64_t)(a_lo + j * a_kstep);
                     const uint64_t b_desc = ((uint64_t)b_hi32 << 32) | (uint64_t)(bb + j * b_kstep);
-                    ptx::umma_bf16(dcol, a_desc, b_desc, idesc, (kb > tl.kb_begin || j > 0) ? 1u : 0u);
+                    // exchanged form (narrow dY): the slab view is the M = 128 operand, dY the N = Cy one
+                    if (p.swap_ab) ptx::umma_bf16(dcol, b_desc, a_desc, idesc, (kb > tl.kb_begin || j > 0) ? 1u : 0u);
+                    else ptx::umma_bf16(dcol, a_desc, b_desc, idesc, (kb > tl.kb_begin || j > 0) ? 1u : 0u);
                   }
                 }
               ptx::umma_commit(empty0 + 8 * s);
@@ -798,8 +800,9 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     const int mod = t_next_dbias_mod;
     t_next_dbias = nullptr;
     t_next_dbias_mod = 0;
+    const bool dy_is_b = p.swap_ab && !p.a_flat;   // the flat exchanged form keeps dY in the stage's first region
     const int cols = p.swap_ab ? p.N_total : std::min(p.M_total[0], 128);
-    const int row_bytes = 2 * (p.swap_ab ? p.b_box_w : p.a_box_w);
+    const int row_bytes = 2 * (dy_is_b ? p.b_box_w : p.a_box_w);
     if (p.kind != KIND_WGRAD || p.total_tiles > num_sms || p.kc != 64 || (row_bytes != 64 && row_bytes != 128) ||
         (cols != 32 && cols != 64 && cols != 128) || (!p.swap_ab && p.M_total[0] % cols) || cols > kBiasSmem) {
       gabril_set_error("gabril_conv_wgrad_dbias_next: the next launch is not a weight gradient with 32 / 64 / 128-wide dY tiles");
@@ -809,8 +812,8 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     p.dbias_mod = mod;
     p.dy_cols = cols;
     p.dy_row_bytes = row_bytes;
-    p.dy_off = p.swap_ab ? p.a_stage_bytes : 0u;
-    p.dy_box_bytes = p.swap_ab ? p.b_box_bytes : p.a_box_bytes;
+    p.dy_off = dy_is_b ? p.a_stage_bytes : 0u;
+    p.dy_box_bytes = dy_is_b ? p.b_box_bytes : p.a_box_bytes;
   }
   auto magic = [](int d) {
     FastDiv f{0u, 0u};

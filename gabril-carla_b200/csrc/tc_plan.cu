@@ -851,21 +851,29 @@ static int conv_wgrad_flat_impl(const void* dy, const void* x, float* dw, int N,
   p.flat_pitch = Wg; p.flat_R = R; p.flat_S = S;
   p.dy_row_off = dy_row_off;
   p.kc = KP;
-  // A = dy^T: M = Cy rows padded to 128 with out-of-range (zero-filled) boxes
+  // Narrow dY (Cy <= 64) over 128 input channels: with A = dy^T half (or three quarters) of every MMA's M rows
+  // would be padding, so the operands are exchanged like in conv_wgrad_swapped: the slab views are the M = 128
+  // operand, dY the N = Cy one, and tap t accumulates [Cx lanes][Cy columns] (conv_2: 16 MMAs of 128 x 64 x 16
+  // per k-block instead of 16 of 128 x 128 x 16).  The shared-memory layout and the producer stay as they are.
+  static int swap_on = -1;
+  if (swap_on < 0) { const char* e = getenv("GABRIL_WGRAD_FLAT_NO_SWAP"); swap_on = (e && e[0] == '1') ? 0 : 1; }
+  const bool swap = swap_on && Cy <= 64 && Cx == 128;
+  p.swap_ab = swap ? 1 : 0;
+  // A = dy^T: M = Cy rows padded to 128 with out-of-range (zero-filled) boxes (exchanged form: one box, N = Cy)
   const int aw = std::min(64, Cy), a_sw = aw * 2;
   p.a_box_w = aw;
-  p.a_boxes = 128 / aw;
+  p.a_boxes = swap ? 1 : 128 / aw;
   p.a_box_bytes = KP * a_sw;
   p.a_stage_bytes = round_up(p.a_boxes * p.a_box_bytes, 1024);
   p.desc_a_hi = desc_hi(p.a_box_bytes, 8 * a_sw, layout_type_for_bytes(a_sw));
   // B = x slabs: 64-channel boxes of KP + S - 1 pixel rows
-  int block_n = std::min(Cx, 128);
+  int block_n = swap ? Cy : std::min(Cx, 128);   // accumulator columns per tap
   while (S * block_n > 512) block_n >>= 1;
-  if (block_n < 64) return GABRIL_ERR_BAD_SHAPE;
+  if (block_n < (swap ? 32 : 64) || (swap && block_n != Cy)) return GABRIL_ERR_BAD_SHAPE;
   const int slab_rows = KP + S - 1;
   p.block_n = block_n;
   p.b_box_w = 64;
-  p.b_boxes = block_n / 64;
+  p.b_boxes = swap ? Cx / 64 : block_n / 64;
   p.slab_tx_bytes = (uint32_t)slab_rows * 128u;
   p.b_tap_bytes = round_up(p.slab_tx_bytes, 1024);  // one slab box
   p.b_box_bytes = p.b_tap_bytes;
@@ -882,8 +890,8 @@ static int conv_wgrad_flat_impl(const void* dy, const void* x, float* dw, int N,
   p.a_kstep = (uint32_t)((16 * a_sw) >> 4);
   p.b_kstep = (uint32_t)((16 * 128) >> 4);
   p.idesc = make_idesc(1, 1, 128, block_n);
-  p.M_total[0] = Cy;
-  p.N_total = Cx;
+  p.M_total[0] = swap ? Cx : Cy;
+  p.N_total = swap ? Cy : Cx;
   p.kb_total = (int)((P + KP - 1) / KP);
   {
     uint64_t dims[2] = {(uint64_t)Cy, (uint64_t)P};
@@ -899,14 +907,14 @@ static int conv_wgrad_flat_impl(const void* dy, const void* x, float* dw, int N,
     rc = tiled_map(&p.mapB, x, 2, dims, strides, box, 128);
     if (rc) return rc;
   }
-  const int m_tiles = (Cy + 127) / 128, n_tiles = Cx / block_n;
+  const int m_tiles = swap ? 1 : (Cy + 127) / 128, n_tiles = swap ? 1 : Cx / block_n;
   const int base = m_tiles * n_tiles * p.tap_groups;
   int splits = std::max(1, std::min(p.kb_total, g_num_sms / base));  // one whole wave
   p.kb_per_split = (p.kb_total + splits - 1) / splits;
   splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
   p.out_mode = tc::OUT_F32_ATOMIC;
   p.out = dw;
-  p.ldo = (long long)T * Cx;
+  p.ldo = (long long)T * Cx;   // exchanged form: element (cy, tap, cx) from lane cx, column cy (kernel: swap_ab)
   p.tap_stride = Cx;
   p.err_flag = g_err_flag;
   size_t smem;
