@@ -9,6 +9,7 @@
 #include <cstring>
 
 #include "common.cuh"
+#include "res_block.cuh"
 #include "tc_gemm.cuh"
 
 namespace {
@@ -280,6 +281,51 @@ int gabril_tc_init(void) { return resolve_driver(); }
 int gabril_conv_epilogue_bits(const void* gate_bits, void* sign_bits_out) {
   tc::set_next_bits(gate_bits, sign_bits_out);
   return GABRIL_OK;
+}
+
+// One Residual block forward (linear_models.py:78-102) in one launch: h = relu(conv3x3(x)), out = relu(x +
+// conv1x1(h)); x is the rectified block input (NHWC bf16, 128 channels), w3 [32][9][128], w1 [128][1][32].
+int gabril_res_block_fwd(const void* x, const void* w3, const void* w1, void* h, void* bits_h, void* out,
+                         void* bits_out, int N, int H, int W, int C, int Ch, cudaStream_t stream) {
+  int rc = resolve_driver();
+  if (rc) return rc;
+  if (!x || !w3 || !w1 || !h || !bits_h || !out || !bits_out) return GABRIL_ERR_NULL;
+  const long long M = (long long)N * H * W;
+  if (C != 128 || Ch != 32 || N <= 0 || H < 1 || W < 1 || M >= (1ll << 31)) {
+    gabril_set_error("gabril_res_block_fwd: built for 128 -> 32 -> 128 channels");
+    return GABRIL_ERR_BAD_SHAPE;
+  }
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(h) | reinterpret_cast<uintptr_t>(out)) & 31)
+    return GABRIL_ERR_BAD_SHAPE;
+  rb::Params p;
+  memset(&p, 0, sizeof(p));
+  rc = im2col_map(&p.mapX, x, N, H, W, C, -1, -1, -1, -1, 64, 128, 1);
+  if (rc) return rc;
+  rc = weight_map(&p.mapW3, w3, Ch, 9, C, 0, 64, Ch);
+  if (rc) return rc;
+  rc = weight_map(&p.mapW1, w1, C, 1, Ch, 0, 32, C);
+  if (rc) return rc;
+  p.x = (const bf16*)x; p.h = (bf16*)h; p.bits_h = (uint32_t*)bits_h; p.out = (bf16*)out; p.bits_out = (uint32_t*)bits_out;
+  p.M = (int)M; p.HW = H * W; p.W = W; p.tiles = (int)((M + 127) / 128);
+  auto magic = [](int d) {
+    tc::FastDiv f{0u, 0u};
+    if (d > 1) {
+      uint32_t l = 0;
+      while ((1ull << l) < (unsigned long long)d) ++l;
+      f.mul = (uint32_t)((((1ull << l) - (unsigned long long)d) << 32) / (unsigned long long)d + 1ull);
+      f.shr = l;
+    }
+    return f;
+  };
+  p.fd_hw = magic(p.HW); p.fd_w = magic(p.W);
+  p.desc_a1_hi = desc_hi(16, 1024, 2);   // K-major, 128-byte rows
+  p.desc_b1_hi = desc_hi(16, 1024, 2);
+  p.desc_a2_hi = desc_hi(16, 512, 4);    // K-major, 64-byte rows
+  p.desc_b2_hi = desc_hi(16, 512, 4);
+  p.idesc1 = make_idesc(0, 0, 128, Ch);
+  p.idesc2 = make_idesc(0, 0, 128, C);
+  p.err_flag = g_err_flag;
+  return rb::launch(p, g_num_sms, stream);
 }
 
 int gabril_conv_wgrad_dbias_next(float* dbias, int mod) {

@@ -86,6 +86,7 @@ class StepEngine:
         self._own_in, self._own_inputs = {}, False
         self._colsum_pending, self._cs_i = False, 0
         self.fused_dbias = os.environ.get("GABRIL_FUSED_DBIAS", "1") != "0"   # A/B switch: 0 = separate colsum passes
+        self.fused_res = os.environ.get("GABRIL_FUSED_RES", "1") != "0"       # A/B switch: 0 = two launches per block
         self._cs_ev = [torch.cuda.Event() for _ in range(8)] if self._side else []
         if self._side:
             self._ev["colsum"] = torch.cuda.Event()
@@ -379,8 +380,13 @@ class StepEngine:
         # conv_4 has no activation of its own; the first Residual's in-place ReLU rectifies it (F7)
         ops.conv_fwd(b["a3"], a.WB(f"{pfx}.conv4.w"), a.P(f"{pfx}.conv4.b"), b["r-1"], 3, 3, 1, 0, relu=True,
                      bits_out=b["sb_r-1"])
+        fused_res = self.fused_res and s.NH == 128 and s.RH == 32
         for i in range(s.NR):
             prev = b[f"r{i - 1}"]
+            if fused_res:   # both convolutions of the block in one launch: h never round-trips through HBM
+                ops.res_block_fwd(prev, a.WB(f"{pfx}.res{i}.c3.w"), a.WB(f"{pfx}.res{i}.c1.w"), b[f"h{i}"],
+                                  b[f"sb_h{i}"], b[f"r{i}"], b[f"sb_r{i}"])
+                continue
             ops.conv_fwd(prev, a.WB(f"{pfx}.res{i}.c3.w"), None, b[f"h{i}"], 3, 3, 1, 1, relu=True,
                          bits_out=b[f"sb_h{i}"])
             # relu(x) + block(x); the next consumer (next Residual / the stack's final ReLU)

@@ -139,6 +139,23 @@ def conv_dgrad(dy, w, dx, R, S, stride, pad, addend=None, gate=None, rowmask=Non
     return dx
 
 
+def res_block_fwd(x, w3, w1, h, bits_h, out, bits_out):
+    """One Residual block forward in one launch: h = relu(conv3x3(x, w3)), out = relu(x + conv1x1(h, w1)), with the
+    sign words of both (x [N,H,W,128] bf16 rectified, w3 [32,9,128], w1 [128,1,32])."""
+    for t, n in ((x, "x"), (w3, "w3"), (w1, "w1"), (h, "h"), (out, "out")):
+        _chk_bf16(t, n)
+    N, H, W, C = x.shape
+    Ch = w3.shape[0]
+    assert w3.shape == (Ch, 9, C) and w1.shape == (C, 1, Ch) and h.numel() == N * H * W * Ch and out.numel() == x.numel()
+    assert bits_h.dtype == torch.int32 and bits_h.numel() * 32 == h.numel()
+    assert bits_out.dtype == torch.int32 and bits_out.numel() * 32 == out.numel()
+    with _span("tc_gemm_kernel", f"res-block {C}->{Ch}->{C}", 2.0 * N * H * W * (9 * C * Ch + Ch * C), "flop"):
+        st = _fn("gabril_res_block_fwd")(ptr(x), ptr(w3), ptr(w1), ptr(h), ptr(bits_h), ptr(out), ptr(bits_out),
+                                          c_int(N), c_int(H), c_int(W), c_int(C), c_int(Ch), stream())
+    _lib.check(st, "gabril_res_block_fwd")
+    return out
+
+
 def conv_wgrad(dy, x, dw, R, S, stride, pad, direct_store=False, dbias=None):
     """dw [Cout,R*S,Cin] fp32 += dy^T * im2col(x).  direct_store overwrites (no split).
     dbias fp32 [Cout] (optional) += column sums of dy, inside the same launch."""

@@ -68,6 +68,16 @@ int gabril_conv_epilogue_bits(const void* gate_bits, void* sign_bits_out);
  * 32, 64 or a multiple of 128; conv_1's space-to-depth form passes mod = C1 (its 4*C1 columns are four quadrants
  * of the same channels). */
 int gabril_conv_wgrad_dbias_next(float* dbias, int mod);
+/* One Residual block forward - linear_models.py:78-102 (`x + _block(x)` with the block's in-place ReLU already
+ * applied to x) - in ONE launch: h = relu(conv3x3(x, w3; pad 1, no bias)) [N,H,W,Ch] and
+ * out = relu(x + conv1x1(h, w1; no bias)) [N,H,W,C], both stored as bf16 together with their packed sign words
+ * (layout of gabril_conv_epilogue_bits; bits_h: one word per pixel, bits_out: C / 32 per pixel).  The
+ * intermediate goes from TMEM through registers into shared memory as the second MMA's operand instead of
+ * through HBM.  Bit-identical to gabril_conv_fwd(3x3, relu) followed by gabril_conv_fwd(1x1, resid = x, relu).
+ * Built for C = 128, Ch = 32 (num_hiddens / num_residual_hiddens of the reference configs); other widths return
+ * GABRIL_ERR_BAD_SHAPE and the caller uses the two convolutions. */
+int gabril_res_block_fwd(const void* x, const void* w3, const void* w1, void* h, void* bits_h, void* out,
+                         void* bits_out, int N, int H, int W, int C, int Ch, cudaStream_t stream);
 /* nn.Conv2d / nn.Linear forward — linear_models.py:141-207, train_bc.py:79-82.
  * y = relu?( conv(x, w) + bias + resid ) * rowmask ; out_f32_atomic = 1: y is fp32 and the raw
  * products are atomically added (split-K linear; the caller zeroes y); = 2: y is fp32

@@ -130,6 +130,37 @@ def test_unsupported_shapes_fail_loudly(ops):
         ops.conv_wgrad(dy, x, dw, 1, 1, 1, 0)  # Cin = 96 is not 32 / 64 / k*128
 
 
+@pytest.mark.parametrize("N", [1, 3, 40])
+def test_res_block_fwd_fused_is_bit_identical(ops, N):
+    """gabril_res_block_fwd (one launch) vs the two convolutions it replaces: same bf16 outputs and sign words,
+    and both vs fp64 convolutions of the same bf16 operands."""
+    from gabril_carla_b200 import _lib
+    H, W, C, Ch = 20, 38, 128, 32
+    g = torch.Generator().manual_seed(100 + N)
+    x = F.relu(torch.randn(N, H, W, C, generator=g) * 0.5).to(torch.bfloat16)
+    w3 = (torch.randn(Ch, C, 3, 3, generator=g) / (C * 9) ** 0.5).to(torch.bfloat16)
+    w1 = (torch.randn(C, Ch, 1, 1, generator=g) / Ch ** 0.5).to(torch.bfloat16)
+    xd, w3d, w1d = x.to(DEV), ops.w_oihw_to_internal(w3).to(DEV), ops.w_oihw_to_internal(w1).to(DEV)
+    h_ref = torch.full((N, H, W, Ch), float("nan"), device=DEV, dtype=torch.bfloat16)
+    o_ref = torch.full((N, H, W, C), float("nan"), device=DEV, dtype=torch.bfloat16)
+    sbh_ref, sbo_ref = ops.sign_bits_like(h_ref), ops.sign_bits_like(o_ref)
+    ops.conv_fwd(xd, w3d, None, h_ref, 3, 3, 1, 1, relu=True, bits_out=sbh_ref)
+    ops.conv_fwd(h_ref, w1d, None, o_ref, 1, 1, 1, 0, relu=True, resid=xd, bits_out=sbo_ref)
+    h = torch.full_like(h_ref, float("nan"))
+    o = torch.full_like(o_ref, float("nan"))
+    sbh, sbo = torch.full_like(sbh_ref, -1), torch.full_like(sbo_ref, -1)
+    for _ in range(2):   # twice: the second launch starts from used barriers / TMEM of nobody (fresh CTAs), same result
+        ops.res_block_fwd(xd, w3d, w1d, h, sbh, o, sbo)
+    torch.cuda.synchronize()
+    _lib.poll_error()
+    assert torch.equal(h, h_ref) and torch.equal(sbh, sbh_ref)
+    assert torch.equal(o, o_ref) and torch.equal(sbo, sbo_ref)
+    h64 = F.relu(F.conv2d(x.double().permute(0, 3, 1, 2), w3.double(), padding=1))
+    assert rel(h.cpu(), h64.permute(0, 2, 3, 1)) <= 4e-3
+    o64 = F.relu(x.double().permute(0, 3, 1, 2) + F.conv2d(h.cpu().double().permute(0, 3, 1, 2), w1.double()))
+    assert rel(o.cpu(), o64.permute(0, 2, 3, 1)) <= 4e-3
+
+
 # ---- flat-slab convolutions (one TMA slab per filter row, taps as shifted descriptor views) ----
 FLAT = [
     # name, H, W, Cin, Cout, R, pad  (stride-1 'same'/valid convs on a zero-bordered grid)
