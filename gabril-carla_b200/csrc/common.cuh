@@ -49,6 +49,17 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
 
+// u8 / 255.0f with the bits of the IEEE division (data_loader_robomimic.py:182): one Newton correction of the
+// reciprocal product.  Bit-exact for all 256 inputs (tests/test_ops_gpu.py::test_obs_format_bit_exact compares fp32 outputs);
+// a 256-entry shared-memory table of the same values made gabril_obs_s4d bound by the L1 data pipe (24
+// bank-conflicted lookups per 16 output bytes).
+__device__ __forceinline__ float u8_over_255(uint32_t v) {
+  const float x = (float)v, rcp = 1.0f / 255.0f;
+  const float q0 = __fmul_rn(x, rcp);
+  const float rem = __fmaf_rn(-q0, 255.0f, x);
+  return __fmaf_rn(rem, rcp, q0);
+}
+
 // ---- PyTorch upsample_bicubic2d index math (fp32, A = -0.75, align_corners = False) -------------
 __device__ __forceinline__ float cubic1(float x) {
   const float A = -0.75f;

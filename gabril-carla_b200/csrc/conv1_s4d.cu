@@ -20,6 +20,7 @@
 #include <algorithm>
 
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace {
 
@@ -36,28 +37,64 @@ __device__ __forceinline__ float to_gray(float r, float g, float b) {
 //   1  gaze.method = Mask / AGIL's second encoder: obs * (ivg * heat + (1 - ivg))
 //   2  gaze.method = ViSaRL: channels (obs_0 .. obs_S-1, ivg*heat_0 .. ivg*heat_S-1), C0 = 2 S
 template <int S_, bool GRAY, int MODE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(384)
 obs_s4d_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__ widx,
                const float* __restrict__ heat, const float* __restrict__ sel,
                bf16* __restrict__ out, long long cells, int L, int center, int H, int W, int SH, int SW,
                int Cp) {
   constexpr int CP = GRAY ? 1 : 3;
   constexpr int C0 = S_ * CP * (MODE == 2 ? 2 : 1);
-  __shared__ float lut[256];   // u8 / 255.0f, correctly rounded (same bits as the division)
-  lut[threadIdx.x & 255] = __fdiv_rn((float)(threadIdx.x & 255), 255.0f);
-  __syncthreads();
-  const long long total = cells * 4;
-  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (long long)gridDim.x * blockDim.x) {
-    const int a = (int)(idx & 3);
-    const long long cell = idx >> 2;
-    const int v = (int)(cell % SW);
-    const long long t = cell / SW;
-    const int u = (int)(t % SH);
-    const long long b = t / SH;
+  // One CTA pass = one row of cells (b, u): the (b, u) split is one 32-bit division per pass instead of two
+  // 64-bit divisions per work item (they were most of the kernel's instructions: 3.0 TB/s, ALU-bound).
+  const int rows = (int)(cells / SW), items = SW * 4;
+  for (int row = blockIdx.x; row < rows; row += gridDim.x)
+  for (int it = threadIdx.x; it < items; it += blockDim.x) {
+    const int a = it & 3, v = it >> 2;
+    const int u = row % SH;
+    const long long b = row / SH;
+    const long long cell = (long long)row * SW + v;
     const int y = 4 * (u - 1) + a, x0 = 4 * (v - 1);
     const bool ok = u >= 1 && v >= 1 && y < H && x0 < W;
     float px[4][C0];
+    if constexpr (GRAY && MODE == 0) {
+      // Plain gray stacks (the headline path): the kernel is bound by instruction issue (ncu: 330 instructions per
+      // 16 output bytes, issue slots 77 % busy, DRAM 35 %), so the /255 and gray arithmetic runs on packed pairs
+      // of pixels (mul / fma / add .f32x2: same operations, same roundings) and padding cells skip it all.
+      if (!ok) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+          for (int c = 0; c < C0; ++c) px[k][c] = 0.f;
+      } else {
+        const uint64_t rcp2 = ptx::pack2(__float_as_uint(1.0f / 255.0f), __float_as_uint(1.0f / 255.0f));
+        const uint64_t m255 = ptx::pack2(__float_as_uint(-255.0f), __float_as_uint(-255.0f));
+        const uint64_t cr = ptx::pack2(__float_as_uint(0.299f), __float_as_uint(0.299f));
+        const uint64_t cg = ptx::pack2(__float_as_uint(0.587f), __float_as_uint(0.587f));
+        const uint64_t cb = ptx::pack2(__float_as_uint(0.114f), __float_as_uint(0.114f));
+#pragma unroll
+        for (int fs = 0; fs < S_; ++fs) {
+          const long long fr = widx ? __ldg(widx + b * S_ + fs) : b * L + frame_index(fs, S_, center, L);
+          const uint32_t* src = reinterpret_cast<const uint32_t*>(frames + ((fr * H + y) * (long long)W + x0) * 3);
+          const uint32_t w0 = __ldg(src), w1 = __ldg(src + 1), w2 = __ldg(src + 2);
+          // bytes: p0 = (w0.0 w0.1 w0.2) p1 = (w0.3 w1.0 w1.1) p2 = (w1.2 w1.3 w2.0) p3 = (w2.1 w2.2 w2.3)
+          auto unit2 = [&](uint32_t ba, uint32_t bb) {   // (ba / 255, bb / 255), see u8_over_255
+            const uint64_t x = ptx::pack2(__float_as_uint((float)ba), __float_as_uint((float)bb));
+            const uint64_t q0 = ptx::mul2(x, rcp2);
+            const uint64_t rem = ptx::fma2(q0, m255, x);
+            return ptx::fma2(rem, rcp2, q0);
+          };
+          auto gray2 = [&](uint64_t r, uint64_t g, uint64_t bl) {   // ((0.299 R) + (0.587 G)) + (0.114 B)
+            return ptx::add2(ptx::add2(ptx::mul2(cr, r), ptx::mul2(cg, g)), ptx::mul2(cb, bl));
+          };
+          const uint64_t g01 = gray2(unit2(w0 & 0xffu, w0 >> 24), unit2((w0 >> 8) & 0xffu, w1 & 0xffu),
+                                     unit2((w0 >> 16) & 0xffu, (w1 >> 8) & 0xffu));
+          const uint64_t g23 = gray2(unit2((w1 >> 16) & 0xffu, (w2 >> 8) & 0xffu), unit2(w1 >> 24, (w2 >> 16) & 0xffu),
+                                     unit2(w2 & 0xffu, w2 >> 24));
+          px[0][fs] = __uint_as_float((uint32_t)g01); px[1][fs] = __uint_as_float((uint32_t)(g01 >> 32));
+          px[2][fs] = __uint_as_float((uint32_t)g23); px[3][fs] = __uint_as_float((uint32_t)(g23 >> 32));
+        }
+      }
+    } else {
 #pragma unroll
     for (int fs = 0; fs < S_; ++fs) {
       uint32_t wv[3] = {0u, 0u, 0u};
@@ -74,7 +111,7 @@ obs_s4d_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           const int byte = 3 * k + c;
-          ch[c] = lut[(wv[byte >> 2] >> (8 * (byte & 3))) & 0xffu];
+          ch[c] = u8_over_255((wv[byte >> 2] >> (8 * (byte & 3))) & 0xffu);
         }
         if (GRAY) {
           px[k][fs] = ok ? to_gray(ch[0], ch[1], ch[2]) : 0.f;
@@ -98,6 +135,7 @@ obs_s4d_kernel(const uint8_t* __restrict__ frames, const long long* __restrict__
         }
       }
     }
+    }   // general path
     uint32_t* d32 = reinterpret_cast<uint32_t*>(out + cell * Cp + a * (4 * C0));
     const float* pf = &px[0][0];
     if ((C0 & 1) == 0) {   // 4*C0 bf16 = C0/2 16-byte stores
@@ -167,9 +205,10 @@ int obs_s4d_impl(const uint8_t* frames, const long long* widx, const float* heat
   // shapes only agree for grayscale stacks (train_bc.py:261,264 raise for RGB)
   if (mode != 0 && (!grayscale || !heat)) return GABRIL_ERR_BAD_SHAPE;
   const long long cells = (long long)B * SH * SW;
-  const int grid = (int)std::min<long long>((cells * 4 + 255) / 256, 148 * 16);
+  const int grid = (int)std::min<long long>((long long)B * SH, 148 * 16);
+  const int threads = std::min(384, (SW * 4 + 31) / 32 * 32);   // one row of cells per pass (W = 320: 328 items, 352 threads)
 #define LAUNCH_S4D(SS, GG, MM)                                                                            \
-  obs_s4d_kernel<SS, GG, MM><<<grid, 256, 0, stream>>>(frames, widx, heat, sel, (bf16*)x4, cells, L, center, H, \
+  obs_s4d_kernel<SS, GG, MM><<<grid, threads, 0, stream>>>(frames, widx, heat, sel, (bf16*)x4, cells, L, center, H, \
                                                        W, SH, SW, Cp)
 #define LAUNCH_S4D_S(GG, MM)                                                                       \
   switch (S) { case 1: LAUNCH_S4D(1, GG, MM); break; case 2: LAUNCH_S4D(2, GG, MM); break;         \

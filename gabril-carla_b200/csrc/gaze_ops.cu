@@ -57,7 +57,7 @@ __device__ __forceinline__ float block_min(float v, float* scratch) {
 // =================================================================================================
 // K1a: uint8 NHWC frame stack -> fp32 NCHW (the reference-facing layout of _format_obs_image)
 // =================================================================================================
-__device__ __forceinline__ float u8_to_unit(uint32_t v) { return __fdiv_rn((float)v, 255.0f); }
+__device__ __forceinline__ float u8_to_unit(uint32_t v) { return u8_over_255(v); }
 __device__ __forceinline__ float to_gray(float r, float g, float b) {
   // ((0.299 R) + (0.587 G)) + (0.114 B), every op rounded separately like the reference's
   // three torch multiplies and two adds (data_loader_robomimic.py:192-193)

@@ -23,5 +23,10 @@ for _ in range(4):
         ops.reg_mse(z, heat[:, 1], heat.stride(0), 180, 320, 50.0, 1e-6, dz, part, stats=stats)
     elif which == "splat":
         pre.splat_into(gaze, 2, 1, heat)
+    elif which == "obs":
+        SH, SW = 47, 82
+        if "x4" not in globals():
+            x4 = torch.zeros(B * SH * SW + 1, ops.conv1_kp(2, True), device=dev, dtype=torch.bfloat16)
+        ops.obs_s4d(frames, 2, 1, True, SH, SW, x4)
 torch.cuda.synchronize()
 print("ok")
