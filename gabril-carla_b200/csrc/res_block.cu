@@ -7,9 +7,10 @@
 // second MMA) and never waits for HBM.
 //
 // Warp roles (384 threads, one persistent CTA per SM):
-//   warp 0        TMEM owner, single-thread tcgen05.mma issuer (3x3: 18 k-blocks of 4 MMAs 128x32x16 per tile;
+//   warp 0        TMEM owner, single-thread tcgen05.mma issuer (3x3: 9 k-blocks of 8 MMAs 128x32x16 per tile;
 //                 1x1: 2 MMAs 128x128x16 from the h tile in shared memory)
-//   warps 1-3     TMA producers: im2col tiles of x into a 6-stage ring; both weight tensors once per CTA
+//   warps 1-3     TMA producers: im2col tiles of x into a 3-stage ring (one filter tap per stage); both weight
+//                 tensors once per CTA
 //   warps 4-7     epilogue group 0: acc1 -> ReLU -> bf16 -> h tile in shared memory (64-byte swizzle, K-major)
 //                 + h / sign words to HBM; then column chunk 0 of the PREVIOUS tile's output
 //   warps 8-11    epilogue group 1: column chunks 1-3 of the output (skip add, ReLU, sign words)
@@ -29,7 +30,8 @@ namespace {
 
 constexpr int kThreads = 384;
 constexpr int kProducers = 3;
-constexpr uint32_t kAStage = 16384;            // 128 pixels x 64 channels bf16
+constexpr uint32_t kABox = 16384;              // 128 pixels x 64 channels bf16
+constexpr uint32_t kAStage = 2 * kABox;        // one filter tap: both channel chunks
 constexpr uint32_t kW3Tile = 4096;             // 32 couts x 64 cin
 constexpr uint32_t kW3Bytes = 18 * kW3Tile;    // 9 taps x 2 channel chunks
 constexpr uint32_t kW1Bytes = 8192;            // 128 couts x 32 cin
@@ -103,16 +105,19 @@ __global__ void __launch_bounds__(kThreads, 1) res_block_fwd_kernel(const __grid
         const int rem = m0 - n_img * p.HW;
         const int oh = fdiv(rem, p.fd_w);
         const int ow = rem - oh * p.W;
-        for (int kb = 0; kb < 18; ++kb) {
+        for (int tap = 0; tap < 9; ++tap) {
           const int s = st;
           const uint32_t ph = st_ph;
           if (++st == kStages) { st = 0; st_ph ^= 1; }
-          if (s % kProducers != me) continue;
+          if (s % kProducers != me) continue;   // a stage always belongs to the same producer (parity waits)
           if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { fail(p, 201); ok = false; break; }
-          const int tap = kb >> 1, rp = tap / 3, sp = tap - rp * 3;
+          const int rp = tap / 3, sp = tap - rp * 3;
+          if (p.debug & 1) { ptx::mbar_arrive(full0 + 8 * s); continue; }
           ptx::mbar_arrive_expect_tx(full0 + 8 * s, kAStage);
-          ptx::tma_load_im2col_4d(smem_base + (uint32_t)s * kAStage, &p.mapX, full0 + 8 * s, (kb & 1) * 64, ow - 1,
-                                  oh - 1, n_img, (uint16_t)sp, (uint16_t)rp);
+#pragma unroll
+          for (int ch = 0; ch < 2; ++ch)
+            ptx::tma_load_im2col_4d(smem_base + (uint32_t)s * kAStage + (uint32_t)ch * kABox, &p.mapX, full0 + 8 * s,
+                                    ch * 64, ow - 1, oh - 1, n_img, (uint16_t)sp, (uint16_t)rp);
         }
       }
     }
@@ -152,16 +157,17 @@ __global__ void __launch_bounds__(kThreads, 1) res_block_fwd_kernel(const __grid
         if (!ptx::mbar_wait(a1e + 8 * b, (u & 1) ^ 1)) { fail(p, 205); ok = false; break; }
         ptx::tc_fence_after();
         const uint32_t d = tmem_base + (uint32_t)b * 32u;
-        for (int kb = 0; kb < 18; ++kb) {
+        for (int tap = 0; tap < 9; ++tap) {
           if (!ptx::mbar_wait(full0 + 8 * s, ph)) { fail(p, 206); ok = false; break; }
           ptx::tc_fence_after();
           const uint32_t a_lo = a1_lo0 + (uint32_t)s * (kAStage >> 4);
-          const uint32_t b_lo = b1_lo0 + (uint32_t)kb * (kW3Tile >> 4);
+          const uint32_t b_lo = b1_lo0 + (uint32_t)(tap * 2) * (kW3Tile >> 4);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint64_t ad = ((uint64_t)a1_hi << 32) | (uint64_t)(a_lo + k * 2u);
-            const uint64_t bd = ((uint64_t)b1_hi << 32) | (uint64_t)(b_lo + k * 2u);
-            ptx::umma_bf16(d, ad, bd, p.idesc1, (kb > 0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < 8; ++k) {   // two 64-channel chunks x four K = 16 steps
+            const uint32_t ch = (uint32_t)(k >> 2), kk = (uint32_t)(k & 3);
+            const uint64_t ad = ((uint64_t)a1_hi << 32) | (uint64_t)(a_lo + ch * (kABox >> 4) + kk * 2u);
+            const uint64_t bd = ((uint64_t)b1_hi << 32) | (uint64_t)(b_lo + ch * (kW3Tile >> 4) + kk * 2u);
+            if (!(p.debug & 2)) ptx::umma_bf16(d, ad, bd, p.idesc1, (tap > 0 || k > 0) ? 1u : 0u);
           }
           ptx::umma_commit(empty0 + 8 * s);
           if (++s == kStages) { s = 0; ph ^= 1; }
@@ -187,7 +193,7 @@ __global__ void __launch_bounds__(kThreads, 1) res_block_fwd_kernel(const __grid
       if (!__all_sync(0xffffffffu, ok)) return false;
       ptx::tc_fence_after();
 #pragma unroll 1
-      for (int c = c0; c < c1; ++c) {
+      for (int c = c0; c < c1 && !(p.debug & 4); ++c) {
         const long long off = row * 128 + c * 32;
         tc::epi_item_bf16<kEF2>(kEF2, lane_addr + kAcc2Col + (uint32_t)b * 128u + (uint32_t)c * 32u, live, nullptr,
                                 p.x + off, nullptr, 0u, 1.0f, 0xffffffffu, p.out + off, p.bits_out + (off >> 5));

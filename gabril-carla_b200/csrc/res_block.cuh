@@ -9,7 +9,7 @@
 
 namespace rb {
 
-constexpr int kStages = 6;   // im2col A tiles in flight (16 KB each)
+constexpr int kStages = 4;   // k-blocks in flight: one filter tap = two 64-channel im2col tiles (32 KB)
 
 struct Params {
   CUtensorMap mapX;    // x [N, H, W, 128] in im2col mode: 64 channels x 128 pixels, pad 1
@@ -25,6 +25,7 @@ struct Params {
   uint64_t desc_a1_hi, desc_b1_hi, desc_a2_hi, desc_b2_hi;   // smem descriptors, start address zero
   uint32_t idesc1, idesc2;
   int* err_flag;
+  int debug;   // perf experiments (GABRIL_RB_DEBUG): 1 = no TMA loads, 2 = no 3x3 MMAs, 4 = no output epilogue work
 };
 
 size_t smem_bytes();

@@ -325,6 +325,9 @@ int gabril_res_block_fwd(const void* x, const void* w3, const void* w1, void* h,
   p.idesc1 = make_idesc(0, 0, 128, Ch);
   p.idesc2 = make_idesc(0, 0, 128, C);
   p.err_flag = g_err_flag;
+  static int dbg = -1;
+  if (dbg < 0) { const char* e = getenv("GABRIL_RB_DEBUG"); dbg = e ? atoi(e) : 0; }
+  p.debug = dbg;
   return rb::launch(p, g_num_sms, stream);
 }
 
