@@ -236,7 +236,8 @@ def load_tc_traffic(args, B):
     """dram__bytes_read.sum + dram__bytes_write.sum of every tc_gemm_kernel launch of ONE step, from the
     committed ncu pass (profiles/r1_tc_traffic.json); only quoted for the configuration it was taken on."""
     try:
-        name = "r2_tc_traffic.json" if os.path.exists(os.path.join(ROOT, "profiles", "r2_tc_traffic.json")) else "r1_tc_traffic.json"
+        name = next(n for n in ("r2b_tc_traffic.json", "r2_tc_traffic.json", "r1_tc_traffic.json")
+                    if os.path.exists(os.path.join(ROOT, "profiles", n)))
         with open(os.path.join(ROOT, "profiles", name)) as f:
             t = json.load(f)
         if B == 1024 and not args.rgb and args.gaze_method == "Reg" and args.dp_method == "None":
@@ -328,8 +329,9 @@ def main_ours(args):
         rows = [r[:4] + (sorted(q[i][4] for q in passes)[1],) for i, r in enumerate(rows)]
     eng.overlap = overlap
     launches_per_step = len(rows) + (2 if args.dp_method == "GMD" else 0)
-    tc_ms = sum(r[4] for r in rows if r[0] == "tc_gemm_kernel")
-    tc_flop = sum(r[2] for r in rows if r[0] == "tc_gemm_kernel")
+    TC_KERNELS = ("tc_gemm_kernel", "res_block_fwd_kernel")   # the tcgen05 / TMEM / TMA GEMM kernels
+    tc_ms = sum(r[4] for r in rows if r[0] in TC_KERNELS)
+    tc_flop = sum(r[2] for r in rows if r[0] in TC_KERNELS)
     traced_ms = sum(r[4] for r in rows)
 
     # ---- timed region 1: device-resident inputs ----
@@ -428,10 +430,11 @@ def main_ours(args):
         "e2e": {"value": (total / (e2e_ms * 1e-3)) if e2e_ms else None, "unit": "samples/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "note": "pinned host batch -> double-buffered H2D on a copy stream -> step -> losses D2H, per rank"},
-        "roofline": {"bound": "tensor", "kernel": "tc_gemm_kernel (every conv / linear fwd, dgrad, wgrad launch of one step)",
+        "roofline": {"bound": "tensor", "kernel": "tcgen05 GEMM kernels: tc_gemm_kernel (every conv / linear fwd, dgrad, wgrad launch of one step, "
+                                                       "bias gradients included) + res_block_fwd_kernel (the two Residual blocks' forward)",
                      "achieved": achieved, "peak": tf_sust, "unit": "TFLOP/s", "frac": achieved / tf_sust,
                      "peak_source": f"bf16_tflops_sustained, {how}", "traffic": traffic,
-                     "traffic_unit": "bytes per step (all tc_gemm_kernel launches), like achieved",
+                     "traffic_unit": "bytes per step (all launches of those kernels), like achieved",
                      "traffic_source": (f"CONSTANT from a committed ncu pass, not measured in this run: {traffic_src}"
                                         if traffic_src else None),
                      "algorithmic_flop_per_step": tc_flop,

@@ -44,7 +44,24 @@ __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
   r.mi = mi;
   r.y = y;
   int cls = 0;
-  while (cls + 1 < p.n_classes && mi >= p.tiles_m[cls]) { mi -= p.tiles_m[cls]; ++cls; }
+  if (p.cls_min_tiles > 0) {
+    // parity classes interleaved (tile 4i + c = tile i of class c), so that the CTAs working at any moment
+    // read the same region of dY through all four class maps: class-major order re-read dY from DRAM once
+    // per class whenever it is larger than L2 (conv_3 dgrad: 997 MB read for a 231 MB tensor).  The
+    // classes' unequal tails follow class by class.
+    const int body = p.cls_min_tiles * p.n_classes;
+    if (mi < body) {
+      const int i = fdiv(mi, p.fd_n_classes);
+      cls = mi - i * p.n_classes;
+      mi = i;
+    } else {
+      mi -= body;
+      while (cls + 1 < p.n_classes && mi >= p.tiles_m[cls] - p.cls_min_tiles) { mi -= p.tiles_m[cls] - p.cls_min_tiles; ++cls; }
+      mi += p.cls_min_tiles;
+    }
+  } else {
+    while (cls + 1 < p.n_classes && mi >= p.tiles_m[cls]) { mi -= p.tiles_m[cls]; ++cls; }
+  }
   r.cls = cls;
   r.m0 = mi * 128 * p.m_sub;
   int n_tile = y, tg = 0;
@@ -766,6 +783,7 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
     return GABRIL_ERR_BAD_SHAPE;
   }
   p.fd_tiles_m = magic(p.tiles_m_total);
+  p.fd_n_classes = magic(p.n_classes);
   p.fd_n_tiles = magic(p.n_tiles);
   p.fd_tap_groups = magic(p.tap_groups);
   p.fd_border_w = magic(p.border_w);

@@ -137,6 +137,7 @@ struct Params {
   uint32_t resident_off;    // offset of the resident weight region from the aligned smem base
   // persistent tile schedule: tile -> (m tile [classes concatenated], n tile, split)
   int tiles_m[4], tiles_m_total, n_tiles, n_splits, total_tiles;
+  int cls_min_tiles;         // > 0: the classes' m tiles are interleaved (decode_tile); = min over classes of tiles_m
   int acc_bufs, acc_stride;  // TMEM accumulator ring (1, 2, 4 or 8 buffers of acc_stride columns)
   int acc_shift;             // log2(acc_bufs), filled by launch()
   // FWD regime: 128-row sub-tiles per CTA tile (1 or 2).  With 2, one A box of 256 rows and ONE weight
@@ -151,6 +152,7 @@ struct Params {
   long long tap_stride;  // WGRAD: element (m, tap, n) at out + m*ldo + tap*tap_stride + n
   long long split_stride;  // FWD split-K with plain stores: split s writes its partial at out + s*split_stride
   // magic numbers of the divisions above, filled by launch() from the fields they belong to
+  FastDiv fd_n_classes;
   FastDiv fd_tiles_m, fd_n_tiles, fd_tap_groups, fd_border_w, fd_border_h, fd_border_hw, fd_quad;
   FastDiv fd_hw[4], fd_ws[4];    // remap: Hs*Ws, Ws per class
   FastDiv fd_ohw[4], fd_ow[4];   // im2col traversal: OHW, OW per class

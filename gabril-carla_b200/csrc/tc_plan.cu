@@ -185,6 +185,14 @@ void finalize_schedule(tc::Params& p, const int* m_tiles, int n_tiles_y, int spl
                        int occ) {
   p.tiles_m_total = 0;
   for (int c = 0; c < p.n_classes; ++c) { p.tiles_m[c] = m_tiles[c]; p.tiles_m_total += m_tiles[c]; }
+  p.cls_min_tiles = 0;
+  if (p.n_classes > 1) {
+    static int inter = -1;
+    if (inter < 0) { const char* e = getenv("GABRIL_TC_CLS_INTERLEAVE"); inter = (e && e[0] == '0') ? 0 : 1; }
+    int mn = m_tiles[0];
+    for (int c = 1; c < p.n_classes; ++c) mn = std::min(mn, m_tiles[c]);
+    if (inter) p.cls_min_tiles = mn;
+  }
   p.n_tiles = n_tiles_y;
   p.n_splits = splits;
   p.total_tiles = p.tiles_m_total * n_tiles_y * splits;

@@ -149,7 +149,7 @@ def res_block_fwd(x, w3, w1, h, bits_h, out, bits_out):
     assert w3.shape == (Ch, 9, C) and w1.shape == (C, 1, Ch) and h.numel() == N * H * W * Ch and out.numel() == x.numel()
     assert bits_h.dtype == torch.int32 and bits_h.numel() * 32 == h.numel()
     assert bits_out.dtype == torch.int32 and bits_out.numel() * 32 == out.numel()
-    with _span("tc_gemm_kernel", f"res-block {C}->{Ch}->{C}", 2.0 * N * H * W * (9 * C * Ch + Ch * C), "flop"):
+    with _span("res_block_fwd_kernel", f"res-block {C}->{Ch}->{C}", 2.0 * N * H * W * (9 * C * Ch + Ch * C), "flop"):
         st = _fn("gabril_res_block_fwd")(ptr(x), ptr(w3), ptr(w1), ptr(h), ptr(bits_h), ptr(out), ptr(bits_out),
                                           c_int(N), c_int(H), c_int(W), c_int(C), c_int(Ch), stream())
     _lib.check(st, "gabril_res_block_fwd")

@@ -42,7 +42,8 @@ for k, x in enumerate(step):
 open(out_txt, "w").write("\n".join(lines) + "\n")
 print("\n".join(lines[:20]))
 if len(sys.argv) > 3:
-    g = agg["tc::tc_gemm_kernel<*>"]
+    fam = [v for k, v in agg.items() if "tc_gemm_kernel" in k or "res_block_fwd_kernel" in k]   # the tcgen05 kernels
+    g = [sum(v[i] for v in fam) for i in range(4)]
     json.dump({"dram_bytes_per_step": g[2] + g[3], "launches": g[0], "tc_share_of_step": g[1] / tot,
                "source": f"{src} (ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum "
                          "--clock-control none, python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-e2e "
