@@ -106,7 +106,15 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
   const uint32_t stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
 
   // fused bias gradient (WGRAD, one tile per CTA): this CTA's epilogue warps also read the dY tile of every stage
-  const bool dbias_cta = p.dbias != nullptr;
+  bool dbias_cta = p.dbias != nullptr;
+  uint32_t dy_center_off = 0;
+  if (dbias_cta && p.shift_dy) {
+    // shifted-dY form: only the CTAs whose tap group holds the centre tap stage dY itself
+    const Tile t0 = decode_tile(p, blockIdx.x);
+    const int ci = p.center_tap - t0.tap0;
+    dbias_cta = ci >= 0 && ci < t0.ntaps;
+    dy_center_off = (uint32_t)ci * p.b_box_bytes;
+  }
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
       ptx::mbar_init(full0 + 8 * s, 1);
@@ -269,6 +277,37 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
               for (int i = 0; i < p.b_boxes; ++i)
                 ptx::tma_load_3d(b_dst + i * p.b_box_bytes, &p.mapB, full, n0 + i * p.b_box_w,
                                  wtap, chunk_c * p.kc);
+            }
+          }
+        } else if (p.shift_dy) {
+          // WGRAD, operands exchanged, shift on dY: A = the activation rows of the k-block (shared by every
+          // tap), B = one im2col tile of dY per tap, walked like a data gradient (tap (r, s) reads dY at
+          // pixel + (pad - r, pad - s) = traversal offset (R-1-r, S-1-s) from the lower corner)
+          const uint32_t tx = p.a_boxes * p.a_box_bytes + (uint32_t)tl.ntaps * p.b_box_bytes;
+          const int Rf = p.taps / p.S;
+          for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+            const int s = st;
+            const uint32_t ph = st_ph;
+            if (++st == p.stages) { st = 0; st_ph ^= 1; }
+            if (s % kProducers != me) continue;
+            if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { report_timeout(p, 111); ok = false; break; }
+            const uint32_t a_dst = smem_base + s * stage_bytes;
+            const uint32_t b_dst = a_dst + p.a_stage_bytes;
+            const uint32_t full = full0 + 8 * s;
+            ptx::mbar_arrive_expect_tx(full, tx);
+            const int p0 = kb * p.kc;
+            for (int i = 0; i < p.a_boxes; ++i)
+              ptx::tma_load_2d(a_dst + i * p.a_box_bytes, &p.mapA[0], full, m0 + i * p.a_box_w, p0);
+            const int n_img = fdiv(p0, p.fd_ohw[0]);
+            const int rem = p0 - n_img * ohw;
+            const int ih = fdiv(rem, p.fd_ow[0]);
+            const int iw = rem - ih * oww;
+            const int w_base = iw + p.lower_w[0], h_base = ih + p.lower_h[0];
+            for (int tt = 0; tt < tl.ntaps; ++tt) {
+              const int tap = tl.tap0 + tt;
+              const int r = tap / p.S, sx = tap - r * p.S;
+              ptx::tma_load_im2col_4d(b_dst + (uint32_t)tt * p.b_box_bytes, &p.mapB, full, n0, w_base, h_base,
+                                      n_img, (uint16_t)(p.S - 1 - sx), (uint16_t)(Rf - 1 - r));
             }
           }
         } else if (p.swap_ab) {
@@ -443,13 +482,19 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
           for (int g = 0; g < mma_groups; ++g) {
             if (g * g_taps >= tl.ntaps) break;
             const uint32_t bg = b_lo + g * b_gstep, dg = d_base + g * d_gstep, ag = a_lo + g * a_gstep;
+            uint32_t idesc_g = idesc;
+            if (p.shift_dy) {
+              // N of this group = its taps x Cout (bits 17..22 of the instruction descriptor hold N >> 3)
+              const int nt = min(g_taps, tl.ntaps - g * g_taps);
+              idesc_g = (idesc & ~(0x3Fu << 17)) | ((uint32_t)((nt * p.block_n) >> 3) << 17);
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               if (j < mma_k) {
                 const uint64_t a_desc = ((uint64_t)a_hi32 << 32) | (uint64_t)(ag + j * a_kstep);
                 const uint64_t b_desc = ((uint64_t)b_hi32 << 32) | (uint64_t)(bg + j * b_kstep);
                 const uint32_t accumulate = (kb > tl.kb_begin || j > 0) ? 1u : 0u;
-                if (!dbg_skip) ptx::umma_bf16(dg, a_desc, b_desc, idesc, accumulate);
+                if (!dbg_skip) ptx::umma_bf16(dg, a_desc, b_desc, idesc_g, accumulate);
               }
             }
           }
@@ -489,15 +534,15 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
       const int cpb = p.dy_row_bytes >> 4;           // chunks per box row: 4 or 8
       const int col = etid & (nc - 1), prow = etid / nc, pstep = nthr / nc;
       const uint32_t cj = (uint32_t)(col & (cpb - 1));
-      const uint32_t tile_off = p.dy_off + (uint32_t)(col / cpb) * p.dy_box_bytes;
+      const uint32_t tile_off = p.dy_off + dy_center_off + (uint32_t)(col / cpb) * p.dy_box_bytes;
       const bool wide = p.dy_row_bytes == 128;
       float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       if (etid < kBiasSmem) bias_s[etid] = 0.f;
       ptx::bar_sync(1, nthr);
       int s = 0;
       uint32_t ph = 0;
-      const int share_n = p.swap_ab ? p.tiles_m_total * p.n_tiles : p.n_tiles;
-      int turn = p.swap_ab ? tl.mi * p.n_tiles + tl.y : tl.y;   // k-blocks until this CTA's next turn
+      const int share_n = p.shift_dy ? 1 : p.swap_ab ? p.tiles_m_total * p.n_tiles : p.n_tiles;
+      int turn = p.shift_dy ? 0 : p.swap_ab ? tl.mi * p.n_tiles + tl.y : tl.y;   // k-blocks until this CTA's next turn
       for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
         if (!ptx::mbar_wait(full0 + 8 * s, ph)) { report_timeout(p, 110); break; }
         const uint32_t st = smem_base + (uint32_t)s * stage_bytes + tile_off;

@@ -91,6 +91,14 @@ struct Params {
   // TMEM lane = cin, column = cout, so the epilogue writes element (cout, tap, cin) transposed.
   int swap_ab;
   uint32_t a_gstep;
+  // WGRAD with exchanged operands and the SHIFT ON dY (stride-1 "same" convolutions with narrow Cout):
+  //   dW[co][r,s][ci] = sum_q x[q][ci] * dY[q - (r - pad, s - pad)][co]
+  // A = the activation rows of the k-block, ONE tile for every tap (plain 2-D map, M = Cin = 128); B = one
+  // im2col tile of dY per tap (the data-gradient traversal), consecutive in the stage, so one MMA covers g_taps
+  // taps with N = g_taps * Cout (the last group of a CTA is narrower: its N is patched into the instruction
+  // descriptor).  Against the form above this loads x once per k-block instead of once per tap.
+  // center_tap = (pad, pad): its tile is dY itself (bias gradient).
+  int shift_dy, center_tap;
   uint64_t desc_a_hi, desc_b_hi;  // smem descriptors with the start-address field zero
   uint32_t idesc;
   uint32_t tmem_cols;

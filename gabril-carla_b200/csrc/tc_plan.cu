@@ -657,6 +657,103 @@ static int conv_wgrad_swapped(const void* dy, const void* x, float* dw, int N, i
   return tc::launch(p, 1 << 30, smem, stream);
 }
 
+// Narrow stride-1 "same" convolutions (conv_6: 128 -> 64, 5x5; Residual 3x3: 128 -> 32) with the shift on dY
+// (tc::Params::shift_dy): the activation tile of a k-block is loaded once for all taps and each tap's
+// operand is an im2col tile of the narrow dY, so a CTA holds several taps (N = taps x Cout per MMA) without
+// the 16 KB-per-tap activation tiles that made multi-tap CTAs lose in conv_wgrad_swapped.  Shared-memory fill
+// per k-block of 64 pixels: conv_6 16 + 5 x 8 KB for 5 taps (was 5 x 24 KB), res3x3 16 + 9 x 4 KB for all 9
+// taps (was 9 x 20 KB) - these launches were bound by the L2 -> SM feed.
+static bool wgrad_shift_disabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("GABRIL_WGRAD_NO_SHIFT"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
+
+static int conv_wgrad_shifted(const void* dy, const void* x, float* dw, int N, int H, int W, int Cin,
+                              int Cout, int R, int S, int pad, int direct_store, cudaStream_t stream) {
+  const long long P = (long long)N * H * W;   // contraction over the INPUT pixels (= output pixels here)
+  const int T = R * S, KP = 64;
+  tc::Params p;
+  zero_params(p);
+  p.kind = tc::KIND_WGRAD;
+  p.n_classes = 1;
+  p.swap_ab = 1;     // TMEM lane = cin, column = (tap, cout): the exchanged form's epilogue
+  p.shift_dy = 1;
+  p.center_tap = pad * S + pad;
+  p.kc = KP;
+  // A = x rows of the k-block: M = 128 input channels = two 64-channel boxes of KP pixels
+  const int aw = 64, a_sw = aw * 2;
+  p.a_box_w = aw;
+  p.a_boxes = 2;
+  p.a_box_bytes = KP * a_sw;
+  p.a_stage_bytes = round_up(p.a_boxes * p.a_box_bytes, 1024);
+  p.desc_a_hi = desc_hi(p.a_box_bytes, 8 * a_sw, layout_type_for_bytes(a_sw));
+  // B = dY of one tap: KP pixels x Cout channels, one box; taps are b_box_bytes apart (whole swizzle atoms),
+  // which is the MN-major leading-dimension stride, so g_taps taps are the N dimension of one instruction
+  const int block_n = Cout, b_sw = Cout * 2;
+  p.block_n = block_n;
+  p.b_box_w = Cout;
+  p.b_boxes = 1;
+  p.b_box_bytes = KP * b_sw;
+  p.desc_b_hi = desc_hi(p.b_box_bytes, 8 * b_sw, layout_type_for_bytes(b_sw));
+  // taps per CTA: TMEM columns, a stage of at most ~56 KB (three or four of them in flight), balanced groups
+  int n_max = std::min(T, std::min(512 / Cout, (int)((56u * 1024u - p.a_stage_bytes) / p.b_box_bytes)));
+  n_max = std::max(1, n_max);
+  const int groups = (T + n_max - 1) / n_max;
+  const int n_acc = (T + groups - 1) / groups;
+  int G = std::max(1, std::min(n_acc, 256 / Cout));   // taps per MMA (N <= 256), balanced
+  const int ng = (n_acc + G - 1) / G;
+  G = (n_acc + ng - 1) / ng;
+  p.n_acc = n_acc;
+  p.taps = T;
+  p.tap_groups = groups;
+  p.S = S;
+  p.b_stage_bytes = round_up((uint32_t)n_acc * p.b_box_bytes, 1024);
+  p.mma_k = KP / 16;
+  p.mma_groups = ng;
+  p.g_taps = G;
+  p.a_kstep = (uint32_t)((16 * a_sw) >> 4);
+  p.b_kstep = (uint32_t)((16 * b_sw) >> 4);
+  p.a_gstep = 0;
+  p.b_gstep = (uint32_t)((G * p.b_box_bytes) >> 4);
+  p.d_gstep = (uint32_t)(G * block_n);
+  p.idesc = make_idesc(1, 1, 128, G * block_n);
+  p.M_total[0] = Cin;
+  p.N_total = Cout;
+  p.kb_total = (int)((P + KP - 1) / KP);
+  // k-block start pixel -> (n, ih, iw) of x; dY is read at (ih, iw) + lower corner + traversal offset
+  p.OW[0] = W; p.OHW[0] = H * W; p.lower_w[0] = pad - (S - 1); p.lower_h[0] = pad - (R - 1);
+  p.trav_stride_w = 1; p.trav_stride_h = 1;
+  int rc;
+  {
+    uint64_t dims[2] = {(uint64_t)Cin, (uint64_t)P};
+    uint64_t strides[1] = {(uint64_t)Cin * 2};
+    uint32_t box[2] = {(uint32_t)aw, (uint32_t)KP};
+    rc = tiled_map(&p.mapA[0], x, 2, dims, strides, box, a_sw);
+    if (rc) return rc;
+  }
+  rc = im2col_map(&p.mapB, dy, N, H, W, Cout, p.lower_w[0], p.lower_h[0], -pad, -pad, Cout, KP, 1);
+  if (rc) return rc;
+  const int m_tiles = Cin / 128;
+  const int occ = 1;   // 288 / 320 accumulator columns round up to all 512
+  int splits = 1;
+  if (!direct_store) splits = std::max(1, std::min(p.kb_total, g_num_sms / (m_tiles * groups)));
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  splits = (p.kb_total + p.kb_per_split - 1) / p.kb_per_split;
+  p.out_mode = direct_store ? tc::OUT_F32_STORE : tc::OUT_F32_ATOMIC;
+  p.out = dw;
+  p.ldo = (long long)T * Cin;
+  p.tap_stride = Cin;
+  p.err_flag = g_err_flag;
+  size_t smem;
+  pick_stages(p, &smem, occ);
+  const int mt[1] = {m_tiles};
+  finalize_schedule(p, mt, groups, splits, n_acc * block_n, occ);
+  p.acc_bufs = 1;
+  p.tmem_cols = (uint32_t)p.acc_stride;
+  return tc::launch(p, 1 << 30, smem, stream);
+}
+
 // dw[Cout][R*S][Cin] (fp32) += sum_pixels dy[p, Cout]^T * im2col(x)[p, (tap, Cin)].
 // The caller zeroes dw (it lives in the flat gradient arena).  Also serves linear layers
 // (R = S = 1, H = W = 1, N = rows): dw[Cout][Cin] += dy[rows,Cout]^T x[rows,Cin].
@@ -670,6 +767,9 @@ int gabril_conv_wgrad(const void* dy, const void* x, float* dw, int N, int H, in
   const long long P = (long long)N * OH * OW;  // contraction length (output pixels)
   const int T = R * S;
   const int KP = 64;
+  if (Cout <= 64 && Cin == 128 && stride == 1 && T > 1 && R == 2 * pad + 1 && S == 2 * pad + 1 && P < (1ll << 31) &&
+      !wgrad_shift_disabled())
+    return conv_wgrad_shifted(dy, x, dw, N, H, W, Cin, Cout, R, S, pad, direct_store, stream);
   if (Cout <= 64 && Cin % 128 == 0 && !wgrad_swap_disabled())
     return conv_wgrad_swapped(dy, x, dw, N, H, W, Cin, Cout, R, S, stride, pad, direct_store, stream);
   tc::Params p;
