@@ -389,20 +389,30 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
     if (ptx::elect_one()) {
       int it = 0, tcount = 0;
       bool ok = true;
-      const int mma_k = p.mma_k, mma_groups = p.mma_groups, g_taps = p.g_taps;
-      const uint32_t a_kstep = p.a_kstep, b_kstep = p.b_kstep, b_gstep = p.b_gstep, d_gstep = p.d_gstep;
-      const uint32_t a_gstep = p.a_gstep;  // swapped wgrad: per tap; FWD with m_sub = 2: per 128-row sub-tile
-      const uint32_t a_hi32 = (uint32_t)(p.desc_a_hi >> 32), b_hi32 = (uint32_t)(p.desc_b_hi >> 32);
-      const uint32_t stage16 = stage_bytes >> 4;
-      const uint32_t a_lo_const = (uint32_t)p.desc_a_hi + (smem_base >> 4);
-      const uint32_t b_lo_const = (uint32_t)p.desc_b_hi + ((smem_base + p.a_stage_bytes) >> 4);
-      const uint32_t idesc = p.idesc;
-      const int stages = p.stages;
+      int mma_k = p.mma_k, mma_groups = p.mma_groups, g_taps = p.g_taps;
+      uint32_t a_kstep = p.a_kstep, b_kstep = p.b_kstep, b_gstep = p.b_gstep, d_gstep = p.d_gstep;
+      uint32_t a_gstep = p.a_gstep;  // swapped wgrad: per tap; FWD with m_sub = 2: per 128-row sub-tile
+      uint32_t a_hi32 = (uint32_t)(p.desc_a_hi >> 32), b_hi32 = (uint32_t)(p.desc_b_hi >> 32);
+      uint32_t stage16 = stage_bytes >> 4;
+      uint32_t a_lo_const = (uint32_t)p.desc_a_hi + (smem_base >> 4);
+      uint32_t b_lo_const = (uint32_t)p.desc_b_hi + ((smem_base + p.a_stage_bytes) >> 4);
+      uint32_t idesc = p.idesc;
+      int stages = p.stages;
+      // opaque register copies: the compiler otherwise re-loads these from the constant bank in every k-block
+      asm volatile("" : "+r"(mma_k), "+r"(mma_groups), "+r"(g_taps), "+r"(a_kstep), "+r"(b_kstep), "+r"(b_gstep),
+                        "+r"(d_gstep), "+r"(a_gstep), "+r"(a_hi32), "+r"(b_hi32), "+r"(stage16), "+r"(a_lo_const),
+                        "+r"(b_lo_const), "+r"(idesc), "+r"(stages));
       const bool dbg_skip = (p.debug & 2) != 0;
       int s = 0;
       uint32_t ph = 0;
       long long pw = 0, pi = 0, pc = 0, pt = 0, pn = 0;
       const bool prof = (p.debug & 4) != 0;
+      // lean loop state (see `fast` below): descriptor low words / barrier address of the current stage
+      const bool fast = !p.a_flat && mma_k == 4 && (p.debug & ~3) == 0;
+      uint32_t a_cur = a_lo_const, b_cur = b_lo_const, full_cur = full0;
+      uint32_t a_k2 = 2 * a_kstep, a_k3 = 3 * a_kstep, b_k2 = 2 * b_kstep, b_k3 = 3 * b_kstep;
+      // opaque copies: the compiler otherwise re-materialises these from the constant bank in every iteration
+      asm volatile("" : "+r"(a_k2), "+r"(a_k3), "+r"(b_k2), "+r"(b_k3));
       for (int t = blockIdx.x; t < p.total_tiles && ok; t += gridDim.x, ++tcount) {
         const long long c0 = prof ? clock64() : 0;
         const Tile tl = decode_tile(p, t);
@@ -466,6 +476,49 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
               ptx::umma_commit(empty0 + 8 * s);
               if (++s == stages) { s = 0; ph ^= 1; }
             }
+          }
+          if (ok) ptx::umma_commit(tfull0 + 8 * buf);
+          continue;
+        }
+        if (fast) {
+          // Lean issue loop (kc = 64: four K-steps per k-block; no debug / profiling branches).  This thread's
+          // INSTRUCTION COUNT per k-block bounds every narrow (N <= 64) or short-K layer: with the TMA copies
+          // and the MMAs both stubbed out conv_6 forward still took 0.32 of its 0.38 ms (~580 clk per k-block
+          // for ~140 instructions, most of them parameter re-loads from the constant bank).  Here the stage's
+          // descriptor words advance by addition and every parameter lives in a register.
+          int ng = mma_groups;
+          uint32_t idesc_last = idesc;
+          if (g_taps > 0) {
+            ng = min(mma_groups, (tl.ntaps + g_taps - 1) / g_taps);
+            if (p.shift_dy) {
+              const int nt = tl.ntaps - (ng - 1) * g_taps;   // taps of the last group: N = nt x Cout
+              idesc_last = (idesc & ~(0x3Fu << 17)) | ((uint32_t)((nt * p.block_n) >> 3) << 17);
+            }
+          }
+          const int kb_end = tl.kb_end;
+          for (int kb = tl.kb_begin; kb < kb_end; ++kb) {
+            if (!ptx::mbar_wait(full_cur, ph)) { report_timeout(p, 103); ok = false; break; }
+            ptx::tc_fence_after();
+            const uint32_t acc0 = kb > tl.kb_begin ? 1u : 0u;
+            if (dbg_skip) {
+            } else if (ng == 1) {
+              ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | a_cur, ((uint64_t)b_hi32 << 32) | b_cur, idesc_last, acc0);
+              ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (a_cur + a_kstep), ((uint64_t)b_hi32 << 32) | (b_cur + b_kstep), idesc_last, 1u);
+              ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (a_cur + a_k2), ((uint64_t)b_hi32 << 32) | (b_cur + b_k2), idesc_last, 1u);
+              ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (a_cur + a_k3), ((uint64_t)b_hi32 << 32) | (b_cur + b_k3), idesc_last, 1u);
+            } else {
+              uint32_t ag = a_cur, bg = b_cur, dg = d_base;
+              for (int g = 0; g < ng; ++g, ag += a_gstep, bg += b_gstep, dg += d_gstep) {
+                const uint32_t id = g == ng - 1 ? idesc_last : idesc;
+                ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | ag, ((uint64_t)b_hi32 << 32) | bg, id, acc0);
+                ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | (ag + a_kstep), ((uint64_t)b_hi32 << 32) | (bg + b_kstep), id, 1u);
+                ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | (ag + a_k2), ((uint64_t)b_hi32 << 32) | (bg + b_k2), id, 1u);
+                ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | (ag + a_k3), ((uint64_t)b_hi32 << 32) | (bg + b_k3), id, 1u);
+              }
+            }
+            ptx::umma_commit(full_cur + 8 * kMaxStages);   // the stage's `empty` barrier
+            a_cur += stage16; b_cur += stage16; full_cur += 8;
+            if (++s == stages) { s = 0; ph ^= 1; a_cur = a_lo_const; b_cur = b_lo_const; full_cur = full0; }
           }
           if (ok) ptx::umma_commit(tfull0 + 8 * buf);
           continue;

@@ -52,10 +52,12 @@ for name, H, W, Cin, Cout, R, stride, pad in LAYERS:
     dx = torch.empty_like(x)
     dw = torch.zeros(Cout, R * R, Cin, device=dev)
     flop = 2.0 * N * OH * OW * Cout * R * R * Cin
+    gbits = torch.randint(-2 ** 31, 2 ** 31 - 1, (x.numel() // 32,), device=dev, dtype=torch.int32)
+    addend = torch.randn_like(x) if name == "res3x3" else None
     t_f = timeit(lambda: ops.conv_fwd(x, w, bias, y, R, R, stride, pad, relu=True))
     line = f"{name:7s} fwd {t_f:7.3f} ms {flop / t_f / 1e9:7.1f} TF/s"
     if name != "conv1":
-        t_d = timeit(lambda: ops.conv_dgrad(dy, w, dx, R, R, stride, pad, gate=x))
+        t_d = timeit(lambda: ops.conv_dgrad(dy, w, dx, R, R, stride, pad, gate_bits=gbits, addend=addend))
         line += f" | dgrad {t_d:7.3f} ms {flop / t_d / 1e9:7.1f}"
     else:
         t_d = 0.0

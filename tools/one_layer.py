@@ -22,13 +22,16 @@ dy = (torch.randn(N, OH, OW, Cout, device=dev) * 0.1).to(bf)
 dx = torch.empty_like(x)
 dw = torch.zeros(Cout, R * R, Cin, device=dev)
 bias = torch.randn(Cout, device=dev)
+# the engine's data-gradient launches: ReLU gate as packed sign words, skip gradient added in the Residual 3x3
+gbits = torch.randint(-2 ** 31, 2 ** 31 - 1, (x.numel() // 32,), device=dev, dtype=torch.int32)
+addend = (torch.randn_like(x) if name == "res3x3" else None)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(reps):
     if what == "fwd":
         ops.conv_fwd(x, w, bias, y, R, R, stride, pad, relu=True)
     elif what == "dgrad":
-        ops.conv_dgrad(dy, w, dx, R, R, stride, pad, gate=x)
+        ops.conv_dgrad(dy, w, dx, R, R, stride, pad, gate_bits=gbits, addend=addend)
     else:
         ops.conv_wgrad(dy, x, dw, R, R, stride, pad)
 e1.record()
