@@ -37,6 +37,14 @@ __device__ __forceinline__ int fdiv(int n, const FastDiv& d) {
 // tile id -> (m tile over the concatenated classes, n tile [x tap group], split)
 __device__ __forceinline__ Tile decode_tile(const Params& p, int t) {
   Tile r;
+  if (p.simple_tiles) {
+    // one class, one column tile, no split (most forward / data-gradient launches): tile = m tile.  The
+    // general decode below is ~80 instructions, paid per tile by the producers, the issuer and every epilogue
+    // warp - all single warps whose instruction count bounds short-K layers.
+    r.mi = t; r.y = 0; r.cls = 0; r.m0 = t * 128 * p.m_sub; r.n0 = 0; r.tap0 = 0; r.ntaps = 1; r.split = 0;
+    r.kb_begin = 0; r.kb_end = p.kb_total;
+    return r;
+  }
   const int rest = fdiv(t, p.fd_tiles_m);
   int mi = t - rest * p.tiles_m_total;
   const int split = fdiv(rest, p.fd_n_tiles);
@@ -251,27 +259,35 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
           int tap = tl.kb_begin / p.chunks_per_tap;
           int chunk = tl.kb_begin - tap * p.chunks_per_tap;
           int rp = tap / p.S, sp = tap - rp * p.S;
-          for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
+          // loop bookkeeping in opaque registers (two of three iterations only skip: keep them short)
+          int n_st = p.stages, cpt = p.chunks_per_tap, fS = p.S;
+          asm volatile("" : "+r"(n_st), "+r"(cpt), "+r"(fS));
+          const int kb_end = tl.kb_end;
+          for (int kb = tl.kb_begin; kb < kb_end; ++kb) {
             const int s = st;
             const uint32_t ph = st_ph;
             const int chunk_c = chunk, rp_c = rp, sp_c = sp;
-            if (++st == p.stages) { st = 0; st_ph ^= 1; }
-            if (++chunk == p.chunks_per_tap) { chunk = 0; if (++sp == p.S) { sp = 0; ++rp; } }
+            if (++st == n_st) { st = 0; st_ph ^= 1; }
+            if (++chunk == cpt) { chunk = 0; if (++sp == fS) { sp = 0; ++rp; } }
             if (s % kProducers != me) continue;  // a stage always belongs to the same producer
             if (!ptx::mbar_wait(empty0 + 8 * s, ph ^ 1)) { report_timeout(p, 101); ok = false; break; }
             const uint32_t a_dst = smem_base + s * stage_bytes;
             const uint32_t b_dst = a_dst + p.a_stage_bytes;
             const uint32_t full = full0 + 8 * s;
             if (p.debug & 1) { ptx::mbar_arrive(full); continue; }
-            ptx::mbar_arrive_expect_tx(full, tx);
-            if (p.a_im2col)
+            // feed experiments: bit 6 = no weight tile, bit 7 = no activation tile (the MMAs then read stale data)
+            ptx::mbar_arrive_expect_tx(full, tx - ((p.debug & 64) ? p.b_boxes * p.b_box_bytes : 0u) -
+                                                 ((p.debug & 128) ? p.a_boxes * p.a_box_bytes : 0u));
+            if (p.debug & 128) {
+            } else if (p.a_im2col)
               ptx::tma_load_im2col_4d(a_dst, &p.mapA[cls], full, chunk_c * p.kc, w_base, h_base,
                                       n_img, (uint16_t)sp_c, (uint16_t)rp_c);
             else
               ptx::tma_load_2d(a_dst, &p.mapA[0], full, kb * p.kc, m0);
             const int wtap =
                 (p.r_base[cls] + p.r_step * rp_c) * p.S_w + p.s_base[cls] + p.s_step * sp_c;
-            if (!p.b_mn) {
+            if (p.debug & 64) {
+            } else if (!p.b_mn) {
               ptx::tma_load_3d(b_dst, &p.mapB, full, chunk_c * p.kc, wtap, n0);
             } else {
               for (int i = 0; i < p.b_boxes; ++i)
@@ -408,7 +424,8 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
       long long pw = 0, pi = 0, pc = 0, pt = 0, pn = 0;
       const bool prof = (p.debug & 4) != 0;
       // lean loop state (see `fast` below): descriptor low words / barrier address of the current stage
-      const bool fast = !p.a_flat && mma_k == 4 && (p.debug & ~3) == 0;
+      const bool fast = !p.a_flat && (mma_k == 4 || mma_k == 2) && (p.debug & ~(3 | 64 | 128)) == 0;
+      const bool k4 = mma_k == 4;   // kc = 64: four K-steps per k-block; kc = 32: two
       uint32_t a_cur = a_lo_const, b_cur = b_lo_const, full_cur = full0;
       uint32_t a_k2 = 2 * a_kstep, a_k3 = 3 * a_kstep, b_k2 = 2 * b_kstep, b_k3 = 3 * b_kstep;
       // opaque copies: the compiler otherwise re-materialises these from the constant bank in every iteration
@@ -504,16 +521,20 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
             } else if (ng == 1) {
               ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | a_cur, ((uint64_t)b_hi32 << 32) | b_cur, idesc_last, acc0);
               ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (a_cur + a_kstep), ((uint64_t)b_hi32 << 32) | (b_cur + b_kstep), idesc_last, 1u);
-              ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (a_cur + a_k2), ((uint64_t)b_hi32 << 32) | (b_cur + b_k2), idesc_last, 1u);
-              ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (a_cur + a_k3), ((uint64_t)b_hi32 << 32) | (b_cur + b_k3), idesc_last, 1u);
+              if (k4) {
+                ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (a_cur + a_k2), ((uint64_t)b_hi32 << 32) | (b_cur + b_k2), idesc_last, 1u);
+                ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (a_cur + a_k3), ((uint64_t)b_hi32 << 32) | (b_cur + b_k3), idesc_last, 1u);
+              }
             } else {
               uint32_t ag = a_cur, bg = b_cur, dg = d_base;
               for (int g = 0; g < ng; ++g, ag += a_gstep, bg += b_gstep, dg += d_gstep) {
                 const uint32_t id = g == ng - 1 ? idesc_last : idesc;
                 ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | ag, ((uint64_t)b_hi32 << 32) | bg, id, acc0);
                 ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | (ag + a_kstep), ((uint64_t)b_hi32 << 32) | (bg + b_kstep), id, 1u);
-                ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | (ag + a_k2), ((uint64_t)b_hi32 << 32) | (bg + b_k2), id, 1u);
-                ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | (ag + a_k3), ((uint64_t)b_hi32 << 32) | (bg + b_k3), id, 1u);
+                if (k4) {
+                  ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | (ag + a_k2), ((uint64_t)b_hi32 << 32) | (bg + b_k2), id, 1u);
+                  ptx::umma_bf16(dg, ((uint64_t)a_hi32 << 32) | (ag + a_k3), ((uint64_t)b_hi32 << 32) | (bg + b_k3), id, 1u);
+                }
               }
             }
             ptx::umma_commit(full_cur + 8 * kMaxStages);   // the stage's `empty` barrier
@@ -859,6 +880,7 @@ int launch(const Params& p_in, int num_sms, size_t smem_bytes, cudaStream_t stre
   };
   if (p.m_sub < 1) p.m_sub = 1;
   if (p.acc_bufs < 1) p.acc_bufs = 1;
+  p.simple_tiles = (p.kind == KIND_FWD && p.n_classes == 1 && p.n_tiles == 1 && p.n_splits == 1) ? 1 : 0;
   p.acc_shift = 0;
   while ((1 << p.acc_shift) < p.acc_bufs) ++p.acc_shift;
   if ((1 << p.acc_shift) != p.acc_bufs || p.acc_bufs > kMaxAcc || p.acc_bufs * p.acc_stride > 512) {

@@ -145,6 +145,7 @@ struct Params {
   uint32_t resident_off;    // offset of the resident weight region from the aligned smem base
   // persistent tile schedule: tile -> (m tile [classes concatenated], n tile, split)
   int tiles_m[4], tiles_m_total, n_tiles, n_splits, total_tiles;
+  int simple_tiles;          // FWD, one class, one column tile, no split: tile id = m tile (filled by launch())
   int cls_min_tiles;         // > 0: the classes' m tiles are interleaved (decode_tile); = min over classes of tiles_m
   int acc_bufs, acc_stride;  // TMEM accumulator ring (1, 2, 4 or 8 buffers of acc_stride columns)
   int acc_shift;             // log2(acc_bufs), filled by launch()
