@@ -220,12 +220,15 @@ struct ActDims { int N, H, W, C; };
 // Measured at batch 1024 (tools/exp_tiles.sh): 256-row tiles pay off only where the k loop is long and
 // the tile wide (conv_5 fwd / dgrad: K = 3200, N = 128: 0.54 -> 0.48 ms); shorter or narrower layers lose
 // more to the single-occupancy CTA (no second CTA to hide the epilogue) than the smaller feed saves.
+// With the lean issue loop (tc_gemm.cu) eight MMAs per k-block no longer saturate the issuing thread, and the
+// threshold moved from 40 to 16 k-blocks: conv_4 dgrad 0.243 -> 0.226 ms, conv_6 dgrad 0.277 -> 0.258 ms,
+// conv_3 / conv_4 forward 2 %; N = 64 tiles (conv_6 forward, conv_3 dgrad) still lose.
 int pick_m_sub(long long M, int block_n, int kb_total) {
   static int want = 0;   // 1: never, 2 (default): where it pays, 3: always (tests)
   if (!want) { const char* e = getenv("GABRIL_TC_MSUB"); want = e ? std::max(1, std::min(atoi(e), 3)) : 2; }
   if (want == 1 || block_n > 128) return 1;
   if (want == 3) return 2;
-  return (block_n == 128 && kb_total >= 40 && M >= 256ll * 4 * g_num_sms) ? 2 : 1;
+  return (block_n == 128 && kb_total >= 16 && M >= 256ll * 4 * g_num_sms) ? 2 : 1;
 }
 
 void fwd_schedule(tc::Params& p, int kc, int block_n, int b_mn, int m_sub = 1) {
