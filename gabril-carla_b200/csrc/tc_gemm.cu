@@ -206,6 +206,7 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
             const uint32_t a_dst = smem_base + s * stage_bytes;
             const uint32_t b_dst = a_dst + p.a_stage_bytes;
             const uint32_t full = full0 + 8 * s;
+            if (p.debug & 1) { ptx::mbar_arrive(full); continue; }
             ptx::mbar_arrive_expect_tx(full, tx);
             ptx::tma_load_2d(a_dst, &p.mapA[0], full, chunk_c * p.kc, m0 + r_c * p.flat_pitch);
             if (!p.b_resident) {
@@ -430,6 +431,15 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
       uint32_t a_k2 = 2 * a_kstep, a_k3 = 3 * a_kstep, b_k2 = 2 * b_kstep, b_k3 = 3 * b_kstep;
       // opaque copies: the compiler otherwise re-materialises these from the constant bank in every iteration
       asm volatile("" : "+r"(a_k2), "+r"(a_k3), "+r"(b_k2), "+r"(b_k3));
+      // flat-slab forward regime: lean loop state
+      const bool fast_flat = p.a_flat && p.kind == KIND_FWD && mma_k == 4 && (p.debug & ~3) == 0 &&
+                             p.kb_per_split == p.kb_total;
+      int ff_kb = p.kb_total, ff_S = p.flat_S, ff_chunks = p.chunks_per_tap, ff_res = p.b_resident;
+      uint32_t ff_tap16 = p.b_tap_bytes >> 4;
+      uint32_t ff_sxb = ff_res ? (uint32_t)ff_chunks * ff_tap16 : ff_tap16;
+      uint32_t ff_rowskip = (uint32_t)((ff_S - 1) * ff_chunks) * ff_tap16;
+      asm volatile("" : "+r"(ff_kb), "+r"(ff_S), "+r"(ff_chunks), "+r"(ff_res), "+r"(ff_tap16), "+r"(ff_sxb),
+                        "+r"(ff_rowskip));
       for (int t = blockIdx.x; t < p.total_tiles && ok; t += gridDim.x, ++tcount) {
         const long long c0 = prof ? clock64() : 0;
         const Tile tl = decode_tile(p, t);
@@ -449,6 +459,33 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
               ptx::tc_fence_after();
             }
             const uint32_t w_lo = (uint32_t)p.desc_b_hi + ((smem_base + p.resident_off) >> 4);
+            if (fast_flat) {
+              // Lean issue loop of the flat-slab forward regime (a tile always walks all k-blocks from 0): the
+              // stage's descriptor words, its barrier and the resident weight tile advance by addition.
+              // conv_2 forward with TMA copies and MMAs both stubbed out took 0.395 of its 0.498 ms alone.
+              uint32_t wk = w_lo;
+              int chunk = 0;
+              for (int kb = 0; kb < ff_kb; ++kb) {
+                if (!ptx::mbar_wait(full_cur, ph)) { report_timeout(p, 103); ok = false; break; }
+                ptx::tc_fence_after();
+                uint32_t as = a_cur, bb = ff_res ? wk : b_cur;
+                for (int sx = 0; sx < ff_S; ++sx, as += 8u, bb += ff_sxb) {
+                  if (dbg_skip) continue;
+                  ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | as, ((uint64_t)b_hi32 << 32) | bb, idesc, (kb > 0 || sx > 0) ? 1u : 0u);
+                  ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (as + a_kstep), ((uint64_t)b_hi32 << 32) | (bb + b_kstep), idesc, 1u);
+                  ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (as + a_k2), ((uint64_t)b_hi32 << 32) | (bb + b_k2), idesc, 1u);
+                  ptx::umma_bf16(d_base, ((uint64_t)a_hi32 << 32) | (as + a_k3), ((uint64_t)b_hi32 << 32) | (bb + b_k3), idesc, 1u);
+                }
+                ptx::umma_commit(full_cur + 8 * kMaxStages);
+                a_cur += stage16; b_cur += stage16; full_cur += 8;
+                if (++s == stages) { s = 0; ph ^= 1; a_cur = a_lo_const; b_cur = b_lo_const; full_cur = full0; }
+                // resident weights are stored (filter row, tap column, chunk): next chunk, or next filter row
+                wk += ff_tap16;
+                if (++chunk == ff_chunks) { chunk = 0; wk += ff_rowskip; }
+              }
+              if (ok) ptx::umma_commit(tfull0 + 8 * buf);
+              continue;
+            }
             int r = tl.kb_begin / chunks, chunk = tl.kb_begin - (tl.kb_begin / chunks) * chunks;
             for (int kb = tl.kb_begin; kb < tl.kb_end; ++kb) {
               if (!ptx::mbar_wait(full0 + 8 * s, ph)) { report_timeout(p, 103); ok = false; break; }
@@ -463,7 +500,7 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
                 for (int j = 0; j < 4; ++j) {
                   const uint64_t a_desc = ((uint64_t)a_hi32 << 32) | (uint64_t)(as + j * a_kstep);
                   const uint64_t b_desc = ((uint64_t)b_hi32 << 32) | (uint64_t)(bb + j * b_kstep);
-                  ptx::umma_bf16(d_base, a_desc, b_desc, idesc, (kb > tl.kb_begin || sx > 0 || j > 0) ? 1u : 0u);
+                  if (!dbg_skip) ptx::umma_bf16(d_base, a_desc, b_desc, idesc, (kb > tl.kb_begin || sx > 0 || j > 0) ? 1u : 0u);
                 }
               }
               ptx::umma_commit(empty0 + 8 * s);
