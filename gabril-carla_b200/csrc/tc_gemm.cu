@@ -692,77 +692,117 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
     const bf16* resid_base = p.resid;
     const bf16* gate_base = p.gate;
     uint32_t* bits_base = p.bits_out;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tcount) {
-      if (p.epi_tile_split && (tcount & (kEpiGroups - 1)) != grp) continue;   // the other group's tile
-      const long long ec0 = eprof ? clock64() : 0;
-      const Tile tl = decode_tile(p, t);
+    // One UNIT = one 128-row sub-tile of a tile.  The row geometry and the global loads of a unit (sign words of
+    // the gate, row mask) are issued one unit AHEAD of its items: issued next to their first use, the sign-word
+    // read was an exposed DRAM round trip per tile - 48 % of this warp's samples in res3x3 dgrad (ncu source page).
+    struct RowPre {
+      bool row_ok;
+      long long orow, off0;
+      uint32_t keep_row;
+      float rm4[4];      // rm4[0]: the row's multiplier; quadrant mode: one per quadrant
+      uint32_t gw[4];    // sign words of every 32-column chunk of this row: 4 bytes per chunk instead of 64
+      int q_sh, q_sw;    // quadrant mode: super-pixel coordinates of this row
+    };
+    auto prep = [&](const Tile& tl, int sub) {
+      RowPre r;
       const int cls = tl.cls, n0 = tl.n0;
+      const int row = tl.m0 + sub * 128 + q * 32 + lane;
+      bool row_ok = row < p.M_total[cls];
+      long long orow = row;
+      if (p.remap && row_ok) {
+        const int hw = p.Hs[cls] * p.Ws[cls];
+        const int n = fdiv(row, p.fd_hw[cls]);
+        const int rem = row - n * hw;
+        const int jh = fdiv(rem, p.fd_ws[cls]);
+        const int jw = rem - jh * p.Ws[cls];
+        orow = ((long long)n * p.OHf + (jh * p.remap_sh + p.ah[cls])) * p.OWf +
+               (jw * p.remap_sw + p.aw[cls]);
+        if (p.valid_h > 0 && (jh >= p.valid_h || jw >= p.valid_w)) row_ok = false;
+      }
+      bool zero_row = false;
+      r.q_sh = 0; r.q_sw = 0;
+      if (p.quad_C > 0) {
+        const int spr = fdiv(row, p.fd_border_w);
+        r.q_sw = row - spr * p.border_w;
+        r.q_sh = spr - fdiv(spr, p.fd_border_h) * p.border_h;
+      } else if (p.s2d_H > 0 && row_ok) {
+        const int qd = row & 3, sp = row >> 2;
+        const int spr = fdiv(sp, p.fd_border_w);
+        const int sw = sp - spr * p.border_w, sh = spr - fdiv(spr, p.fd_border_h) * p.border_h;
+        const int ih = 2 * sh + (qd >> 1) - 1, iw = 2 * sw + (qd & 1) - 1;
+        zero_row = ih < 0 || ih >= p.s2d_H || iw < 0 || iw >= p.s2d_W;
+      } else if (p.border_h > 0 && row_ok) {
+        const int hw = p.border_h * p.border_w;
+        const int rem = row - fdiv(row, p.fd_border_hw) * hw;
+        const int y = fdiv(rem, p.fd_border_w);
+        const int x = rem - y * p.border_w;
+        zero_row = (y == 0) || (y == p.border_h - 1) || (x == 0) || (x == p.border_w - 1);
+      }
+      r.rm4[0] = 1.0f; r.rm4[1] = 1.0f; r.rm4[2] = 1.0f; r.rm4[3] = 1.0f;
+      if (p.rowmask && row_ok) {
+        if (p.quad_C > 0) {
+          const float4 r4 = __ldg(reinterpret_cast<const float4*>(p.rowmask) + orow);
+          r.rm4[0] = r4.x; r.rm4[1] = r4.y; r.rm4[2] = r4.z; r.rm4[3] = r4.w;
+        } else {
+          r.rm4[0] = p.rowmask[orow];
+        }
+      }
+      r.keep_row = zero_row ? 0u : 0xffffffffu;
+      r.off0 = orow * p.ldo + n0;
+      r.gw[0] = 0u; r.gw[1] = 0u; r.gw[2] = 0u; r.gw[3] = 0u;
+      if (p.out_mode == OUT_BF16 && row_ok && p.gate_bits) {
+        const uint32_t* gb = p.gate_bits + (r.off0 >> 5);
+#pragma unroll
+        for (int ci = 0; ci < 4; ++ci)
+          if (ci * 32 < p.block_n && n0 + ci * 32 < p.N_total) r.gw[ci] = __ldg(gb + ci);
+      }
+      r.row_ok = row_ok;
+      r.orow = orow;
+      return r;
+    };
+    const int tstep = (int)gridDim.x * (p.epi_tile_split ? kEpiGroups : 1);   // with the tile split the groups alternate tiles
+    const int tcstep = p.epi_tile_split ? kEpiGroups : 1;
+    int t = blockIdx.x + (p.epi_tile_split ? grp * (int)gridDim.x : 0);
+    tcount = p.epi_tile_split ? grp : 0;
+    int sub = 0;
+    bool have = t < p.total_tiles;
+    Tile tl;
+    RowPre cur;
+    if (have) { tl = decode_tile(p, t); cur = prep(tl, 0); }
+#pragma unroll 1
+    while (have) {
+      const long long ec0 = eprof ? clock64() : 0;
+      // the unit after this one: its loads fly while this one's items run
+      int nt = t, nsub = sub + 1, ntc = tcount;
+      if (nsub == p.m_sub) { nsub = 0; nt = t + tstep; ntc = tcount + tcstep; }
+      const bool nhave = nt < p.total_tiles;
+      Tile ntl = tl;
+      RowPre nxt = cur;
+      if (nhave) {
+        if (nsub == 0) ntl = decode_tile(p, nt);
+        nxt = prep(ntl, nsub);
+      }
+      const int n0 = tl.n0;
       const int buf = tcount & (p.acc_bufs - 1);
       const int use = tcount >> p.acc_shift;
-      bool dead = false;
-      int item = 0;
-      for (int sub = 0; sub < p.m_sub; ++sub) {   // 128-row sub-tiles of this tile (FWD regime: 1 or 2)
-        const int row = tl.m0 + sub * 128 + q * 32 + lane;
-        bool row_ok = row < p.M_total[cls];
-        long long orow = row;
-        if (p.remap && row_ok) {
-          const int hw = p.Hs[cls] * p.Ws[cls];
-          const int n = fdiv(row, p.fd_hw[cls]);
-          const int rem = row - n * hw;
-          const int jh = fdiv(rem, p.fd_ws[cls]);
-          const int jw = rem - jh * p.Ws[cls];
-          orow = ((long long)n * p.OHf + (jh * p.remap_sh + p.ah[cls])) * p.OWf +
-                 (jw * p.remap_sw + p.aw[cls]);
-          if (p.valid_h > 0 && (jh >= p.valid_h || jw >= p.valid_w)) row_ok = false;
-        }
-        bool zero_row = false;
-        int q_sh = 0, q_sw = 0;   // quadrant mode: super-pixel coordinates of this row
-        if (p.quad_C > 0) {
-          const int spr = fdiv(row, p.fd_border_w);
-          q_sw = row - spr * p.border_w;
-          q_sh = spr - fdiv(spr, p.fd_border_h) * p.border_h;
-        } else if (p.s2d_H > 0 && row_ok) {
-          const int qd = row & 3, sp = row >> 2;
-          const int spr = fdiv(sp, p.fd_border_w);
-          const int sw = sp - spr * p.border_w, sh = spr - fdiv(spr, p.fd_border_h) * p.border_h;
-          const int ih = 2 * sh + (qd >> 1) - 1, iw = 2 * sw + (qd & 1) - 1;
-          zero_row = ih < 0 || ih >= p.s2d_H || iw < 0 || iw >= p.s2d_W;
-        } else if (p.border_h > 0 && row_ok) {
-          const int hw = p.border_h * p.border_w;
-          const int rem = row - fdiv(row, p.fd_border_hw) * hw;
-          const int y = fdiv(rem, p.fd_border_w);
-          const int x = rem - y * p.border_w;
-          zero_row = (y == 0) || (y == p.border_h - 1) || (x == 0) || (x == p.border_w - 1);
-        }
-        float rm4[4] = {1.0f, 1.0f, 1.0f, 1.0f};   // rm4[0]: the row's multiplier; quadrant mode: one per quadrant
-        if (p.rowmask && row_ok) {
-          if (p.quad_C > 0) {
-            const float4 r4 = __ldg(reinterpret_cast<const float4*>(p.rowmask) + orow);
-            rm4[0] = r4.x; rm4[1] = r4.y; rm4[2] = r4.z; rm4[3] = r4.w;
-          } else {
-            rm4[0] = p.rowmask[orow];
-          }
-        }
-        const uint32_t keep_row = zero_row ? 0u : 0xffffffffu;
-        const long long off0 = orow * p.ldo + n0;
-        // the sign words of every 32-column chunk of this row: 4 bytes per chunk instead of 64
-        uint32_t gw[4] = {0u, 0u, 0u, 0u};
-        if (p.out_mode == OUT_BF16 && row_ok && p.gate_bits) {
-          const uint32_t* gb = p.gate_bits + (off0 >> 5);
-#pragma unroll
-          for (int ci = 0; ci < 4; ++ci)
-            if (ci * 32 < p.block_n && n0 + ci * 32 < p.N_total) gw[ci] = __ldg(gb + ci);
-        }
-        if (sub == 0) {
-          const long long ec1 = eprof ? clock64() : 0;
-          if (eprof) e_pre += ec1 - ec0;
-          bool ok = ptx::mbar_wait(tfull0 + 8 * buf, use & 1);
-          if (eprof) e_wait += clock64() - ec1;
-          if (!ok) report_timeout(p, 104);
-          ok = __all_sync(0xffffffffu, ok);
-          if (!ok) { dead = true; break; }
-          ptx::tc_fence_after();
-        }
+      if (sub == 0) {
+        const long long ec1 = eprof ? clock64() : 0;
+        if (eprof) e_pre += ec1 - ec0;
+        bool ok = ptx::mbar_wait(tfull0 + 8 * buf, use & 1);
+        if (eprof) e_wait += clock64() - ec1;
+        if (!ok) report_timeout(p, 104);
+        ok = __all_sync(0xffffffffu, ok);
+        if (!ok) break;
+        ptx::tc_fence_after();
+      }
+      {
+        const bool row_ok = cur.row_ok;
+        const long long orow = cur.orow, off0 = cur.off0;
+        const uint32_t keep_row = cur.keep_row;
+        const int q_sh = cur.q_sh, q_sw = cur.q_sw;
+        const float* rm4 = cur.rm4;
+        const uint32_t* gw = cur.gw;
+        int item = sub * tl.ntaps * n_chunks;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + buf * p.acc_stride + sub * p.block_n;
         // The item loop is deliberately NOT unrolled: a rolled body of ~150 instructions stays in the
         // instruction cache across chunks and tiles.
@@ -830,13 +870,15 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
             }   // fp32 output path
           }
         }
-      }  // sub
-      if (dead) break;
+      }
       if (eprof) { e_tile += clock64() - ec0; ++e_n; }
-      // accumulator buffer drained: hand it back to the MMA issuer
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(tempty0 + 8 * buf);
+      if (sub == p.m_sub - 1) {
+        // accumulator buffer drained: hand it back to the MMA issuer
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(tempty0 + 8 * buf);
+      }
+      t = nt; sub = nsub; tcount = ntc; tl = ntl; cur = nxt; have = nhave;
     }
     if (eprof) {
       atomicAdd(&g_prof[8], (unsigned long long)e_pre); atomicAdd(&g_prof[9], (unsigned long long)e_wait);
