@@ -434,6 +434,7 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
       // flat-slab forward regime: lean loop state
       const bool fast_flat = p.a_flat && p.kind == KIND_FWD && mma_k == 4 && (p.debug & ~3) == 0 &&
                              p.kb_per_split == p.kb_total;
+      const bool fast_flatw = p.a_flat && p.kind == KIND_WGRAD && mma_k == 4 && p.debug == 0;
       int ff_kb = p.kb_total, ff_S = p.flat_S, ff_chunks = p.chunks_per_tap, ff_res = p.b_resident;
       uint32_t ff_tap16 = p.b_tap_bytes >> 4;
       uint32_t ff_sxb = ff_res ? (uint32_t)ff_chunks * ff_tap16 : ff_tap16;
@@ -506,6 +507,38 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
               ptx::umma_commit(empty0 + 8 * s);
               if (++s == stages) { s = 0; ph ^= 1; }
               if (++chunk == chunks) { chunk = 0; ++r; }
+            }
+          } else if (fast_flatw) {
+            // lean issue loop of the flat weight gradient (one tile per CTA, long k loop)
+            const int nrows = tl.ntaps / FS;
+            uint32_t row16 = (uint32_t)p.b_boxes * tap16, bn = (uint32_t)p.block_n;
+            int swp = p.swap_ab;
+            asm volatile("" : "+r"(row16), "+r"(bn), "+r"(swp));
+            const int kb_end = tl.kb_end;
+            for (int kb = tl.kb_begin; kb < kb_end; ++kb) {
+              if (!ptx::mbar_wait(full_cur, ph)) { report_timeout(p, 103); ok = false; break; }
+              ptx::tc_fence_after();
+              const uint32_t acc0 = kb > tl.kb_begin ? 1u : 0u;
+              uint32_t brow = b_cur, dcol = d_base;
+              for (int rr = 0; rr < nrows; ++rr, brow += row16) {
+                uint32_t bb = brow;
+                for (int sx = 0; sx < ff_S; ++sx, bb += 8u, dcol += bn) {
+                  const uint64_t a0 = ((uint64_t)a_hi32 << 32) | a_cur, a1 = ((uint64_t)a_hi32 << 32) | (a_cur + a_kstep);
+                  const uint64_t a2 = ((uint64_t)a_hi32 << 32) | (a_cur + a_k2), a3 = ((uint64_t)a_hi32 << 32) | (a_cur + a_k3);
+                  const uint64_t b0 = ((uint64_t)b_hi32 << 32) | bb, b1 = ((uint64_t)b_hi32 << 32) | (bb + b_kstep);
+                  const uint64_t b2 = ((uint64_t)b_hi32 << 32) | (bb + b_k2), b3 = ((uint64_t)b_hi32 << 32) | (bb + b_k3);
+                  if (swp) {   // exchanged form (narrow dY): the slab view is the M = 128 operand, dY the N = Cy one
+                    ptx::umma_bf16(dcol, b0, a0, idesc, acc0); ptx::umma_bf16(dcol, b1, a1, idesc, 1u);
+                    ptx::umma_bf16(dcol, b2, a2, idesc, 1u); ptx::umma_bf16(dcol, b3, a3, idesc, 1u);
+                  } else {
+                    ptx::umma_bf16(dcol, a0, b0, idesc, acc0); ptx::umma_bf16(dcol, a1, b1, idesc, 1u);
+                    ptx::umma_bf16(dcol, a2, b2, idesc, 1u); ptx::umma_bf16(dcol, a3, b3, idesc, 1u);
+                  }
+                }
+              }
+              ptx::umma_commit(full_cur + 8 * kMaxStages);
+              a_cur += stage16; b_cur += stage16; full_cur += 8;
+              if (++s == stages) { s = 0; ph ^= 1; a_cur = a_lo_const; b_cur = b_lo_const; full_cur = full0; }
             }
           } else {
             const int nrows = tl.ntaps / FS;
