@@ -234,9 +234,9 @@ def quick_run(device, gaze_method, dp_method, rgb, B, steps=10, warmup=3, seed=0
 
 def load_tc_traffic(args, B):
     """dram__bytes_read.sum + dram__bytes_write.sum of every tc_gemm_kernel launch of ONE step, from the
-    committed ncu pass (profiles/r1_tc_traffic.json); only quoted for the configuration it was taken on."""
+    committed ncu pass (profiles/r2c_tc_traffic.json, else the older ones); only quoted for the configuration it was taken on."""
     try:
-        name = next(n for n in ("r2b_tc_traffic.json", "r2_tc_traffic.json", "r1_tc_traffic.json")
+        name = next(n for n in ("r2c_tc_traffic.json", "r2b_tc_traffic.json", "r2_tc_traffic.json", "r1_tc_traffic.json")
                     if os.path.exists(os.path.join(ROOT, "profiles", n)))
         with open(os.path.join(ROOT, "profiles", name)) as f:
             t = json.load(f)
