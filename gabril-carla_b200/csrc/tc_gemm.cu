@@ -288,6 +288,12 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
             const int wtap =
                 (p.r_base[cls] + p.r_step * rp_c) * p.S_w + p.s_base[cls] + p.s_step * sp_c;
             if (p.debug & 64) {
+            } else if (p.cls_n) {
+              // stacked parity classes: box i = the weight tap of class i, all Cin columns
+              for (int i = 0; i < p.b_boxes; ++i)
+                ptx::tma_load_3d(b_dst + i * p.b_box_bytes, &p.mapB, full, 0,
+                                 (p.r_base[i] + p.r_step * rp_c) * p.S_w + p.s_base[i] + p.s_step * sp_c,
+                                 chunk_c * p.kc);
             } else if (!p.b_mn) {
               ptx::tma_load_3d(b_dst, &p.mapB, full, chunk_c * p.kc, wtap, n0);
             } else {
@@ -733,8 +739,9 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
       long long orow, off0;
       uint32_t keep_row;
       float rm4[4];      // rm4[0]: the row's multiplier; quadrant mode: one per quadrant
-      uint32_t gw[4];    // sign words of every 32-column chunk of this row: 4 bytes per chunk instead of 64
+      uint32_t gw[8];    // sign words of every 32-column chunk of this row: 4 bytes per chunk instead of 64
       int q_sh, q_sw;    // quadrant mode: super-pixel coordinates of this row
+      uint32_t vmask;    // stacked parity classes: bit c = pixel (2jh + ah_c, 2jw + aw_c) exists
     };
     auto prep = [&](const Tile& tl, int sub) {
       RowPre r;
@@ -742,7 +749,18 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
       const int row = tl.m0 + sub * 128 + q * 32 + lane;
       bool row_ok = row < p.M_total[cls];
       long long orow = row;
-      if (p.remap && row_ok) {
+      r.vmask = 0u;
+      if (p.cls_n) {
+        // row = base pixel (n, jh, jw); orow = pixel (2jh, 2jw) of the output, class c adds ah_c * OWf + aw_c
+        const int hw = p.Hs[0] * p.Ws[0];
+        const int n = fdiv(row, p.fd_hw[0]);
+        const int rem = row - n * hw;
+        const int jh = fdiv(rem, p.fd_ws[0]);
+        const int jw = rem - jh * p.Ws[0];
+        orow = ((long long)n * p.OHf + 2 * jh) * p.OWf + 2 * jw;
+        const bool h1 = 2 * jh + 1 < p.OHf, w1 = 2 * jw + 1 < p.OWf;
+        r.vmask = row_ok ? (1u | (w1 ? 2u : 0u) | (h1 ? 4u : 0u) | (h1 && w1 ? 8u : 0u)) : 0u;
+      } else if (p.remap && row_ok) {
         const int hw = p.Hs[cls] * p.Ws[cls];
         const int n = fdiv(row, p.fd_hw[cls]);
         const int rem = row - n * hw;
@@ -782,12 +800,23 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
       }
       r.keep_row = zero_row ? 0u : 0xffffffffu;
       r.off0 = orow * p.ldo + n0;
-      r.gw[0] = 0u; r.gw[1] = 0u; r.gw[2] = 0u; r.gw[3] = 0u;
-      if (p.out_mode == OUT_BF16 && row_ok && p.gate_bits) {
-        const uint32_t* gb = p.gate_bits + (r.off0 >> 5);
 #pragma unroll
-        for (int ci = 0; ci < 4; ++ci)
-          if (ci * 32 < p.block_n && n0 + ci * 32 < p.N_total) r.gw[ci] = __ldg(gb + ci);
+      for (int ci = 0; ci < 8; ++ci) r.gw[ci] = 0u;
+      if (p.out_mode == OUT_BF16 && row_ok && p.gate_bits) {
+        if (p.cls_n) {
+          const int cpc = p.ldo >> 5;   // 32-column chunks per class
+#pragma unroll
+          for (int ci = 0; ci < 8; ++ci) {
+            const int c = ci / cpc;     // cpc = 2 (Cin = 64): classes 0 .. 3
+            if ((r.vmask >> c) & 1u)
+              r.gw[ci] = __ldg(p.gate_bits + ((r.off0 + ((c >> 1) * p.OWf + (c & 1)) * p.ldo + (ci - c * cpc) * 32) >> 5));
+          }
+        } else {
+          const uint32_t* gb = p.gate_bits + (r.off0 >> 5);
+#pragma unroll
+          for (int ci = 0; ci < 4; ++ci)
+            if (ci * 32 < p.block_n && n0 + ci * 32 < p.N_total) r.gw[ci] = __ldg(gb + ci);
+        }
       }
       r.row_ok = row_ok;
       r.orow = orow;
@@ -845,7 +874,13 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
             if (!p.epi_tile_split && (item & (kEpiGroups - 1)) != grp) continue;   // the other group's chunk
             const int c = ci * 32;
             const int col0 = n0 + c;
-            const bool live = row_ok && col0 < p.N_total;
+            bool live = row_ok && col0 < p.N_total;
+            long long coff = c;   // offset of this chunk from the row's first element
+            if (p.cls_n) {
+              const int cpc = p.ldo >> 5, k = ci / cpc;
+              live = ((cur.vmask >> k) & 1u) != 0u;
+              coff = (long long)((k >> 1) * p.OWf + (k & 1)) * p.ldo + (ci - k * cpc) * 32;
+            }
             uint32_t keep = keep_row;
             float rmask = rm4[0];
             if (p.quad_C > 0) {
@@ -856,8 +891,9 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
             }
             if constexpr ((kEF & EF_F32) == 0u) {
               if ((kEF & EF_RUNTIME) == 0u || out_bf16) {
-                const long long off = off0 + c;
-                const uint32_t gword = ci == 0 ? gw[0] : ci == 1 ? gw[1] : ci == 2 ? gw[2] : gw[3];
+                const long long off = off0 + coff;
+                const uint32_t gword = ci == 0 ? gw[0] : ci == 1 ? gw[1] : ci == 2 ? gw[2] : ci == 3 ? gw[3] :
+                                       ci == 4 ? gw[4] : ci == 5 ? gw[5] : ci == 6 ? gw[6] : gw[7];
                 epi_item_bf16<kEF>(epi_flags, t_lane + a * p.block_n + c, live, bias_base + col0, resid_base + off,
                                    gate_base + off, gword, rmask, keep, reinterpret_cast<bf16*>(p.out) + off,
                                    bits_base + (off >> 5));

@@ -99,6 +99,14 @@ struct Params {
   // descriptor).  Against the form above this loads x once per k-block instead of once per tap.
   // center_tap = (pad, pad): its tile is dY itself (bias gradient).
   int shift_dy, center_tap;
+  // FWD regime, data gradient of a k4 / s2 / pad-0 convolution with the FOUR INPUT-PARITY CLASSES STACKED ALONG N:
+  // without padding every class (ah, aw) reads the same 2x2 neighbourhood of dY, dY[jh-1+r', jw-1+s'], and differs
+  // only in its weight taps (kh, kw) = (ah + 2 - 2r', aw + 2 - 2s').  One tile = 128 base pixels (jh, jw) x
+  // (4 classes x Cin) columns: the dY tile is staged once instead of once per class, one N = 4*Cin MMA replaces
+  // four N = Cin ones (an N = 64 MMA occupies the tensor pipe as long as an N = 128 one), and there are a quarter
+  // of the tiles.  B box i of a stage = class i's weight tap (r_base[i], s_base[i]); the epilogue scatters column
+  // chunk c to pixel (2jh + ah, 2jw + aw) of class c / (Cin / 32).
+  int cls_n;
   uint64_t desc_a_hi, desc_b_hi;  // smem descriptors with the start-address field zero
   uint32_t idesc;
   uint32_t tmem_cols;

@@ -438,6 +438,12 @@ int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void*
                        out_f32_atomic, splits, stream);
 }
 
+static bool dgrad_stack_disabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("GABRIL_DGRAD_NO_STACK"); v = (e && e[0] == '1') ? 1 : 0; }
+  return v == 1;
+}
+
 // dx[N,H,W,Cin] = gate( conv_transpose(dy[N,OH,OW,Cout], w[Cout][R*S][Cin]) + addend )
 //   gate: dx = gate_tensor > 0 ? dx : 0 (ReLU backward of the layer below), rowmask: per-pixel
 //   multiplier (GMD).  stride 1 (any R,S,pad) and the k4/s2/p1 encoder convs are supported.
@@ -483,6 +489,45 @@ static int conv_dgrad_impl(const void* dy, const void* w, const float* bias, int
                       tile_rows, 1);
     }
     if (rc) return rc;
+  } else if (stride == 2 && R == 4 && S == 4 && pad == 0 && Cin == 64 && kc == 64 && m_sub == 1 && !bias && !rowmask &&
+             !gate && !dgrad_stack_disabled()) {   // (per-column / per-row epilogue terms are not class-aware)
+    // the four parity classes stacked along N (tc::Params::cls_n): one launch geometry, N = 4 * Cin = 256
+    p.cls_n = 4;
+    p.n_classes = 1;
+    p.a_im2col = 1;
+    p.remap = 1; p.remap_sh = 2; p.remap_sw = 2;
+    p.OHf = H; p.OWf = W;
+    p.taps = 4;
+    p.S = 2;
+    p.r_step = -2; p.s_step = -2;
+    fwd_schedule(p, kc, 4 * Cin, 1, 1);   // four 64-column weight boxes per stage, one per class
+    p.N_total = 4 * Cin;
+    for (int c = 0; c < 4; ++c) {
+      const int ah = c >> 1, aw = c & 1;
+      p.ah[c] = ah; p.aw[c] = aw;
+      p.r_base[c] = (ah & 1) + 2; p.s_base[c] = (aw & 1) + 2;
+    }
+    const int Hs = (H + 1) / 2, Ws = (W + 1) / 2;   // base grid = class (0, 0), the largest
+    p.Hs[0] = Hs; p.Ws[0] = Ws;
+    p.M_total[0] = N * Hs * Ws;
+    p.OW[0] = Ws; p.OHW[0] = Hs * Ws;
+    p.lower_w[0] = -1; p.lower_h[0] = -1;
+    rc = im2col_map(&p.mapA[0], dy, N, OH, OW, Cout, -1, -1, -1 + Ws - OW, -1 + Hs - OH, kc, 128, 1);
+    if (rc) return rc;
+    p.kb_total = p.taps * p.chunks_per_tap;
+    p.kb_per_split = p.kb_total;
+    rc = weight_map(&p.mapB, w, Cout, R * S, Cin, 1, kc, Cin);
+    if (rc) return rc;
+    p.out_mode = tc::OUT_BF16;
+    p.out = dx; p.ldo = Cin;
+    p.bias = bias; p.resid = (const bf16*)addend; p.gate = (const bf16*)gate; p.rowmask = rowmask;
+    p.relu = relu;
+    p.err_flag = g_err_flag;
+    size_t smem1;
+    pick_stages(p, &smem1, 1);
+    const int mt1[1] = {(p.M_total[0] + 127) / 128};
+    finalize_schedule(p, mt1, 1, 1, 4 * Cin, 1);
+    return tc::launch(p, g_num_sms, smem1, stream);
   } else if (stride == 2 && R == 4 && S == 4 && (pad == 1 || pad == 0)) {
     // Input pixel ih = 2*jh + a_h receives exactly two filter rows: kh = b_h + 2 - 2r' with
     // b_h = (a_h + pad) & 1, read from dy row jh + c_h - 1 + r', c_h = (a_h + pad - b_h) / 2

@@ -13,6 +13,7 @@ LAYERS = [
     ("conv1_gemm_rgb", 1, 1, 128, 32, 1, 1, 1, 0),
     ("conv2", 90, 160, 32, 64, 4, 4, 2, 1),
     ("conv3", 45, 80, 64, 128, 4, 4, 2, 1),
+    ("conv3_p0", 47, 82, 64, 128, 4, 4, 2, 0),   # the engine's form (zero-bordered input): parity classes stacked along N
     ("conv4", 22, 40, 128, 128, 3, 3, 1, 0),
     ("res3x3", 20, 38, 128, 32, 3, 3, 1, 1),
     ("res1x1", 20, 38, 32, 128, 1, 1, 1, 0),
