@@ -31,6 +31,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 GLOBAL_BATCH = 1024
+SPINUP_S = 1.5   # untimed steps before the first measurement (GPU clock ramp of a fresh box), see main_ours
 FLOP_PER_SAMPLE = {True: 5.3816e9, False: 5.4996e9}  # fwd+bwd, gray / RGB
 
 
@@ -103,7 +104,8 @@ def workload_config(args, B, world):
                         f"({'grayscale' if gray else 'RGB'} stack 2, 180x320, action_dim 7, Adam), "
                         "synthetic Bench2Drive-shaped frames + gaze coords",
             "global_batch": B * world, "per_gpu_batch": B, "parallelism": f"dp{world}",
-            "l2": "per-step working set (>6 MB/sample activations, >6 GB per step) exceeds the 126 MB L2; no flush needed"}
+            "l2": "per-step working set (>6 MB/sample activations, >6 GB per step) exceeds the 126 MB L2; no flush needed",
+            "spinup": f"{SPINUP_S} s of untimed steps before the first measurement (clock ramp of a fresh box), then W warm-up steps"}
 
 
 def main_reference(args):
@@ -313,6 +315,23 @@ def main_ours(args):
     # ---- count our launches in one step (every traced call is one kernel launch of ours, the
     #      GMD mask call is three) and collect the roofline evidence ----
     for _ in range(max(3, args.warmup)):
+        step(dev_batch)
+    barrier()
+    # Clock spin-up: the first process on a fresh box starts on a GPU that has not reached its steady clocks -
+    # measured on one box: per-launch event times 5.7 % longer in the first process (traced ~50 ms after its
+    # first kernel) than in the next process of the same build.  ~1.5 s of untimed steps before any measurement;
+    # every rank runs the same count (the steps contain collectives).
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(5):
+        step(dev_batch)
+    ev1.record()
+    barrier()
+    spin_ms = torch.tensor([ev0.elapsed_time(ev1) / 5.0], device=device)
+    if is_dist:
+        dist.all_reduce(spin_ms, op=dist.ReduceOp.MAX)
+    n_spin = int(min(2000, max(0.0, SPINUP_S * 1e3 / max(float(spin_ms.item()), 0.05))))
+    for _ in range(n_spin):
         step(dev_batch)
     barrier()
     # the traced step runs eagerly and serially (no side stream), so that every launch is timed alone
