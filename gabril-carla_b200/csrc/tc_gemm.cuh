@@ -103,7 +103,7 @@ struct Params {
   // without padding every class (ah, aw) reads the same 2x2 neighbourhood of dY, dY[jh-1+r', jw-1+s'], and differs
   // only in its weight taps (kh, kw) = (ah + 2 - 2r', aw + 2 - 2s').  One tile = 128 base pixels (jh, jw) x
   // (4 classes x Cin) columns: the dY tile is staged once instead of once per class, one N = 4*Cin MMA replaces
-  // four N = Cin ones (an N = 64 MMA occupies the tensor pipe as long as an N = 128 one), and there are a quarter
+  // four N = Cin ones (narrow MMAs cost the tensor pipe clearly more than N / 128 of a wide one), and there are a quarter
   // of the tiles.  B box i of a stage = class i's weight tap (r_base[i], s_base[i]); the epilogue scatters column
   // chunk c to pixel (2jh + ah, 2jw + aw) of class c / (Cin / 32).
   int cls_n;
