@@ -780,7 +780,8 @@ static int conv_wgrad_shifted(const void* dy, const void* x, float* dw, int N, i
     rc = tiled_map(&p.mapA[0], x, 2, dims, strides, box, a_sw);
     if (rc) return rc;
   }
-  rc = im2col_map(&p.mapB, dy, N, H, W, Cout, p.lower_w[0], p.lower_h[0], -pad, -pad, Cout, KP, 1);
+  // one base position per x pixel: the traversal box has the tensor's own extent (upper corner = lower corner)
+  rc = im2col_map(&p.mapB, dy, N, H, W, Cout, p.lower_w[0], p.lower_h[0], p.lower_w[0], p.lower_h[0], Cout, KP, 1);
   if (rc) return rc;
   const int m_tiles = Cin / 128;
   const int occ = 1;   // 288 / 320 accumulator columns round up to all 512
@@ -1047,6 +1048,12 @@ static int conv_wgrad_flat_impl(const void* dy, const void* x, float* dw, int N,
   if (!mn_ok(Cx) || Cx < 64 || Cy % 32 || N <= 0 || S > 8) return GABRIL_ERR_BAD_SHAPE;
   const long long P = (long long)N * Hg * Wg;
   if (P >= (1ll << 31)) return GABRIL_ERR_BAD_SHAPE;
+  // conv_2 on the space-to-depth grid (2x2, dY one pixel down-right of its flat row, zero-bordered dY): the same
+  // sum as the weight gradient with the shift on dY of a 2x2 convolution with "pad" 1 - one N = 4 * Cy = 256 MMA
+  // per K step instead of four N = 64 ones, x staged once (the flat form wraps where im2col zero-fills; on a
+  // zero-bordered dY both read zeros)
+  if (R == 2 && S == 2 && dy_row_off == Wg + 1 && Cx == 128 && Cy == 64 && x_pitch_c == 0 && !wgrad_shift_disabled())
+    return conv_wgrad_shifted(dy, x, dw, N, Hg, Wg, Cx, Cy, 2, 2, 1, 0, stream);
   const int KP = 64, T = R * S;
   tc::Params p;
   zero_params(p);

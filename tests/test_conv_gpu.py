@@ -230,6 +230,31 @@ def test_conv_flat_fwd_dgrad_wgrad(ops, layer, N):
     _lib.poll_error()
 
 
+@pytest.mark.parametrize("N", [2, 19])
+def test_conv2_s2d_wgrad(ops, N):
+    """conv_2's weight gradient on the space-to-depth grid (2x2 taps, dY one pixel down-right, zero-bordered dY): the
+    engine's call, served by the weight gradient with the shift on dY; vs the fp64 flat sum it stands for."""
+    from gabril_carla_b200 import _lib
+    SH, SW, Cx, Cy = 47, 82, 128, 64
+    g = torch.Generator().manual_seed(31 + N)
+    x = (torch.randn(N, SH, SW, Cx, generator=g) * 0.5).to(torch.bfloat16)
+    dy = torch.zeros(N, SH, SW, Cy, dtype=torch.bfloat16)
+    dy[:, 1:46, 1:81] = (torch.randn(N, 45, 80, Cy, generator=g) * 0.5).to(torch.bfloat16)
+    P = N * SH * SW
+    X, D = x.reshape(P, Cx).double(), dy.reshape(P, Cy).double()
+    ref = torch.zeros(Cy, 4, Cx, dtype=torch.float64)
+    for r in range(2):
+        for s_ in range(2):
+            sh = SW + 1 - (r * SW + s_)          # dw[cy][r,s][cx] = sum_q dy[q + SW + 1][cy] x[q + r*SW + s][cx]
+            ref[:, r * 2 + s_] = D[sh:].t() @ X[:P - sh]
+    dw = torch.zeros(Cy, 4, Cx, device=DEV)
+    db = torch.zeros(Cy, device=DEV)
+    ops.conv_wgrad_flat(dy.to(DEV), x.to(DEV), dw, 2, 2, SW + 1, dbias=db)
+    assert rel(dw.cpu(), ref) <= 2e-5
+    assert rel(db.cpu(), dy.double().sum((0, 1, 2))) <= 2e-5
+    _lib.poll_error()
+
+
 # ---- conv_1 over the 4x4 space-to-depth frame image (csrc/conv1_s4d.cu) ---------------------------
 @pytest.mark.parametrize("gray,S,L", [(True, 2, 2), (False, 2, 3), (True, 1, 2), (True, 3, 5)])
 def test_obs_s4d_bit_exact(ops, gray, S, L):
