@@ -96,12 +96,13 @@ int tiled_map(CUtensorMap* m, const void* ptr, int rank, const uint64_t* dims,
 
 // NHWC activation seen as (C, W, H, N); the traversal walks `box_pix` base pixels with `stride`.
 int im2col_map(CUtensorMap* m, const void* ptr, int N, int H, int W, int C, int lower_w,
-               int lower_h, int upper_w, int upper_h, int box_c, int box_pix, int stride) {
+               int lower_h, int upper_w, int upper_h, int box_c, int box_pix, int stride, int stride_h = 0) {
+  if (stride_h <= 0) stride_h = stride;
   cuuint64_t gd[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   cuuint64_t gs[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
   int lo[2] = {lower_w, lower_h};
   int up[2] = {upper_w, upper_h};
-  cuuint32_t es[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  cuuint32_t es[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride_h, 1};
   CUresult r = g_encode_im2col(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), gd,
                                gs, lo, up, (cuuint32_t)box_c, (cuuint32_t)box_pix, es,
                                CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for_bytes(box_c * 2),
@@ -280,6 +281,22 @@ int weight_map(CUtensorMap* m, const void* w, int Cout, int T, int Cin, int b_mn
   return tiled_map(m, w, 3, dims, strides, box, bw * 2);
 }
 
+// w[Cout][R*S][Cin] -> w_pair[2*Cout][R*(S+1)][Cin]: rows [0, Cout) = w(r, t') for t' < S, rows [Cout, 2*Cout) =
+// w(r, t' - 1) for t' >= 1, zeros elsewhere (gabril_conv_fwd_pairs)
+__global__ void pack_wpairs_kernel(const uint4* __restrict__ w, uint4* __restrict__ wp, int Cout, int R, int S, int Cin8) {
+  // one 16-byte group of 8 input channels per thread
+  const int total = 2 * Cout * R * (S + 1) * Cin8;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c8 = i % Cin8;
+  int t = i / Cin8;
+  const int sp = t % (S + 1); t /= (S + 1);
+  const int r = t % R;
+  const int co2 = t / R;
+  const int half = co2 / Cout, co = co2 - half * Cout, s0 = sp - half;
+  wp[i] = (s0 >= 0 && s0 < S) ? __ldg(w + ((long long)co * R * S + r * S + s0) * Cin8 + c8) : make_uint4(0u, 0u, 0u, 0u);
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -442,6 +459,67 @@ static bool dgrad_stack_disabled() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("GABRIL_DGRAD_NO_STACK"); v = (e && e[0] == '1') ? 1 : 0; }
   return v == 1;
+}
+
+int gabril_conv_pack_wpairs(const void* w, void* w_pair, int Cout, int R, int S, int Cin, cudaStream_t stream) {
+  if (!w || !w_pair) return GABRIL_ERR_NULL;
+  if (Cout <= 0 || R <= 0 || S <= 0 || Cin <= 0) return GABRIL_ERR_BAD_SHAPE;
+  if (Cin % 8 || ((reinterpret_cast<uintptr_t>(w) | reinterpret_cast<uintptr_t>(w_pair)) & 15)) return GABRIL_ERR_BAD_SHAPE;
+  const long long total = 2ll * Cout * R * (S + 1) * (Cin / 8);
+  if (total >= (1ll << 31)) return GABRIL_ERR_BAD_SHAPE;
+  pack_wpairs_kernel<<<(unsigned)((total + 127) / 128), 128, 0, stream>>>((const uint4*)w, (uint4*)w_pair, Cout, R, S, Cin / 8);
+  GABRIL_CHECK_LAUNCH();
+  return GABRIL_OK;
+}
+
+// Two adjacent output pixels along N (see include/gabril_b200.h): a stride-1 convolution Cin -> Cout <= 64 runs as
+// Cin -> 2*Cout over every second pixel with an R x (S+1) filter; output row (n, oh, ow') of 2*Cout columns IS the
+// NHWC pixel pair (2ow', 2ow'+1), so the epilogue stores as usual.
+int gabril_conv_fwd_pairs(const void* x, const void* w_pair, const float* bias, void* y, int N, int H, int W,
+                          int Cin, int Cout, int R, int S, int pad, int relu, cudaStream_t stream) {
+  int rc = resolve_driver();
+  if (rc) return rc;
+  if (!x || !w_pair || !y) return GABRIL_ERR_NULL;
+  if (Cin % 64 || (Cout != 32 && Cout != 64) || N <= 0 || (W & 1) || R != 2 * pad + 1 || S != 2 * pad + 1) {
+    gabril_set_error("gabril_conv_fwd_pairs: stride-1 same convolution, Cin % 64 == 0, Cout 32 or 64, even W");
+    return GABRIL_ERR_BAD_SHAPE;
+  }
+  const int kc = 64, block_n = 2 * Cout, S2 = S + 1, W2 = W / 2;
+  const long long M = (long long)N * H * W2;
+  if (M >= (1ll << 31)) return GABRIL_ERR_BAD_SHAPE;
+  tc::Params p;
+  zero_params(p);
+  p.kind = tc::KIND_FWD;
+  p.n_classes = 1;
+  p.b_mn = 0;
+  fwd_schedule(p, kc, block_n, 0, 1);
+  p.a_im2col = 1;
+  p.M_total[0] = (int)M;
+  p.N_total = block_n;
+  p.taps = R * S2;
+  p.S = S2;
+  p.chunks_per_tap = Cin / kc;
+  p.kb_total = p.taps * p.chunks_per_tap;
+  p.kb_per_split = p.kb_total;
+  p.OW[0] = W2; p.OHW[0] = H * W2; p.lower_w[0] = -pad; p.lower_h[0] = -pad;
+  p.trav_stride_w = 2; p.trav_stride_h = 1;
+  p.r_base[0] = 0; p.s_base[0] = 0; p.r_step = 1; p.s_step = 1; p.S_w = S2;
+  // the filter covers columns p - pad .. p + pad + 1: right padding pad + 1, width S + 1
+  rc = im2col_map(&p.mapA[0], x, N, H, W, Cin, -pad, -pad, (pad + 1) - (S2 - 1), pad - (R - 1), kc, 128, 2, 1);
+  if (rc) return rc;
+  rc = weight_map(&p.mapB, w_pair, block_n, R * S2, Cin, 0, kc, block_n);
+  if (rc) return rc;
+  p.out_mode = tc::OUT_BF16;
+  p.out = y; p.ldo = block_n;
+  p.bias = bias; p.bias_mod = bias ? Cout : 0;
+  p.relu = relu;
+  p.err_flag = g_err_flag;
+  size_t smem;
+  const int occ = occ_setting();
+  pick_stages(p, &smem, occ);
+  const int mt[1] = {(int)((M + 127) / 128)};
+  finalize_schedule(p, mt, 1, 1, block_n, occ);
+  return tc::launch(p, g_num_sms * occ, smem, stream);
 }
 
 // dx[N,H,W,Cin] = gate( conv_transpose(dy[N,OH,OW,Cout], w[Cout][R*S][Cin]) + addend )

@@ -86,6 +86,7 @@ class StepEngine:
         self._own_in, self._own_inputs = {}, False
         self._colsum_pending, self._cs_i = False, 0
         self.fused_dbias = os.environ.get("GABRIL_FUSED_DBIAS", "1") != "0"   # A/B switch: 0 = separate colsum passes
+        self.conv6_pairs = os.environ.get("GABRIL_CONV6_PAIRS", "1") != "0"   # A/B switch: 0 = plain conv_6 forward
         self.fused_res = os.environ.get("GABRIL_FUSED_RES", "1") != "0"       # A/B switch: 0 = two launches per block
         self._cs_ev = [torch.cuda.Event() for _ in range(8)] if self._side else []
         if self._side:
@@ -124,6 +125,8 @@ class StepEngine:
                 e[f"h{i}"] = act(s.h, s.w, s.RH)
                 e[f"r{i}"] = act(s.h, s.w, s.NH)
             e["a5"], e["z"] = act(s.h, s.w, s.NH), act(s.h, s.w, s.E)
+            # conv_6's weights packed for the pixel-pair forward (ops.conv_fwd_pairs), rebuilt from the bf16 shadow per step
+            e["w6p"] = torch.zeros(2 * s.E, 5 * 6, s.NH, device=dev, dtype=bf)
             # packed ReLU sign words of every rectified activation (1 bit per element, written by the
             # forward epilogues, read by the dgrad epilogues in place of the activation itself); zeroed:
             # words of never-stored border pixels must read as "not positive"
@@ -396,8 +399,13 @@ class StepEngine:
         last = b[f"r{s.NR - 1}"]
         ops.conv_fwd(last, a.WB(f"{pfx}.conv5.w"), a.P(f"{pfx}.conv5.b"), b["a5"], 5, 5, 1, 2, relu=True,
                      bits_out=b["sb_a5"])
-        ops.conv_fwd(b["a5"], a.WB(f"{pfx}.conv6.w"), a.P(f"{pfx}.conv6.b"), b["z"], 5, 5, 1, 2, relu=False,
-                     rowmask=rowmask.view(-1) if rowmask is not None else None)
+        if rowmask is None and s.E in (32, 64) and s.NH % 64 == 0 and s.w % 2 == 0 and self.conv6_pairs:
+            # narrow layer (N = 64): two adjacent output pixels stacked along N, bit-identical to conv_fwd
+            ops.conv_pack_wpairs(a.WB(f"{pfx}.conv6.w"), b["w6p"], 5, 5)
+            ops.conv_fwd_pairs(b["a5"], b["w6p"], a.P(f"{pfx}.conv6.b"), b["z"], 5, 5, 2, relu=False)
+        else:   # the in-encoder GMD mask is a per-pixel epilogue term: the plain form
+            ops.conv_fwd(b["a5"], a.WB(f"{pfx}.conv6.w"), a.P(f"{pfx}.conv6.b"), b["z"], 5, 5, 1, 2, relu=False,
+                         rowmask=rowmask.view(-1) if rowmask is not None else None)
 
     def _heads_fwd(self, actions, center):
         s, a, b, B = self.spec, self.arena, self.buf, self.B

@@ -122,6 +122,32 @@ def conv_fwd(x, w, bias, y, R, S, stride, pad, relu=False, resid=None, rowmask=N
     return y
 
 
+def conv_pack_wpairs(w, w_pair, R, S):
+    """w [Cout,R*S,Cin] bf16 -> w_pair [2*Cout, R*(S+1), Cin] bf16: the operand of conv_fwd_pairs."""
+    _chk_bf16(w, "w"); _chk_bf16(w_pair, "w_pair")
+    Cout, T, Cin = w.shape
+    assert T == R * S and tuple(w_pair.shape) == (2 * Cout, R * (S + 1), Cin), (w.shape, w_pair.shape)
+    with _span("gabril_conv_pack_wpairs", "", 2.0 * (w.numel() + w_pair.numel()), "byte"):
+        st = _fn("gabril_conv_pack_wpairs")(ptr(w), ptr(w_pair), c_int(Cout), c_int(R), c_int(S), c_int(Cin), stream())
+    _lib.check(st, "gabril_conv_pack_wpairs")
+    return w_pair
+
+
+def conv_fwd_pairs(x, w_pair, bias, y, R, S, pad, relu=False):
+    """Narrow stride-1 same convolution with two adjacent output pixels stacked along N (bit-identical to conv_fwd):
+    x [N,H,W,Cin] bf16, w_pair from conv_pack_wpairs, bias fp32 [Cout] or None -> y [N,H,W,Cout] bf16."""
+    _chk_bf16(x, "x"); _chk_bf16(w_pair, "w_pair"); _chk_bf16(y, "y")
+    N, H, W, Cin = x.shape
+    Cout = w_pair.shape[0] // 2
+    assert w_pair.shape[1] == R * (S + 1) and w_pair.shape[2] == Cin and y.numel() == N * H * W * Cout
+    with _span("tc_gemm_kernel", f"fwd {Cin}->{Cout} k{R}s1", 2.0 * N * H * W * Cout * R * S * Cin, "flop"):
+        st = _fn("gabril_conv_fwd_pairs")(ptr(x), ptr(w_pair), ptr(bias), ptr(y), c_int(N), c_int(H), c_int(W),
+                                          c_int(Cin), c_int(Cout), c_int(R), c_int(S), c_int(pad), c_int(int(relu)),
+                                          stream())
+    _lib.check(st, "gabril_conv_fwd_pairs")
+    return y
+
+
 def conv_dgrad(dy, w, dx, R, S, stride, pad, addend=None, gate=None, rowmask=None, gate_bits=None):
     """dy [N,OH,OW,Cout] bf16 -> dx [N,H,W,Cin] bf16 (shape taken from dx)."""
     _chk_bf16(dy, "dy"); _chk_bf16(w, "w"); _chk_bf16(dx, "dx")

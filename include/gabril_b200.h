@@ -85,6 +85,15 @@ int gabril_res_block_fwd(const void* x, const void* w3, const void* w1, void* h,
  * stores (deterministic; planes = gabril_conv_fwd_splits(Cin, R, S, splits), summed in order by
  * gabril_bias_act_cast_planes).  Epilogue terms are ignored in both fp32 modes. */
 int gabril_conv_fwd_splits(int Cin, int R, int S, int splits);
+/* The same nn.Conv2d forward (linear_models.py:141-207) for NARROW stride-1 convolutions (Cout <= 64, W even, conv_6
+ * of the encoder) with two adjacent output pixels stacked along the GEMM's N dimension: tile row = every second pixel
+ * p, columns = [y(p) | y(p+1)]; y(p+1) = sum_t' x(p + t') w(t' - 1), so one activation tile per tap t' in 0..S and the
+ * pair-packed weight w_pair[2*Cout][R*(S+1)][Cin] (gabril_conv_pack_wpairs: [w(r,t') | w(r,t'-1)], zero where out of
+ * range) give both; an M = 128 tensor-core instruction is not proportionally cheaper below N = 128.  Bit-identical to
+ * gabril_conv_fwd (the extra taps add exact zeros).  y = relu?(conv(x, w) + bias), bf16 NHWC. */
+int gabril_conv_pack_wpairs(const void* w, void* w_pair, int Cout, int R, int S, int Cin, cudaStream_t stream);
+int gabril_conv_fwd_pairs(const void* x, const void* w_pair, const float* bias, void* y, int N, int H, int W,
+                          int Cin, int Cout, int R, int S, int pad, int relu, cudaStream_t stream);
 int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void* resid,
                     const float* rowmask, void* y, int N, int H, int W, int Cin, int Cout, int R,
                     int S, int stride, int pad, int relu, int out_f32_atomic, int splits,

@@ -103,6 +103,31 @@ def test_conv_fwd_dgrad_wgrad(ops, layer, N):
     _lib.poll_error()
 
 
+@pytest.mark.parametrize("N", [1, 3, 40])
+@pytest.mark.parametrize("layer", [("conv6", 20, 38, 128, 64, 5, 2), ("res3x3", 20, 38, 128, 32, 3, 1)], ids=["conv6", "res3x3"])
+def test_conv_fwd_pairs_is_bit_identical(ops, layer, N):
+    """gabril_conv_fwd_pairs (two adjacent output pixels stacked along N, pair-packed weights) vs gabril_conv_fwd."""
+    from gabril_carla_b200 import _lib
+    name, H, W, Cin, Cout, R, pad = layer
+    g = torch.Generator().manual_seed(77 + N + Cout)
+    x = (torch.randn(N, H, W, Cin, generator=g) * 0.5).to(torch.bfloat16).to(DEV)
+    w = ops.w_oihw_to_internal((torch.randn(Cout, Cin, R, R, generator=g) / (Cin * R * R) ** 0.5).to(torch.bfloat16)).to(DEV)
+    bias = torch.randn(Cout, generator=g).to(DEV)
+    y_ref = torch.full((N, H, W, Cout), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.conv_fwd(x, w, bias, y_ref, R, R, 1, pad, relu=False)
+    wp = torch.full((2 * Cout, R * (R + 1), Cin), float("nan"), device=DEV, dtype=torch.bfloat16)
+    ops.conv_pack_wpairs(w, wp, R, R)
+    wpc, wc = wp.cpu().view(2, Cout, R, R + 1, Cin), w.cpu().view(Cout, R, R, Cin)
+    assert torch.equal(wpc[0, :, :, :R], wc) and torch.equal(wpc[1, :, :, 1:], wc)
+    assert (wpc[0, :, :, R] == 0).all() and (wpc[1, :, :, 0] == 0).all()
+    y = torch.full_like(y_ref, float("nan"))
+    for _ in range(2):
+        ops.conv_fwd_pairs(x, wp, bias, y, R, R, pad, relu=False)
+    torch.cuda.synchronize()
+    _lib.poll_error()
+    assert torch.equal(y, y_ref)
+
+
 def test_pre_actor_shapes(ops):
     from gabril_carla_b200 import _lib
     g = torch.Generator().manual_seed(7)
