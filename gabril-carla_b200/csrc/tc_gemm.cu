@@ -794,6 +794,9 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
         if (p.quad_C > 0) {
           const float4 r4 = __ldg(reinterpret_cast<const float4*>(p.rowmask) + orow);
           r.rm4[0] = r4.x; r.rm4[1] = r4.y; r.rm4[2] = r4.z; r.rm4[3] = r4.w;
+        } else if (p.pair_C > 0) {   // a row holds two adjacent pixels: one multiplier per half
+          const float2 r2 = __ldg(reinterpret_cast<const float2*>(p.rowmask) + orow);
+          r.rm4[0] = r2.x; r.rm4[1] = r2.y;
         } else {
           r.rm4[0] = p.rowmask[orow];
         }
@@ -883,6 +886,7 @@ tc_gemm_kernel(const __grid_constant__ Params p) {
             }
             uint32_t keep = keep_row;
             float rmask = rm4[0];
+            if (p.pair_C > 0 && col0 >= p.pair_C) rmask = rm4[1];
             if (p.quad_C > 0) {
               const int qd = fdiv(col0, p.fd_quad);
               const int ih = 2 * q_sh + (qd >> 1) - 1, iw = 2 * q_sw + (qd & 1) - 1;

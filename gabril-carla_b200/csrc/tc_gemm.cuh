@@ -137,6 +137,9 @@ struct Params {
   // the columns four quadrants (qh, qw) of quad_C channels = pixels (2sh+qh-1, 2sw+qw-1) of the image;
   // quadrants outside it store 0, rowmask is indexed [row*4 + quadrant], bias by column % bias_mod.
   int quad_C, bias_mod;
+  // pair_C > 0 (gabril_conv_fwd_pairs): a row holds two adjacent pixels of pair_C channels; rowmask has one entry per
+  // pixel, i.e. [row*2 + half]
+  int pair_C;
   // remap validity: rows with jh >= valid_h or jw >= valid_w are not stored (0 = no check)
   int valid_h, valid_w;
   // flat-slab mode: the A rows (FWD) / B rows (WGRAD) are the flat pixels of a zero-bordered

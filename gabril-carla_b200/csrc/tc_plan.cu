@@ -475,8 +475,9 @@ int gabril_conv_pack_wpairs(const void* w, void* w_pair, int Cout, int R, int S,
 // Two adjacent output pixels along N (see include/gabril_b200.h): a stride-1 convolution Cin -> Cout <= 64 runs as
 // Cin -> 2*Cout over every second pixel with an R x (S+1) filter; output row (n, oh, ow') of 2*Cout columns IS the
 // NHWC pixel pair (2ow', 2ow'+1), so the epilogue stores as usual.
-int gabril_conv_fwd_pairs(const void* x, const void* w_pair, const float* bias, void* y, int N, int H, int W,
-                          int Cin, int Cout, int R, int S, int pad, int relu, cudaStream_t stream) {
+static int conv_fwd_pairs_impl(const void* x, const void* w_pair, const float* bias, const float* rowmask, void* y,
+                               int N, int H, int W, int Cin, int Cout, int R, int S, int pad, int relu,
+                               cudaStream_t stream) {
   int rc = resolve_driver();
   if (rc) return rc;
   if (!x || !w_pair || !y) return GABRIL_ERR_NULL;
@@ -512,6 +513,7 @@ int gabril_conv_fwd_pairs(const void* x, const void* w_pair, const float* bias, 
   p.out_mode = tc::OUT_BF16;
   p.out = y; p.ldo = block_n;
   p.bias = bias; p.bias_mod = bias ? Cout : 0;
+  p.rowmask = rowmask; p.pair_C = Cout;
   p.relu = relu;
   p.err_flag = g_err_flag;
   size_t smem;
@@ -520,6 +522,19 @@ int gabril_conv_fwd_pairs(const void* x, const void* w_pair, const float* bias, 
   const int mt[1] = {(int)((M + 127) / 128)};
   finalize_schedule(p, mt, 1, 1, block_n, occ);
   return tc::launch(p, g_num_sms * occ, smem, stream);
+}
+
+int gabril_conv_fwd_pairs(const void* x, const void* w_pair, const float* bias, void* y, int N, int H, int W,
+                          int Cin, int Cout, int R, int S, int pad, int relu, cudaStream_t stream) {
+  return conv_fwd_pairs_impl(x, w_pair, bias, nullptr, y, N, H, W, Cin, Cout, R, S, pad, relu, stream);
+}
+// rowmask: one multiplier per output pixel (fp32 [N*H*W], 8-byte aligned), applied after bias / ReLU - the
+// in-encoder gaze dropout of linear_models.py:194-199
+int gabril_conv_fwd_pairs_masked(const void* x, const void* w_pair, const float* bias, const float* rowmask, void* y,
+                                 int N, int H, int W, int Cin, int Cout, int R, int S, int pad, int relu,
+                                 cudaStream_t stream) {
+  if (rowmask && (reinterpret_cast<uintptr_t>(rowmask) & 7)) return GABRIL_ERR_BAD_SHAPE;
+  return conv_fwd_pairs_impl(x, w_pair, bias, rowmask, y, N, H, W, Cin, Cout, R, S, pad, relu, stream);
 }
 
 // dx[N,H,W,Cin] = gate( conv_transpose(dy[N,OH,OW,Cout], w[Cout][R*S][Cin]) + addend )

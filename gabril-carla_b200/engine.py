@@ -399,11 +399,12 @@ class StepEngine:
         last = b[f"r{s.NR - 1}"]
         ops.conv_fwd(last, a.WB(f"{pfx}.conv5.w"), a.P(f"{pfx}.conv5.b"), b["a5"], 5, 5, 1, 2, relu=True,
                      bits_out=b["sb_a5"])
-        if rowmask is None and s.E in (32, 64) and s.NH % 64 == 0 and s.w % 2 == 0 and self.conv6_pairs:
+        if s.E in (32, 64) and s.NH % 64 == 0 and s.w % 2 == 0 and self.conv6_pairs:
             # narrow layer (N = 64): two adjacent output pixels stacked along N, bit-identical to conv_fwd
             ops.conv_pack_wpairs(a.WB(f"{pfx}.conv6.w"), b["w6p"], 5, 5)
-            ops.conv_fwd_pairs(b["a5"], b["w6p"], a.P(f"{pfx}.conv6.b"), b["z"], 5, 5, 2, relu=False)
-        else:   # the in-encoder GMD mask is a per-pixel epilogue term: the plain form
+            ops.conv_fwd_pairs(b["a5"], b["w6p"], a.P(f"{pfx}.conv6.b"), b["z"], 5, 5, 2, relu=False,
+                               rowmask=rowmask.view(-1) if rowmask is not None else None)
+        else:
             ops.conv_fwd(b["a5"], a.WB(f"{pfx}.conv6.w"), a.P(f"{pfx}.conv6.b"), b["z"], 5, 5, 1, 2, relu=False,
                          rowmask=rowmask.view(-1) if rowmask is not None else None)
 

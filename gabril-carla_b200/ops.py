@@ -133,7 +133,7 @@ def conv_pack_wpairs(w, w_pair, R, S):
     return w_pair
 
 
-def conv_fwd_pairs(x, w_pair, bias, y, R, S, pad, relu=False):
+def conv_fwd_pairs(x, w_pair, bias, y, R, S, pad, relu=False, rowmask=None):
     """Narrow stride-1 same convolution with two adjacent output pixels stacked along N (bit-identical to conv_fwd):
     x [N,H,W,Cin] bf16, w_pair from conv_pack_wpairs, bias fp32 [Cout] or None -> y [N,H,W,Cout] bf16."""
     _chk_bf16(x, "x"); _chk_bf16(w_pair, "w_pair"); _chk_bf16(y, "y")
@@ -141,10 +141,11 @@ def conv_fwd_pairs(x, w_pair, bias, y, R, S, pad, relu=False):
     Cout = w_pair.shape[0] // 2
     assert w_pair.shape[1] == R * (S + 1) and w_pair.shape[2] == Cin and y.numel() == N * H * W * Cout
     with _span("tc_gemm_kernel", f"fwd {Cin}->{Cout} k{R}s1", 2.0 * N * H * W * Cout * R * S * Cin, "flop"):
-        st = _fn("gabril_conv_fwd_pairs")(ptr(x), ptr(w_pair), ptr(bias), ptr(y), c_int(N), c_int(H), c_int(W),
-                                          c_int(Cin), c_int(Cout), c_int(R), c_int(S), c_int(pad), c_int(int(relu)),
-                                          stream())
-    _lib.check(st, "gabril_conv_fwd_pairs")
+        assert rowmask is None or (rowmask.dtype == torch.float32 and rowmask.numel() == N * H * W)
+        st = _fn("gabril_conv_fwd_pairs_masked")(ptr(x), ptr(w_pair), ptr(bias), ptr(rowmask), ptr(y), c_int(N),
+                                                 c_int(H), c_int(W), c_int(Cin), c_int(Cout), c_int(R), c_int(S),
+                                                 c_int(pad), c_int(int(relu)), stream())
+    _lib.check(st, "gabril_conv_fwd_pairs_masked")
     return y
 
 

@@ -94,6 +94,10 @@ int gabril_conv_fwd_splits(int Cin, int R, int S, int splits);
 int gabril_conv_pack_wpairs(const void* w, void* w_pair, int Cout, int R, int S, int Cin, cudaStream_t stream);
 int gabril_conv_fwd_pairs(const void* x, const void* w_pair, const float* bias, void* y, int N, int H, int W,
                           int Cin, int Cout, int R, int S, int pad, int relu, cudaStream_t stream);
+/* ... with the per-pixel multiplier of the in-encoder gaze dropout (linear_models.py:194-199), rowmask fp32 [N*H*W]. */
+int gabril_conv_fwd_pairs_masked(const void* x, const void* w_pair, const float* bias, const float* rowmask, void* y,
+                                 int N, int H, int W, int Cin, int Cout, int R, int S, int pad, int relu,
+                                 cudaStream_t stream);
 int gabril_conv_fwd(const void* x, const void* w, const float* bias, const void* resid,
                     const float* rowmask, void* y, int N, int H, int W, int Cin, int Cout, int R,
                     int S, int stride, int pad, int relu, int out_f32_atomic, int splits,

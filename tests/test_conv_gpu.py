@@ -126,6 +126,14 @@ def test_conv_fwd_pairs_is_bit_identical(ops, layer, N):
     torch.cuda.synchronize()
     _lib.poll_error()
     assert torch.equal(y, y_ref)
+    # with the per-pixel multiplier of the in-encoder gaze dropout
+    rowmask = (torch.rand(N * H * W, generator=g) > 0.3).float().to(DEV)
+    ops.conv_fwd(x, w, bias, y_ref, R, R, 1, pad, relu=False, rowmask=rowmask)
+    y.fill_(float("nan"))
+    ops.conv_fwd_pairs(x, wp, bias, y, R, R, pad, relu=False, rowmask=rowmask)
+    torch.cuda.synchronize()
+    _lib.poll_error()
+    assert torch.equal(y, y_ref)
 
 
 def test_pre_actor_shapes(ops):
